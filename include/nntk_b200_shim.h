@@ -1,0 +1,134 @@
+/*
+ * nntk_b200_shim.h -- the thin C-ABI between the host C layer code (nntoolkitcore_b200/host/*.c) and the
+ * hand-written sm_100a CUDA kernels (nntoolkitcore_b200/csrc/*.cu).
+ *
+ * This is what replaces the reference's backend for the inference path: where the reference's layers call the
+ * 25 op_* primitives of core/ops.h:19-67 (implemented by core/default_ops.cc on Eigen/NEON/libm) and DFTPerform
+ * (signal/dft.c:34-47 on kissfft), the host code here calls ONE shim function per fused stage.  A per-op_* GPU
+ * port would launch a kernel per 128-float vector add, so the boundary sits at layer-Apply granularity.
+ *
+ * Rules: plain C types only; every pointer named d_* is a DEVICE pointer; every function enqueues on the library
+ * stream (nntk_cuda_stream) and returns 0 or a negative NNTK_ERR_* code with the text in nntk_cuda_last_error().
+ * There is no CPU implementation behind any of these: without a CUDA device they fail.
+ */
+#ifndef NNTK_B200_SHIM_H
+#define NNTK_B200_SHIM_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* activation kind tags (also stored in ActivationFunction objects) */
+enum {
+    NNTK_ACT_NONE = 0,
+    NNTK_ACT_IDENTITY = 1,
+    NNTK_ACT_SIGMOID = 2,
+    NNTK_ACT_TANH = 3,
+    NNTK_ACT_RELU = 4,
+    NNTK_ACT_SOFTMAX = 5,
+    NNTK_ACT_CUSTOM = 100
+};
+
+enum { NNTK_CELL_RNN = 1, NNTK_CELL_GRU = 3, NNTK_CELL_LSTM = 4 }; /* value = gate count G */
+
+/* ---- runtime ---------------------------------------------------------------------------------------------------- */
+int nntk_cuda_init(int device); /* device < 0: keep the current device */
+int nntk_cuda_ensure_init(void);
+int nntk_cuda_set_stream(void *stream);
+void *nntk_cuda_stream(void);
+int nntk_cuda_sync(void);
+const char *nntk_cuda_last_error(void);
+void nntk_cuda_clear_error(void);
+void nntk_cuda_set_error(int code, const char *fmt, ...);
+int nntk_cuda_set_math_mode(int mode);
+int nntk_cuda_math_mode(void);
+int nntk_cuda_sm_count(void);
+
+int nntk_cuda_malloc(void **d_ptr, size_t bytes);
+void nntk_cuda_free(void *d_ptr);
+int nntk_cuda_host_alloc(void **h_ptr, size_t bytes); /* pinned; falls back to malloc when no device exists so that
+                                                         Create/GetWeights work on a CPU-only box (Apply still fails) */
+void nntk_cuda_host_free(void *h_ptr);
+int nntk_cuda_h2d(void *d_dst, const void *h_src, size_t bytes);
+int nntk_cuda_d2h(void *h_dst, const void *d_src, size_t bytes);
+int nntk_cuda_d2d(void *d_dst, const void *d_src, size_t bytes);
+int nntk_cuda_memset(void *d_dst, int value, size_t bytes);
+/* 1 = device (or managed) pointer, 0 = host pointer */
+int nntk_cuda_is_device_ptr(const void *ptr);
+
+/* Host-buffer pipeline: runs `launch(ctx, d_in, d_out, first_unit, n_units)` over `n_units` independent units whose
+ * inputs/outputs live in HOST memory, in chunks, with H2D / compute / D2H of neighbouring chunks overlapped on three
+ * streams and two device slots.  Synchronous: the outputs are in h_out on return. */
+typedef int (*nntk_launch_fn)(void *ctx, const float *d_in, float *d_out, long long first_unit, int n_units);
+int nntk_cuda_staged_run(const void *h_in, void *h_out, size_t unit_in_bytes, size_t unit_out_bytes,
+                         long long n_units, nntk_launch_fn launch, void *ctx);
+
+/* ---- K1: spectrogram ---------------------------------------------------------------------------------------------- */
+typedef struct {
+    int nfft, window_size, step, input_size, nfreq, ntime;
+    float norm_factor; /* fft_normalization_factor (signal/spectrogram.c:130-131) */
+    int mode;          /* 0 magnitude (spectrogram.c:29-34), 1 PSD (spectrogram.c:41-47) */
+    float scale;       /* sum(w) or fs*sum(w^2), computed on the host like spectrogram.c:36-38,49-57 */
+    const float *d_window;  /* [window_size] */
+    const float *d_twiddle; /* [nfft][2] = (cos, sin)(-2*pi*i/nfft) rounded from double (kiss_fft.c:357-363) */
+} nntk_spectrogram_args;
+/* d_in [n_clips, input_size] -> d_out [n_clips, ntime, nfreq] */
+int nntk_cuda_spectrogram(const nntk_spectrogram_args *a, const float *d_in, float *d_out, int n_clips);
+
+/* ---- K5: element-wise --------------------------------------------------------------------------------------------- */
+/* d_params = gamma|beta|mean|var (4*C floats); rows x C elements; layers/batch_norm.c:140-163 */
+int nntk_cuda_batch_norm(const float *d_params, int C, float eps, const float *d_in, float *d_out, long long rows);
+/* kind != softmax: n elements.  softmax: n vectors of vector_size; layers/activation_default.c */
+int nntk_cuda_activation(int kind, float relu_a, int vector_size, const float *d_in, float *d_out, long long n);
+
+/* ---- K2/K3: (implicit) GEMM + bias + BatchNorm + activation --------------------------------------------------------- */
+typedef struct {
+    /* A is `batch` slabs of `rows` rows: row r of slab s starts at d_A + s*a_slab_stride + r*lda, K floats long.
+     * Conv1d: rows = T_out, lda = stride*Cin, K = kernel*Cin, a_slab_stride = T*Cin (overlapping im2col rows).
+     * Dense / projections: rows = M, lda = K, batch = 1. */
+    const float *d_A;
+    long long a_slab_stride;
+    int lda;
+    int batch, rows;
+    int N, K;
+    const float *d_B;    /* [K][N] row-major */
+    const float *d_bias; /* [N] or NULL */
+    const float *d_bn;   /* gamma|beta|mean|var (4*N) or NULL; applied after the bias */
+    float bn_eps;
+    int act;             /* NNTK_ACT_* element-wise kinds only (softmax is a second pass by the caller) */
+    float act_a;
+    float *d_C;          /* row r of slab s at d_C + s*c_slab_stride + r*ldc */
+    long long c_slab_stride;
+    int ldc;
+} nntk_gemm_args;
+int nntk_cuda_gemm(const nntk_gemm_args *g);
+/* conv weights W[Cout][Cin][K] -> B[(k*Cin + ci)][co]   (layers/conv_1d.c:128-140 order -> implicit-GEMM order) */
+int nntk_cuda_pack_conv_weights(const float *d_W, float *d_B, int cout, int cin, int k);
+
+/* ---- K3+K4: recurrent layers ---------------------------------------------------------------------------------------- */
+typedef struct {
+    int cell;            /* NNTK_CELL_* */
+    int in, H, T, batch;
+    int return_sequences;
+    int v2;              /* RNN/LSTM: add b_h (rnn.c:161-163, lstm.c:207-209); GRU always adds it (gru.c:151) */
+    int act[5];          /* RNN: [0]; GRU: z, r, h~; LSTM: i, f, g, o, out */
+    const float *d_W;    /* [in][G*H] */
+    const float *d_U;    /* [H][G*H]  */
+    const float *d_bi;   /* [G*H] */
+    const float *d_bh;   /* [G*H] */
+    const float *d_x;    /* [batch, T, in] */
+    float *d_h;          /* [batch, H] state: read as h_0, overwritten with h_T */
+    float *d_c;          /* [batch, H] LSTM cell state (in/out), else NULL */
+    float *d_out;        /* [batch, T, H] or [batch, H] */
+    float *d_work;       /* workspace of nntk_cuda_recurrent_workspace() bytes */
+    size_t work_bytes;
+} nntk_recurrent_args;
+size_t nntk_cuda_recurrent_workspace(const nntk_recurrent_args *r);
+int nntk_cuda_recurrent(const nntk_recurrent_args *r);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NNTK_B200_SHIM_H */
