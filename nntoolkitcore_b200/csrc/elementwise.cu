@@ -1,0 +1,166 @@
+// elementwise.cu -- K5: standalone BatchNorm and activation kernels (replace layers/batch_norm.c:140-189 and
+// layers/activation_default.c:28-33,65-67,98-103,123-129,149-167 of the reference for the inference path).
+// Single pass over the tensor (the reference makes 6 passes for BN, 3-4 per activation): HBM roofline = 8 B/element.
+// When a BatchNorm / activation directly follows a Conv1d / Dense it is fused into that kernel's epilogue instead
+// (csrc/gemm.cu); these kernels serve the stand-alone calls.
+#include "common.cuh"
+
+namespace {
+
+// 16-byte streaming accesses: every element is touched once, keep it out of L1.  Not .nc: in == out is legal.
+__device__ __forceinline__ float4 ld_stream(const float4 *p) {
+    float4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void st_stream(float4 *p, float4 v) {
+    asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1, %2, %3, %4};"
+                 :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// prm = gamma | beta | mean | var.  sd = sqrtf(var + eps) is the same value for every row, so it is evaluated per
+// element only in the sense of the reference's op order: x_mu / sd with an IEEE divide (batch_norm.c:151-162).
+// VEC: C % 4 == 0 and 16-byte aligned pointers.
+template <bool VEC>
+__global__ void __launch_bounds__(256) batch_norm_kernel(const float *__restrict__ prm, int C, float eps,
+                                                         const float *__restrict__ in, float *__restrict__ out,
+                                                         long long total) {
+    const float *gamma = prm, *beta = prm + C, *mean = prm + 2 * C, *var = prm + 3 * C;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (VEC) {
+        const long long nvec = total >> 2;
+        const int cvec = C >> 2;
+        for (; i < nvec; i += stride) {
+            const int c = (int)(i % cvec) * 4;
+            float4 x = ld_stream(reinterpret_cast<const float4 *>(in) + i);
+            const float4 g = __ldg(reinterpret_cast<const float4 *>(gamma + c));
+            const float4 b = __ldg(reinterpret_cast<const float4 *>(beta + c));
+            const float4 m = __ldg(reinterpret_cast<const float4 *>(mean + c));
+            const float4 v = __ldg(reinterpret_cast<const float4 *>(var + c));
+            x.x = nntk_bn(x.x, g.x, b.x, m.x, v.x, eps);
+            x.y = nntk_bn(x.y, g.y, b.y, m.y, v.y, eps);
+            x.z = nntk_bn(x.z, g.z, b.z, m.z, v.z, eps);
+            x.w = nntk_bn(x.w, g.w, b.w, m.w, v.w, eps);
+            st_stream(reinterpret_cast<float4 *>(out) + i, x);
+        }
+    } else {
+        for (; i < total; i += stride) {
+            const int c = (int)(i % C);
+            out[i] = nntk_bn(__ldg(in + i), __ldg(gamma + c), __ldg(beta + c), __ldg(mean + c), __ldg(var + c), eps);
+        }
+    }
+}
+
+template <bool VEC>
+__global__ void __launch_bounds__(256) activation_kernel(int kind, float a, const float *__restrict__ in,
+                                                         float *__restrict__ out, long long total) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (VEC) {
+        const long long nvec = total >> 2;
+        for (long long v = i; v < nvec; v += stride) {
+            float4 x = ld_stream(reinterpret_cast<const float4 *>(in) + v);
+            x.x = nntk_act(kind, a, x.x);
+            x.y = nntk_act(kind, a, x.y);
+            x.z = nntk_act(kind, a, x.z);
+            x.w = nntk_act(kind, a, x.w);
+            st_stream(reinterpret_cast<float4 *>(out) + v, x);
+        }
+        for (long long s = (nvec << 2) + i; s < total; s += stride) out[s] = nntk_act(kind, a, in[s]);
+    } else {
+        for (; i < total; i += stride) out[i] = nntk_act(kind, a, in[i]);
+    }
+}
+
+// softmax without max-subtraction, exactly the reference's definition (activation_default.c:149-167):
+// e_j = expf(x_j); y_j = e_j / sum(e).  One warp per vector; the sum is a lane-strided partial + shuffle tree
+// (the reference sums sequentially: results agree to rounding, not bit-for-bit).
+__global__ void __launch_bounds__(256) softmax_kernel(int V, const float *__restrict__ in, float *__restrict__ out,
+                                                      long long n_vec) {
+    const int lane = threadIdx.x & 31;
+    const long long warps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long r = (((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5); r < n_vec; r += warps) {
+        const float *x = in + r * V;
+        float *y = out + r * V;
+        float s = 0.0f;
+        if (V <= 32) {
+            float e = (lane < V) ? expf(x[lane]) : 0.0f;
+            s = e;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if (lane < V) y[lane] = e / s;
+        } else {
+            for (int j = lane; j < V; j += 32) s += expf(x[j]);
+#pragma unroll
+            for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            for (int j = lane; j < V; j += 32) y[j] = expf(x[j]) / s;
+        }
+    }
+}
+
+inline unsigned grid_for(long long work_items, int per_block) {
+    // enough CTAs for ~8 resident per SM, grid-stride beyond that
+    long long blocks = (work_items + per_block - 1) / per_block;
+    long long cap = (long long)nntk_cuda_sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (unsigned)blocks;
+}
+
+}  // namespace
+
+extern "C" int nntk_cuda_batch_norm(const float *d_params, int C, float eps, const float *d_in, float *d_out,
+                                    long long rows) {
+    int rc = nntk_cuda_ensure_init();
+    if (rc) return rc;
+    if (!d_params || !d_in || !d_out || C < 1 || rows < 0) {
+        nntk_cuda_set_error(NNTK_ERR_ARG_, "batch_norm: bad arguments");
+        return NNTK_ERR_ARG_;
+    }
+    const long long total = rows * C;
+    if (total == 0) return 0;
+    const bool vec = (C % 4 == 0) && ((((uintptr_t)d_in) | ((uintptr_t)d_out) | ((uintptr_t)d_params)) & 15) == 0;
+    if (vec)
+        batch_norm_kernel<true><<<grid_for(total >> 2, 256), 256, 0, nntk_stream()>>>(d_params, C, eps, d_in, d_out, total);
+    else
+        batch_norm_kernel<false><<<grid_for(total, 256), 256, 0, nntk_stream()>>>(d_params, C, eps, d_in, d_out, total);
+    NNTK_LAUNCH_CHECK("batch_norm_kernel");
+    return 0;
+}
+
+extern "C" int nntk_cuda_activation(int kind, float relu_a, int vector_size, const float *d_in, float *d_out,
+                                    long long n) {
+    int rc = nntk_cuda_ensure_init();
+    if (rc) return rc;
+    if (!d_in || !d_out || n < 0) {
+        nntk_cuda_set_error(NNTK_ERR_ARG_, "activation: bad arguments");
+        return NNTK_ERR_ARG_;
+    }
+    if (n == 0) return 0;
+    if (kind == NNTK_ACT_SOFTMAX) {
+        if (vector_size < 1) {
+            nntk_cuda_set_error(NNTK_ERR_ARG_, "softmax: vector_size %d", vector_size);
+            return NNTK_ERR_ARG_;
+        }
+        softmax_kernel<<<grid_for(n, 8), 256, 0, nntk_stream()>>>(vector_size, d_in, d_out, n);
+        NNTK_LAUNCH_CHECK("softmax_kernel");
+        return 0;
+    }
+    if (kind == NNTK_ACT_CUSTOM) {
+        nntk_cuda_set_error(NNTK_ERR_UNSUPPORTED_, "activation: custom host callbacks cannot run on the device");
+        return NNTK_ERR_UNSUPPORTED_;
+    }
+    if ((kind == NNTK_ACT_IDENTITY || kind == NNTK_ACT_NONE)) {
+        if (d_in != d_out) NNTK_CUDA_TRY(cudaMemcpyAsync(d_out, d_in, (size_t)n * sizeof(float), cudaMemcpyDeviceToDevice, nntk_stream()));
+        return 0;
+    }
+    const bool vec = ((((uintptr_t)d_in) | ((uintptr_t)d_out)) & 15) == 0;
+    if (vec)
+        activation_kernel<true><<<grid_for((n + 3) >> 2, 256), 256, 0, nntk_stream()>>>(kind, relu_a, d_in, d_out, n);
+    else
+        activation_kernel<false><<<grid_for(n, 256), 256, 0, nntk_stream()>>>(kind, relu_a, d_in, d_out, n);
+    NNTK_LAUNCH_CHECK("activation_kernel");
+    return 0;
+}
