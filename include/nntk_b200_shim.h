@@ -58,6 +58,10 @@ int nntk_cuda_memset(void *d_dst, int value, size_t bytes);
 /* 1 = device (or managed) pointer, 0 = host pointer */
 int nntk_cuda_is_device_ptr(const void *ptr);
 
+/* Shared grow-only device scratch: asks for `want` bytes, accepts anything >= at_least (capped by NNTK_WORKSPACE_MB,
+ * default 16 GiB, and by half the free memory). */
+int nntk_cuda_workspace(size_t want, size_t at_least, void **d_ptr, size_t *got);
+
 /* Host-buffer pipeline: runs `launch(ctx, d_in, d_out, first_unit, n_units)` over `n_units` independent units whose
  * inputs/outputs live in HOST memory, in chunks, with H2D / compute / D2H of neighbouring chunks overlapped on three
  * streams and two device slots.  Synchronous: the outputs are in h_out on return. */
@@ -114,6 +118,7 @@ typedef struct {
     int return_sequences;
     int v2;              /* RNN/LSTM: add b_h (rnn.c:161-163, lstm.c:207-209); GRU always adds it (gru.c:151) */
     int act[5];          /* RNN: [0]; GRU: z, r, h~; LSTM: i, f, g, o, out */
+    float act_a[5];      /* ReLU output scale `a` per slot (activation_default.c:123-129) */
     const float *d_W;    /* [in][G*H] */
     const float *d_U;    /* [H][G*H]  */
     const float *d_bi;   /* [G*H] */

@@ -1,0 +1,253 @@
+// gemm.cu -- K2/K3, fp32 path: (implicit) GEMM + bias + BatchNorm + activation in one kernel.
+//
+// Replaces, for the inference path, the reference's Conv1d triple loop of K-tap dot products (layers/conv_1d.c:122-147),
+// the per-row Eigen GEMV of Dense / TimeDistributedDense (layers/dense.c:122-133, time_distributed_dense.c:52-58) and
+// the per-timestep x*W GEMV of the recurrent cells (rnn.c:157, gru.c:144, lstm.c:201), plus the separate BatchNorm and
+// activation passes that follow a Conv1d (batch_norm.c:166, activation.c:23).
+//
+// Implicit GEMM: with channels-last activations, im2col row x of a Conv1d is the CONTIGUOUS span
+// in[x*stride : x*stride + K, :], so A is never materialised: row r of slab s starts at A + s*slab + r*lda and is
+// K*Cin floats long (overlapping rows).  The reference's transpose pass (conv_1d.c:125) disappears.
+//
+// This file is the NNTK_MATH_FP32 mode: FFMA on the CUDA cores, fp32 operands and accumulators, 1e-5 parity with the
+// reference.  128x128x16 CTA tile, 8x8 register micro-tile per thread, register-staged double buffering.
+// Roofline: fp32 FFMA peak (148 SMs x 128 lanes x 2 flop x clock).  The tcgen05 kind::tf32 mode lives in
+// gemm_tc.cu and shares the argument struct and the epilogue definition.
+#include "common.cuh"
+
+namespace {
+
+constexpr int BM = 128, BN = 128, BK = 16;
+constexpr int AS_LD = BM + 4;   // padded leading dimension of the transposed A tile
+
+struct GemmDev {
+    const float *A;
+    long long a_slab;
+    int lda, rows;
+    long long M;        // batch * rows
+    int N, K;
+    const float *B;
+    const float *bias;
+    const float *bn;    // gamma|beta|mean|var or null
+    float bn_eps;
+    int act;
+    float act_a;
+    float *C;
+    long long c_slab;
+    int ldc;
+    int n_tiles;
+};
+
+__device__ __forceinline__ float epilogue(const GemmDev &g, float v, int n) {
+    if (g.bias) v += __ldg(g.bias + n);
+    if (g.bn) v = nntk_bn(v, __ldg(g.bn + n), __ldg(g.bn + g.N + n), __ldg(g.bn + 2 * g.N + n),
+                          __ldg(g.bn + 3 * g.N + n), g.bn_eps);
+    return nntk_act(g.act, g.act_a, v);
+}
+
+template <bool VEC_A, bool VEC_B>
+__global__ void __launch_bounds__(256, 2) gemm_fp32_kernel(GemmDev g) {
+    __shared__ __align__(16) float As[2][BK][AS_LD];
+    __shared__ __align__(16) float Bs[2][BK][BN];
+
+    const int tid = threadIdx.x;
+    const int n_tile = blockIdx.x % g.n_tiles;
+    const long long m_tile = blockIdx.x / g.n_tiles;
+    const long long m0 = m_tile * BM;
+    const int n0 = n_tile * BN;
+
+    // ---- global -> register staging maps ---------------------------------------------------------------------------
+    // A tile: 128 rows x 16 k.  thread -> rows (tid>>2) and (tid>>2)+64, k quad (tid&3)*4
+    const int a_kq = (tid & 3) * 4;
+    const float *a_ptr[2];
+    bool a_ok[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const long long gr = m0 + (tid >> 2) + 64 * i;
+        a_ok[i] = gr < g.M;
+        const long long s = a_ok[i] ? gr / g.rows : 0;
+        const long long r = a_ok[i] ? gr - s * g.rows : 0;
+        a_ptr[i] = g.A + s * g.a_slab + r * (long long)g.lda;
+    }
+    // B tile: 16 k x 128 n.  thread -> k rows (tid>>5) and (tid>>5)+8, n quad (tid&31)*4
+    const int b_k = tid >> 5, b_n = n0 + (tid & 31) * 4;
+
+    float4 ra[2], rb[2];
+    auto load_tiles = [&](int k0) {
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int k = k0 + a_kq;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (a_ok[i]) {
+                if (VEC_A && k + 3 < g.K) {
+                    v = __ldg(reinterpret_cast<const float4 *>(a_ptr[i] + k));
+                } else {
+                    if (k < g.K) v.x = __ldg(a_ptr[i] + k);
+                    if (k + 1 < g.K) v.y = __ldg(a_ptr[i] + k + 1);
+                    if (k + 2 < g.K) v.z = __ldg(a_ptr[i] + k + 2);
+                    if (k + 3 < g.K) v.w = __ldg(a_ptr[i] + k + 3);
+                }
+            }
+            ra[i] = v;
+        }
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int k = k0 + b_k + 8 * i;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (k < g.K) {
+                const float *p = g.B + (long long)k * g.N + b_n;
+                if (VEC_B && b_n + 3 < g.N) {
+                    v = __ldg(reinterpret_cast<const float4 *>(p));
+                } else {
+                    if (b_n < g.N) v.x = __ldg(p);
+                    if (b_n + 1 < g.N) v.y = __ldg(p + 1);
+                    if (b_n + 2 < g.N) v.z = __ldg(p + 2);
+                    if (b_n + 3 < g.N) v.w = __ldg(p + 3);
+                }
+            }
+            rb[i] = v;
+        }
+    };
+    auto store_tiles = [&](int buf) {
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int m = (tid >> 2) + 64 * i;
+            As[buf][a_kq + 0][m] = ra[i].x;
+            As[buf][a_kq + 1][m] = ra[i].y;
+            As[buf][a_kq + 2][m] = ra[i].z;
+            As[buf][a_kq + 3][m] = ra[i].w;
+        }
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+            *reinterpret_cast<float4 *>(&Bs[buf][b_k + 8 * i][(tid & 31) * 4]) = rb[i];
+    };
+
+    // ---- compute maps: thread (ty, tx) owns rows {4ty..4ty+3, 64+4ty..} x cols {4tx..4tx+3, 64+4tx..} ---------------
+    const int tx = tid & 15, ty = tid >> 4;
+    float acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+
+    const int k_iters = (g.K + BK - 1) / BK;
+    load_tiles(0);
+    store_tiles(0);
+    __syncthreads();
+    for (int it = 0; it < k_iters; ++it) {
+        const int buf = it & 1;
+        if (it + 1 < k_iters) load_tiles((it + 1) * BK);
+#pragma unroll
+        for (int k = 0; k < BK; ++k) {
+            const float4 a0 = *reinterpret_cast<const float4 *>(&As[buf][k][4 * ty]);
+            const float4 a1 = *reinterpret_cast<const float4 *>(&As[buf][k][64 + 4 * ty]);
+            const float4 b0 = *reinterpret_cast<const float4 *>(&Bs[buf][k][4 * tx]);
+            const float4 b1 = *reinterpret_cast<const float4 *>(&Bs[buf][k][64 + 4 * tx]);
+            const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        }
+        if (it + 1 < k_iters) {
+            store_tiles(buf ^ 1);
+            __syncthreads();
+        }
+    }
+
+    // ---- epilogue: bias -> BatchNorm -> activation -> store ----------------------------------------------------------
+    const bool vec_c = ((g.ldc & 3) == 0) && ((g.c_slab & 3) == 0) && ((((uintptr_t)g.C) & 15) == 0);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const long long gr = m0 + (i < 4 ? 4 * ty + i : 64 + 4 * ty + (i - 4));
+        if (gr >= g.M) continue;
+        const long long s = gr / g.rows;
+        const long long r = gr - s * g.rows;
+        float *crow = g.C + s * g.c_slab + r * (long long)g.ldc;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int n = n0 + 64 * h + 4 * tx;
+            if (n >= g.N) continue;
+            float v[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = (n + j < g.N) ? epilogue(g, acc[i][4 * h + j], n + j) : 0.f;
+            if (vec_c && n + 3 < g.N) {
+                *reinterpret_cast<float4 *>(crow + n) = make_float4(v[0], v[1], v[2], v[3]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (n + j < g.N) crow[n + j] = v[j];
+            }
+        }
+    }
+}
+
+// conv weights W[Cout][Cin][K] -> B[(k*Cin + ci)][co]
+__global__ void pack_conv_weights_kernel(const float *__restrict__ W, float *__restrict__ B, int cout, int cin, int ks) {
+    const long long total = (long long)cout * cin * ks;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        // i indexes the destination: i = (k*cin + ci)*cout + co  (coalesced writes)
+        const int co = (int)(i % cout);
+        const long long rest = i / cout;
+        const int ci = (int)(rest % cin);
+        const int k = (int)(rest / cin);
+        B[i] = __ldg(W + ((long long)co * cin + ci) * ks + k);
+    }
+}
+
+}  // namespace
+
+extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *g);   // gemm_tc.cu
+
+extern "C" int nntk_cuda_gemm(const nntk_gemm_args *a) {
+    int rc = nntk_cuda_ensure_init();
+    if (rc) return rc;
+    if (!a || !a->d_A || !a->d_B || !a->d_C || a->batch < 0 || a->rows < 0 || a->N < 1 || a->K < 1) {
+        nntk_cuda_set_error(NNTK_ERR_ARG_, "gemm: bad arguments");
+        return NNTK_ERR_ARG_;
+    }
+    if (a->act == NNTK_ACT_SOFTMAX || a->act == NNTK_ACT_CUSTOM) {
+        nntk_cuda_set_error(NNTK_ERR_UNSUPPORTED_, "gemm: activation kind %d cannot be fused", a->act);
+        return NNTK_ERR_UNSUPPORTED_;
+    }
+    const long long M = (long long)a->batch * a->rows;
+    if (M == 0) return 0;
+    if (nntk_cuda_math_mode() != 0) {
+        rc = nntk_cuda_gemm_tf32(a);
+        if (rc != 1) return rc;   // 1 = shape not eligible for the tensor-core kernel: use the fp32 kernel
+    }
+    GemmDev g;
+    g.A = a->d_A; g.a_slab = a->a_slab_stride; g.lda = a->lda; g.rows = a->rows; g.M = M;
+    g.N = a->N; g.K = a->K; g.B = a->d_B; g.bias = a->d_bias; g.bn = a->d_bn; g.bn_eps = a->bn_eps;
+    g.act = a->act; g.act_a = a->act_a; g.C = a->d_C; g.c_slab = a->c_slab_stride; g.ldc = a->ldc;
+    g.n_tiles = (a->N + BN - 1) / BN;
+    const long long m_tiles = (M + BM - 1) / BM;
+    const long long grid = m_tiles * g.n_tiles;
+    if (grid > 0x7fffffffLL) {
+        nntk_cuda_set_error(NNTK_ERR_ARG_, "gemm: problem too large for one launch");
+        return NNTK_ERR_ARG_;
+    }
+    const bool vec_a = ((a->lda & 3) == 0) && ((a->a_slab_stride & 3) == 0) && ((((uintptr_t)a->d_A) & 15) == 0);
+    const bool vec_b = ((a->N & 3) == 0) && ((((uintptr_t)a->d_B) & 15) == 0);
+    cudaStream_t st = nntk_stream();
+    if (vec_a && vec_b) gemm_fp32_kernel<true, true><<<(unsigned)grid, 256, 0, st>>>(g);
+    else if (vec_a) gemm_fp32_kernel<true, false><<<(unsigned)grid, 256, 0, st>>>(g);
+    else if (vec_b) gemm_fp32_kernel<false, true><<<(unsigned)grid, 256, 0, st>>>(g);
+    else gemm_fp32_kernel<false, false><<<(unsigned)grid, 256, 0, st>>>(g);
+    NNTK_LAUNCH_CHECK("gemm_fp32_kernel");
+    return 0;
+}
+
+extern "C" int nntk_cuda_pack_conv_weights(const float *d_W, float *d_B, int cout, int cin, int k) {
+    int rc = nntk_cuda_ensure_init();
+    if (rc) return rc;
+    const long long total = (long long)cout * cin * k;
+    if (total <= 0) return 0;
+    long long blocks = (total + 255) / 256;
+    if (blocks > 4096) blocks = 4096;
+    pack_conv_weights_kernel<<<(unsigned)blocks, 256, 0, nntk_stream()>>>(d_W, d_B, cout, cin, k);
+    NNTK_LAUNCH_CHECK("pack_conv_weights_kernel");
+    return 0;
+}

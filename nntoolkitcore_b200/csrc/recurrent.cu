@@ -1,0 +1,284 @@
+// recurrent.cu -- K3 + K4: RNN / GRU / LSTM inference forward over [batch, T, in] (replaces layers/rnn.c:144-166,223-244,
+// layers/gru.c:129-204 and layers/lstm.c:185-268 of the reference for the inference path).
+//
+// The reference runs, per sequence and per timestep, two GEMVs (x_t*W and h*U) plus ~15 element-wise passes over H floats.
+// Here:
+//   1. the input projection is hoisted out of the time loop: xw[b,t,:] = x[b,t,:]*W + b_i for ALL timesteps in one GEMM
+//      (csrc/gemm.cu / gemm_tc.cu), M = batch*T rows;
+//   2. each timestep is ONE kernel: the recurrent GEMM h_{t-1}[B,H] x U[H,G*H] with the gate nonlinearities, the state
+//      update and the return_sequences store fused into its epilogue.  A thread owns all G gate columns of its hidden
+//      units, so the gate math never leaves registers.  h_{t-1} is read from the previous output row (or a ping-pong
+//      buffer), h_t is written to the next: no extra state copies.
+// Gate order and formulas follow the reference exactly: GRU [z, r, h~] with reset-after (gru.c:140-186), LSTM [i, f, g, o]
+// (lstm.c:199-238), RNN (rnn.c:156-165).
+#include "common.cuh"
+
+namespace {
+
+constexpr int SM_ROWS = 128, SU = 32, SK = 16;
+constexpr int SA_LD = SM_ROWS + 4;
+
+struct StepDev {
+    int B, H;
+    const float *h_prev; long long ld_prev;   // [B, H] view with row stride
+    float *h_next; long long ld_next;
+    float *c;                                  // [B, H] (LSTM) in/out
+    const float *U;                            // [H][G*H]
+    const float *bh;                           // [G*H] or null (not added)
+    const float *xw; long long ld_xw;          // row b: xw + b*ld_xw, G*H floats (b_i already added)
+    int act[5];
+    float act_a[5];
+    int u_tiles;
+};
+
+template <int G>
+__global__ void __launch_bounds__(256, 2) recurrent_step_kernel(StepDev p) {
+    __shared__ __align__(16) float As[2][SK][SA_LD];
+    __shared__ __align__(16) float Us[2][SK][G][SU];
+    const int tid = threadIdx.x;
+    const int u_tile = blockIdx.x % p.u_tiles;
+    const int m_tile = blockIdx.x / p.u_tiles;
+    const int m0 = m_tile * SM_ROWS, u0 = u_tile * SU;
+    const int GH = G * p.H;
+    const bool vec_a = ((p.ld_prev & 3) == 0) && ((((uintptr_t)p.h_prev) & 15) == 0);
+    const bool vec_u = ((p.H & 3) == 0) && ((((uintptr_t)p.U) & 15) == 0);
+
+    const int a_kq = (tid & 3) * 4;
+    const float *a_ptr[2];
+    bool a_ok[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int row = m0 + (tid >> 2) + 64 * i;
+        a_ok[i] = row < p.B;
+        a_ptr[i] = p.h_prev + (long long)(a_ok[i] ? row : 0) * p.ld_prev;
+    }
+    // U tile: SK x G x 8 quads; quad q -> k = q / (8G), g = (q / 8) % G, u4 = (q % 8) * 4
+    constexpr int UQ = SK * G * 8;
+    constexpr int UQ_PER_THREAD = (UQ + 255) / 256;
+
+    float4 ra[2], ru[UQ_PER_THREAD];
+    auto load_tiles = [&](int k0) {
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int k = k0 + a_kq;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (a_ok[i]) {
+                if (vec_a && k + 3 < p.H) v = *reinterpret_cast<const float4 *>(a_ptr[i] + k);
+                else {
+                    if (k < p.H) v.x = a_ptr[i][k];
+                    if (k + 1 < p.H) v.y = a_ptr[i][k + 1];
+                    if (k + 2 < p.H) v.z = a_ptr[i][k + 2];
+                    if (k + 3 < p.H) v.w = a_ptr[i][k + 3];
+                }
+            }
+            ra[i] = v;
+        }
+#pragma unroll
+        for (int j = 0; j < UQ_PER_THREAD; ++j) {
+            const int q = tid + 256 * j;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (q < UQ) {
+                const int k = k0 + q / (8 * G), gg = (q >> 3) % G, u = u0 + (q & 7) * 4;
+                if (k < p.H) {
+                    const float *src = p.U + (long long)k * GH + gg * p.H + u;
+                    if (vec_u && u + 3 < p.H) v = __ldg(reinterpret_cast<const float4 *>(src));
+                    else {
+                        if (u < p.H) v.x = __ldg(src);
+                        if (u + 1 < p.H) v.y = __ldg(src + 1);
+                        if (u + 2 < p.H) v.z = __ldg(src + 2);
+                        if (u + 3 < p.H) v.w = __ldg(src + 3);
+                    }
+                }
+            }
+            ru[j] = v;
+        }
+    };
+    auto store_tiles = [&](int buf) {
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int m = (tid >> 2) + 64 * i;
+            As[buf][a_kq + 0][m] = ra[i].x;
+            As[buf][a_kq + 1][m] = ra[i].y;
+            As[buf][a_kq + 2][m] = ra[i].z;
+            As[buf][a_kq + 3][m] = ra[i].w;
+        }
+#pragma unroll
+        for (int j = 0; j < UQ_PER_THREAD; ++j) {
+            const int q = tid + 256 * j;
+            if (q < UQ) *reinterpret_cast<float4 *>(&Us[buf][q / (8 * G)][(q >> 3) % G][(q & 7) * 4]) = ru[j];
+        }
+    };
+
+    const int ux = tid & 15, ty = tid >> 4;
+    float acc[8][G][2];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int gg = 0; gg < G; ++gg) acc[i][gg][0] = acc[i][gg][1] = 0.f;
+
+    const int k_iters = (p.H + SK - 1) / SK;
+    load_tiles(0);
+    store_tiles(0);
+    __syncthreads();
+    for (int it = 0; it < k_iters; ++it) {
+        const int buf = it & 1;
+        if (it + 1 < k_iters) load_tiles((it + 1) * SK);
+#pragma unroll
+        for (int k = 0; k < SK; ++k) {
+            const float4 a0 = *reinterpret_cast<const float4 *>(&As[buf][k][4 * ty]);
+            const float4 a1 = *reinterpret_cast<const float4 *>(&As[buf][k][64 + 4 * ty]);
+            const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+#pragma unroll
+            for (int gg = 0; gg < G; ++gg) {
+                const float2 b = *reinterpret_cast<const float2 *>(&Us[buf][k][gg][2 * ux]);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    acc[i][gg][0] = fmaf(a[i], b.x, acc[i][gg][0]);
+                    acc[i][gg][1] = fmaf(a[i], b.y, acc[i][gg][1]);
+                }
+            }
+        }
+        if (it + 1 < k_iters) {
+            store_tiles(buf ^ 1);
+            __syncthreads();
+        }
+    }
+
+    // ---- fused gate epilogue ------------------------------------------------------------------------------------------
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int row = m0 + (i < 4 ? 4 * ty + i : 64 + 4 * ty + (i - 4));
+        if (row >= p.B) continue;
+        const float *xw = p.xw + (long long)row * p.ld_xw;
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const int u = u0 + 2 * ux + e;
+            if (u >= p.H) continue;
+            float hu[G], xv[G];
+#pragma unroll
+            for (int gg = 0; gg < G; ++gg) {
+                hu[gg] = acc[i][gg][e];
+                if (p.bh) hu[gg] = __fadd_rn(hu[gg], __ldg(p.bh + gg * p.H + u));
+                xv[gg] = xw[gg * p.H + u];
+            }
+            float hn;
+            if (G == 3) {   // gru.c:156-186
+                const float hp = p.h_prev[(long long)row * p.ld_prev + u];
+                const float z = nntk_act(p.act[0], p.act_a[0], __fadd_rn(xv[0], hu[0]));
+                const float r = nntk_act(p.act[1], p.act_a[1], __fadd_rn(xv[1], hu[1]));
+                const float hh = nntk_act(p.act[2], p.act_a[2], __fadd_rn(__fmul_rn(r, hu[2]), xv[2]));
+                const float one_minus_z = __fadd_rn(-z, 1.0f);
+                hn = __fadd_rn(__fmul_rn(one_minus_z, hh), __fmul_rn(z, hp));
+            } else if (G == 4) {   // lstm.c:199-238
+                float *cp = p.c + (long long)row * p.H + u;
+                const float ig = nntk_act(p.act[0], p.act_a[0], __fadd_rn(xv[0], hu[0]));
+                const float fg = nntk_act(p.act[1], p.act_a[1], __fadd_rn(xv[1], hu[1]));
+                const float gg_ = nntk_act(p.act[2], p.act_a[2], __fadd_rn(xv[2], hu[2]));
+                const float og = nntk_act(p.act[3], p.act_a[3], __fadd_rn(xv[3], hu[3]));
+                const float cn = __fadd_rn(__fmul_rn(fg, *cp), __fmul_rn(ig, gg_));
+                *cp = cn;
+                hn = __fmul_rn(og, nntk_act(p.act[4], p.act_a[4], cn));
+            } else {   // rnn.c:156-165
+                hn = nntk_act(p.act[0], p.act_a[0], __fadd_rn(hu[0], xv[0]));
+            }
+            p.h_next[(long long)row * p.ld_next + u] = hn;
+        }
+    }
+}
+
+}  // namespace
+
+extern "C" size_t nntk_cuda_recurrent_workspace(const nntk_recurrent_args *r) {
+    if (!r) return 0;
+    const size_t G = (size_t)r->cell;
+    size_t xw = (size_t)r->batch * r->T * G * r->H * sizeof(float);
+    size_t pp = r->return_sequences ? 0 : (size_t)2 * r->batch * r->H * sizeof(float);
+    return xw + pp + 256;
+}
+
+static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *work) {
+    const int G = r->cell, H = r->H, T = r->T, GH = G * H;
+    const float *x = r->d_x + (long long)b0 * T * r->in;
+    float *h = r->d_h + (long long)b0 * H;
+    float *c = r->d_c ? r->d_c + (long long)b0 * H : nullptr;
+    float *out = r->d_out + (long long)b0 * (r->return_sequences ? (long long)T * H : H);
+    float *xw = work;
+    float *pp = work + (size_t)nb * T * GH;
+    // 1. hoisted input projection: xw = x*W + b_i over all timesteps
+    nntk_gemm_args g = {};
+    g.d_A = x; g.a_slab_stride = 0; g.lda = r->in; g.batch = 1; g.rows = nb * T; g.N = GH; g.K = r->in;
+    g.d_B = r->d_W; g.d_bias = r->d_bi; g.d_bn = nullptr; g.act = NNTK_ACT_NONE; g.act_a = 1.f;
+    g.d_C = xw; g.c_slab_stride = 0; g.ldc = GH;
+    if ((long long)nb * T > 0x7fffffffLL) return NNTK_ERR_ARG_;
+    int rc = nntk_cuda_gemm(&g);
+    if (rc) return rc;
+    // 2. T fused step kernels
+    StepDev p;
+    p.B = nb; p.H = H; p.c = c; p.U = r->d_U;
+    const bool add_bh = (G == 3) || r->v2;   // gru.c:151 always; rnn.c:161-163 / lstm.c:207-209 only if v2
+    p.bh = add_bh ? r->d_bh : nullptr;
+    p.ld_xw = (long long)T * GH;
+    for (int i = 0; i < 5; ++i) p.act[i] = r->act[i];
+    for (int i = 0; i < 5; ++i) p.act_a[i] = r->act_a[i];
+    p.u_tiles = (H + SU - 1) / SU;
+    const int m_tiles = (nb + SM_ROWS - 1) / SM_ROWS;
+    const unsigned grid = (unsigned)(m_tiles * p.u_tiles);
+    cudaStream_t st = nntk_stream();
+    for (int t = 0; t < T; ++t) {
+        if (t == 0) { p.h_prev = h; p.ld_prev = H; }
+        else if (r->return_sequences) { p.h_prev = out + (long long)(t - 1) * H; p.ld_prev = (long long)T * H; }
+        else { p.h_prev = pp + (size_t)((t - 1) & 1) * nb * H; p.ld_prev = H; }
+        if (r->return_sequences) { p.h_next = out + (long long)t * H; p.ld_next = (long long)T * H; }
+        else { p.h_next = pp + (size_t)(t & 1) * nb * H; p.ld_next = H; }
+        p.xw = xw + (long long)t * GH;
+        if (G == 1) recurrent_step_kernel<1><<<grid, 256, 0, st>>>(p);
+        else if (G == 3) recurrent_step_kernel<3><<<grid, 256, 0, st>>>(p);
+        else recurrent_step_kernel<4><<<grid, 256, 0, st>>>(p);
+    }
+    NNTK_LAUNCH_CHECK("recurrent_step_kernel");
+    // 3. carry the final state back (reference: f_copy(filter->h, h_t), gru.c:201 / lstm.c:264-265 / rnn.c:241)
+    if (T > 0) {
+        if (r->return_sequences) {
+            NNTK_CUDA_TRY(cudaMemcpy2DAsync(h, (size_t)H * sizeof(float), out + (long long)(T - 1) * H,
+                                            (size_t)T * H * sizeof(float), (size_t)H * sizeof(float), nb,
+                                            cudaMemcpyDeviceToDevice, st));
+        } else {
+            const float *last = pp + (size_t)((T - 1) & 1) * nb * H;
+            NNTK_CUDA_TRY(cudaMemcpyAsync(out, last, (size_t)nb * H * sizeof(float), cudaMemcpyDeviceToDevice, st));
+            NNTK_CUDA_TRY(cudaMemcpyAsync(h, last, (size_t)nb * H * sizeof(float), cudaMemcpyDeviceToDevice, st));
+        }
+    }
+    return 0;
+}
+
+extern "C" int nntk_cuda_recurrent(const nntk_recurrent_args *r) {
+    int rc = nntk_cuda_ensure_init();
+    if (rc) return rc;
+    if (!r || (r->cell != 1 && r->cell != 3 && r->cell != 4) || r->in < 1 || r->H < 1 || r->T < 0 || r->batch < 0 ||
+        !r->d_W || !r->d_U || !r->d_bi || !r->d_bh || !r->d_x || !r->d_h || !r->d_out || !r->d_work ||
+        (r->cell == 4 && !r->d_c)) {
+        nntk_cuda_set_error(NNTK_ERR_ARG_, "recurrent: bad arguments");
+        return NNTK_ERR_ARG_;
+    }
+    for (int i = 0; i < 5; ++i)
+        if (r->act[i] == NNTK_ACT_SOFTMAX || r->act[i] == NNTK_ACT_CUSTOM) {
+            nntk_cuda_set_error(NNTK_ERR_UNSUPPORTED_, "recurrent: gate activation kind %d cannot run fused on the device", r->act[i]);
+            return NNTK_ERR_UNSUPPORTED_;
+        }
+    if (r->batch == 0 || r->T == 0) return 0;
+    // batch chunks that fit the workspace
+    const size_t per_seq = ((size_t)r->T * r->cell * r->H + (r->return_sequences ? 0 : 2 * (size_t)r->H)) * sizeof(float);
+    size_t avail = r->work_bytes > 256 ? r->work_bytes - 256 : 0;
+    long long chunk = (long long)(avail / per_seq);
+    if (chunk < 1) {
+        nntk_cuda_set_error(NNTK_ERR_ARG_, "recurrent: workspace of %zu bytes holds no sequence (%zu needed each)", r->work_bytes, per_seq);
+        return NNTK_ERR_ARG_;
+    }
+    if (chunk > r->batch) chunk = r->batch;
+    for (int b0 = 0; b0 < r->batch; b0 += (int)chunk) {
+        const int nb = (int)((b0 + chunk <= r->batch) ? chunk : (r->batch - b0));
+        rc = recurrent_chunk(r, b0, nb, r->d_work);
+        if (rc) return rc;
+    }
+    return 0;
+}

@@ -239,3 +239,28 @@ extern "C" int nntk_cuda_staged_run(const void *h_in, void *h_out, size_t unit_i
     }
     return result;
 }
+
+// ---- shared device workspace ------------------------------------------------------------------------------------
+// One grow-only scratch block for the whole library (hoisted projections, zero states, packed weights are per handle;
+// this is only for per-call scratch).  All work is stream-ordered on the library stream, so sharing is safe.
+namespace { void *g_work = nullptr; size_t g_work_bytes = 0; }
+extern "C" int nntk_cuda_workspace(size_t want, size_t at_least, void **d_ptr, size_t *got) {
+    *d_ptr = nullptr; *got = 0;
+    int rc = nntk_cuda_ensure_init();
+    if (rc) return rc;
+    size_t cap = (size_t)16 << 30;
+    if (const char *e = getenv("NNTK_WORKSPACE_MB")) { long long mb = atoll(e); if (mb > 0) cap = (size_t)mb << 20; }
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) { size_t lim = (free_b + g_work_bytes) / 2; if (cap > lim) cap = lim; }
+    size_t need = want < cap ? want : cap;
+    if (need < at_least) need = at_least;
+    if (need > g_work_bytes) {
+        NNTK_CUDA_TRY(cudaDeviceSynchronize());
+        if (g_work) cudaFree(g_work);
+        g_work = nullptr; g_work_bytes = 0;
+        NNTK_CUDA_TRY(cudaMalloc(&g_work, need));
+        g_work_bytes = need;
+    }
+    *d_ptr = g_work; *got = g_work_bytes;
+    return 0;
+}

@@ -1,0 +1,135 @@
+/* conv_1d.c -- Conv1d inference (reference: layers/conv_1d.c:73-155; batched layout from Conv1dApplyTrainingBatch
+ * :167-183).  Valid strided cross-correlation, channels-last in and out, weights W[Cout][Cin][K] | b[Cout] in one block
+ * (private/weights_private.c:16-21).  On the device the weights are repacked to the implicit-GEMM operand
+ * B[(k*Cin + ci)][co]; BatchNorm and a built-in activation can ride in the same kernel's epilogue. */
+#include <stdlib.h>
+#include "internal.h"
+
+const float *nntk_batch_norm_device_params(BatchNorm f, int *channels, float *eps); /* batch_norm.c */
+
+struct Conv1dStruct {
+    nntk_layer_hdr hdr; /* must be first */
+    Conv1dConfig config;
+    ConvWeights weights;
+    float *d_packed; /* [K*Cin][Cout] */
+};
+
+Conv1dConfig Conv1dConfigCreate(int input_feature_channels, int output_feature_channels, int kernel_size, int stride,
+                                int inputSize) {
+    Conv1dConfig c;
+    c.input_feature_channels = input_feature_channels;
+    c.output_feature_channels = output_feature_channels;
+    c.kernel_size = kernel_size;
+    c.stride = stride;
+    c.input_size = inputSize;
+    c.output_size = stride > 0 ? (inputSize - (kernel_size - stride)) / stride : 0; /* conv_1d.c:85 */
+    return c;
+}
+
+static int conv_repack(nntk_layer_hdr *h) {
+    Conv1d f = (Conv1d)h;
+    const Conv1dConfig *c = &f->config;
+    if (!f->d_packed) {
+        void *d = NULL;
+        int rc = nntk_cuda_malloc(&d, sizeof(float) * (size_t)c->output_feature_channels * c->input_feature_channels * c->kernel_size);
+        if (rc) return rc;
+        f->d_packed = (float *)d;
+    }
+    return nntk_cuda_pack_conv_weights(h->d_block, f->d_packed, c->output_feature_channels, c->input_feature_channels,
+                                       c->kernel_size);
+}
+
+Conv1d Conv1dCreateForInference(Conv1dConfig config) {
+    if (config.input_feature_channels < 1 || config.output_feature_channels < 1 || config.kernel_size < 1 ||
+        config.stride < 1 || config.output_size < 0) {
+        nntk_cuda_set_error(NNTK_ERR_ARG, "Conv1d: invalid config");
+        return NULL;
+    }
+    Conv1d f = (Conv1d)calloc(1, sizeof(*f));
+    if (!f) return NULL;
+    const size_t w = (size_t)config.output_feature_channels * config.input_feature_channels * config.kernel_size;
+    if (nntk_layer_init(&f->hdr, NNTK_L_CONV1D, w + (size_t)config.output_feature_channels)) { free(f); return NULL; }
+    f->hdr.after_stage = conv_repack;
+    f->config = config;
+    f->weights.W = f->hdr.h_block;
+    f->weights.b = f->hdr.h_block + w;
+    return f;
+}
+
+ConvWeights *Conv1dGetWeights(Conv1d filter) { return &filter->weights; }
+
+void Conv1dDestroy(Conv1d filter) {
+    if (!filter) return;
+    nntk_cuda_free(filter->d_packed);
+    nntk_layer_release(&filter->hdr);
+    free(filter);
+}
+
+typedef struct { Conv1d f; const float *d_bn; float eps; int act; float act_a; } conv_ctx;
+
+static int conv_launch(void *ctx, const float *d_in, float *d_out, long long first, int n) {
+    (void)first;
+    conv_ctx *cc = (conv_ctx *)ctx;
+    const Conv1dConfig *c = &cc->f->config;
+    const size_t w = (size_t)c->output_feature_channels * c->input_feature_channels * c->kernel_size;
+    nntk_gemm_args g;
+    g.d_A = d_in;
+    g.a_slab_stride = (long long)c->input_size * c->input_feature_channels;
+    g.lda = c->stride * c->input_feature_channels;
+    g.batch = n;
+    g.rows = c->output_size;
+    g.N = c->output_feature_channels;
+    g.K = c->kernel_size * c->input_feature_channels;
+    g.d_B = cc->f->d_packed;
+    g.d_bias = cc->f->hdr.d_block + w;
+    g.d_bn = cc->d_bn;
+    g.bn_eps = cc->eps;
+    g.act = cc->act;
+    g.act_a = cc->act_a;
+    g.d_C = d_out;
+    g.c_slab_stride = (long long)c->output_size * c->output_feature_channels;
+    g.ldc = c->output_feature_channels;
+    return nntk_cuda_gemm(&g);
+}
+
+int Conv1dBNActApplyInferenceBatch(Conv1d filter, BatchNorm bn, ActivationFunction act, const float *input,
+                                   float *output, int batch) {
+    if (!filter || batch < 0) {
+        nntk_cuda_set_error(NNTK_ERR_ARG, "Conv1dApplyInference: bad arguments");
+        return NNTK_ERR_ARG;
+    }
+    int kind = nntk_ptr_kind(input, output, "Conv1dApplyInference");
+    if (kind < 0) return kind;
+    conv_ctx cc = {filter, NULL, 0.0f, NNTK_ACT_NONE, 1.0f};
+    if (act) {
+        if (act->kind == NNTK_ACT_SOFTMAX || act->kind == NNTK_ACT_CUSTOM) {
+            nntk_cuda_set_error(NNTK_ERR_UNSUPPORTED, "Conv1dBNAct: only identity/sigmoid/tanh/ReLU can be fused");
+            return NNTK_ERR_UNSUPPORTED;
+        }
+        cc.act = act->kind;
+        cc.act_a = act->a;
+    }
+    int rc = nntk_layer_stage(&filter->hdr);
+    if (rc) return rc;
+    if (bn) {
+        int ch = 0;
+        cc.d_bn = nntk_batch_norm_device_params(bn, &ch, &cc.eps);
+        if (!cc.d_bn) return NNTK_ERR_CUDA;
+        if (ch != filter->config.output_feature_channels) {
+            nntk_cuda_set_error(NNTK_ERR_ARG, "Conv1dBNAct: BatchNorm has %d channels, Conv1d emits %d", ch,
+                                filter->config.output_feature_channels);
+            return NNTK_ERR_ARG;
+        }
+    }
+    if (kind == 1) return conv_launch(&cc, input, output, 0, batch);
+    const Conv1dConfig *c = &filter->config;
+    return nntk_cuda_staged_run(input, output, sizeof(float) * (size_t)c->input_size * c->input_feature_channels,
+                                sizeof(float) * (size_t)c->output_size * c->output_feature_channels, batch, conv_launch, &cc);
+}
+
+int Conv1dApplyInferenceBatch(Conv1d filter, const float *input, float *output, int batch) {
+    return Conv1dBNActApplyInferenceBatch(filter, NULL, NULL, input, output, batch);
+}
+int Conv1dApplyInference(Conv1d filter, const float *input, float *output) {
+    return Conv1dBNActApplyInferenceBatch(filter, NULL, NULL, input, output, 1);
+}

@@ -1,0 +1,49 @@
+/* internal.h -- private definitions shared by the host C layer code (nntoolkitcore_b200/host/*.c).
+ * The public handle types are opaque in the reference too (struct bodies live in its .c files), so the layouts here
+ * are ours: every layer starts with the same header so that NNTKWeightsFreeze / NNTKResetState can take any handle. */
+#ifndef NNTK_HOST_INTERNAL_H
+#define NNTK_HOST_INTERNAL_H
+
+#include <stddef.h>
+#include <stdint.h>
+#include <stdbool.h>
+#include "nntk_b200_shim.h"
+#include "nntoolkitcore/b200_ext.h"
+
+#define NNTK_LAYER_MAGIC 0x4e544b4cu /* 'NTKL' */
+enum { NNTK_L_BATCHNORM = 1, NNTK_L_CONV1D, NNTK_L_DENSE, NNTK_L_TDD, NNTK_L_RNN, NNTK_L_GRU, NNTK_L_LSTM };
+
+typedef struct nntk_layer_hdr {
+    uint32_t magic;
+    int kind;
+    float *h_block;   /* host weight block the caller writes through XGetWeights (pinned when a device exists) */
+    float *d_block;   /* device mirror, same layout */
+    size_t n_floats;
+    int frozen;       /* NNTKWeightsFreeze: skip the per-Apply restage */
+    int staged;       /* device mirror valid */
+    int (*after_stage)(struct nntk_layer_hdr *self); /* device-side repack hook, may be NULL */
+} nntk_layer_hdr;
+
+int nntk_layer_init(nntk_layer_hdr *h, int kind, size_t n_floats);
+void nntk_layer_release(nntk_layer_hdr *h);
+/* makes the device mirror current (H2D on the library stream unless frozen and already staged) */
+int nntk_layer_stage(nntk_layer_hdr *h);
+
+/* 0 both host, 1 both device, <0 mixed (error recorded) */
+int nntk_ptr_kind(const void *in, const void *out, const char *who);
+
+struct ActivationFunctionStruct {
+    int kind;        /* NNTK_ACT_* */
+    float a;         /* ReLU output scale */
+    int input_size;  /* elements (softmax: number of vectors) */
+    int vector_size; /* softmax */
+    void *implementer;
+    ActivationImplementerDestroy destroy_fn;
+    ActivationFunctionImpl function;
+    ActivationFunctionDerivative derivative, cached_derivative;
+};
+
+static inline int nntk_act_kind(ActivationFunction f) { return f ? f->kind : NNTK_ACT_NONE; }
+static inline float nntk_act_a(ActivationFunction f) { return f ? f->a : 1.0f; }
+
+#endif
