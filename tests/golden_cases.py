@@ -1,0 +1,81 @@
+"""The golden cases: each entry builds seeded inputs + weights, runs them through the C API of the library it is given
+(reference when generating, product when checking on the GPU) and returns the output.  The oracle port is checked against
+the same stored outputs through tests/test_oracle.py."""
+import numpy as np
+
+import helpers
+from nntoolkitcore_b200 import layers as L
+
+
+def _spec(nfft, win, nov, n, window, fs=None, norm=1.0, clip=0):
+    def run(lib):
+        s = L.Spectrogram(lib, nfft, win, nov, n, norm, window, fs)
+        x = helpers.audio_clip(clip, n)
+        out = s.apply(x)
+        s.close()
+        return out
+    return run
+
+
+def _rec(cell, in_size, H, T, rs, v2, seed):
+    def run(lib):
+        r = L.Recurrent(lib, cell, in_size, H, T, rs, v2)
+        helpers.fill_recurrent(r, seed)
+        x = np.random.Generator(np.random.PCG64(seed + 1)).standard_normal((T, in_size)).astype(np.float32)
+        out = r.apply(x)
+        r.close()
+        return out
+    return run
+
+
+def _conv(cin, cout, k, s, T, seed):
+    def run(lib):
+        c = L.Conv1d(lib, cin, cout, k, s, T)
+        helpers.fill_conv(c, seed)
+        x = np.random.Generator(np.random.PCG64(seed + 1)).standard_normal((T, cin)).astype(np.float32)
+        out = c.apply(x)
+        c.close()
+        return out
+    return run
+
+
+def _bn(C_, count, seed):
+    def run(lib):
+        b = L.BatchNorm(lib, C_, 1e-3, count)
+        helpers.fill_bn(b, seed)
+        x = np.random.Generator(np.random.PCG64(seed + 1)).standard_normal((count, C_)).astype(np.float32)
+        out = b.apply(x)
+        b.close()
+        return out
+    return run
+
+
+def _dense(i, o, act, ts, seed):
+    def run(lib):
+        d = L.Dense(lib, i, o, act, ts=ts)
+        helpers.fill_dense(d, seed)
+        shape = (i,) if ts is None else (ts, i)
+        x = np.random.Generator(np.random.PCG64(seed + 1)).standard_normal(shape).astype(np.float32)
+        out = d.apply(x)
+        d.close()
+        return out
+    return run
+
+
+CASES = {
+    "spec_c2_1s_hann": _spec(512, 512, 352, 16000, "hann_window"),
+    "spec_c5_1s_hann400": _spec(512, 400, 240, 16000, "hann_window", clip=1),
+    "spec_psd_hamming": _spec(512, 512, 352, 8000, "hamming_window", fs=16000, clip=2),
+    "spec_nfft256": _spec(256, 256, 128, 4096, "hann_window", clip=3),
+    "spec_nfft100_norm": _spec(100, 100, 50, 2000, "blackman_window", norm=0.5, clip=4),
+    "gru_c1": _rec("gru", 40, 128, 100, True, True, 100),          # BASELINE configs[0]
+    "gru_last_only": _rec("gru", 40, 128, 30, False, True, 110),
+    "lstm_v2": _rec("lstm", 64, 96, 20, True, True, 120),
+    "lstm_v1": _rec("lstm", 64, 96, 20, True, False, 130),
+    "rnn_v2_last": _rec("rnn", 40, 64, 25, False, True, 140),
+    "conv_128_256_k5": _conv(128, 256, 5, 1, 40, 150),
+    "conv_stride2": _conv(16, 24, 3, 2, 41, 160),
+    "bn_257": _bn(257, 20, 170),
+    "dense_relu": _dense(256, 12, L.ACT_RELU, None, 180),
+    "tdd_softmax": _dense(256, 12, L.ACT_SOFTMAX, 10, 190),
+}

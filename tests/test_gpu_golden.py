@@ -1,0 +1,17 @@
+"""GPU tier: the CUDA path against the committed golden vectors of the unmodified reference."""
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import golden_cases
+from helpers import assert_parity
+
+pytestmark = pytest.mark.gpu
+GOLDEN = np.load(Path(__file__).parent / "golden" / "golden_v1.npz")
+
+
+@pytest.mark.parametrize("name", sorted(golden_cases.CASES))
+def test_product_matches_golden(cuda, product, name):
+    got = golden_cases.CASES[name](product)
+    assert_parity(got, GOLDEN[name], what=name)
