@@ -1,4 +1,371 @@
-// gemm_tc.cu -- K2/K3, tensor-core path (NNTK_MATH_TF32): placeholder until the tcgen05 kernel lands.
-// Returns 1 = "shape not eligible", which makes nntk_cuda_gemm run the fp32 FFMA kernel.
+// gemm_tc.cu -- K2/K3, tensor-core path (NNTK_MATH_TF32): (implicit) GEMM on tcgen05 with TMA-staged tiles and TMEM
+// accumulators, bias + BatchNorm + activation fused in the epilogue.  Same contract as csrc/gemm.cu (nntk_gemm_args);
+// operands are rounded to TF32 by the tensor core, accumulation is fp32, so parity with the reference is 1e-3, not 1e-5.
+//
+// Structure (persistent, warp specialised, one CTA per SM):
+//   warp 0      TMA producer: A tile [128 rows x 32 k] and B tile [BN x 32 k] per stage, SWIZZLE_128B, mbarrier tx-count
+//   warp 1      MMA issuer: one elected lane issues tcgen05.mma.kind::tf32 (M=128, N=BN, K=8) x4 per stage into one of two
+//               TMEM accumulator buffers; tcgen05.commit releases the smem stage / publishes the accumulator
+//   warps 2-5   epilogue: tcgen05.ld (32 lanes x 32 columns per warp), v*scale[n]+shift[n] (bias and BatchNorm folded per
+//               channel), activation, 16-byte stores; overlaps the next tile's main loop through the second TMEM buffer
+// Conv1d needs no im2col: with channels-last input the im2col row x is the contiguous span in[x*stride : x*stride+K, :],
+// so A is a 3-D TMA tensor {K*Cin, T_out, batch} with OVERLAPPING rows (row stride = stride*Cin floats).
+// Weights are re-laid K-major (Bt[N][K]) per call -- they may legally change between Applies.
+#include <cuda.h>
 #include "common.cuh"
-extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *g) { (void)g; return 1; }
+
+namespace {
+
+constexpr int BM = 128, BK = 32;          // BK floats = 128 bytes = one SWIZZLE_128B atom
+constexpr int UMMA_K = 8;                 // tf32: 32 bytes per MMA along K
+constexpr int NUM_THREADS = 192;
+
+struct TcParams {
+    int N, n_tiles, m_tiles_per_slab, k_blocks;
+    long long total_tiles;
+    int rows;
+    float *C;
+    long long c_slab;
+    int ldc;
+    const float *scale, *shift;   // folded epilogue: y = act(acc * scale[n] + shift[n])
+    int act;
+    float act_a;
+};
+
+// ---- PTX wrappers ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra WAIT_DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "WAIT_DONE:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *map, uint64_t *bar, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, uint64_t *bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor: rows of 128 bytes, 8-row groups 1024 bytes apart.
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3fff);        // start address
+    d |= (uint64_t)1 << 16;                        // leading byte offset (unused for swizzled K-major)
+    d |= (uint64_t)(1024 >> 4) << 32;              // stride byte offset: 8 rows x 128 B
+    d |= (uint64_t)1 << 46;                        // descriptor version (Blackwell)
+    d |= (uint64_t)2 << 61;                        // SWIZZLE_128B
+    return d;
+}
+
+template <int BN, int STAGES>
+struct SmemLayout {
+    static constexpr int A_BYTES = BM * BK * 4;
+    static constexpr int B_BYTES = BN * BK * 4;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
+    static constexpr int TOTAL = BAR_OFFSET + (2 * STAGES + 4) * 8 + 16 + 1024;   // + alignment slack
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, TcParams p) {
+    using SL = SmemLayout<BN, STAGES>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + SL::BAR_OFFSET);
+    uint64_t *empty_bar = full_bar + STAGES;
+    uint64_t *tmem_full = empty_bar + STAGES;     // [2]
+    uint64_t *tmem_empty = tmem_full + 2;         // [2]
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    constexpr uint32_t TMEM_COLS = 2 * BN;        // two accumulator buffers (256 or 512 columns: powers of two)
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (long long tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+                const int n_t = (int)(tile % p.n_tiles);
+                const long long rest = tile / p.n_tiles;
+                const int m_t = (int)(rest % p.m_tiles_per_slab);
+                const int slab = (int)(rest / p.m_tiles_per_slab);
+                for (int kb = 0; kb < p.k_blocks; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t *sa = smem + stage * SL::STAGE_BYTES;
+                    mbar_expect_tx(&full_bar[stage], SL::STAGE_BYTES);
+                    tma_load_3d(sa, &map_a, &full_bar[stage], kb * BK, m_t * BM, slab);
+                    tma_load_2d(sa + SL::A_BYTES, &map_b, &full_bar[stage], kb * BK, n_t * BN);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            // instruction descriptor: D=f32, A=B=tf32, both K-major, N>>3 at bit 17, M>>4 at bit 24
+            constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+            int stage = 0; uint32_t phase = 0;
+            uint32_t it = 0;
+            for (long long tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+                const uint32_t buf = it & 1, use = it >> 1;
+                mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);     // epilogue has drained this accumulator
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + buf * BN;
+                for (int kb = 0; kb < p.k_blocks; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * SL::STAGE_BYTES);
+                    const uint64_t da = make_desc(sa), db = make_desc(sa + SL::A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) {
+                        // advance 32 bytes along K inside the 128-byte swizzle atom: +2 in the (addr >> 4) field
+                        tc_mma_tf32(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                    }
+                    tc_commit(&empty_bar[stage]);               // smem stage free once these MMAs have read it
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                tc_commit(&tmem_full[buf]);                      // accumulator complete
+            }
+        }
+    } else {
+        // ===== epilogue warps (2..5): TMEM lane quarter = warp % 4 =====
+        const int q = warp & 3;
+        const int row_in_tile = q * 32 + lane;
+        uint32_t it = 0;
+        const bool vec_ok = ((p.ldc & 3) == 0) && ((p.c_slab & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
+        for (long long tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+            const int n_t = (int)(tile % p.n_tiles);
+            const long long rest = tile / p.n_tiles;
+            const int m_t = (int)(rest % p.m_tiles_per_slab);
+            const long long slab = rest / p.m_tiles_per_slab;
+            const uint32_t buf = it & 1, use = it >> 1;
+            mbar_wait(&tmem_full[buf], use & 1);
+            tc_fence_after();
+            const int row = m_t * BM + row_in_tile;
+            const bool row_ok = row < p.rows;
+            float *crow = p.C + slab * p.c_slab + (long long)row * p.ldc;
+            const uint32_t taddr = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+            for (int c0 = 0; c0 < BN; c0 += 32) {
+                uint32_t r[32];
+                tc_ld_32x32(taddr + c0, r);
+                const int n0 = n_t * BN + c0;
+                if (row_ok && n0 < p.N) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        float v[4];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const int n = n0 + j + e;
+                            float x = __uint_as_float(r[j + e]);
+                            if (n < p.N) x = nntk_act(p.act, p.act_a, fmaf(x, __ldg(p.scale + n), __ldg(p.shift + n)));
+                            v[e] = x;
+                        }
+                        const int n = n0 + j;
+                        if (vec_ok && n + 3 < p.N) *reinterpret_cast<float4 *>(crow + n) = make_float4(v[0], v[1], v[2], v[3]);
+                        else
+                            for (int e = 0; e < 4; ++e) if (n + e < p.N) crow[n + e] = v[e];
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+    }
+}
+
+// Bt[n][k] = B[k][n], leading dimension ldbt (multiple of 4); tail columns k in [K, ldbt) zeroed.
+__global__ void transpose_weights_kernel(const float *__restrict__ B, float *__restrict__ Bt, int K, int N, int ldbt) {
+    __shared__ float tile[32][33];
+    const int k0 = blockIdx.x * 32, n0 = blockIdx.y * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int k = k0 + i, n = n0 + threadIdx.x;
+        tile[i][threadIdx.x] = (k < K && n < N) ? B[(long long)k * N + n] : 0.0f;
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int n = n0 + i, k = k0 + threadIdx.x;
+        if (n < N && k < ldbt) Bt[(long long)n * ldbt + k] = tile[threadIdx.x][i];
+    }
+}
+
+// scale[n], shift[n] such that act(acc*scale + shift) == act(BN(acc + bias)) up to rounding
+__global__ void fold_epilogue_kernel(const float *bias, const float *bn, float eps, int N, float *scale, float *shift) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    const float b = bias ? bias[n] : 0.0f;
+    if (bn) {
+        const float s = bn[n] / sqrtf(bn[3 * N + n] + eps);
+        scale[n] = s;
+        shift[n] = (b - bn[2 * N + n]) * s + bn[N + n];
+    } else {
+        scale[n] = 1.0f;
+        shift[n] = b;
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    }
+    return fn;
+}
+
+float *g_scratch = nullptr;      // Bt | scale | shift
+size_t g_scratch_floats = 0;
+
+}  // namespace
+
+template <int BN, int STAGES>
+static int launch_tc(const CUtensorMap &ma, const CUtensorMap &mb, TcParams &p, cudaStream_t st) {
+    using SL = SmemLayout<BN, STAGES>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        NNTK_CUDA_TRY(cudaFuncSetAttribute(gemm_tf32_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::TOTAL));
+        attr_done = true;
+    }
+    long long grid = p.total_tiles < nntk_cuda_sm_count() ? p.total_tiles : nntk_cuda_sm_count();
+    gemm_tf32_kernel<BN, STAGES><<<(unsigned)grid, NUM_THREADS, SL::TOTAL, st>>>(ma, mb, p);
+    NNTK_LAUNCH_CHECK("gemm_tf32_kernel");
+    return 0;
+}
+
+// returns 0 done, 1 not eligible (caller runs the fp32 kernel), <0 error
+extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *a) {
+    if ((a->lda & 3) || (a->a_slab_stride & 3) || (((uintptr_t)a->d_A) & 15) || a->rows < 1 || a->batch < 1) return 1;
+    EncodeTiledFn encode = get_encode();
+    if (!encode) {
+        nntk_cuda_set_error(NNTK_ERR_CUDA_, "gemm_tf32: cuTensorMapEncodeTiled is not available from this driver");
+        return NNTK_ERR_CUDA_;
+    }
+    cudaStream_t st = nntk_stream();
+    const int K = a->K, N = a->N;
+    const int ldbt = (K + 3) & ~3;
+    const size_t need = (size_t)N * ldbt + 2 * (size_t)N + 64;
+    if (need > g_scratch_floats) {
+        NNTK_CUDA_TRY(cudaStreamSynchronize(st));
+        if (g_scratch) cudaFree(g_scratch);
+        g_scratch = nullptr; g_scratch_floats = 0;
+        NNTK_CUDA_TRY(cudaMalloc(&g_scratch, need * sizeof(float)));
+        g_scratch_floats = need;
+    }
+    float *Bt = g_scratch;
+    float *scale = g_scratch + (((size_t)N * ldbt + 3) & ~(size_t)3);
+    float *shift = scale + N;
+    dim3 tb(32, 8), tg((ldbt + 31) / 32, (N + 31) / 32);
+    transpose_weights_kernel<<<tg, tb, 0, st>>>(a->d_B, Bt, K, N, ldbt);
+    fold_epilogue_kernel<<<(N + 127) / 128, 128, 0, st>>>(a->d_bias, a->d_bn, a->bn_eps, N, scale, shift);
+    NNTK_LAUNCH_CHECK("gemm_tf32 prologue");
+
+    const int BN = N > 128 ? 256 : 128;
+    CUtensorMap ma, mb;
+    {
+        cuuint64_t dims[3] = {(cuuint64_t)K, (cuuint64_t)a->rows, (cuuint64_t)a->batch};
+        cuuint64_t slab_bytes = (cuuint64_t)(a->batch > 1 ? a->a_slab_stride : (long long)a->rows * a->lda) * 4;
+        if (slab_bytes == 0) slab_bytes = 16;
+        cuuint64_t strides[2] = {(cuuint64_t)a->lda * 4, slab_bytes};
+        cuuint32_t box[3] = {BK, BM, 1};
+        cuuint32_t estr[3] = {1, 1, 1};
+        CUresult r = encode(&ma, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void *)a->d_A, dims, strides, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) {
+            nntk_cuda_set_error(NNTK_ERR_CUDA_, "gemm_tf32: tensor map for A rejected (CUresult %d): K %d rows %d batch %d lda %d", (int)r, K, a->rows, a->batch, a->lda);
+            return NNTK_ERR_CUDA_;
+        }
+    }
+    {
+        cuuint64_t dims[2] = {(cuuint64_t)ldbt, (cuuint64_t)N};
+        cuuint64_t strides[1] = {(cuuint64_t)ldbt * 4};
+        cuuint32_t box[2] = {BK, (cuuint32_t)BN};
+        cuuint32_t estr[2] = {1, 1};
+        CUresult r = encode(&mb, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)Bt, dims, strides, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) {
+            nntk_cuda_set_error(NNTK_ERR_CUDA_, "gemm_tf32: tensor map for B rejected (CUresult %d)", (int)r);
+            return NNTK_ERR_CUDA_;
+        }
+    }
+    TcParams p;
+    p.N = N;
+    p.n_tiles = (N + BN - 1) / BN;
+    p.m_tiles_per_slab = (a->rows + BM - 1) / BM;
+    p.k_blocks = (K + BK - 1) / BK;
+    p.total_tiles = (long long)p.n_tiles * p.m_tiles_per_slab * a->batch;
+    p.rows = a->rows;
+    p.C = a->d_C; p.c_slab = a->c_slab_stride; p.ldc = a->ldc;
+    p.scale = scale; p.shift = shift; p.act = a->act; p.act_a = a->act_a;
+    return BN == 256 ? launch_tc<256, 4>(ma, mb, p, st) : launch_tc<128, 6>(ma, mb, p, st);
+}

@@ -5,7 +5,8 @@
 // (F-1)*step + window_size samples, is read from HBM ONCE with 16-byte loads into shared memory; the frame overlap
 // (hop 160 vs window 512 => every sample belongs to 3.2 frames) is served from shared memory.  One warp transforms
 // TWO real frames as one 512-point complex FFT held in registers (csrc/spectrogram_core.h), the window multiply is
-// fused into the register load, magnitude / PSD scaling into the split pass, and the [F, 257] result tile -- a flat
+// fused into the register load, the two frames are separated IN REGISTERS (no third exchange), magnitude / PSD scaling
+// is applied there, and the [F, 257] result tile -- a flat
 // contiguous span of the [n_clips, ntime, nfreq] output, whose 257-float rows are never 16-byte aligned -- is staged
 // in shared memory with the alignment of its global address and written back with 16-byte stores.
 //
@@ -110,29 +111,27 @@ spectrogram512_kernel(SpecParams p, int in_cap, int out_cap, const float *__rest
         spec_xchg2_load(lane, v, sx);
         __syncwarp();
         spec_pass3(v);
-        spec_xchg3_store(lane, v, sx);
-        __syncwarp();
-        // split the packed pair, scale, stage
+        // split the packed pair in registers, scale, stage
+        float pa[9], pb[9];
+        spec_split_regs(lane, v, pa, pb);
         float *oa_row = s_out + oa + fa * p.nfreq;
         float *ob_row = oa_row + p.nfreq;
+        const int c1 = lane, c2 = lane == 0 ? 32 : 64 - lane;
 #pragma unroll
-        for (int j = 0; j < 9; ++j) {
-            const int k = lane + 32 * j;
-            if (j < 8 || lane == 0) {
-                float pa, pb;
-                spec_split_power(sx, k, pa, pb);
-                float ra, rb;
-                if (p.mode == 0) {
-                    ra = sqrt_approx(pa) * p.mag_mul;
-                    rb = sqrt_approx(pb) * p.mag_mul;
-                } else {
-                    const float m = (k == 0 || k == p.nfreq - 1) ? p.psd_edge : p.psd_mid;
-                    ra = pa * m;
-                    rb = pb * m;
-                }
-                oa_row[k] = ra;
-                if (has_b) ob_row[k] = rb;
+        for (int slot = 0; slot < 9; ++slot) {
+            if (slot == 8 && lane != 0) break;
+            const int k = slot == 8 ? 256 : 64 * (slot & 3) + ((slot >> 2) ? c2 : c1);
+            float ra, rb;
+            if (p.mode == 0) {
+                ra = sqrt_approx(pa[slot]) * p.mag_mul;
+                rb = sqrt_approx(pb[slot]) * p.mag_mul;
+            } else {
+                const float m = (k == 0 || k == p.nfreq - 1) ? p.psd_edge : p.psd_mid;
+                ra = pa[slot] * m;
+                rb = pb[slot] * m;
             }
+            oa_row[k] = ra;
+            if (has_b) ob_row[k] = rb;
         }
         __syncwarp();
     }

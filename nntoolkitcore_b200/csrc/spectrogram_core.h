@@ -6,7 +6,7 @@
 // Algorithm.  The reference runs a 512-point COMPLEX kissfft on each real frame with imag = 0
 // (signal/spectrogram.c:120-128, signal/dft.c:34-47).  Here two consecutive real frames a, b are packed as one complex
 // signal z = a + i*b, transformed by one 512-point complex FFT (three radix-8 decimation-in-frequency passes,
-// 16 points per lane, data in registers, three shared-memory exchanges), and separated with the conjugate symmetry
+// 16 points per lane, data in registers, TWO shared-memory exchanges), and separated with the conjugate symmetry
 //   A[k] = (Z[k] + conj(Z[N-k])) / 2,   B[k] = (Z[k] - conj(Z[N-k])) / (2i).
 // Twiddles come from the host table built exactly like kiss_fft.c:357-363 (double cos/sin rounded to float).
 //
@@ -16,10 +16,9 @@
 //   xchg 1    E1[q*72 + n']   (float2 units; 72 = 64 + 8 pad -> conflict-free LDS.64/STS.64)
 //   pass 2    butterfly b = L + 32 s, q = b / 8, n'' = b % 8: inputs E1[q*72 + n'' + 8 m];
 //             u_{q'}[n''] = (sum_m . W8^{m q'}) W64^{n'' q'}
-//   xchg 2    E2[(8 q + q') * 9 + n'']   (row stride 9)
-//   pass 3    butterfly b = L + 32 s = 8 q + q': inputs E2[b*9 + n''];  Z[64 k'' + 8 q' + q] = sum_{n''} . W8^{n'' k''}
-//   xchg 3    ZS[pad(k)] with pad(k) = k + 2 (k >> 4), natural order
-//   split     k = L + 32 j (j = 0..7) and k = 256 on lane 0.
+//   xchg 2    E2[c*8 + (n'' ^ ((c>>1)&7))], c = 8 q' + q   (XOR-swizzled, no padding)
+//   pass 3    butterfly c (lane L owns c = L and c = 64 - L): Z[64 k'' + c] = sum_{n''} E2[c][n''] W8^{n'' k''}
+//   split     in registers: bins 64 k'' + c and their mirrors 64 (7 - k'') + (64 - c) are in the same lane.
 #pragma once
 
 #ifdef __CUDACC__
@@ -31,7 +30,7 @@ static inline float2 make_float2(float x, float y) { float2 r; r.x = x; r.y = y;
 #endif
 
 #define NNTK_SPEC_N 512
-#define NNTK_SPEC_SMEM_F2 576 /* float2 slots per warp for every exchange: 8*72 = 64*9 = 512 + 64 */
+#define NNTK_SPEC_SMEM_F2 576 /* float2 slots per warp: exchange 1 uses 8*72, exchange 2 uses 512 */
 
 NNTK_HD float2 c_add(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 NNTK_HD float2 c_sub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
@@ -104,33 +103,52 @@ NNTK_HD void spec_pass2(float2 *v, const SpecLaneConst &c) {
         for (int q = 1; q < 8; ++q) x[q] = c_mul(x[q], c.tw2[q - 1]);
     }
 }
+// Exchange 2 layout: the 8 inputs of last-pass butterfly c (c = 8 q' + q = low 6 bits of the output bin) live at
+// E2[c*8 + (n'' ^ ((c >> 1) & 7))] -- 512 float2, no padding; the XOR makes both the store (lanes vary q, n'') and the
+// mirrored load below (lanes vary c) conflict-free for 64-bit accesses.
+NNTK_HD int spec_e2_index(int c, int n2) { return c * 8 + (n2 ^ ((c >> 1) & 7)); }
 NNTK_HD void spec_xchg2_store(int lane, const float2 *v, float2 *sm) {
     for (int s = 0; s < 2; ++s) {
         int q = (lane >> 3) + 4 * s, n2 = lane & 7;
-        for (int qp = 0; qp < 8; ++qp) sm[(8 * q + qp) * 9 + n2] = v[8 * s + qp];
+        for (int qp = 0; qp < 8; ++qp) sm[spec_e2_index(8 * qp + q, n2)] = v[8 * s + qp];
     }
 }
+// Last-pass butterfly assignment: lane L owns c1 = L and c2 = 64 - L (lane 0: c = 0 and 32).  Butterfly c emits
+// Z[64 k'' + c], and the conjugate-symmetry partner of bin 64 k'' + c is 64 (7 - k'') + (64 - c): with this assignment
+// BOTH bins of every pair sit in the same lane, so the two packed real frames are separated in registers and the
+// third exchange of the textbook scheme disappears.
+NNTK_HD int spec_lane_c(int lane, int s) { return s == 0 ? lane : (lane == 0 ? 32 : 64 - lane); }
 NNTK_HD void spec_xchg2_load(int lane, float2 *v, const float2 *sm) {
-    for (int s = 0; s < 2; ++s)
-        for (int n2 = 0; n2 < 8; ++n2) v[8 * s + n2] = sm[(lane + 32 * s) * 9 + n2];
+    for (int s = 0; s < 2; ++s) {
+        int c = spec_lane_c(lane, s);
+        for (int n2 = 0; n2 < 8; ++n2) v[8 * s + n2] = sm[spec_e2_index(c, n2)];
+    }
 }
-NNTK_HD void spec_pass3(float2 *v) {
+NNTK_HD void spec_pass3(float2 *v) {   // v[k''] = Z[64 k'' + c1], v[8 + k''] = Z[64 k'' + c2]
     radix8(v);
     radix8(v + 8);
 }
-NNTK_HD int spec_pad(int k) { return k + 2 * (k >> 4); }
-NNTK_HD void spec_xchg3_store(int lane, const float2 *v, float2 *sm) {
-    for (int s = 0; s < 2; ++s) {
-        int q = (lane >> 3) + 4 * s, qp = lane & 7;
-        for (int k2 = 0; k2 < 8; ++k2) sm[spec_pad(64 * k2 + 8 * qp + q)] = v[8 * s + k2];
-    }
-}
-// Squared magnitudes (times 4) of the two packed real frames at bin k: pa = 4|A[k]|^2, pb = 4|B[k]|^2.
-NNTK_HD void spec_split_power(const float2 *sm, int k, float &pa, float &pb) {
-    float2 z = sm[spec_pad(k)];
-    float2 n = sm[spec_pad((NNTK_SPEC_N - k) & (NNTK_SPEC_N - 1))];
-    float ar = z.x + n.x, ai = z.y - n.y;  // 2 A[k]
-    float br = z.y + n.y, bi = z.x - n.x;  // 2 B[k] = (br, -bi)
+// pa = 4|A[k]|^2, pb = 4|B[k]|^2 from z = Z[k], m = Z[N-k]:  2A = z + conj(m),  2B = (z - conj(m)) / i
+NNTK_HD void spec_pair_power(float2 z, float2 m, float &pa, float &pb) {
+    float ar = z.x + m.x, ai = z.y - m.y;
+    float br = z.y + m.y, bi = z.x - m.x;
     pa = ar * ar + ai * ai;
     pb = br * br + bi * bi;
+}
+// In-register split.  Slot j = 0..3: bin 64 j + c1;  slot 4 + j: bin 64 j + c2;  slot 8 (lane 0 only): bin 256.
+NNTK_HD int spec_slot_bin(int lane, int slot) {
+    if (slot == 8) return 256;
+    return 64 * (slot & 3) + spec_lane_c(lane, slot >> 2);
+}
+NNTK_HD void spec_split_regs(int lane, const float2 *v, float *pa, float *pb) {
+    const bool l0 = lane == 0;
+    for (int j = 0; j < 4; ++j) {
+        // partner of 64 j + c1: lane 0 (c1 = 0): Z[64 (8 - j) mod 512] = v[(8 - j) & 7]; else Z[64 (7 - j) + c2] = v[15 - j]
+        float2 m1 = l0 ? v[(8 - j) & 7] : v[15 - j];
+        spec_pair_power(v[j], m1, pa[j], pb[j]);
+        // partner of 64 j + c2: lane 0 (c2 = 32): v[15 - j]; else Z[64 (7 - j) + c1] = v[7 - j]
+        float2 m2 = l0 ? v[15 - j] : v[7 - j];
+        spec_pair_power(v[8 + j], m2, pa[4 + j], pb[4 + j]);
+    }
+    spec_pair_power(v[4], v[4], pa[8], pb[8]);   // bin 256 (meaningful on lane 0 only)
 }

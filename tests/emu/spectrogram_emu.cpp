@@ -21,8 +21,19 @@ extern "C" void emu_spectrogram512_pair(const float *za, const float *zb, const 
     for (int l = 0; l < 32; ++l) spec_xchg2_store(l, v[l], sm.data());
     for (int l = 0; l < 32; ++l) spec_xchg2_load(l, v[l], sm.data());
     for (int l = 0; l < 32; ++l) spec_pass3(v[l]);
-    for (int l = 0; l < 32; ++l) spec_xchg3_store(l, v[l], sm.data());
-    for (int k = 0; k <= 256; ++k) spec_split_power(sm.data(), k, pa[k], pb[k]);
-    if (zout)
-        for (int k = 0; k < 512; ++k) { zout[2 * k] = sm[spec_pad(k)].x; zout[2 * k + 1] = sm[spec_pad(k)].y; }
+    for (int l = 0; l < 32; ++l) {
+        float qa[9], qb[9];
+        spec_split_regs(l, v[l], qa, qb);
+        for (int slot = 0; slot < 9; ++slot) {
+            if (slot == 8 && l != 0) continue;
+            int k = spec_slot_bin(l, slot);
+            if (k <= 256) { pa[k] = qa[slot]; pb[k] = qb[slot]; }
+        }
+        if (zout)
+            for (int s2 = 0; s2 < 2; ++s2)
+                for (int k2 = 0; k2 < 8; ++k2) {
+                    int k = 64 * k2 + spec_lane_c(l, s2);
+                    zout[2 * k] = v[l][8 * s2 + k2].x; zout[2 * k + 1] = v[l][8 * s2 + k2].y;
+                }
+    }
 }
