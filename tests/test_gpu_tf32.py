@@ -1,0 +1,68 @@
+"""GPU tier: the optional tensor-core math mode (NNTK_MATH_TF32: tcgen05 kind::tf32 + TMA + TMEM, csrc/gemm_tc.cu)
+against the unmodified reference at the stated 1e-3 tolerance; the default fp32 mode is restored afterwards."""
+import numpy as np
+import pytest
+
+import helpers
+from helpers import assert_parity, TF32_TOL
+from nntoolkitcore_b200 import layers as L
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300)]
+
+
+@pytest.fixture()
+def tf32(cuda, product):
+    assert product.NNTKSetMathMode(1) == 0
+    yield product
+    product.NNTKSetMathMode(0)
+
+
+@pytest.mark.parametrize("cin,cout,k,s,T,B", [(128, 256, 5, 1, 300, 3), (64, 96, 3, 2, 257, 2), (256, 256, 5, 1, 130, 2),
+                                              (16, 8, 1, 1, 40, 1)])
+def test_conv1d_tf32(tf32, ref, cin, cout, k, s, T, B):
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal((B, T, cin)).astype(np.float32)
+    c_ref, c_new = L.Conv1d(ref, cin, cout, k, s, T), L.Conv1d(tf32, cin, cout, k, s, T)
+    helpers.fill_conv(c_ref, 300); helpers.copy_weights(c_new, c_ref)
+    t_out = c_ref.out_shape[0]
+    bn_ref, bn_new = L.BatchNorm(ref, cout, 1e-3, t_out), L.BatchNorm(tf32, cout, 1e-3, t_out)
+    helpers.fill_bn(bn_ref, 302); helpers.copy_weights(bn_new, bn_ref)
+    r_ref, r_new = L.Activation(ref, L.ACT_RELU, t_out * cout), L.Activation(tf32, L.ACT_RELU, t_out * cout)
+    want = np.stack([r_ref.apply(bn_ref.apply(c_ref.apply(v))) for v in x])
+    got = c_new.apply_batch(x, bn=bn_new, act=r_new)
+    err, l2 = assert_parity(got, want, tol=TF32_TOL, what="conv tf32")
+    assert l2 > 1e-7, "suspiciously exact: the tensor-core path did not run"
+
+
+def test_dense_and_tdd_tf32(tf32, ref):
+    rng = np.random.default_rng(9)
+    x = rng.standard_normal((3, 200, 256)).astype(np.float32)
+    d_ref, d_new = L.Dense(ref, 256, 12, L.ACT_SOFTMAX, ts=200), L.Dense(tf32, 256, 12, L.ACT_SOFTMAX, ts=200)
+    helpers.fill_dense(d_ref, 501); helpers.copy_weights(d_new, d_ref)
+    want = np.stack([d_ref.apply(v) for v in x])
+    assert_parity(d_new.apply_batch(x), want, tol=TF32_TOL, what="tdd tf32")
+
+
+@pytest.mark.parametrize("cell,in_size,H,T,B", [("gru", 256, 256, 10, 200), ("lstm", 512, 512, 6, 130)])
+def test_recurrent_projection_tf32(tf32, ref, cell, in_size, H, T, B):
+    """the hoisted x*W projection runs on the tensor cores; the recurrent step stays fp32"""
+    rng = np.random.default_rng(4)
+    x = rng.standard_normal((B, T, in_size)).astype(np.float32)
+    outs = []
+    for v in x[:4]:
+        r = L.Recurrent(ref, cell, in_size, H, T)
+        helpers.fill_recurrent(r, 400)
+        outs.append(r.apply(v)); r.close()
+    r = L.Recurrent(tf32, cell, in_size, H, T)
+    helpers.fill_recurrent(r, 400)
+    got = r.apply_batch(x)
+    assert_parity(got[:4], np.stack(outs), tol=TF32_TOL, what=f"{cell} tf32 projection")
+
+
+def test_unaligned_shapes_fall_back_to_fp32_kernel(tf32, ref):
+    """Cin = 257 rows are not 16-byte aligned: TMA cannot address them, the fp32 kernel runs (still on the GPU)"""
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal((2, 40, 257)).astype(np.float32)
+    c_ref, c_new = L.Conv1d(ref, 257, 64, 5, 1, 40), L.Conv1d(tf32, 257, 64, 5, 1, 40)
+    helpers.fill_conv(c_ref, 7); helpers.copy_weights(c_new, c_ref)
+    assert_parity(c_new.apply_batch(x), np.stack([c_ref.apply(v) for v in x]), what="fallback")
