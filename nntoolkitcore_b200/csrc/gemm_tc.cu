@@ -237,13 +237,28 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     }
 }
 
-// Bt[n][k] = B[k][n], leading dimension ldbt (multiple of 4); tail columns k in [K, ldbt) zeroed.
+// The tensor core reads only the upper 19 bits of an fp32 operand (TF32: the low 13 mantissa bits are TRUNCATED, not
+// rounded).  Truncation shrinks every operand by 2^-11 / m on average (m = its mantissa in [1, 2)), i.e. every product
+// carries a systematic relative bias of about -0.72 * 2^-11 per truncated operand -- on the GPU this showed up as outputs
+// uniformly ~7e-4 too small (rel-L2 7.4e-4 against the reference with both operands truncated).  Two cheap counter-measures:
+//   * weights are rounded to NEAREST-even TF32 here (they pass through this kernel anyway): unbiased, half the error;
+//   * activations are read raw by TMA, so their mean truncation bias is compensated in the epilogue scale:
+//     acc * (1 + TF32_TRUNC_BIAS), TF32_TRUNC_BIAS = 2^-11 * E[1/m] with E[1/m] = 1/(2 ln 2) for log-uniform mantissas.
+// What remains is the zero-mean part of the rounding errors, ~1e-4 relative on the conv / projection shapes.
+constexpr float TF32_TRUNC_BIAS = 3.5222e-4f;
+__device__ __forceinline__ float round_tf32(float x) {
+    uint32_t u;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+    return __uint_as_float(u);
+}
+
+// Bt[n][k] = tf32(B[k][n]), leading dimension ldbt (multiple of 4); tail columns k in [K, ldbt) zeroed.
 __global__ void transpose_weights_kernel(const float *__restrict__ B, float *__restrict__ Bt, int K, int N, int ldbt) {
     __shared__ float tile[32][33];
     const int k0 = blockIdx.x * 32, n0 = blockIdx.y * 32;
     for (int i = threadIdx.y; i < 32; i += blockDim.y) {
         const int k = k0 + i, n = n0 + threadIdx.x;
-        tile[i][threadIdx.x] = (k < K && n < N) ? B[(long long)k * N + n] : 0.0f;
+        tile[i][threadIdx.x] = (k < K && n < N) ? round_tf32(B[(long long)k * N + n]) : 0.0f;
     }
     __syncthreads();
     for (int i = threadIdx.y; i < 32; i += blockDim.y) {
@@ -252,17 +267,19 @@ __global__ void transpose_weights_kernel(const float *__restrict__ B, float *__r
     }
 }
 
-// scale[n], shift[n] such that act(acc*scale + shift) == act(BN(acc + bias)) up to rounding
+// scale[n], shift[n] such that act(acc*scale + shift) == act(BN(acc + bias)) up to rounding; the scale also carries the
+// compensation of the A-operand truncation bias (see TF32_TRUNC_BIAS).
 __global__ void fold_epilogue_kernel(const float *bias, const float *bn, float eps, int N, float *scale, float *shift) {
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= N) return;
     const float b = bias ? bias[n] : 0.0f;
+    const float comp = 1.0f + TF32_TRUNC_BIAS;
     if (bn) {
         const float s = bn[n] / sqrtf(bn[3 * N + n] + eps);
-        scale[n] = s;
+        scale[n] = s * comp;
         shift[n] = (b - bn[2 * N + n]) * s + bn[N + n];
     } else {
-        scale[n] = 1.0f;
+        scale[n] = comp;
         shift[n] = b;
     }
 }

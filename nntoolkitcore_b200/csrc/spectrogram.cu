@@ -1,14 +1,17 @@
 // spectrogram.cu -- K1: batched STFT front-end (replaces signal/spectrogram.c:113-135 + signal/dft.c:34-47 +
 // third_party/kissfft/kiss_fft.c:236-300 of the reference for the inference path).
 //
-// Fast path (nfft == 512): one CTA owns a tile of F consecutive frames of one clip.  The clip span the tile needs,
-// (F-1)*step + window_size samples, is read from HBM ONCE with 16-byte loads into shared memory; the frame overlap
-// (hop 160 vs window 512 => every sample belongs to 3.2 frames) is served from shared memory.  One warp transforms
-// TWO real frames as one 512-point complex FFT held in registers (csrc/spectrogram_core.h), the window multiply is
-// fused into the register load, the two frames are separated IN REGISTERS (no third exchange), magnitude / PSD scaling
-// is applied there, and the [F, 257] result tile -- a flat
-// contiguous span of the [n_clips, ntime, nfreq] output, whose 257-float rows are never 16-byte aligned -- is staged
-// in shared memory with the alignment of its global address and written back with 16-byte stores.
+// Fast path (nfft == 512): a PERSISTENT grid (2 CTAs per SM) walks tiles of F = 32 consecutive frames of one clip.
+//   * The clip span a tile needs, (F-1)*step + window_size samples, is read from HBM once with 16-byte cp.async
+//     (LDGSTS) into one of two shared-memory buffers; the copy of tile i+1 is in flight while tile i is transformed.
+//     The frame overlap (hop 160 vs window 512 => every sample belongs to 3.2 frames) is served from shared memory.
+//   * One warp transforms TWO real frames as one 512-point complex FFT held in registers (csrc/spectrogram_core.h):
+//     window (per-lane registers) multiplied on load, three radix-8 passes, two shared-memory exchanges whose addresses
+//     are all "per-lane base + immediate", the two frames separated IN REGISTERS (no third exchange), magnitude / PSD
+//     scaling applied there.
+//   * Each lane writes its bins straight to HBM: per store instruction the warp covers 32 consecutive floats of an
+//     output row (128 bytes), so no output staging buffer and no second pass over shared memory is needed
+//     (rows are 257 floats, never 16-byte aligned -- L2 merges the partial sectors of neighbouring stores).
 //
 // Generic path (any other nfft): one CTA per frame, shared-memory radix-2 FFT when nfft is a power of two, direct
 // O(nfft^2) DFT from the twiddle table otherwise.  Correct for every nfft the reference accepts, not tuned.
@@ -19,15 +22,18 @@
 
 namespace {
 
+constexpr int SPEC_THREADS = 256, SPEC_WARPS = SPEC_THREADS / 32, SPEC_F = 32;
+
 struct SpecParams {
     int window_size, step, input_size, ntime, nfreq;
     int frames_per_tile, tiles_per_clip;
-    int mode;           // 0 magnitude, 1 PSD
+    long long total_tiles;
+    int in_cap;         // floats per input buffer
     float mag_mul;      // magnitude: |norm| * 0.5 / scale            (the split pass yields 2|X|)
     float psd_mid;      // PSD bins 1..nfreq-2: norm^2 * 0.25 * 2/scale (the split pass yields 4|X|^2)
     float psd_edge;     // PSD bins 0, nfreq-1: norm^2 * 0.25 / scale
+    int mode;           // 0 magnitude, 1 PSD (generic kernel only; the 512 kernel is templated on it)
     int in_vec_ok;      // input base pointer 16-byte aligned
-    int out_vec_ok;     // output base pointer 16-byte aligned
 };
 
 __device__ __forceinline__ float sqrt_approx(float x) {
@@ -35,123 +41,148 @@ __device__ __forceinline__ float sqrt_approx(float x) {
     asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void *smem, const void *gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-// Shared memory layout (floats):
-//   [0, in_cap)                    clip span, stored at offset (global index & 3) so 16-byte global loads line up
-//   [in_cap, in_cap + out_cap)     output stage, stored at offset (global index & 3)
-//   then 8 warps x 576 float2      FFT exchange buffers
-__global__ void __launch_bounds__(256, 2)
-spectrogram512_kernel(SpecParams p, int in_cap, int out_cap, const float *__restrict__ window,
-                      const float2 *__restrict__ tw512, const float *__restrict__ in, float *__restrict__ out) {
+struct TileGeom {
+    long long clip;
+    int f0, nf, ia;
+    long long gi0;
+};
+__device__ __forceinline__ TileGeom tile_geom(const SpecParams &p, long long tile) {
+    TileGeom g;
+    g.clip = tile / p.tiles_per_clip;
+    const int t = (int)(tile - g.clip * p.tiles_per_clip);
+    g.f0 = t * p.frames_per_tile;
+    g.nf = min(p.frames_per_tile, p.ntime - g.f0);
+    g.gi0 = g.clip * (long long)p.input_size + (long long)g.f0 * p.step;
+    g.ia = p.in_vec_ok ? (int)(g.gi0 & 3) : 0;
+    return g;
+}
+// clip span of a tile -> shared memory (smem index s <-> global gi0 - ia + s), asynchronously
+__device__ __forceinline__ void tile_load_async(const SpecParams &p, const TileGeom &g, const float *__restrict__ in,
+                                                float *s_buf, int tid) {
+    const int total = g.ia + (g.nf - 1) * p.step + p.window_size;
+    const float *gbase = in + (g.gi0 - g.ia);
+    int done = 0;
+    if (p.in_vec_ok) {
+        const int nvec = total >> 2;
+        for (int v = tid; v < nvec; v += SPEC_THREADS) cp_async16(s_buf + 4 * v, gbase + 4 * v);
+        done = 4 * nvec;
+    }
+    for (int s = done + tid; s < total; s += SPEC_THREADS) cp_async4(s_buf + s, gbase + s);
+}
+
+// Shared memory layout (floats): [2][in_cap] clip-span double buffer, then SPEC_WARPS x 656 float2 exchange buffers.
+template <bool FULLWIN, int MODE>
+__global__ void __launch_bounds__(SPEC_THREADS, 2)
+spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const float2 *__restrict__ tw512,
+                      const float *__restrict__ in, float *__restrict__ out) {
     extern __shared__ __align__(16) float smem[];
     float *s_in = smem;
-    float *s_out = smem + in_cap;
-    float2 *s_x = reinterpret_cast<float2 *>(smem + in_cap + out_cap);
+    float2 *s_x = reinterpret_cast<float2 *>(smem + 2 * p.in_cap);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const long long clip = blockIdx.x / p.tiles_per_clip;
-    const int tile = blockIdx.x - (int)(clip * p.tiles_per_clip);
-    const int f0 = tile * p.frames_per_tile;
-    const int nf = min(p.frames_per_tile, p.ntime - f0);
+    long long tile = blockIdx.x;
+    if (tile >= p.total_tiles) return;
+    TileGeom g = tile_geom(p, tile);
+    tile_load_async(p, g, in, s_in, tid);
+    cp_async_commit();
 
-    // ---- 1. clip span -> shared memory (each sample read from HBM once per tile) -------------------------------
-    const long long gi0 = clip * (long long)p.input_size + (long long)f0 * p.step;
-    const int span = (nf - 1) * p.step + p.window_size;
-    const int ia = p.in_vec_ok ? (int)(gi0 & 3) : 0;
-    if (p.in_vec_ok) {
-        // smem index s <-> global gi0 - ia + s ; vector v covers s = 4v..4v+3
-        const float *gbase = in + (gi0 - ia);
-        const int total = ia + span;
-        const int nvec = total >> 2;
-        for (int v = tid; v < nvec; v += 256) {
-            float4 x = __ldg(reinterpret_cast<const float4 *>(gbase) + v);
-            *reinterpret_cast<float4 *>(s_in + 4 * v) = x;
-        }
-        for (int s = 4 * nvec + tid; s < total; s += 256) s_in[s] = __ldg(gbase + s);
-    } else {
-        const float *gbase = in + gi0;
-        for (int s = tid; s < span; s += 256) s_in[s] = __ldg(gbase + s);
-    }
-
-    // per-lane FFT constants (registers) while the loads are in flight
+    // per-lane constants (registers), fetched while the first tile is in flight
     SpecLaneConst lc;
     spec_lane_const(lane, tw512, lc);
-    __syncthreads();
-
-    // ---- 2. FFTs: warp w handles frame pairs w, w+8, ... --------------------------------------------------------
-    const long long go0 = (clip * (long long)p.ntime + f0) * (long long)p.nfreq;
-    const int oa = p.out_vec_ok ? (int)(go0 & 3) : 0;
-    float2 *sx = s_x + warp * NNTK_SPEC_SMEM_F2;
-    const int npairs = (nf + 1) >> 1;
-    for (int pr = warp; pr < npairs; pr += 8) {
-        const int fa = 2 * pr, fb = 2 * pr + 1;
-        const bool has_b = fb < nf;
-        const float *xa = s_in + ia + fa * p.step;
-        const float *xb = s_in + ia + (has_b ? fb : fa) * p.step;
-        float2 v[16];
+    float w[16];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            const int n = lane + 32 * j;
-            float w = 0.0f, a = 0.0f, b = 0.0f;
-            if (n < p.window_size) {
-                w = __ldg(window + n);
-                a = xa[n];
-                b = xb[n];
-            }
-            v[j] = make_float2(w * a, has_b ? w * b : 0.0f);
-        }
-        spec_pass1(v, lc);
-        spec_xchg1_store(lane, v, sx);
-        __syncwarp();
-        spec_xchg1_load(lane, v, sx);
-        __syncwarp();
-        spec_pass2(v, lc);
-        spec_xchg2_store(lane, v, sx);
-        __syncwarp();
-        spec_xchg2_load(lane, v, sx);
-        __syncwarp();
-        spec_pass3(v);
-        // split the packed pair in registers, scale, stage
-        float pa[9], pb[9];
-        spec_split_regs(lane, v, pa, pb);
-        float *oa_row = s_out + oa + fa * p.nfreq;
-        float *ob_row = oa_row + p.nfreq;
-        const int c1 = lane, c2 = lane == 0 ? 32 : 64 - lane;
-#pragma unroll
-        for (int slot = 0; slot < 9; ++slot) {
-            if (slot == 8 && lane != 0) break;
-            const int k = slot == 8 ? 256 : 64 * (slot & 3) + ((slot >> 2) ? c2 : c1);
-            float ra, rb;
-            if (p.mode == 0) {
-                ra = sqrt_approx(pa[slot]) * p.mag_mul;
-                rb = sqrt_approx(pb[slot]) * p.mag_mul;
-            } else {
-                const float m = (k == 0 || k == p.nfreq - 1) ? p.psd_edge : p.psd_mid;
-                ra = pa[slot] * m;
-                rb = pb[slot] * m;
-            }
-            oa_row[k] = ra;
-            if (has_b) ob_row[k] = rb;
-        }
-        __syncwarp();
+    for (int j = 0; j < 16; ++j) {
+        const int n = lane + 32 * j;
+        w[j] = (FULLWIN || n < p.window_size) ? __ldg(window + n) : 0.0f;
     }
-    __syncthreads();
+    float2 *sx = s_x + warp * NNTK_SPEC_SMEM_F2;
+    float2 *x1_st = sx + spec_x1_st_base(lane);
+    const float2 *x1_ld = sx + spec_x1_ld_base(lane);
+    float2 *x2_st = sx + spec_x2_st_base(lane);
+    const float2 *x2_ld0 = sx + spec_x2_ld_base(lane, 0);
+    const float2 *x2_ld1 = sx + spec_x2_ld_base(lane, 1);
+    const int c2 = spec_lane_c(lane, 1);
+    const bool l0 = lane == 0;
 
-    // ---- 3. output stage -> HBM, one flat span -------------------------------------------------------------------
-    const int n_out = nf * p.nfreq;
-    if (p.out_vec_ok) {
-        float *gbase = out + (go0 - oa);   // 16-byte aligned
-        const int head = oa ? (4 - oa) : 0;                 // scalars before the first aligned vector
-        const int first_vec = oa ? 1 : 0;
-        const int end = oa + n_out;
-        const int last_vec = end >> 2;                      // vectors [first_vec, last_vec) are complete
-        for (int s = oa + tid; s < oa + head && s < end; s += 256) gbase[s] = s_out[s];
-        for (int v = first_vec + tid; v < last_vec; v += 256)
-            reinterpret_cast<float4 *>(gbase)[v] = *reinterpret_cast<const float4 *>(s_out + 4 * v);
-        for (int s = max(4 * last_vec, oa + head) + tid; s < end; s += 256) gbase[s] = s_out[s];
-    } else {
-        float *gbase = out + go0;
-        for (int s = tid; s < n_out; s += 256) gbase[s] = s_out[s];
+    for (int it = 0;; ++it) {
+        cp_async_wait_all();
+        __syncthreads();   // tile `it` has landed for every thread; every warp is done with the other buffer
+        const long long next = tile + gridDim.x;
+        const bool more = next < p.total_tiles;
+        TileGeom gn = g;
+        if (more) {
+            gn = tile_geom(p, next);
+            tile_load_async(p, gn, in, s_in + ((it + 1) & 1) * p.in_cap, tid);
+        }
+        cp_async_commit();
+
+        const float *buf = s_in + (it & 1) * p.in_cap + g.ia + lane;
+        float *orow = out + (g.clip * (long long)p.ntime + g.f0) * 257LL;
+        const int npairs = (g.nf + 1) >> 1;
+#pragma unroll 1
+        for (int pr = warp; pr < npairs; pr += SPEC_WARPS) {
+            const int fa = 2 * pr;
+            const bool has_b = fa + 1 < g.nf;
+            const float *xa = buf + fa * p.step;
+            const float *xb = has_b ? xa + p.step : xa;
+            float2 v[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                float a = 0.0f, b = 0.0f;
+                if (FULLWIN || lane + 32 * j < p.window_size) {
+                    a = xa[32 * j];
+                    b = xb[32 * j];
+                }
+                v[j] = make_float2(w[j] * a, w[j] * b);
+            }
+            spec_pass1(v, lc);
+            spec_xchg1_store(v, x1_st);
+            __syncwarp();
+            spec_xchg1_load(v, x1_ld);
+            __syncwarp();
+            spec_pass2(v, lc);
+            spec_xchg2_store(v, x2_st);
+            __syncwarp();
+            spec_xchg2_load(v, x2_ld0, x2_ld1);
+            __syncwarp();
+            spec_pass3(v);
+            // split the packed pair in registers, scale, store: slot j -> bin 64 j + lane, slot 4 + j -> bin 64 j + c2
+            float pa[9], pb[9];
+            spec_split_regs(lane, v, pa, pb);
+            float *ra = orow + (long long)fa * 257;
+            float *ra1 = ra + lane, *ra2 = ra + c2;
+#pragma unroll
+            for (int slot = 0; slot < 8; ++slot) {
+                float va, vb;
+                if (MODE == 0) {
+                    va = sqrt_approx(pa[slot]) * p.mag_mul;
+                    vb = sqrt_approx(pb[slot]) * p.mag_mul;
+                } else {
+                    const float m = (slot == 0 && l0) ? p.psd_edge : p.psd_mid;
+                    va = pa[slot] * m;
+                    vb = pb[slot] * m;
+                }
+                float *dst = (slot < 4 ? ra1 : ra2) + 64 * (slot & 3);
+                dst[0] = va;
+                if (has_b) dst[257] = vb;
+            }
+            if (l0) {   // bin 256
+                ra[256] = MODE == 0 ? sqrt_approx(pa[8]) * p.mag_mul : pa[8] * p.psd_edge;
+                if (has_b) ra[256 + 257] = MODE == 0 ? sqrt_approx(pb[8]) * p.mag_mul : pb[8] * p.psd_edge;
+            }
+        }
+        if (!more) break;
+        tile = next;
+        g = gn;
     }
 }
 
@@ -251,19 +282,17 @@ extern "C" int nntk_cuda_spectrogram(const nntk_spectrogram_args *a, const float
     p.psd_mid = an * an * 0.25f * (2.0f / a->scale);
     p.psd_edge = an * an * 0.25f / a->scale;
     p.in_vec_ok = (((uintptr_t)d_in) & 15) == 0;
-    p.out_vec_ok = (((uintptr_t)d_out) & 15) == 0;
     cudaStream_t st = nntk_stream();
 
     if (a->nfft == NNTK_SPEC_N) {
         // frames per tile: largest of 32/16/8/4/2 whose shared memory lets two CTAs share an SM
-        const size_t xchg = (size_t)8 * NNTK_SPEC_SMEM_F2 * sizeof(float2);
-        int F = 32;
+        const size_t xchg = (size_t)SPEC_WARPS * NNTK_SPEC_SMEM_F2 * sizeof(float2);
+        int F = SPEC_F;
         size_t bytes = 0;
-        int in_cap = 0, out_cap = 0;
+        int in_cap = 0;
         for (;; F >>= 1) {
             in_cap = (((F - 1) * a->step + a->window_size + 3 + 3) / 4) * 4;
-            out_cap = ((F * a->nfreq + 3 + 3) / 4) * 4;
-            bytes = (size_t)(in_cap + out_cap) * sizeof(float) + xchg;
+            bytes = (size_t)2 * in_cap * sizeof(float) + xchg;
             if (bytes <= 112 * 1024 || F == 2) break;
         }
         if (bytes > 227 * 1024) {
@@ -272,20 +301,23 @@ extern "C" int nntk_cuda_spectrogram(const nntk_spectrogram_args *a, const float
         }
         p.frames_per_tile = F;
         p.tiles_per_clip = (a->ntime + F - 1) / F;
-        static size_t attr_bytes = 0;
-        if (bytes > attr_bytes) {
-            NNTK_CUDA_TRY(cudaFuncSetAttribute(spectrogram512_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                               (int)bytes));
-            attr_bytes = bytes;
+        p.total_tiles = (long long)n_clips * p.tiles_per_clip;
+        p.in_cap = in_cap;
+        const bool fullwin = a->window_size == NNTK_SPEC_N;
+        void (*kern)(SpecParams, const float *, const float2 *, const float *, float *) =
+            a->mode == 0 ? (fullwin ? spectrogram512_kernel<true, 0> : spectrogram512_kernel<false, 0>)
+                         : (fullwin ? spectrogram512_kernel<true, 1> : spectrogram512_kernel<false, 1>);
+        static size_t attr_bytes[4] = {0, 0, 0, 0};
+        const int ki = (a->mode ? 2 : 0) + (fullwin ? 1 : 0);
+        if (bytes > attr_bytes[ki]) {
+            NNTK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+            attr_bytes[ki] = bytes;
         }
-        long long grid = (long long)n_clips * p.tiles_per_clip;
-        if (grid > 0x7fffffffLL) {
-            nntk_cuda_set_error(NNTK_ERR_ARG_, "spectrogram: %d clips exceed one launch", n_clips);
-            return NNTK_ERR_ARG_;
-        }
-        spectrogram512_kernel<<<(unsigned)grid, 256, bytes, st>>>(p, in_cap, out_cap, a->d_window,
-                                                                 reinterpret_cast<const float2 *>(a->d_twiddle), d_in,
-                                                                 d_out);
+        // persistent: two CTAs per SM, each walks tiles blockIdx.x, blockIdx.x + gridDim.x, ...
+        long long grid = 2LL * nntk_cuda_sm_count();
+        if (grid > p.total_tiles) grid = p.total_tiles;
+        kern<<<(unsigned)grid, SPEC_THREADS, bytes, st>>>(p, a->d_window, reinterpret_cast<const float2 *>(a->d_twiddle),
+                                                          d_in, d_out);
         NNTK_LAUNCH_CHECK("spectrogram512_kernel");
         return 0;
     }
@@ -301,6 +333,8 @@ extern "C" int nntk_cuda_spectrogram(const nntk_spectrogram_args *a, const float
     }
     p.frames_per_tile = 1;
     p.tiles_per_clip = a->ntime;
+    p.total_tiles = (long long)n_clips * a->ntime;
+    p.in_cap = 0;
     static size_t attr_bytes_g = 48 * 1024;
     if (bytes > attr_bytes_g) {
         NNTK_CUDA_TRY(cudaFuncSetAttribute(spectrogram_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

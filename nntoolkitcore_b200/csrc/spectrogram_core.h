@@ -1,7 +1,8 @@
 // spectrogram_core.h -- the per-warp arithmetic of the K1 spectrogram kernel (nfft = 512), written once and used by
 //   * csrc/spectrogram.cu                 (the sm_100a kernel; one warp = two frames), and
 //   * tests/emu/spectrogram_emu.cpp       (a CPU emulation of the 32 lanes, used by the CPU test tier to check the
-//                                           index maps / butterflies against the oracle before any GPU time is spent).
+//                                           index maps / butterflies against the oracle, and to count shared-memory
+//                                           bank conflicts of every exchange, before any GPU time is spent).
 //
 // Algorithm.  The reference runs a 512-point COMPLEX kissfft on each real frame with imag = 0
 // (signal/spectrogram.c:120-128, signal/dft.c:34-47).  Here two consecutive real frames a, b are packed as one complex
@@ -10,14 +11,18 @@
 //   A[k] = (Z[k] + conj(Z[N-k])) / 2,   B[k] = (Z[k] - conj(Z[N-k])) / (2i).
 // Twiddles come from the host table built exactly like kiss_fft.c:357-363 (double cos/sin rounded to float).
 //
-// Index maps (N = 512, lane L = 0..31):
+// Index maps (N = 512, lane L = 0..31; shared-memory indices are in float2 units):
 //   load      v[j]            = z[L + 32 j]                               j = 0..15
 //   pass 1    butterfly s=0,1 : inputs v[s + 2m] = z[n' + 64 m], n' = L + 32 s;  y_q[n'] = (sum_m . W8^{mq}) W512^{n' q}
-//   xchg 1    E1[q*72 + n']   (float2 units; 72 = 64 + 8 pad -> conflict-free LDS.64/STS.64)
-//   pass 2    butterfly b = L + 32 s, q = b / 8, n'' = b % 8: inputs E1[q*72 + n'' + 8 m];
+//   xchg 1    E1[q*64 + 2L + s]: the lane's two values of a q are ADJACENT -> 8 x 16-byte stores; the consumer's inputs
+//             n'' + 8m and n'' + 8(m+4) are adjacent too -> 8 x 16-byte loads.  No padding, conflict-free.
+//   pass 2    butterfly b = L + 32 s, q = b / 8, n'' = b % 8: inputs y_q[n'' + 8 m];
 //             u_{q'}[n''] = (sum_m . W8^{m q'}) W64^{n'' q'}
-//   xchg 2    E2[c*8 + (n'' ^ ((c>>1)&7))], c = 8 q' + q   (XOR-swizzled, no padding)
-//   pass 3    butterfly c (lane L owns c = L and c = 64 - L): Z[64 k'' + c] = sum_{n''} E2[c][n''] W8^{n'' k''}
+//   xchg 2    E2[82 q + 10 n'' + q']: the lane's q' run is contiguous -> 8 x 16-byte stores (n'' stride of 80 bytes
+//             spreads a quarter-warp over all 16-byte slots of a 128-byte line); the consumer reads 16 x 8 bytes
+//             (q stride 82 = 2 mod 16 spreads a half-warp over the sixteen 8-byte bank pairs).  Padding only, so every
+//             address is one per-lane base plus a compile-time immediate.
+//   pass 3    butterfly c = q + 8 q' (lane L owns c = L and c = 64 - L): Z[64 k'' + c] = sum_{n''} E2[c][n''] W8^{n'' k''}
 //   split     in registers: bins 64 k'' + c and their mirrors 64 (7 - k'') + (64 - c) are in the same lane.
 #pragma once
 
@@ -30,7 +35,9 @@ static inline float2 make_float2(float x, float y) { float2 r; r.x = x; r.y = y;
 #endif
 
 #define NNTK_SPEC_N 512
-#define NNTK_SPEC_SMEM_F2 576 /* float2 slots per warp: exchange 1 uses 8*72, exchange 2 uses 512 */
+#define NNTK_SPEC_E2_Q 82    /* exchange-2 stride of q   (float2 units) */
+#define NNTK_SPEC_E2_N 10    /* exchange-2 stride of n'' (float2 units) */
+#define NNTK_SPEC_SMEM_F2 656 /* float2 slots per warp: exchange 1 uses 512, exchange 2 uses 82*7 + 10*7 + 8 = 652 */
 
 NNTK_HD float2 c_add(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 NNTK_HD float2 c_sub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
@@ -38,29 +45,57 @@ NNTK_HD float2 c_sub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b
 NNTK_HD float2 c_mul(float2 a, float2 w) { return make_float2(a.x * w.x - a.y * w.y, a.x * w.y + a.y * w.x); }
 NNTK_HD float2 c_mul_mi(float2 a) { return make_float2(a.y, -a.x); }  // a * (-i)
 
+// Two adjacent float2 slots moved as one 16-byte access on the device (idx must be even).  The emulator hooks
+// NNTK_SPEC_TRACE to record addresses and widths for the bank-conflict count.
+#ifndef NNTK_SPEC_TRACE
+#define NNTK_SPEC_TRACE(kind, ptr, width)
+#endif
+NNTK_HD void sm_st2(float2 *sm, int idx, float2 a, float2 b) {
+    NNTK_SPEC_TRACE(0, sm + idx, 16);
+#ifdef __CUDA_ARCH__
+    *reinterpret_cast<float4 *>(sm + idx) = make_float4(a.x, a.y, b.x, b.y);
+#else
+    sm[idx] = a; sm[idx + 1] = b;
+#endif
+}
+NNTK_HD void sm_ld2(const float2 *sm, int idx, float2 &a, float2 &b) {
+    NNTK_SPEC_TRACE(1, sm + idx, 16);
+#ifdef __CUDA_ARCH__
+    const float4 t = *reinterpret_cast<const float4 *>(sm + idx);
+    a = make_float2(t.x, t.y); b = make_float2(t.z, t.w);
+#else
+    a = sm[idx]; b = sm[idx + 1];
+#endif
+}
+NNTK_HD float2 sm_ld1(const float2 *sm, int idx) {
+    NNTK_SPEC_TRACE(1, sm + idx, 8);
+    return sm[idx];
+}
+
 // 8-point forward DFT, natural-order in and out: x[q] <- sum_m x[m] * exp(-2 pi i m q / 8).
+// The sqrt(1/2) factors of W8^1 and W8^3 are folded into the last stage as FMAs.
 NNTK_HD void radix8(float2 *x) {
     const float R = 0.70710678118654752440f;
     float2 a0 = c_add(x[0], x[4]), b0 = c_sub(x[0], x[4]);
     float2 a1 = c_add(x[1], x[5]), b1 = c_sub(x[1], x[5]);
     float2 a2 = c_add(x[2], x[6]), b2 = c_sub(x[2], x[6]);
     float2 a3 = c_add(x[3], x[7]), b3 = c_sub(x[3], x[7]);
-    // b_m *= W8^m
-    b1 = make_float2((b1.x + b1.y) * R, (b1.y - b1.x) * R);
-    b2 = c_mul_mi(b2);
-    b3 = make_float2((b3.y - b3.x) * R, -(b3.x + b3.y) * R);
     // even outputs: 4-point DFT of a
     float2 e0 = c_add(a0, a2), e1 = c_sub(a0, a2), o0 = c_add(a1, a3), o1 = c_mul_mi(c_sub(a1, a3));
     x[0] = c_add(e0, o0);
     x[4] = c_sub(e0, o0);
     x[2] = c_add(e1, o1);
     x[6] = c_sub(e1, o1);
-    // odd outputs: 4-point DFT of the twiddled b
-    float2 f0 = c_add(b0, b2), f1 = c_sub(b0, b2), g0 = c_add(b1, b3), g1 = c_mul_mi(c_sub(b1, b3));
-    x[1] = c_add(f0, g0);
-    x[5] = c_sub(f0, g0);
-    x[3] = c_add(f1, g1);
-    x[7] = c_sub(f1, g1);
+    // odd outputs: 4-point DFT of (b0, b1 W8, b2 W8^2, b3 W8^3) with b1 W8 = R p1, b3 W8^3 = R p3
+    b2 = c_mul_mi(b2);
+    float2 p1 = make_float2(b1.x + b1.y, b1.y - b1.x);
+    float2 p3 = make_float2(b3.y - b3.x, -(b3.x + b3.y));
+    float2 f0 = c_add(b0, b2), f1 = c_sub(b0, b2);
+    float2 g0 = c_add(p1, p3), g1 = c_mul_mi(c_sub(p1, p3));
+    x[1] = make_float2(fmaf(R, g0.x, f0.x), fmaf(R, g0.y, f0.y));
+    x[5] = make_float2(fmaf(-R, g0.x, f0.x), fmaf(-R, g0.y, f0.y));
+    x[3] = make_float2(fmaf(R, g1.x, f1.x), fmaf(R, g1.y, f1.y));
+    x[7] = make_float2(fmaf(-R, g1.x, f1.x), fmaf(-R, g1.y, f1.y));
 }
 
 // Per-lane constants, loaded once per CTA lifetime.
@@ -85,15 +120,16 @@ NNTK_HD void spec_pass1(float2 *v, const SpecLaneConst &c) {
         for (int q = 1; q < 8; ++q) v[s + 2 * q] = c_mul(x[q], c.tw1[s][q - 1]);
     }
 }
-NNTK_HD void spec_xchg1_store(int lane, const float2 *v, float2 *sm) {
-    for (int s = 0; s < 2; ++s)
-        for (int q = 0; q < 8; ++q) sm[q * 72 + lane + 32 * s] = v[s + 2 * q];
+// Exchange 1.  `sm_st` = sm + 2*lane and `sm_ld` = sm + (lane >> 3)*64 + 2*(lane & 7) are the per-lane bases; every
+// index below is a compile-time constant.
+NNTK_HD int spec_x1_st_base(int lane) { return 2 * lane; }
+NNTK_HD int spec_x1_ld_base(int lane) { return (lane >> 3) * 64 + 2 * (lane & 7); }
+NNTK_HD void spec_xchg1_store(const float2 *v, float2 *sm_st) {
+    for (int q = 0; q < 8; ++q) sm_st2(sm_st, q * 64, v[2 * q], v[2 * q + 1]);
 }
-NNTK_HD void spec_xchg1_load(int lane, float2 *v, const float2 *sm) {
-    for (int s = 0; s < 2; ++s) {
-        int q = (lane >> 3) + 4 * s, n2 = lane & 7;
-        for (int m = 0; m < 8; ++m) v[8 * s + m] = sm[q * 72 + n2 + 8 * m];
-    }
+NNTK_HD void spec_xchg1_load(float2 *v, const float2 *sm_ld) {
+    for (int s = 0; s < 2; ++s)
+        for (int m = 0; m < 4; ++m) sm_ld2(sm_ld, 256 * s + 16 * m, v[8 * s + m], v[8 * s + m + 4]);
 }
 // pass 2 on v[8 s + m]
 NNTK_HD void spec_pass2(float2 *v, const SpecLaneConst &c) {
@@ -103,26 +139,25 @@ NNTK_HD void spec_pass2(float2 *v, const SpecLaneConst &c) {
         for (int q = 1; q < 8; ++q) x[q] = c_mul(x[q], c.tw2[q - 1]);
     }
 }
-// Exchange 2 layout: the 8 inputs of last-pass butterfly c (c = 8 q' + q = low 6 bits of the output bin) live at
-// E2[c*8 + (n'' ^ ((c >> 1) & 7))] -- 512 float2, no padding; the XOR makes both the store (lanes vary q, n'') and the
-// mirrored load below (lanes vary c) conflict-free for 64-bit accesses.
-NNTK_HD int spec_e2_index(int c, int n2) { return c * 8 + (n2 ^ ((c >> 1) & 7)); }
-NNTK_HD void spec_xchg2_store(int lane, const float2 *v, float2 *sm) {
-    for (int s = 0; s < 2; ++s) {
-        int q = (lane >> 3) + 4 * s, n2 = lane & 7;
-        for (int qp = 0; qp < 8; ++qp) sm[spec_e2_index(8 * qp + q, n2)] = v[8 * s + qp];
-    }
-}
+// Exchange 2: element (q, q', n'') at E2[82 q + 10 n'' + q'].
+NNTK_HD int spec_x2_st_base(int lane) { return NNTK_SPEC_E2_Q * (lane >> 3) + NNTK_SPEC_E2_N * (lane & 7); }
 // Last-pass butterfly assignment: lane L owns c1 = L and c2 = 64 - L (lane 0: c = 0 and 32).  Butterfly c emits
 // Z[64 k'' + c], and the conjugate-symmetry partner of bin 64 k'' + c is 64 (7 - k'') + (64 - c): with this assignment
 // BOTH bins of every pair sit in the same lane, so the two packed real frames are separated in registers and the
 // third exchange of the textbook scheme disappears.
 NNTK_HD int spec_lane_c(int lane, int s) { return s == 0 ? lane : (lane == 0 ? 32 : 64 - lane); }
-NNTK_HD void spec_xchg2_load(int lane, float2 *v, const float2 *sm) {
-    for (int s = 0; s < 2; ++s) {
-        int c = spec_lane_c(lane, s);
-        for (int n2 = 0; n2 < 8; ++n2) v[8 * s + n2] = sm[spec_e2_index(c, n2)];
-    }
+NNTK_HD int spec_x2_ld_base(int lane, int s) {
+    const int c = spec_lane_c(lane, s);
+    return NNTK_SPEC_E2_Q * (c & 7) + (c >> 3);
+}
+NNTK_HD void spec_xchg2_store(const float2 *v, float2 *sm_st) {
+    for (int s = 0; s < 2; ++s)
+        for (int p = 0; p < 4; ++p)
+            sm_st2(sm_st, 4 * NNTK_SPEC_E2_Q * s + 2 * p, v[8 * s + 2 * p], v[8 * s + 2 * p + 1]);
+}
+NNTK_HD void spec_xchg2_load(float2 *v, const float2 *sm_ld0, const float2 *sm_ld1_) {
+    for (int n2 = 0; n2 < 8; ++n2) v[n2] = sm_ld1(sm_ld0, NNTK_SPEC_E2_N * n2);
+    for (int n2 = 0; n2 < 8; ++n2) v[8 + n2] = sm_ld1(sm_ld1_, NNTK_SPEC_E2_N * n2);
 }
 NNTK_HD void spec_pass3(float2 *v) {   // v[k''] = Z[64 k'' + c1], v[8 + k''] = Z[64 k'' + c2]
     radix8(v);
@@ -132,8 +167,8 @@ NNTK_HD void spec_pass3(float2 *v) {   // v[k''] = Z[64 k'' + c1], v[8 + k''] = 
 NNTK_HD void spec_pair_power(float2 z, float2 m, float &pa, float &pb) {
     float ar = z.x + m.x, ai = z.y - m.y;
     float br = z.y + m.y, bi = z.x - m.x;
-    pa = ar * ar + ai * ai;
-    pb = br * br + bi * bi;
+    pa = fmaf(ar, ar, ai * ai);
+    pb = fmaf(br, br, bi * bi);
 }
 // In-register split.  Slot j = 0..3: bin 64 j + c1;  slot 4 + j: bin 64 j + c2;  slot 8 (lane 0 only): bin 256.
 NNTK_HD int spec_slot_bin(int lane, int slot) {
