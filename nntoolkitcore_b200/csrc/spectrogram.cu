@@ -22,12 +22,13 @@
 
 namespace {
 
-constexpr int SPEC_THREADS = 256, SPEC_WARPS = SPEC_THREADS / 32, SPEC_F = 32;
+constexpr int SPEC_THREADS = 256, SPEC_WARPS = SPEC_THREADS / 32, SPEC_FW = 4;   // frames per warp tile
 
 struct SpecParams {
     int window_size, step, input_size, ntime, nfreq;
     int frames_per_tile, tiles_per_clip;
     long long total_tiles;
+    int n_clips;
     int in_cap;         // floats per input buffer
     float mag_mul;      // magnitude: |norm| * 0.5 / scale            (the split pass yields 2|X|)
     float psd_mid;      // PSD bins 1..nfreq-2: norm^2 * 0.25 * 2/scale (the split pass yields 4|X|^2)
@@ -50,59 +51,102 @@ __device__ __forceinline__ void cp_async4(void *smem, const void *gmem) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-struct TileGeom {
-    long long clip;
-    int f0, nf, ia;
-    long long gi0;
-};
-__device__ __forceinline__ TileGeom tile_geom(const SpecParams &p, long long tile) {
-    TileGeom g;
-    g.clip = tile / p.tiles_per_clip;
-    const int t = (int)(tile - g.clip * p.tiles_per_clip);
-    g.f0 = t * p.frames_per_tile;
-    g.nf = min(p.frames_per_tile, p.ntime - g.f0);
-    g.gi0 = g.clip * (long long)p.input_size + (long long)g.f0 * p.step;
-    g.ia = p.in_vec_ok ? (int)(g.gi0 & 3) : 0;
-    return g;
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count));
 }
-// clip span of a tile -> shared memory (smem index s <-> global gi0 - ia + s), asynchronously
-__device__ __forceinline__ void tile_load_async(const SpecParams &p, const TileGeom &g, const float *__restrict__ in,
-                                                float *s_buf, int tid) {
-    const int total = g.ia + (g.nf - 1) * p.step + p.window_size;
-    const float *gbase = in + (g.gi0 - g.ia);
-    int done = 0;
-    if (p.in_vec_ok) {
-        const int nvec = total >> 2;
-        for (int v = tid; v < nvec; v += SPEC_THREADS) cp_async16(s_buf + 4 * v, gbase + 4 * v);
-        done = 4 * nvec;
-    }
-    for (int s = done + tid; s < total; s += SPEC_THREADS) cp_async4(s_buf + s, gbase + s);
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "SPEC_WAIT:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra SPEC_DONE;\n\t"
+        "bra SPEC_WAIT;\n\t"
+        "SPEC_DONE:\n\t}" ::"r"(smem_addr(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *smem, const void *gmem, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_addr(smem)), "l"(gmem), "r"(bytes), "r"(smem_addr(bar)) : "memory");
 }
 
-// Shared memory layout (floats): [2][in_cap] clip-span double buffer, then SPEC_WARPS x 656 float2 exchange buffers.
+// A tile = frames [f0, f0 + nf) of one clip.  Geometry is advanced incrementally (no divisions in the loop).
+struct TileGeom {
+    int clip, t;   // clip index, tile index inside the clip
+};
+__device__ __forceinline__ void tile_advance(const SpecParams &p, TileGeom &g, int dc, int dt) {
+    g.clip += dc;
+    g.t += dt;
+    if (g.t >= p.tiles_per_clip) { g.t -= p.tiles_per_clip; ++g.clip; }
+}
+// Clip span of a tile -> the warp's shared-memory buffer (smem index s <-> global gi0 - ia + s), asynchronously.
+//   16-byte aligned input: lane 0 issues ONE bulk copy (TMA, completion on `bar`) for the whole 16-byte vectors and copies
+//   the <= 3 trailing floats itself before arming the barrier (its arrive releases those stores).
+//   otherwise: the 32 lanes issue 4-byte cp.async (completion by wait_group + __syncwarp).
+__device__ __forceinline__ void tile_load_async(const SpecParams &p, const TileGeom &g, const float *__restrict__ in,
+                                                float *s_buf, uint64_t *bar, int lane) {
+    const int f0 = g.t * p.frames_per_tile;
+    const int nf = min(p.frames_per_tile, p.ntime - f0);
+    const long long gi0 = (long long)g.clip * p.input_size + (long long)f0 * p.step;
+    const int span = (nf - 1) * p.step + p.window_size;
+    if (p.in_vec_ok) {
+        if (lane == 0) {
+            const int ia = (int)(gi0 & 3);
+            const float *gbase = in + (gi0 - ia);
+            const int total = ia + span, nvec = total >> 2;
+            for (int s = 4 * nvec; s < total; ++s) s_buf[s] = __ldg(gbase + s);
+            mbar_arrive_expect_tx(bar, 16u * nvec);
+            bulk_g2s(s_buf, gbase, 16u * nvec, bar);
+        }
+    } else {
+        const float *gbase = in + gi0;
+        for (int s = lane; s < span; s += 32) cp_async4(s_buf + s, gbase + s);
+    }
+}
+
+// Every WARP is an independent pipeline: it owns a double-buffered clip-span buffer, two mbarriers and an exchange
+// buffer, walks tiles (gw, gw + n_warps, ...) of SPEC_FW frames and never meets a CTA-wide barrier, so the warps of an SM
+// drift apart and one warp's shared-memory exchange overlaps another's butterflies.
+// Shared memory layout: [SPEC_WARPS][2][in_cap] floats | SPEC_WARPS x 656 float2 | [SPEC_WARPS][2] mbarriers.
 template <bool FULLWIN, int MODE>
 __global__ void __launch_bounds__(SPEC_THREADS, 2)
 spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const float2 *__restrict__ tw512,
                       const float *__restrict__ in, float *__restrict__ out) {
     extern __shared__ __align__(16) float smem[];
-    float *s_in = smem;
-    float2 *s_x = reinterpret_cast<float2 *>(smem + 2 * p.in_cap);
-
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    long long tile = blockIdx.x;
-    if (tile >= p.total_tiles) return;
-    TileGeom g = tile_geom(p, tile);
-    tile_load_async(p, g, in, s_in, tid);
+    float *s_in = smem + warp * 2 * p.in_cap;
+    float2 *s_x = reinterpret_cast<float2 *>(smem + SPEC_WARPS * 2 * p.in_cap);
+    uint64_t *full = reinterpret_cast<uint64_t *>(s_x + SPEC_WARPS * NNTK_SPEC_SMEM_F2) + 2 * warp;
+
+    const int n_warps = gridDim.x * SPEC_WARPS, gw = blockIdx.x * SPEC_WARPS + warp;
+    const int dc = n_warps / p.tiles_per_clip, dt = n_warps - dc * p.tiles_per_clip;
+    TileGeom g;
+    g.clip = gw / p.tiles_per_clip;
+    g.t = gw - g.clip * p.tiles_per_clip;
+    if (g.clip >= p.n_clips) return;
+    if (lane == 0) {
+        mbar_init(&full[0], 1);
+        mbar_init(&full[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    tile_load_async(p, g, in, s_in, &full[0], lane);
     cp_async_commit();
 
-    // per-lane constants (registers), fetched while the first tile is in flight
+    // per-lane constants (registers), fetched while the first tile is in flight.  The output scale is folded into the
+    // window: |FFT(m w x)| = m |FFT(w x)| (magnitude), |FFT(sqrt(m) w x)|^2 = m |FFT(w x)|^2 (PSD).
+    // (A negative scale -- only reachable through SpectrogramSetScaleFactor -- flips the sign afterwards.)
     SpecLaneConst lc;
     spec_lane_const(lane, tw512, lc);
+    const float wscale = MODE == 0 ? fabsf(p.mag_mul) : sqrtf(fabsf(p.psd_mid));
+    const bool neg = (MODE == 0 ? p.mag_mul : p.psd_mid) < 0.0f;
     float w[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
         const int n = lane + 32 * j;
-        w[j] = (FULLWIN || n < p.window_size) ? __ldg(window + n) : 0.0f;
+        w[j] = (FULLWIN || n < p.window_size) ? __ldg(window + n) * wscale : 0.0f;
     }
     float2 *sx = s_x + warp * NNTK_SPEC_SMEM_F2;
     float2 *x1_st = sx + spec_x1_st_base(lane);
@@ -110,28 +154,34 @@ spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const floa
     float2 *x2_st = sx + spec_x2_st_base(lane);
     const float2 *x2_ld0 = sx + spec_x2_ld_base(lane, 0);
     const float2 *x2_ld1 = sx + spec_x2_ld_base(lane, 1);
-    const int c2 = spec_lane_c(lane, 1);
+    const int c1 = spec_lane_c(lane, 0), c2 = spec_lane_c(lane, 1);
     const bool l0 = lane == 0;
+    // PSD: bins 0 and nfreq-1 are not doubled (spectrogram.c:41-47): psd_edge / psd_mid = 0.5
+    const float edge = 0.5f;
 
     for (int it = 0;; ++it) {
-        cp_async_wait_all();
-        __syncthreads();   // tile `it` has landed for every thread; every warp is done with the other buffer
-        const long long next = tile + gridDim.x;
-        const bool more = next < p.total_tiles;
+        __syncwarp();   // every lane is done reading the other buffer
         TileGeom gn = g;
-        if (more) {
-            gn = tile_geom(p, next);
-            tile_load_async(p, gn, in, s_in + ((it + 1) & 1) * p.in_cap, tid);
+        tile_advance(p, gn, dc, dt);
+        const bool more = gn.clip < p.n_clips;
+        if (more) tile_load_async(p, gn, in, s_in + ((it + 1) & 1) * p.in_cap, &full[(it + 1) & 1], lane);
+        if (p.in_vec_ok) {
+            mbar_wait(&full[it & 1], (it >> 1) & 1);
+        } else {
+            cp_async_commit();
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+            __syncwarp();
         }
-        cp_async_commit();
 
-        const float *buf = s_in + (it & 1) * p.in_cap + g.ia + lane;
-        float *orow = out + (g.clip * (long long)p.ntime + g.f0) * 257LL;
-        const int npairs = (g.nf + 1) >> 1;
+        const int f0 = g.t * p.frames_per_tile;
+        const int nf = min(p.frames_per_tile, p.ntime - f0);
+        const long long gi0 = (long long)g.clip * p.input_size + (long long)f0 * p.step;
+        const int ia = p.in_vec_ok ? (int)(gi0 & 3) : 0;
+        const float *buf = s_in + (it & 1) * p.in_cap + ia + lane;
+        float *orow = out + ((long long)g.clip * p.ntime + f0) * 257LL;
 #pragma unroll 1
-        for (int pr = warp; pr < npairs; pr += SPEC_WARPS) {
-            const int fa = 2 * pr;
-            const bool has_b = fa + 1 < g.nf;
+        for (int fa = 0; fa < nf; fa += 2) {
+            const bool has_b = fa + 1 < nf;
             const float *xa = buf + fa * p.step;
             const float *xb = has_b ? xa + p.step : xa;
             float2 v[16];
@@ -155,33 +205,34 @@ spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const floa
             spec_xchg2_load(v, x2_ld0, x2_ld1);
             __syncwarp();
             spec_pass3(v);
-            // split the packed pair in registers, scale, store: slot j -> bin 64 j + lane, slot 4 + j -> bin 64 j + c2
+            // split the packed pair in registers and store: slot j -> bin 64 j + c1, slot 4 + j -> bin 64 j + c2
             float pa[9], pb[9];
             spec_split_regs(lane, v, pa, pb);
             float *ra = orow + (long long)fa * 257;
-            float *ra1 = ra + lane, *ra2 = ra + c2;
+            float *ra1 = ra + c1, *ra2 = ra + c2;
+            if (MODE == 0) {
+#pragma unroll
+                for (int slot = 0; slot < 9; ++slot) { pa[slot] = sqrt_approx(pa[slot]); pb[slot] = sqrt_approx(pb[slot]); }
+            } else {
+                pa[8] *= edge; pb[8] *= edge;
+                if (l0) { pa[0] *= edge; pb[0] *= edge; }
+            }
+            if (neg) {
+#pragma unroll
+                for (int slot = 0; slot < 9; ++slot) { pa[slot] = -pa[slot]; pb[slot] = -pb[slot]; }
+            }
 #pragma unroll
             for (int slot = 0; slot < 8; ++slot) {
-                float va, vb;
-                if (MODE == 0) {
-                    va = sqrt_approx(pa[slot]) * p.mag_mul;
-                    vb = sqrt_approx(pb[slot]) * p.mag_mul;
-                } else {
-                    const float m = (slot == 0 && l0) ? p.psd_edge : p.psd_mid;
-                    va = pa[slot] * m;
-                    vb = pb[slot] * m;
-                }
                 float *dst = (slot < 4 ? ra1 : ra2) + 64 * (slot & 3);
-                dst[0] = va;
-                if (has_b) dst[257] = vb;
+                dst[0] = pa[slot];
+                if (has_b) dst[257] = pb[slot];
             }
             if (l0) {   // bin 256
-                ra[256] = MODE == 0 ? sqrt_approx(pa[8]) * p.mag_mul : pa[8] * p.psd_edge;
-                if (has_b) ra[256 + 257] = MODE == 0 ? sqrt_approx(pb[8]) * p.mag_mul : pb[8] * p.psd_edge;
+                ra[256] = pa[8];
+                if (has_b) ra[256 + 257] = pb[8];
             }
         }
         if (!more) break;
-        tile = next;
         g = gn;
     }
 }
@@ -285,14 +336,14 @@ extern "C" int nntk_cuda_spectrogram(const nntk_spectrogram_args *a, const float
     cudaStream_t st = nntk_stream();
 
     if (a->nfft == NNTK_SPEC_N) {
-        // frames per tile: largest of 32/16/8/4/2 whose shared memory lets two CTAs share an SM
+        // frames per warp tile: 4, or 2 when the hop is so large that two CTAs no longer fit an SM
         const size_t xchg = (size_t)SPEC_WARPS * NNTK_SPEC_SMEM_F2 * sizeof(float2);
-        int F = SPEC_F;
+        int F = SPEC_FW;
         size_t bytes = 0;
         int in_cap = 0;
         for (;; F >>= 1) {
             in_cap = (((F - 1) * a->step + a->window_size + 3 + 3) / 4) * 4;
-            bytes = (size_t)2 * in_cap * sizeof(float) + xchg;
+            bytes = (size_t)SPEC_WARPS * 2 * in_cap * sizeof(float) + xchg + SPEC_WARPS * 2 * sizeof(uint64_t);
             if (bytes <= 112 * 1024 || F == 2) break;
         }
         if (bytes > 227 * 1024) {
@@ -303,6 +354,7 @@ extern "C" int nntk_cuda_spectrogram(const nntk_spectrogram_args *a, const float
         p.tiles_per_clip = (a->ntime + F - 1) / F;
         p.total_tiles = (long long)n_clips * p.tiles_per_clip;
         p.in_cap = in_cap;
+        p.n_clips = n_clips;
         const bool fullwin = a->window_size == NNTK_SPEC_N;
         void (*kern)(SpecParams, const float *, const float2 *, const float *, float *) =
             a->mode == 0 ? (fullwin ? spectrogram512_kernel<true, 0> : spectrogram512_kernel<false, 0>)
@@ -313,9 +365,14 @@ extern "C" int nntk_cuda_spectrogram(const nntk_spectrogram_args *a, const float
             NNTK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
             attr_bytes[ki] = bytes;
         }
-        // persistent: two CTAs per SM, each walks tiles blockIdx.x, blockIdx.x + gridDim.x, ...
+        // persistent: two CTAs per SM; warp gw walks tiles gw, gw + n_warps, ...
+        if (p.total_tiles > 0x7fffffffLL) {
+            nntk_cuda_set_error(NNTK_ERR_ARG_, "spectrogram: %d clips exceed one launch", n_clips);
+            return NNTK_ERR_ARG_;
+        }
         long long grid = 2LL * nntk_cuda_sm_count();
-        if (grid > p.total_tiles) grid = p.total_tiles;
+        const long long need = (p.total_tiles + SPEC_WARPS - 1) / SPEC_WARPS;
+        if (grid > need) grid = need;
         kern<<<(unsigned)grid, SPEC_THREADS, bytes, st>>>(p, a->d_window, reinterpret_cast<const float2 *>(a->d_twiddle),
                                                           d_in, d_out);
         NNTK_LAUNCH_CHECK("spectrogram512_kernel");
@@ -335,6 +392,7 @@ extern "C" int nntk_cuda_spectrogram(const nntk_spectrogram_args *a, const float
     p.tiles_per_clip = a->ntime;
     p.total_tiles = (long long)n_clips * a->ntime;
     p.in_cap = 0;
+    p.n_clips = n_clips;
     static size_t attr_bytes_g = 48 * 1024;
     if (bytes > attr_bytes_g) {
         NNTK_CUDA_TRY(cudaFuncSetAttribute(spectrogram_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -22,7 +22,7 @@
 //             spreads a quarter-warp over all 16-byte slots of a 128-byte line); the consumer reads 16 x 8 bytes
 //             (q stride 82 = 2 mod 16 spreads a half-warp over the sixteen 8-byte bank pairs).  Padding only, so every
 //             address is one per-lane base plus a compile-time immediate.
-//   pass 3    butterfly c = q + 8 q' (lane L owns c = L and c = 64 - L): Z[64 k'' + c] = sum_{n''} E2[c][n''] W8^{n'' k''}
+//   pass 3    butterfly c = q + 8 q' (lane L owns c1 = pi(L) and c2 = 64 - c1): Z[64 k'' + c] = sum_{n''} E2[c][n''] W8^{n'' k''}
 //   split     in registers: bins 64 k'' + c and their mirrors 64 (7 - k'') + (64 - c) are in the same lane.
 #pragma once
 
@@ -141,11 +141,20 @@ NNTK_HD void spec_pass2(float2 *v, const SpecLaneConst &c) {
 }
 // Exchange 2: element (q, q', n'') at E2[82 q + 10 n'' + q'].
 NNTK_HD int spec_x2_st_base(int lane) { return NNTK_SPEC_E2_Q * (lane >> 3) + NNTK_SPEC_E2_N * (lane & 7); }
-// Last-pass butterfly assignment: lane L owns c1 = L and c2 = 64 - L (lane 0: c = 0 and 32).  Butterfly c emits
+// Last-pass butterfly assignment: lane L owns c1 = pi(L) and c2 = 64 - c1 (c1 = 0: c2 = 32).  Butterfly c emits
 // Z[64 k'' + c], and the conjugate-symmetry partner of bin 64 k'' + c is 64 (7 - k'') + (64 - c): with this assignment
 // BOTH bins of every pair sit in the same lane, so the two packed real frames are separated in registers and the
-// third exchange of the textbook scheme disappears.
-NNTK_HD int spec_lane_c(int lane, int s) { return s == 0 ? lane : (lane == 0 ? 32 : 64 - lane); }
+// third exchange of the textbook scheme disappears.  pi is the identity except for the swaps 1 <-> 16 and 9 <-> 24:
+// with the identity, the sixteen c2 values of a half-warp straddle three q' rows of exchange 2 and two of them share an
+// 8-byte bank pair (one extra wavefront per load); the two swaps make c1 AND c2 conflict-free in both half-warps
+// (found by exhaustive search over the 2^16 bank-preserving assignments; checked by tests/test_spectrogram_emu.py).
+NNTK_HD int spec_lane_c1(int lane) {
+    return lane == 1 ? 16 : lane == 16 ? 1 : lane == 9 ? 24 : lane == 24 ? 9 : lane;
+}
+NNTK_HD int spec_lane_c(int lane, int s) {
+    const int c1 = spec_lane_c1(lane);
+    return s == 0 ? c1 : (c1 == 0 ? 32 : 64 - c1);
+}
 NNTK_HD int spec_x2_ld_base(int lane, int s) {
     const int c = spec_lane_c(lane, s);
     return NNTK_SPEC_E2_Q * (c & 7) + (c >> 3);

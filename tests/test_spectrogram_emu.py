@@ -61,11 +61,9 @@ def test_impulse_and_dc(emu):
 
 
 def test_exchanges_bank_conflicts(emu):
-    """8+8 (exchange 1) and 8+16 (exchange 2) warp-wide instructions; the only conflicts are the known two-way ones of
-    the c2 = 64 - L loads of exchange 2 (one per half-warp and load: the 16 c values of a half-warp straddle three q'
-    rows), 16 extra wavefronts on top of the 160 conflict-free ones."""
+    """8+8 (exchange 1) and 8+16 (exchange 2) warp-wide instructions, all conflict-free: 160 wavefronts per frame pair."""
     rng = np.random.default_rng(5)
     a = rng.standard_normal(512).astype(np.float32)
     _, _, _, extra = _run(emu, a, a)
     assert emu.emu_spectrogram512_smem_instructions() == 40
-    assert extra <= 16, f"{extra} extra shared-memory wavefronts per frame pair"
+    assert extra == 0, f"{extra} extra shared-memory wavefronts per frame pair"
