@@ -11,6 +11,8 @@
 //      buffer), h_t is written to the next: no extra state copies.
 // Gate order and formulas follow the reference exactly: GRU [z, r, h~] with reset-after (gru.c:140-186), LSTM [i, f, g, o]
 // (lstm.c:199-238), RNN (rnn.c:156-165).
+#include <cooperative_groups.h>
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace {
@@ -186,6 +188,166 @@ __global__ void __launch_bounds__(256, 2) recurrent_step_kernel(StepDev p) {
     }
 }
 
+
+// ---- K4 persistent cluster kernel (small / medium batch) ---------------------------------------------------------------
+// One thread-block CLUSTER of C = H/32 CTAs owns BS sequences for ALL T timesteps (one launch per layer instead of T):
+//   * CTA j keeps the recurrent-weight columns of hidden units [32 j, 32 j + 32) -- all G gates -- resident in shared
+//     memory for the whole sequence (U slice: H x 32 G floats, row stride padded by 4 floats so a quarter-warp's 16-byte
+//     loads of 8 consecutive k rows fall into distinct banks);
+//   * h_{t-1} (BS x H) lives in a double-buffered shared-memory vector in EVERY CTA of the cluster;
+//   * per step: warp w computes the 4 G pre-activation columns of its 4 hidden units; the 32 lanes split K = H
+//     (k = lane + 32 i), FFMA into registers, then warp-shuffle (xor butterfly) reductions; lane 4 b + u applies the gate
+//     nonlinearities / state update of unit u of sequence b (reference op order, see recurrent_step_kernel), stores
+//     h_t to HBM (return_sequences) and into the h buffer of ALL C CTAs through distributed shared memory;
+//   * one cluster barrier (arrive.release / wait.acquire) per timestep publishes h_t.
+// The input projection xw = x W + b_i is hoisted (same GEMM as the per-step path).  fp32 FFMA throughout: 1e-5 parity.
+constexpr int CL_THREADS = 256, CL_WARPS = 8, CL_UPW = 4, CL_UNITS = CL_WARPS * CL_UPW;   // 32 hidden units per CTA
+
+struct ClusterDev {
+    int B, H, T, C;                 // C = cluster size = H / 32
+    int return_sequences;
+    const float *U, *bh;            // [H][G*H], [G*H] or null
+    const float *xw;                // [B][T][G*H]
+    float *h_state, *c_state;       // [B][H] in/out
+    float *out;                     // [B][T][H] or [B][H]
+    int act[5];
+    float act_a[5];
+};
+
+template <int G, int BS>
+__global__ void __launch_bounds__(CL_THREADS, 1) recurrent_cluster_kernel(ClusterDev p) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    constexpr int NCOLW = G * CL_UPW;          // columns per warp, ordered [gate][unit]
+    constexpr int NCOL = NCOLW * CL_WARPS;     // columns per CTA
+    constexpr int LDU = NCOL + 4;
+    extern __shared__ __align__(16) float smem[];
+    float *Us = smem;                                  // [H][LDU]
+    float *hb = smem + (size_t)p.H * LDU;              // [2][BS][H]
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int rank = (int)cluster.block_rank();
+    const int group = blockIdx.x / p.C;                // batch group of this cluster
+    const int b0 = group * BS;
+    const int nb = min(BS, p.B - b0);
+    const int H = p.H, GH = G * H;
+    const int unit0 = rank * CL_UNITS;
+
+    // U slice -> shared memory: column (w, g, u) <- U[k][g*H + unit0 + 4w + u]
+    for (int idx = tid; idx < H * NCOL; idx += CL_THREADS) {
+        const int k = idx / NCOL, c = idx - k * NCOL;
+        const int w = c / NCOLW, r = c - w * NCOLW, g = r / CL_UPW, u = r - g * CL_UPW;
+        Us[k * LDU + c] = __ldg(p.U + (size_t)k * GH + g * H + unit0 + CL_UPW * w + u);
+    }
+    for (int idx = tid; idx < BS * H; idx += CL_THREADS) {
+        const int b = idx / H, k = idx - b * H;
+        hb[idx] = b < nb ? p.h_state[(size_t)(b0 + b) * H + k] : 0.0f;
+    }
+    // gate lane: lane = 4 b + u  (b < BS)
+    const int gb = lane >> 2, gu = lane & 3;
+    const bool gate_lane = gb < nb && lane < 4 * BS;
+    const int unit = unit0 + CL_UPW * warp + gu;
+    float bh[G], cstate = 0.0f;
+#pragma unroll
+    for (int g = 0; g < G; ++g) bh[g] = (gate_lane && p.bh) ? __ldg(p.bh + g * H + unit) : 0.0f;
+    if (G == 4 && gate_lane) cstate = p.c_state[(size_t)(b0 + gb) * H + unit];
+    float *remote[16];
+#pragma unroll
+    for (int r = 0; r < 16; ++r) remote[r] = r < p.C ? cluster.map_shared_rank(hb, r) : nullptr;
+    cluster.sync();   // every CTA's buffers are initialised before anybody writes remotely
+
+    const float *urow = Us + lane * LDU + warp * NCOLW;
+    const float *xw_row = p.xw + (size_t)(b0 + (gate_lane ? gb : 0)) * p.T * GH + unit;
+    float hn = 0.0f;
+    for (int t = 0; t < p.T; ++t) {
+        const float *hcur = hb + (t & 1) * BS * H;
+        const int nxt = ((t + 1) & 1) * BS * H;
+        float xv[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) xv[g] = gate_lane ? __ldg(xw_row + (size_t)t * GH + g * H) : 0.0f;
+        float acc[BS][NCOLW];
+#pragma unroll
+        for (int b = 0; b < BS; ++b)
+#pragma unroll
+            for (int c = 0; c < NCOLW; ++c) acc[b][c] = 0.0f;
+#pragma unroll 2
+        for (int k0 = 0; k0 < H; k0 += 32) {
+            float hv[BS];
+#pragma unroll
+            for (int b = 0; b < BS; ++b) hv[b] = hcur[b * H + k0 + lane];
+            const float *ur = urow + k0 * LDU;
+#pragma unroll
+            for (int c4 = 0; c4 < NCOLW / 4; ++c4) {
+                const float4 u = *reinterpret_cast<const float4 *>(ur + 4 * c4);
+#pragma unroll
+                for (int b = 0; b < BS; ++b) {
+                    acc[b][4 * c4 + 0] = fmaf(hv[b], u.x, acc[b][4 * c4 + 0]);
+                    acc[b][4 * c4 + 1] = fmaf(hv[b], u.y, acc[b][4 * c4 + 1]);
+                    acc[b][4 * c4 + 2] = fmaf(hv[b], u.z, acc[b][4 * c4 + 2]);
+                    acc[b][4 * c4 + 3] = fmaf(hv[b], u.w, acc[b][4 * c4 + 3]);
+                }
+            }
+        }
+        // warp-shuffle reductions: every lane ends with every column sum
+#pragma unroll
+        for (int b = 0; b < BS; ++b)
+#pragma unroll
+            for (int c = 0; c < NCOLW; ++c) {
+                float v = acc[b][c];
+                v += __shfl_xor_sync(0xffffffffu, v, 16);
+                v += __shfl_xor_sync(0xffffffffu, v, 8);
+                v += __shfl_xor_sync(0xffffffffu, v, 4);
+                v += __shfl_xor_sync(0xffffffffu, v, 2);
+                v += __shfl_xor_sync(0xffffffffu, v, 1);
+                acc[b][c] = v;
+            }
+        // this lane's (b, u) pre-activations
+        float hu[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) hu[g] = 0.0f;
+#pragma unroll
+        for (int b = 0; b < BS; ++b)
+#pragma unroll
+            for (int u = 0; u < CL_UPW; ++u)
+                if (lane == 4 * b + u) {
+#pragma unroll
+                    for (int g = 0; g < G; ++g) hu[g] = acc[b][g * CL_UPW + u];
+                }
+        if (gate_lane) {
+#pragma unroll
+            for (int g = 0; g < G; ++g)
+                if (p.bh) hu[g] = __fadd_rn(hu[g], bh[g]);
+            if (G == 3) {   // gru.c:156-186
+                const float hp = hcur[gb * H + unit];
+                const float z = nntk_act(p.act[0], p.act_a[0], __fadd_rn(xv[0], hu[0]));
+                const float r = nntk_act(p.act[1], p.act_a[1], __fadd_rn(xv[1], hu[1]));
+                const float hh = nntk_act(p.act[2], p.act_a[2], __fadd_rn(__fmul_rn(r, hu[2]), xv[2]));
+                hn = __fadd_rn(__fmul_rn(__fadd_rn(-z, 1.0f), hh), __fmul_rn(z, hp));
+            } else if (G == 4) {   // lstm.c:199-238
+                const float ig = nntk_act(p.act[0], p.act_a[0], __fadd_rn(xv[0], hu[0]));
+                const float fg = nntk_act(p.act[1], p.act_a[1], __fadd_rn(xv[1], hu[1]));
+                const float gg = nntk_act(p.act[2], p.act_a[2], __fadd_rn(xv[2], hu[2]));
+                const float og = nntk_act(p.act[3], p.act_a[3], __fadd_rn(xv[3], hu[3]));
+                cstate = __fadd_rn(__fmul_rn(fg, cstate), __fmul_rn(ig, gg));
+                hn = __fmul_rn(og, nntk_act(p.act[4], p.act_a[4], cstate));
+            } else {   // rnn.c:156-165
+                hn = nntk_act(p.act[0], p.act_a[0], __fadd_rn(hu[0], xv[0]));
+            }
+            if (p.return_sequences) p.out[((size_t)(b0 + gb) * p.T + t) * H + unit] = hn;
+            const int off = nxt + gb * H + unit;
+#pragma unroll
+            for (int r = 0; r < 16; ++r)
+                if (r < p.C) remote[r][off] = hn;
+        }
+        cluster.sync();   // h_t is visible in every CTA; everybody is done reading h_{t-1}
+    }
+    if (gate_lane && p.T > 0) {
+        p.h_state[(size_t)(b0 + gb) * H + unit] = hn;
+        if (G == 4) p.c_state[(size_t)(b0 + gb) * H + unit] = cstate;
+        if (!p.return_sequences) p.out[(size_t)(b0 + gb) * H + unit] = hn;
+    }
+}
+
 }  // namespace
 
 extern "C" size_t nntk_cuda_recurrent_workspace(const nntk_recurrent_args *r) {
@@ -194,6 +356,70 @@ extern "C" size_t nntk_cuda_recurrent_workspace(const nntk_recurrent_args *r) {
     size_t xw = (size_t)r->batch * r->T * G * r->H * sizeof(float);
     size_t pp = r->return_sequences ? 0 : (size_t)2 * r->batch * r->H * sizeof(float);
     return xw + pp + 256;
+}
+
+template <int G, int BS>
+static int launch_cluster(const ClusterDev &p, int groups, size_t smem, cudaStream_t st) {
+    auto kern = recurrent_cluster_kernel<G, BS>;
+    static size_t attr_smem = 0;
+    static bool attr_np = false;
+    if (smem > attr_smem) {
+        NNTK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_smem = smem;
+    }
+    if (p.C > 8 && !attr_np) {
+        NNTK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        attr_np = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(groups * p.C));
+    cfg.blockDim = dim3(CL_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)p.C;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    NNTK_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, p));
+    return 0;
+}
+
+// Eligibility of the persistent cluster kernel: H a multiple of 32, cluster of H/32 <= 16 CTAs, the U slice plus the h
+// buffers within 227 KB of shared memory, and a batch small enough that one launch beats T GEMM-shaped step kernels
+// (NNTK_CLUSTER_MAX_BATCH, default 256).
+static int recurrent_cluster_try(const nntk_recurrent_args *r, int nb, const float *xw, float *h, float *c, float *out,
+                                 int *used) {
+    *used = 0;
+    static int max_batch = -1;
+    if (max_batch < 0) {
+        const char *e = getenv("NNTK_CLUSTER_MAX_BATCH");
+        max_batch = e ? atoi(e) : 256;
+    }
+    const int G = r->cell, H = r->H;
+    if (nb > max_batch || (H & 31) || H / 32 > 16 || r->T < 1) return 0;
+    const int BS = nb >= 4 ? 4 : (nb >= 2 ? 2 : 1);
+    const size_t smem = ((size_t)H * (G * CL_UNITS + 4) + (size_t)2 * BS * H) * sizeof(float);
+    if (smem > 227 * 1024) return 0;
+    ClusterDev p;
+    p.B = nb; p.H = H; p.T = r->T; p.C = H / 32; p.return_sequences = r->return_sequences;
+    p.U = r->d_U;
+    p.bh = ((G == 3) || r->v2) ? r->d_bh : nullptr;
+    p.xw = xw; p.h_state = h; p.c_state = c; p.out = out;
+    for (int i = 0; i < 5; ++i) { p.act[i] = r->act[i]; p.act_a[i] = r->act_a[i]; }
+    const int groups = (nb + BS - 1) / BS;
+    cudaStream_t st = nntk_stream();
+    int rc;
+#define NNTK_CL(GG, BB) rc = launch_cluster<GG, BB>(p, groups, smem, st)
+    if (G == 1) { if (BS == 4) NNTK_CL(1, 4); else if (BS == 2) NNTK_CL(1, 2); else NNTK_CL(1, 1); }
+    else if (G == 3) { if (BS == 4) NNTK_CL(3, 4); else if (BS == 2) NNTK_CL(3, 2); else NNTK_CL(3, 1); }
+    else { if (BS == 4) NNTK_CL(4, 4); else if (BS == 2) NNTK_CL(4, 2); else NNTK_CL(4, 1); }
+#undef NNTK_CL
+    if (rc) return rc;
+    *used = 1;
+    return 0;
 }
 
 static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *work) {
@@ -212,7 +438,14 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     if ((long long)nb * T > 0x7fffffffLL) return NNTK_ERR_ARG_;
     int rc = nntk_cuda_gemm(&g);
     if (rc) return rc;
-    // 2. T fused step kernels
+    // 2a. small / medium batch: ONE persistent cluster kernel for all T steps (U resident in shared memory, DSMEM exchange)
+    {
+        int used = 0;
+        rc = recurrent_cluster_try(r, nb, xw, h, c, out, &used);
+        if (rc) return rc;
+        if (used) return 0;
+    }
+    // 2b. large batch: T fused step kernels
     StepDev p;
     p.B = nb; p.H = H; p.c = c; p.U = r->d_U;
     const bool add_bh = (G == 3) || r->v2;   // gru.c:151 always; rnn.c:161-163 / lstm.c:207-209 only if v2
