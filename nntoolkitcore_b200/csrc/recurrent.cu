@@ -354,7 +354,7 @@ extern "C" size_t nntk_cuda_recurrent_workspace(const nntk_recurrent_args *r) {
     if (!r) return 0;
     const size_t G = (size_t)r->cell;
     size_t xw = (size_t)r->batch * r->T * G * r->H * sizeof(float);
-    size_t pp = r->return_sequences ? 0 : (size_t)2 * r->batch * r->H * sizeof(float);
+    size_t pp = (size_t)4 * r->batch * r->H * sizeof(float);   // exact + TF32-rounded h ping-pong
     return xw + pp + 256;
 }
 
@@ -422,6 +422,9 @@ static int recurrent_cluster_try(const nntk_recurrent_args *r, int nb, const flo
     return 0;
 }
 
+extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, const float *xw, float *h, float *c, float *out,
+                                      float *pp, int *used);   // recurrent_tc.cu
+
 static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *work) {
     const int G = r->cell, H = r->H, T = r->T, GH = G * H;
     const float *x = r->d_x + (long long)b0 * T * r->in;
@@ -445,7 +448,16 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
         if (rc) return rc;
         if (used) return 0;
     }
-    // 2b. large batch: T fused step kernels
+    cudaStream_t st = nntk_stream();
+    // 2b. large batch, TF32 mode: T tensor-core step kernels with the cell fused into the GEMM epilogue (recurrent_tc.cu)
+    if (nntk_cuda_math_mode() != 0) {
+        int used = 0;
+        rc = nntk_cuda_recurrent_tc(r, nb, xw, h, c, out, pp, &used);
+        if (rc) return rc;
+        if (used) goto carry_state;
+    }
+    {
+    // 2c. large batch, fp32 mode: T fused FFMA step kernels
     StepDev p;
     p.B = nb; p.H = H; p.c = c; p.U = r->d_U;
     const bool add_bh = (G == 3) || r->v2;   // gru.c:151 always; rnn.c:161-163 / lstm.c:207-209 only if v2
@@ -456,7 +468,6 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     p.u_tiles = (H + SU - 1) / SU;
     const int m_tiles = (nb + SM_ROWS - 1) / SM_ROWS;
     const unsigned grid = (unsigned)(m_tiles * p.u_tiles);
-    cudaStream_t st = nntk_stream();
     for (int t = 0; t < T; ++t) {
         if (t == 0) { p.h_prev = h; p.ld_prev = H; }
         else if (r->return_sequences) { p.h_prev = out + (long long)(t - 1) * H; p.ld_prev = (long long)T * H; }
@@ -469,6 +480,8 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
         else recurrent_step_kernel<4><<<grid, 256, 0, st>>>(p);
     }
     NNTK_LAUNCH_CHECK("recurrent_step_kernel");
+    }
+carry_state:
     // 3. carry the final state back (reference: f_copy(filter->h, h_t), gru.c:201 / lstm.c:264-265 / rnn.c:241)
     if (T > 0) {
         if (r->return_sequences) {
@@ -500,7 +513,7 @@ extern "C" int nntk_cuda_recurrent(const nntk_recurrent_args *r) {
         }
     if (r->batch == 0 || r->T == 0) return 0;
     // batch chunks that fit the workspace
-    const size_t per_seq = ((size_t)r->T * r->cell * r->H + (r->return_sequences ? 0 : 2 * (size_t)r->H)) * sizeof(float);
+    const size_t per_seq = ((size_t)r->T * r->cell * r->H + 4 * (size_t)r->H) * sizeof(float);
     size_t avail = r->work_bytes > 256 ? r->work_bytes - 256 : 0;
     long long chunk = (long long)(avail / per_seq);
     if (chunk < 1) {

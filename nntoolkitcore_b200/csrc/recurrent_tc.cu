@@ -1,0 +1,388 @@
+// recurrent_tc.cu -- K4, tensor-core path (NNTK_MATH_TF32, large batch): one timestep of RNN / GRU / LSTM as a tcgen05
+// GEMM  h_{t-1}[B, H] x U[H, G*H]  whose epilogue IS the cell: it reads the accumulator from TMEM, adds b_h and the hoisted
+// input projection xw_t, applies the gate nonlinearities and the state update in the reference's op order
+// (gru.c:156-186, lstm.c:199-238, rnn.c:156-165) and writes h_t (and c_t) -- no pre-activation ever reaches HBM.
+//
+//   * U is re-laid ONCE per call: column (tile j, gate g, unit u) <- U[:, g*H + 64 j + u], K-major, rounded to nearest
+//     TF32.  An N tile therefore holds ALL gates of its 64 hidden units and the gate math stays inside one thread.
+//   * A = h_{t-1}: the epilogue of step t-1 writes h twice -- exact fp32 to the [B, T, H] output (or an exact ping-pong
+//     buffer without return_sequences) and ROUNDED TO NEAREST TF32 to a [2, B, H] ping-pong buffer that TMA reads as the A
+//     operand of step t (one 3-D tensor map {H, 2, B}; the buffer index is a TMA coordinate).  Both operands are then
+//     unbiased TF32; only step 0 reads the caller's raw state (truncated by the tensor core, bias-compensated).
+//   * warp 0 = TMA producer, warp 1 = MMA issuer (M = 128, N = 64 G, K = 8 per instruction), warps 2..9 = two epilogue
+//     warpgroups (each thread owns one batch row and 32 of the tile's 64 units); two TMEM accumulator buffers let the
+//     epilogue of tile i overlap the MMAs of tile i+1.  Persistent over the (B/128) x (H/64) tiles of the step.
+// Operands are TF32 (A truncated by the tensor core and bias-compensated, see tc_common.cuh), accumulation and all gate
+// math fp32: 1e-3 parity class.  The fp32 (1e-5) mode never comes here.
+#include <stdlib.h>
+#include "tc_common.cuh"
+
+namespace {
+
+constexpr int R_BM = 128, R_BK = 32, R_UT = 64;     // rows, k per stage, hidden units per N tile
+constexpr int R_THREADS = 320;                      // 10 warps
+constexpr int R_EPI_WARPS = 8;
+
+struct RtcParams {
+    int B, H, n_tiles, m_tiles, k_blocks, total_tiles;
+    int a_t;                           // TMA coordinate of h_{t-1} along the time axis of map_a
+    const float *bh;                   // permuted like the columns of Bt, or null
+    const float *xw; long long ld_xw;  // row b: xw + b*ld_xw, original column order g*H + unit
+    const float *h_prev; long long ld_prev;
+    float *h_next; long long ld_next;
+    float *hr_next;                    // [B, H]: h_t rounded to nearest TF32 = the A operand of step t+1
+    int dbg;                           // development switches (NNTK_RTC_DBG): 1 no loads, 2 no stores
+    float comp;                        // 1 + truncation-bias compensation when A is raw fp32 (step 0), else 1
+    float *c;                          // [B, H] LSTM
+    int act[5];
+    float act_a[5];
+};
+
+template <int G, int STAGES>
+struct RtcSmem {
+    static constexpr int BN = G * R_UT;
+    static constexpr int A_BYTES = R_BM * R_BK * 4;
+    static constexpr int B_BYTES = BN * R_BK * 4;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
+    static constexpr int TOTAL = BAR_OFFSET + (2 * STAGES + 4) * 8 + 16 + 1024;
+    static constexpr int ACC_STRIDE = BN <= 64 ? 64 : 256;       // TMEM columns between the two accumulators
+    static constexpr int TMEM_COLS = 2 * ACC_STRIDE;
+};
+
+__device__ __forceinline__ void tc_ld_32x16(uint32_t taddr, float (&r)[16]) {
+    uint32_t u[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]), "=r"(u[8]),
+          "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) r[i] = __uint_as_float(u[i]);
+}
+
+__device__ __forceinline__ void tc_ld_32x8(uint32_t taddr, float (&r)[8]) {
+    uint32_t u[8];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7])
+                 : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r[i] = __uint_as_float(u[i]);
+}
+
+// Activations of the TF32 path: MUFU-based exp and division (relative error ~1e-6, far inside the 1e-3 class of this
+// mode; the fp32 mode keeps expf / tanhf / IEEE division, common.cuh).  tanh(x) = 1 - 2 / (1 + e^{2x}) saturates cleanly.
+__device__ __forceinline__ float act_fast(int kind, float a, float x) {
+    switch (kind) {
+    case NNTK_ACT_SIGMOID: return __fdividef(1.0f, 1.0f + __expf(-x));
+    case NNTK_ACT_TANH: return 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * x));
+    case NNTK_ACT_RELU: {
+        const float t = fmaxf(x, 0.0f);
+        return (a != 1.0f) ? t * a : t;
+    }
+    default: return x;
+    }
+}
+
+template <int G, int STAGES>
+__global__ void __launch_bounds__(R_THREADS, 1)
+recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, RtcParams p) {
+    using SL = RtcSmem<G, STAGES>;
+    constexpr int BN = SL::BN;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + SL::BAR_OFFSET);
+    uint64_t *empty_bar = full_bar + STAGES;
+    uint64_t *tmem_full = empty_bar + STAGES;     // [2]
+    uint64_t *tmem_empty = tmem_full + 2;         // [2]
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], R_EPI_WARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(SL::TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+                const int n_t = tile % p.n_tiles, m_t = tile / p.n_tiles;
+                for (int kb = 0; kb < p.k_blocks; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t *sa = smem + stage * SL::STAGE_BYTES;
+                    mbar_expect_tx(&full_bar[stage], SL::STAGE_BYTES);
+                    tma_load_3d(sa, &map_a, &full_bar[stage], kb * R_BK, p.a_t, m_t * R_BM);
+                    tma_load_2d(sa + SL::A_BYTES, &map_b, &full_bar[stage], kb * R_BK, n_t * BN);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(R_BM >> 4) << 24);
+            int stage = 0; uint32_t phase = 0, it = 0;
+            for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+                const uint32_t buf = it & 1, use = it >> 1;
+                mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + buf * SL::ACC_STRIDE;
+                for (int kb = 0; kb < p.k_blocks; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * SL::STAGE_BYTES);
+                    const uint64_t da = make_desc(sa), db = make_desc(sa + SL::A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < R_BK / 8; ++k) tc_mma_tf32(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                    tc_commit(&empty_bar[stage]);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                tc_commit(&tmem_full[buf]);
+            }
+        }
+    } else {
+        // ===== epilogue: thread = one batch row x 32 hidden units, in four chunks of 8 units.  Everything a chunk needs
+        // from HBM (xw, c, h_{t-1}) is independent of the accumulator, so it is loaded one chunk AHEAD -- the first chunk
+        // even before the tile's MMAs have finished -- and the load latency hides behind the previous chunk's gate math.
+        const int q = warp & 3;                       // TMEM lane quarter this warp may read
+        const int half = (warp - 2) >> 2;             // which 32 units of the tile's 64
+        const int row_in_tile = q * 32 + lane;
+        const float comp = p.comp;
+        constexpr int CH = 8, NCH = 32 / CH;
+        struct Pre { float4 xv[G][2]; float4 st[2]; };    // st: c (LSTM) or h_{t-1} (GRU)
+        uint32_t it = 0;
+        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+            const int n_t = tile % p.n_tiles, m_t = tile / p.n_tiles;
+            const uint32_t buf = it & 1, use = it >> 1;
+            const int row = m_t * R_BM + row_in_tile;
+            const bool row_ok = row < p.B;
+            const long long rr = row_ok ? row : 0;
+            const int ubase = n_t * R_UT + half * 32;          // first hidden unit of this thread
+            const float *xw = p.xw + rr * p.ld_xw + ubase;
+            const float *stp = (G == 4) ? p.c + rr * p.H + ubase : p.h_prev + rr * p.ld_prev + ubase;
+            float *hn = p.h_next + rr * p.ld_next + ubase;
+            float *hr = p.hr_next + rr * p.H + ubase;
+            float *cw = (G == 4) ? p.c + rr * p.H + ubase : nullptr;
+            const float *bh = p.bh ? p.bh + n_t * BN + half * 32 : nullptr;
+            auto prefetch = [&](int ch, Pre &P) {
+#pragma unroll
+                for (int v = 0; v < 2; ++v) {
+                    const int u = ch * CH + 4 * v;
+                    const bool ok = row_ok && ubase + u < p.H && !(p.dbg & 1);
+#pragma unroll
+                    for (int g = 0; g < G; ++g)
+                        P.xv[g][v] = ok ? *reinterpret_cast<const float4 *>(xw + (long long)g * p.H + u) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    P.st[v] = (ok && G != 1) ? *reinterpret_cast<const float4 *>(stp + u) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            };
+            Pre cur;
+            prefetch(0, cur);
+            mbar_wait(&tmem_full[buf], use & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + buf * SL::ACC_STRIDE + ((uint32_t)(q * 32) << 16) + half * 32;
+#pragma unroll
+            for (int ch = 0; ch < NCH; ++ch) {
+                Pre nxt;
+                if (ch + 1 < NCH) prefetch(ch + 1, nxt);
+                float acc[G][CH];
+#pragma unroll
+                for (int g = 0; g < G; ++g) tc_ld_32x8(taddr + g * R_UT + ch * CH, acc[g]);
+#pragma unroll
+                for (int v = 0; v < 2; ++v) {
+                    const int u = ch * CH + 4 * v;
+                    if (!(row_ok && ubase + u < p.H)) continue;          // H is a multiple of 4
+                    float4 bv[G];
+#pragma unroll
+                    for (int g = 0; g < G; ++g)
+                        bv[g] = bh ? __ldg(reinterpret_cast<const float4 *>(bh + g * R_UT + u)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    float out[4], cn[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        float hu[G], x[G];
+#pragma unroll
+                        for (int g = 0; g < G; ++g) {
+                            hu[g] = fmaf(acc[g][4 * v + e], comp, (&bv[g].x)[e]);
+                            x[g] = (&cur.xv[g][v].x)[e];
+                        }
+                        const float sv = (&cur.st[v].x)[e];
+                        if (G == 3) {
+                            const float z = act_fast(p.act[0], p.act_a[0], x[0] + hu[0]);
+                            const float r = act_fast(p.act[1], p.act_a[1], x[1] + hu[1]);
+                            const float hh = act_fast(p.act[2], p.act_a[2], fmaf(r, hu[2], x[2]));
+                            out[e] = fmaf(z, sv - hh, hh);                   // (1 - z) hh + z h_{t-1}
+                        } else if (G == 4) {
+                            const float ig = act_fast(p.act[0], p.act_a[0], x[0] + hu[0]);
+                            const float fg = act_fast(p.act[1], p.act_a[1], x[1] + hu[1]);
+                            const float gg = act_fast(p.act[2], p.act_a[2], x[2] + hu[2]);
+                            const float og = act_fast(p.act[3], p.act_a[3], x[3] + hu[3]);
+                            cn[e] = fmaf(fg, sv, ig * gg);
+                            out[e] = og * act_fast(p.act[4], p.act_a[4], cn[e]);
+                        } else {
+                            out[e] = act_fast(p.act[0], p.act_a[0], hu[0] + x[0]);
+                        }
+                    }
+                    if (p.dbg & 2) { if (out[0] == 123.456f) hn[u] = out[1] + out[2] + out[3] + cn[0] + cn[1] + cn[2] + cn[3]; continue; }
+                    *reinterpret_cast<float4 *>(hn + u) = make_float4(out[0], out[1], out[2], out[3]);
+                    *reinterpret_cast<float4 *>(hr + u) = make_float4(round_tf32(out[0]), round_tf32(out[1]), round_tf32(out[2]), round_tf32(out[3]));
+                    if (G == 4) *reinterpret_cast<float4 *>(cw + u) = make_float4(cn[0], cn[1], cn[2], cn[3]);
+                }
+                cur = nxt;
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(SL::TMEM_COLS) : "memory");
+    }
+}
+
+// Bt[(j*G + g)*64 + u][k] = tf32(U[k][g*H + 64 j + u]); padded units and k in [H, ldbt) are zero.  bhp likewise.
+__global__ void pack_recurrent_weights_kernel(const float *__restrict__ U, const float *__restrict__ bh, float *__restrict__ Bt,
+                                              float *__restrict__ bhp, int H, int G, int ldbt, int n_rows) {
+    const long long total = (long long)n_rows * ldbt;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int n = (int)(i / ldbt), k = (int)(i - (long long)n * ldbt);
+        const int j = n / (G * R_UT), r = n - j * G * R_UT, g = r / R_UT, u = r - g * R_UT;
+        const int unit = j * R_UT + u;
+        const bool ok = unit < H && k < H;
+        Bt[i] = ok ? round_tf32(__ldg(U + (long long)k * G * H + g * H + unit)) : 0.0f;
+        if (k == 0 && bhp) bhp[n] = (unit < H && bh) ? bh[g * H + unit] : 0.0f;
+    }
+}
+
+float *g_rtc_scratch = nullptr;
+size_t g_rtc_floats = 0;
+
+}  // namespace
+
+template <int G, int STAGES>
+static int launch_rtc(const CUtensorMap &ma, const CUtensorMap &mb, const RtcParams &p, cudaStream_t st) {
+    using SL = RtcSmem<G, STAGES>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        NNTK_CUDA_TRY(cudaFuncSetAttribute(recurrent_tc_step_kernel<G, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::TOTAL));
+        attr_done = true;
+    }
+    const int grid = p.total_tiles < nntk_cuda_sm_count() ? p.total_tiles : nntk_cuda_sm_count();
+    recurrent_tc_step_kernel<G, STAGES><<<grid, R_THREADS, SL::TOTAL, st>>>(ma, mb, p);
+    return 0;
+}
+
+static int encode_h_map(EncodeTiledFn encode, CUtensorMap *m, const float *base, int H, int n_t, long long t_stride,
+                        int rows, long long row_stride) {
+    cuuint64_t dims[3] = {(cuuint64_t)H, (cuuint64_t)n_t, (cuuint64_t)rows};
+    cuuint64_t strides[2] = {(cuuint64_t)t_stride * 4, (cuuint64_t)row_stride * 4};
+    cuuint32_t box[3] = {R_BK, 1, R_BM};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void *)base, dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        nntk_cuda_set_error(NNTK_ERR_CUDA_, "recurrent_tc: tensor map for h rejected (CUresult %d): H %d rows %d", (int)r, H, rows);
+        return NNTK_ERR_CUDA_;
+    }
+    return 0;
+}
+
+// Runs all T steps of one batch chunk on the tensor cores.  *used = 0 when the shape is not eligible (caller falls back to
+// the fp32 step kernels).  xw: hoisted projection [nb, T, G*H]; h/c: state [nb, H]; pp: [4, nb, H] (exact ping-pong, then
+// the TF32-rounded ping-pong).
+extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, const float *xw, float *h, float *c, float *out,
+                                      float *pp, int *used) {
+    *used = 0;
+    const int G = r->cell, H = r->H, T = r->T;
+    if ((H & 3) || T < 1 || nb < 1) return 0;
+    if ((((uintptr_t)h) | ((uintptr_t)out) | ((uintptr_t)xw) | ((uintptr_t)pp) | ((uintptr_t)c)) & 15) return 0;
+    EncodeTiledFn encode = get_encode();
+    if (!encode) {
+        nntk_cuda_set_error(NNTK_ERR_CUDA_, "recurrent_tc: cuTensorMapEncodeTiled is not available from this driver");
+        return NNTK_ERR_CUDA_;
+    }
+    cudaStream_t st = nntk_stream();
+    const int n_tiles = (H + R_UT - 1) / R_UT;
+    const int n_rows = n_tiles * G * R_UT;
+    const int ldbt = H;   // multiple of 4
+    const size_t need = (size_t)n_rows * ldbt + n_rows + 64;
+    if (need > g_rtc_floats) {
+        NNTK_CUDA_TRY(cudaStreamSynchronize(st));
+        if (g_rtc_scratch) cudaFree(g_rtc_scratch);
+        g_rtc_scratch = nullptr; g_rtc_floats = 0;
+        NNTK_CUDA_TRY(cudaMalloc(&g_rtc_scratch, need * sizeof(float)));
+        g_rtc_floats = need;
+    }
+    float *Bt = g_rtc_scratch;
+    float *bhp = g_rtc_scratch + (((size_t)n_rows * ldbt + 3) & ~(size_t)3);
+    const bool add_bh = (G == 3) || r->v2;
+    {
+        long long total = (long long)n_rows * ldbt;
+        int blocks = (int)((total + 255) / 256 < 2048 ? (total + 255) / 256 : 2048);
+        pack_recurrent_weights_kernel<<<blocks, 256, 0, st>>>(r->d_U, add_bh ? r->d_bh : nullptr, Bt, bhp, H, G, ldbt, n_rows);
+        NNTK_LAUNCH_CHECK("pack_recurrent_weights_kernel");
+    }
+    CUtensorMap m_state, m_hr, mb;
+    int rc;
+    float *hr = pp + (size_t)2 * nb * H;   // rounded ping-pong [2][nb][H] behind the exact one
+    if ((rc = encode_h_map(encode, &m_state, h, H, 1, H, nb, H))) return rc;
+    if ((rc = encode_h_map(encode, &m_hr, hr, H, 2, (long long)nb * H, nb, H))) return rc;
+    {
+        cuuint64_t dims[2] = {(cuuint64_t)ldbt, (cuuint64_t)n_rows};
+        cuuint64_t strides[1] = {(cuuint64_t)ldbt * 4};
+        cuuint32_t box[2] = {R_BK, (cuuint32_t)(G * R_UT)};
+        cuuint32_t estr[2] = {1, 1};
+        CUresult cr = encode(&mb, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)Bt, dims, strides, box, estr,
+                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (cr != CUDA_SUCCESS) {
+            nntk_cuda_set_error(NNTK_ERR_CUDA_, "recurrent_tc: tensor map for U rejected (CUresult %d)", (int)cr);
+            return NNTK_ERR_CUDA_;
+        }
+    }
+    RtcParams p;
+    p.B = nb; p.H = H; p.n_tiles = n_tiles; p.m_tiles = (nb + R_BM - 1) / R_BM;
+    p.k_blocks = (H + R_BK - 1) / R_BK;
+    p.total_tiles = p.n_tiles * p.m_tiles;
+    p.bh = add_bh ? bhp : nullptr;
+    p.ld_xw = (long long)T * G * H;
+    { const char *e = getenv("NNTK_RTC_DBG"); p.dbg = e ? atoi(e) : 0; }
+    p.c = c;
+    for (int i = 0; i < 5; ++i) { p.act[i] = r->act[i]; p.act_a[i] = r->act_a[i]; }
+    for (int t = 0; t < T; ++t) {
+        const CUtensorMap *ma;
+        if (t == 0) { ma = &m_state; p.a_t = 0; p.h_prev = h; p.ld_prev = H; p.comp = 1.0f + TF32_TRUNC_BIAS; }
+        else {
+            ma = &m_hr; p.a_t = (t - 1) & 1; p.comp = 1.0f;
+            if (r->return_sequences) { p.h_prev = out + (long long)(t - 1) * H; p.ld_prev = (long long)T * H; }
+            else { p.h_prev = pp + (size_t)((t - 1) & 1) * nb * H; p.ld_prev = H; }
+        }
+        if (r->return_sequences) { p.h_next = out + (long long)t * H; p.ld_next = (long long)T * H; }
+        else { p.h_next = pp + (size_t)(t & 1) * nb * H; p.ld_next = H; }
+        p.hr_next = hr + (size_t)(t & 1) * nb * H;
+        p.xw = xw + (long long)t * G * H;
+        if (G == 1) rc = launch_rtc<1, 6>(*ma, mb, p, st);
+        else if (G == 3) rc = launch_rtc<3, 4>(*ma, mb, p, st);
+        else rc = launch_rtc<4, 4>(*ma, mb, p, st);
+        if (rc) return rc;
+    }
+    NNTK_LAUNCH_CHECK("recurrent_tc_step_kernel");
+    *used = 1;
+    return 0;
+}

@@ -126,7 +126,7 @@ static int rec_launch(void *ctx, const float *d_in, float *d_out, long long firs
     const size_t state_slots = (rc_->mode == 0) ? 0 : (G == NNTK_CELL_LSTM ? 2 : 1);
     const size_t state_total = ((state_slots * state_bytes + 255) / 256) * 256;
     size_t want = nntk_cuda_recurrent_workspace(&r) + state_total;
-    const size_t per_seq = sizeof(float) * ((size_t)T * G * H + 2 * (size_t)H);
+    const size_t per_seq = sizeof(float) * ((size_t)T * G * H + 4 * (size_t)H);
     void *ws = NULL; size_t got = 0;
     int rc = nntk_cuda_workspace(want, state_total + per_seq + 256, &ws, &got);
     if (rc) return rc;

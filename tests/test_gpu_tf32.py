@@ -66,3 +66,40 @@ def test_unaligned_shapes_fall_back_to_fp32_kernel(tf32, ref):
     c_ref, c_new = L.Conv1d(ref, 257, 64, 5, 1, 40), L.Conv1d(tf32, 257, 64, 5, 1, 40)
     helpers.fill_conv(c_ref, 7); helpers.copy_weights(c_new, c_ref)
     assert_parity(c_new.apply_batch(x), np.stack([c_ref.apply(v) for v in x]), what="fallback")
+
+
+@pytest.mark.parametrize("cell,in_size,H,T,B,seq", [("gru", 64, 256, 12, 300, True), ("lstm", 96, 128, 40, 260, True),
+                                                    ("rnn", 40, 96, 4, 257, True), ("lstm", 64, 192, 7, 385, False),
+                                                    ("gru", 32, 64, 50, 270, False)])
+def test_recurrent_step_on_tensor_cores(tf32, port, cell, in_size, H, T, B, seq):
+    """batch > NNTK_CLUSTER_MAX_BATCH (256): every timestep is a tcgen05 GEMM with the cell fused into its epilogue
+    (csrc/recurrent_tc.cu); rows from the first, a middle and the last 128-row tile are checked against the oracle port
+    (the reference's own RNNApplyInference is undefined for sequences, rnn.c:237-241).  The un-gated tanh RNN is kept to
+    T = 4: with Glorot U its Jacobian does not contract, so the TF32 operand rounding (2^-11 per operand) grows step by
+    step (measured 1.4e-3 at T = 9), unlike the gated cells, which hold 1e-3 at T = 500 (test below)."""
+    import port_cases
+    rng = np.random.default_rng(6)
+    x = rng.standard_normal((B, T, in_size)).astype(np.float32)
+    pick = [0, 1, 127, 128, B // 2, B - 2, B - 1]
+    w = port_cases.recurrent_weights(cell, in_size, H, 410)
+    outs = [port_cases.recurrent(port, cell, in_size, H, T, seq, True, w, x[i]) for i in pick]
+    r = L.Recurrent(tf32, cell, in_size, H, T, return_sequences=seq)
+    helpers.fill_recurrent(r, 410)
+    got = r.apply_batch(x)
+    assert_parity(got[pick], np.stack(outs), tol=TF32_TOL, what=f"{cell} tensor-core step")
+
+
+def test_lstm_c4_shape_long_sequence_tf32(tf32, port):
+    """BASELINE config 4 unit (LSTM in=H=512, T=500) through the tensor-core step path: the TF32 rounding must not
+    accumulate over 500 recurrent steps beyond the stated 1e-3"""
+    import port_cases
+    H, T, B = 512, 500, 260
+    rng = np.random.default_rng(8)
+    x = rng.standard_normal((B, T, H)).astype(np.float32)
+    pick = [0, 129, B - 1]
+    w = port_cases.recurrent_weights("lstm", H, H, 400)
+    outs = [port_cases.recurrent(port, "lstm", H, H, T, True, True, w, x[i]) for i in pick]
+    r = L.Recurrent(tf32, "lstm", H, H, T)
+    helpers.fill_recurrent(r, 400)
+    got = r.apply_batch(x)
+    assert_parity(got[pick], np.stack(outs), tol=TF32_TOL, what="lstm C4 shape, T=500, tensor-core step")
