@@ -6,8 +6,11 @@
 //   warp 0      TMA producer: A tile [128 rows x 32 k] and B tile [BN x 32 k] per stage, SWIZZLE_128B, mbarrier tx-count
 //   warp 1      MMA issuer: one elected lane issues tcgen05.mma.kind::tf32 (M=128, N=BN, K=8) x4 per stage into one of two
 //               TMEM accumulator buffers; tcgen05.commit releases the smem stage / publishes the accumulator
-//   warps 2-5   epilogue: tcgen05.ld (32 lanes x 32 columns per warp), v*scale[n]+shift[n] (bias and BatchNorm folded per
-//               channel), activation, 16-byte stores; overlaps the next tile's main loop through the second TMEM buffer
+//   warps 2-9   epilogue: two warps per TMEM lane quarter, each draining half of the tile's columns in 32-column chunks:
+//               tcgen05.ld, v*scale[n]+shift[n] (bias and BatchNorm folded per channel; read as warp-broadcast 16-byte
+//               loads issued under the TMEM read), activation, 16-byte stores; overlaps the next tile's main loop through
+//               the second TMEM buffer.  (ncu, r1: with 4 warps and per-element scalar scale/shift loads + bound checks the
+//               MMA issuer spent its time waiting on tmem_empty -- the epilogue, not TMA or the tensor pipe, set the pace.)
 // Conv1d needs no im2col: with channels-last input the im2col row x is the contiguous span in[x*stride : x*stride+K, :],
 // so A is a 3-D TMA tensor {K*Cin, T_out, batch} with OVERLAPPING rows (row stride = stride*Cin floats).
 // Weights are re-laid K-major (Bt[N][K]) per call -- they may legally change between Applies.
@@ -17,7 +20,8 @@ namespace {
 
 constexpr int BM = 128, BK = 32;          // BK floats = 128 bytes = one SWIZZLE_128B atom
 constexpr int UMMA_K = 8;                 // tf32: 32 bytes per MMA along K
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_THREADS = 320;         // TMA warp, MMA warp, 8 epilogue warps
+constexpr int EPI_WARPS = 8;
 
 struct TcParams {
     int N, n_tiles, m_tiles_per_slab, k_blocks;
@@ -40,7 +44,7 @@ struct SmemLayout {
     static constexpr int TOTAL = BAR_OFFSET + (2 * STAGES + 4) * 8 + 16 + 1024;   // + alignment slack
 };
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, bool FAST>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, TcParams p) {
     using SL = SmemLayout<BN, STAGES>;
@@ -59,7 +63,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
         for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], 4); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -119,8 +123,9 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             }
         }
     } else {
-        // ===== epilogue warps (2..5): TMEM lane quarter = warp % 4 =====
+        // ===== epilogue warps (2..9): TMEM lane quarter = warp % 4, column half = (warp - 2) / 4 =====
         const int q = warp & 3;
+        const int half = (warp - 2) >> 2;
         const int row_in_tile = q * 32 + lane;
         uint32_t it = 0;
         const bool vec_ok = ((p.ldc & 3) == 0) && ((p.c_slab & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
@@ -130,32 +135,79 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             const int m_t = (int)(rest % p.m_tiles_per_slab);
             const long long slab = rest / p.m_tiles_per_slab;
             const uint32_t buf = it & 1, use = it >> 1;
-            mbar_wait(&tmem_full[buf], use & 1);
-            tc_fence_after();
             const int row = m_t * BM + row_in_tile;
             const bool row_ok = row < p.rows;
             float *crow = p.C + slab * p.c_slab + (long long)row * p.ldc;
             const uint32_t taddr = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16);
+            mbar_wait(&tmem_full[buf], use & 1);
+            tc_fence_after();
 #pragma unroll 1
-            for (int c0 = 0; c0 < BN; c0 += 32) {
-                uint32_t r[32];
-                tc_ld_32x32(taddr + c0, r);
+            for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 32) {
                 const int n0 = n_t * BN + c0;
-                if (row_ok && n0 < p.N) {
+                if (n0 >= p.N) break;                       // warp-uniform
+                uint32_t r[32];
+                if (FAST) {
+                    // N % 32 == 0 and 16-byte aligned rows: the only predicate left is the row bound.  scale / shift come as
+                    // warp-broadcast 16-byte loads issued BEFORE the TMEM read is waited for.
+                    tc_ld_32x32_nowait(taddr + c0, r);
+                    float4 sc[8], sh[8];
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4) {
-                        float v[4];
+                    for (int j = 0; j < 8; ++j) {
+                        sc[j] = __ldg(reinterpret_cast<const float4 *>(p.scale + n0) + j);
+                        sh[j] = __ldg(reinterpret_cast<const float4 *>(p.shift + n0) + j);
+                    }
+                    tc_ld_wait();
+                    float4 *dst = reinterpret_cast<float4 *>(crow + n0);
+                    if (p.act == NNTK_ACT_RELU) {
+                        const float a = p.act_a;
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            const int n = n0 + j + e;
-                            float x = __uint_as_float(r[j + e]);
-                            if (n < p.N) x = nntk_act(p.act, p.act_a, fmaf(x, __ldg(p.scale + n), __ldg(p.shift + n)));
-                            v[e] = x;
+                        for (int j = 0; j < 8; ++j) {
+                            float4 v;
+                            v.x = fmaxf(fmaf(__uint_as_float(r[4 * j + 0]), sc[j].x, sh[j].x), 0.0f) * a;
+                            v.y = fmaxf(fmaf(__uint_as_float(r[4 * j + 1]), sc[j].y, sh[j].y), 0.0f) * a;
+                            v.z = fmaxf(fmaf(__uint_as_float(r[4 * j + 2]), sc[j].z, sh[j].z), 0.0f) * a;
+                            v.w = fmaxf(fmaf(__uint_as_float(r[4 * j + 3]), sc[j].w, sh[j].w), 0.0f) * a;
+                            if (row_ok) dst[j] = v;
                         }
-                        const int n = n0 + j;
-                        if (vec_ok && n + 3 < p.N) *reinterpret_cast<float4 *>(crow + n) = make_float4(v[0], v[1], v[2], v[3]);
-                        else
-                            for (int e = 0; e < 4; ++e) if (n + e < p.N) crow[n + e] = v[e];
+                    } else if (p.act == NNTK_ACT_SIGMOID || p.act == NNTK_ACT_TANH) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            float4 v;
+                            v.x = nntk_act(p.act, 1.0f, fmaf(__uint_as_float(r[4 * j + 0]), sc[j].x, sh[j].x));
+                            v.y = nntk_act(p.act, 1.0f, fmaf(__uint_as_float(r[4 * j + 1]), sc[j].y, sh[j].y));
+                            v.z = nntk_act(p.act, 1.0f, fmaf(__uint_as_float(r[4 * j + 2]), sc[j].z, sh[j].z));
+                            v.w = nntk_act(p.act, 1.0f, fmaf(__uint_as_float(r[4 * j + 3]), sc[j].w, sh[j].w));
+                            if (row_ok) dst[j] = v;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            float4 v;
+                            v.x = fmaf(__uint_as_float(r[4 * j + 0]), sc[j].x, sh[j].x);
+                            v.y = fmaf(__uint_as_float(r[4 * j + 1]), sc[j].y, sh[j].y);
+                            v.z = fmaf(__uint_as_float(r[4 * j + 2]), sc[j].z, sh[j].z);
+                            v.w = fmaf(__uint_as_float(r[4 * j + 3]), sc[j].w, sh[j].w);
+                            if (row_ok) dst[j] = v;
+                        }
+                    }
+                } else {
+                    tc_ld_32x32(taddr + c0, r);
+                    if (row_ok) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            float v[4];
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                const int n = n0 + j + e;
+                                float x = __uint_as_float(r[j + e]);
+                                if (n < p.N) x = nntk_act(p.act, p.act_a, fmaf(x, __ldg(p.scale + n), __ldg(p.shift + n)));
+                                v[e] = x;
+                            }
+                            const int n = n0 + j;
+                            if (vec_ok && n + 3 < p.N) *reinterpret_cast<float4 *>(crow + n) = make_float4(v[0], v[1], v[2], v[3]);
+                            else
+                                for (int e = 0; e < 4; ++e) if (n + e < p.N) crow[n + e] = v[e];
+                        }
                     }
                 }
             }
@@ -209,16 +261,16 @@ size_t g_scratch_floats = 0;
 
 }  // namespace
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, bool FAST>
 static int launch_tc(const CUtensorMap &ma, const CUtensorMap &mb, TcParams &p, cudaStream_t st) {
     using SL = SmemLayout<BN, STAGES>;
     static bool attr_done = false;
     if (!attr_done) {
-        NNTK_CUDA_TRY(cudaFuncSetAttribute(gemm_tf32_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::TOTAL));
+        NNTK_CUDA_TRY(cudaFuncSetAttribute(gemm_tf32_kernel<BN, STAGES, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::TOTAL));
         attr_done = true;
     }
     long long grid = p.total_tiles < nntk_cuda_sm_count() ? p.total_tiles : nntk_cuda_sm_count();
-    gemm_tf32_kernel<BN, STAGES><<<(unsigned)grid, NUM_THREADS, SL::TOTAL, st>>>(ma, mb, p);
+    gemm_tf32_kernel<BN, STAGES, FAST><<<(unsigned)grid, NUM_THREADS, SL::TOTAL, st>>>(ma, mb, p);
     NNTK_LAUNCH_CHECK("gemm_tf32_kernel");
     return 0;
 }
@@ -289,5 +341,8 @@ extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *a) {
     p.rows = a->rows;
     p.C = a->d_C; p.c_slab = a->c_slab_stride; p.ldc = a->ldc;
     p.scale = scale; p.shift = shift; p.act = a->act; p.act_a = a->act_a;
-    return BN == 256 ? launch_tc<256, 4>(ma, mb, p, st) : launch_tc<128, 6>(ma, mb, p, st);
+    // FAST epilogue: whole 32-column chunks and 16-byte aligned output rows (every BASELINE shape except the 12-wide TDD)
+    const bool fast = (N % 32 == 0) && (a->ldc % 4 == 0) && (a->c_slab_stride % 4 == 0) && ((((uintptr_t)a->d_C) & 15) == 0);
+    if (BN == 256) return fast ? launch_tc<256, 4, true>(ma, mb, p, st) : launch_tc<256, 4, false>(ma, mb, p, st);
+    return fast ? launch_tc<128, 6, true>(ma, mb, p, st) : launch_tc<128, 6, false>(ma, mb, p, st);
 }

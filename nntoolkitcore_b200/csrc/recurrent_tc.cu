@@ -311,14 +311,7 @@ extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, cons
     *used = 0;
     const int G = r->cell, H = r->H, T = r->T;
     if ((H & 3) || T < 1 || nb < 1) return 0;
-    // The un-gated RNN is not contractive (|dh_t/dh_{t-1}| ~ |U| with Glorot U), so TF32 operand rounding of h grows step
-    // by step and misses the stated 1e-3 already at T = 4 (measured 1.06e-3).  Its step therefore stays on the FFMA kernel
-    // (only the hoisted projection runs on the tensor cores); NNTK_RNN_TC=1 forces the tensor-core step for experiments.
-    if (G == 1) {
-        static int rnn_tc = -1;
-        if (rnn_tc < 0) { const char *e = getenv("NNTK_RNN_TC"); rnn_tc = (e && atoi(e)) ? 1 : 0; }
-        if (!rnn_tc) return 0;
-    }
+    if (G == 1) return 0;   // the un-gated RNN stays fp32 in every math mode (see recurrent.cu)
     if ((((uintptr_t)h) | ((uintptr_t)out) | ((uintptr_t)xw) | ((uintptr_t)pp) | ((uintptr_t)c)) & 15) return 0;
     EncodeTiledFn encode = get_encode();
     if (!encode) {

@@ -75,9 +75,9 @@ def test_recurrent_step_on_tensor_cores(tf32, port, cell, in_size, H, T, B, seq)
     """batch > NNTK_CLUSTER_MAX_BATCH (256): every timestep is a tcgen05 GEMM with the cell fused into its epilogue
     (csrc/recurrent_tc.cu); rows from the first, a middle and the last 128-row tile are checked against the oracle port
     (the reference's own RNNApplyInference is undefined for sequences, rnn.c:237-241).  The un-gated tanh RNN is the
-    exception: with Glorot U its Jacobian does not contract, so TF32 rounding of h grows step by step (measured 1.06e-3 at
-    T = 4, 1.4e-3 at T = 9) -- the library keeps its STEP on the FFMA kernel in TF32 mode (only the hoisted projection is
-    TF32), which this case checks; the gated cells hold 1e-3 on the tensor cores at T = 500 (test below)."""
+    exception: with Glorot U its Jacobian does not contract, so TF32 rounding grows step by step (measured 1.06e-3 at
+    T = 4 with the step on tensor cores, 1.2e-3 at T = 12 with only the projection in TF32) -- the library keeps the RNN in
+    fp32 in every math mode, which this case checks; the gated cells hold 1e-3 on the tensor cores at T = 500 (below)."""
     import port_cases
     rng = np.random.default_rng(6)
     x = rng.standard_normal((B, T, in_size)).astype(np.float32)
