@@ -199,7 +199,7 @@ __global__ void pack_conv_weights_kernel(const float *__restrict__ W, float *__r
 
 }  // namespace
 
-extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *g);   // gemm_tc.cu
+extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *g, int split);   // gemm_tc.cu
 
 extern "C" int nntk_cuda_gemm(const nntk_gemm_args *a) {
     int rc = nntk_cuda_ensure_init();
@@ -215,7 +215,7 @@ extern "C" int nntk_cuda_gemm(const nntk_gemm_args *a) {
     const long long M = (long long)a->batch * a->rows;
     if (M == 0) return 0;
     if (nntk_cuda_math_mode() != 0) {
-        rc = nntk_cuda_gemm_tf32(a);
+        rc = nntk_cuda_gemm_tf32(a, nntk_cuda_math_mode() == 2);
         if (rc != 1) return rc;   // 1 = shape not eligible for the tensor-core kernel: use the fp32 kernel
     }
     GemmDev g;

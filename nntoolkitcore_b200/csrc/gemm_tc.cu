@@ -24,7 +24,9 @@ constexpr int NUM_THREADS = 320;         // TMA warp, MMA warp, 8 epilogue warps
 constexpr int EPI_WARPS = 8;
 
 struct TcParams {
-    int N, n_tiles, m_tiles_per_slab, k_blocks;
+    int N, n_tiles, m_tiles_per_slab, k_blocks;   // k_blocks: total over all passes (3x in split mode)
+    int kb_pass;                                  // k-blocks per pass = ceil(K / 32)
+    int lo_slab;                                  // split mode: slab coordinate offset of the lo copy of A (= batch), else 0
     long long total_tiles;
     int rows;
     float *C;
@@ -88,7 +90,11 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t *sa = smem + stage * SL::STAGE_BYTES;
                     mbar_expect_tx(&full_bar[stage], SL::STAGE_BYTES);
-                    tma_load_3d(sa, &map_a, &full_bar[stage], kb * BK, m_t * BM, slab);
+                    // split (3xTF32) mode: passes hi*Wlo, lo*Whi, hi*Whi -- B' = [Wlo; Whi; Whi] along K, A = hi, lo, hi.  The
+                    // two small passes come FIRST: the tensor core's fp32 accumulate truncates (measured: error grows
+                    // with the number of accumulation steps at full magnitude), so they run while the sum is still tiny.
+                    const int pass = kb / p.kb_pass, akb = kb - pass * p.kb_pass;
+                    tma_load_3d(sa, &map_a, &full_bar[stage], akb * BK, m_t * BM, slab + (pass == 1 ? p.lo_slab : 0));
                     tma_load_2d(sa + SL::A_BYTES, &map_b, &full_bar[stage], kb * BK, n_t * BN);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -224,28 +230,51 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     }
 }
 
-// Bt[n][k] = tf32(B[k][n]), leading dimension ldbt (multiple of 4); tail columns k in [K, ldbt) zeroed.
-__global__ void transpose_weights_kernel(const float *__restrict__ B, float *__restrict__ Bt, int K, int N, int ldbt) {
+// Bt[n][k] = tf32(B[k][n]), leading dimension ldbt (multiple of 4); tail columns k in [K, kpad) zeroed.  Split mode
+// (parts == 3): row n holds [lo | hi | hi], each kpad wide, hi = rn_tf32(B), lo = rn_tf32(B - hi).
+__global__ void transpose_weights_kernel(const float *__restrict__ B, float *__restrict__ Bt, int K, int N, int kpad, int ldbt,
+                                         int parts) {
     __shared__ float tile[32][33];
     const int k0 = blockIdx.x * 32, n0 = blockIdx.y * 32;
     for (int i = threadIdx.y; i < 32; i += blockDim.y) {
         const int k = k0 + i, n = n0 + threadIdx.x;
-        tile[i][threadIdx.x] = (k < K && n < N) ? round_tf32(B[(long long)k * N + n]) : 0.0f;
+        tile[i][threadIdx.x] = (k < K && n < N) ? B[(long long)k * N + n] : 0.0f;
     }
     __syncthreads();
     for (int i = threadIdx.y; i < 32; i += blockDim.y) {
         const int n = n0 + i, k = k0 + threadIdx.x;
-        if (n < N && k < ldbt) Bt[(long long)n * ldbt + k] = tile[threadIdx.x][i];
+        if (n < N && k < kpad) {
+            const float v = tile[threadIdx.x][i], hi = round_tf32(v);
+            float *row = Bt + (long long)n * ldbt;
+            if (parts == 3) { row[k] = round_tf32(v - hi); row[kpad + k] = hi; row[2 * kpad + k] = hi; }
+            else row[k] = hi;
+        }
+    }
+}
+
+// split mode: hi = rn_tf32(x), lo = rn_tf32(x - hi) over the whole extent of A (x - hi is exact in fp32)
+__global__ void split_tf32_kernel(const float *__restrict__ x, float *__restrict__ hi, float *__restrict__ lo, long long n) {
+    const long long n4 = n >> 2, stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        const float4 v = __ldg(reinterpret_cast<const float4 *>(x) + i);
+        float4 h, l;
+        h.x = round_tf32(v.x); h.y = round_tf32(v.y); h.z = round_tf32(v.z); h.w = round_tf32(v.w);
+        l.x = round_tf32(v.x - h.x); l.y = round_tf32(v.y - h.y); l.z = round_tf32(v.z - h.z); l.w = round_tf32(v.w - h.w);
+        reinterpret_cast<float4 *>(hi)[i] = h;
+        reinterpret_cast<float4 *>(lo)[i] = l;
+    }
+    for (long long i = (n4 << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float v = x[i], h = round_tf32(v);
+        hi[i] = h; lo[i] = round_tf32(v - h);
     }
 }
 
 // scale[n], shift[n] such that act(acc*scale + shift) == act(BN(acc + bias)) up to rounding; the scale also carries the
 // compensation of the A-operand truncation bias (see TF32_TRUNC_BIAS).
-__global__ void fold_epilogue_kernel(const float *bias, const float *bn, float eps, int N, float *scale, float *shift) {
+__global__ void fold_epilogue_kernel(const float *bias, const float *bn, float eps, int N, float *scale, float *shift, float comp) {
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= N) return;
     const float b = bias ? bias[n] : 0.0f;
-    const float comp = 1.0f + TF32_TRUNC_BIAS;
     if (bn) {
         const float s = bn[n] / sqrtf(bn[3 * N + n] + eps);
         scale[n] = s * comp;
@@ -258,6 +287,8 @@ __global__ void fold_epilogue_kernel(const float *bias, const float *bn, float e
 
 float *g_scratch = nullptr;      // Bt | scale | shift
 size_t g_scratch_floats = 0;
+float *g_split = nullptr;        // split mode: hi | lo copies of A
+size_t g_split_floats = 0;
 
 }  // namespace
 
@@ -275,8 +306,9 @@ static int launch_tc(const CUtensorMap &ma, const CUtensorMap &mb, TcParams &p, 
     return 0;
 }
 
-// returns 0 done, 1 not eligible (caller runs the fp32 kernel), <0 error
-extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *a) {
+// returns 0 done, 1 not eligible (caller runs the fp32 kernel), <0 error.  split != 0: 3xTF32 (hi/lo operand split, three
+// passes folded into ONE K loop of length 3K -- the kernel is unchanged), fp32-class accuracy at a third of the TF32 rate.
+extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *a, int split) {
     if ((a->lda & 3) || (a->a_slab_stride & 3) || (((uintptr_t)a->d_A) & 15) || a->rows < 1 || a->batch < 1) return 1;
     EncodeTiledFn encode = get_encode();
     if (!encode) {
@@ -285,7 +317,9 @@ extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *a) {
     }
     cudaStream_t st = nntk_stream();
     const int K = a->K, N = a->N;
-    const int ldbt = (K + 3) & ~3;
+    const int parts = split ? 3 : 1;
+    const int kpad = split ? ((K + BK - 1) / BK) * BK : ((K + 3) & ~3);
+    const int ldbt = parts * kpad;
     const size_t need = (size_t)N * ldbt + 2 * (size_t)N + 64;
     if (need > g_scratch_floats) {
         NNTK_CUDA_TRY(cudaStreamSynchronize(st));
@@ -297,21 +331,45 @@ extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *a) {
     float *Bt = g_scratch;
     float *scale = g_scratch + (((size_t)N * ldbt + 3) & ~(size_t)3);
     float *shift = scale + N;
-    dim3 tb(32, 8), tg((ldbt + 31) / 32, (N + 31) / 32);
-    transpose_weights_kernel<<<tg, tb, 0, st>>>(a->d_B, Bt, K, N, ldbt);
-    fold_epilogue_kernel<<<(N + 127) / 128, 128, 0, st>>>(a->d_bias, a->d_bn, a->bn_eps, N, scale, shift);
+    dim3 tb(32, 8), tg((kpad + 31) / 32, (N + 31) / 32);
+    transpose_weights_kernel<<<tg, tb, 0, st>>>(a->d_B, Bt, K, N, kpad, ldbt, parts);
+    fold_epilogue_kernel<<<(N + 127) / 128, 128, 0, st>>>(a->d_bias, a->d_bn, a->bn_eps, N, scale, shift,
+                                                          split ? 1.0f : 1.0f + TF32_TRUNC_BIAS);
     NNTK_LAUNCH_CHECK("gemm_tf32 prologue");
+
+    // slab stride of A as the tensor map sees it; in split mode the lo copy sits `batch` slabs behind the hi copy
+    const long long slab_floats = a->batch > 1 ? a->a_slab_stride : (long long)a->rows * a->lda;
+    const float *A = a->d_A;
+    if (split) {
+        if (a->batch > 1 && a->a_slab_stride < (long long)(a->rows - 1) * a->lda + K) return 1;   // slabs must not interleave
+        const long long extent = (long long)(a->batch - 1) * slab_floats + (long long)(a->rows - 1) * a->lda + K;
+        const long long lo_off = (long long)a->batch * slab_floats;
+        const size_t want = (size_t)(lo_off + extent + 64);
+        if (want > g_split_floats) {
+            NNTK_CUDA_TRY(cudaStreamSynchronize(st));
+            if (g_split) cudaFree(g_split);
+            g_split = nullptr; g_split_floats = 0;
+            NNTK_CUDA_TRY(cudaMalloc(&g_split, want * sizeof(float)));
+            g_split_floats = want;
+        }
+        long long blocks = (extent / 4 + 255) / 256;
+        if (blocks > 148 * 16) blocks = 148 * 16;
+        if (blocks < 1) blocks = 1;
+        split_tf32_kernel<<<(unsigned)blocks, 256, 0, st>>>(a->d_A, g_split, g_split + lo_off, extent);
+        NNTK_LAUNCH_CHECK("split_tf32_kernel");
+        A = g_split;
+    }
 
     const int BN = N > 128 ? 256 : 128;
     CUtensorMap ma, mb;
     {
-        cuuint64_t dims[3] = {(cuuint64_t)K, (cuuint64_t)a->rows, (cuuint64_t)a->batch};
-        cuuint64_t slab_bytes = (cuuint64_t)(a->batch > 1 ? a->a_slab_stride : (long long)a->rows * a->lda) * 4;
+        cuuint64_t dims[3] = {(cuuint64_t)K, (cuuint64_t)a->rows, (cuuint64_t)a->batch * (split ? 2 : 1)};
+        cuuint64_t slab_bytes = (cuuint64_t)slab_floats * 4;
         if (slab_bytes == 0) slab_bytes = 16;
         cuuint64_t strides[2] = {(cuuint64_t)a->lda * 4, slab_bytes};
         cuuint32_t box[3] = {BK, BM, 1};
         cuuint32_t estr[3] = {1, 1, 1};
-        CUresult r = encode(&ma, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void *)a->d_A, dims, strides, box, estr,
+        CUresult r = encode(&ma, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void *)A, dims, strides, box, estr,
                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) {
@@ -336,7 +394,9 @@ extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *a) {
     p.N = N;
     p.n_tiles = (N + BN - 1) / BN;
     p.m_tiles_per_slab = (a->rows + BM - 1) / BM;
-    p.k_blocks = (K + BK - 1) / BK;
+    p.kb_pass = (K + BK - 1) / BK;
+    p.k_blocks = parts * p.kb_pass;
+    p.lo_slab = split ? a->batch : 0;
     p.total_tiles = (long long)p.n_tiles * p.m_tiles_per_slab * a->batch;
     p.rows = a->rows;
     p.C = a->d_C; p.c_slab = a->c_slab_stride; p.ldc = a->ldc;

@@ -425,6 +425,9 @@ static int recurrent_cluster_try(const nntk_recurrent_args *r, int nb, const flo
 extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, const float *xw, float *h, float *c, float *out,
                                       float *pp, int *used);   // recurrent_tc.cu
 
+extern "C" int nntk_cuda_recurrent_cluster_tc(const nntk_recurrent_args *r, int nb, const float *xw, float *h, float *c,
+                                              float *out, int *used);   // recurrent_cluster_tc.cu
+
 static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *work) {
     const int G = r->cell, H = r->H, T = r->T, GH = G * H;
     const float *x = r->d_x + (long long)b0 * T * r->in;
@@ -442,10 +445,26 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     // The un-gated RNN amplifies operand rounding step by step (its Jacobian ~ U does not contract): measured 1.2e-3 at
     // T = 12 with only the PROJECTION in TF32.  It has no BASELINE config, so it simply stays fp32 in every math mode.
     const int mode = nntk_cuda_math_mode();
-    if (G == 1 && mode != 0) nntk_cuda_set_math_mode(0);
+    // TF32 mode runs the projection as 3xTF32 (split operands): emulation of the C5 GRU over 300 steps showed that the
+    // single-pass TF32 rounding of x and W in the PROJECTION alone costs 1.2e-3 (each operand ~7e-4), the recurrent TF32
+    // rounding only 3.5e-4 -- and the projection is the cheap part.  The tensor-core STEP kernels stay single-pass TF32.
+    const int proj_mode = (G == 1) ? 0 : (mode == 1 ? 2 : mode);
+    if (proj_mode != mode) nntk_cuda_set_math_mode(proj_mode);
     int rc = nntk_cuda_gemm(&g);
-    if (G == 1 && mode != 0) nntk_cuda_set_math_mode(mode);
+    if (proj_mode != mode) nntk_cuda_set_math_mode(mode);
     if (rc) return rc;
+    // 2a'. TF32 mode, H <= 256, batch >= NNTK_CLUSTER_TC_MIN_BATCH (default 32): ONE persistent tensor-core cluster kernel
+    //      for all T steps (recurrent_cluster_tc.cu: U resident in shared memory, DSMEM bulk-copy h exchange)
+    if (mode == 1 && G != 1) {
+        static int min_batch = -1;
+        if (min_batch < 0) { const char *e = getenv("NNTK_CLUSTER_TC_MIN_BATCH"); min_batch = e ? atoi(e) : 32; }
+        if (nb >= min_batch) {
+            int used = 0;
+            rc = nntk_cuda_recurrent_cluster_tc(r, nb, xw, h, c, out, &used);
+            if (rc) return rc;
+            if (used) return 0;
+        }
+    }
     // 2a. small / medium batch: ONE persistent cluster kernel for all T steps (U resident in shared memory, DSMEM exchange)
     {
         int used = 0;
@@ -455,7 +474,7 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     }
     cudaStream_t st = nntk_stream();
     // 2b. large batch, TF32 mode: T tensor-core step kernels with the cell fused into the GEMM epilogue (recurrent_tc.cu)
-    if (mode != 0 && G != 1) {
+    if (mode == 1 && G != 1) {
         int used = 0;
         rc = nntk_cuda_recurrent_tc(r, nb, xw, h, c, out, pp, &used);
         if (rc) return rc;

@@ -50,19 +50,6 @@ struct RtcSmem {
     static constexpr int TMEM_COLS = 2 * ACC_STRIDE;
 };
 
-__device__ __forceinline__ void tc_ld_32x16(uint32_t taddr, float (&r)[16]) {
-    uint32_t u[16];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-        : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]), "=r"(u[8]),
-          "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
-        : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 16; ++i) r[i] = __uint_as_float(u[i]);
-}
-
 __device__ __forceinline__ void tc_ld_32x8(uint32_t taddr, float (&r)[8]) {
     uint32_t u[8];
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
@@ -71,20 +58,6 @@ __device__ __forceinline__ void tc_ld_32x8(uint32_t taddr, float (&r)[8]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
     for (int i = 0; i < 8; ++i) r[i] = __uint_as_float(u[i]);
-}
-
-// Activations of the TF32 path: MUFU-based exp and division (relative error ~1e-6, far inside the 1e-3 class of this
-// mode; the fp32 mode keeps expf / tanhf / IEEE division, common.cuh).  tanh(x) = 1 - 2 / (1 + e^{2x}) saturates cleanly.
-__device__ __forceinline__ float act_fast(int kind, float a, float x) {
-    switch (kind) {
-    case NNTK_ACT_SIGMOID: return __fdividef(1.0f, 1.0f + __expf(-x));
-    case NNTK_ACT_TANH: return 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * x));
-    case NNTK_ACT_RELU: {
-        const float t = fmaxf(x, 0.0f);
-        return (a != 1.0f) ? t * a : t;
-    }
-    default: return x;
-    }
 }
 
 template <int G, int STAGES>

@@ -73,6 +73,33 @@ __device__ __forceinline__ void tc_ld_32x32_nowait(uint32_t taddr, uint32_t (&r)
 }
 __device__ __forceinline__ void tc_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+__device__ __forceinline__ void tc_ld_32x16(uint32_t taddr, float (&r)[16]) {
+    uint32_t u[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]), "=r"(u[8]),
+          "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) r[i] = __uint_as_float(u[i]);
+}
+
+// Activations of the TF32 path: MUFU-based exp and division (relative error ~1e-6, far inside the 1e-3 class of this
+// mode; the fp32 mode keeps expf / tanhf / IEEE division, common.cuh).  tanh(x) = 1 - 2 / (1 + e^{2x}) saturates cleanly.
+__device__ __forceinline__ float act_fast(int kind, float a, float x) {
+    switch (kind) {
+    case NNTK_ACT_SIGMOID: return __fdividef(1.0f, 1.0f + __expf(-x));
+    case NNTK_ACT_TANH: return 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * x));
+    case NNTK_ACT_RELU: {
+        const float t = fmaxf(x, 0.0f);
+        return (a != 1.0f) ? t * a : t;
+    }
+    default: return x;
+    }
+}
+
 // K-major, SWIZZLE_128B shared-memory matrix descriptor: rows of 128 bytes, 8-row groups 1024 bytes apart.
 __device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
     uint64_t d = 0;

@@ -45,7 +45,8 @@ def test_dense_and_tdd_tf32(tf32, ref):
 
 @pytest.mark.parametrize("cell,in_size,H,T,B", [("gru", 256, 256, 10, 200), ("lstm", 512, 512, 6, 130)])
 def test_recurrent_projection_tf32(tf32, ref, cell, in_size, H, T, B):
-    """the hoisted x*W projection runs on the tensor cores; the recurrent step stays fp32"""
+    """TF32 mode: the hoisted x*W projection runs on the tensor cores as 3xTF32 (its single-pass rounding alone would cost
+    ~1e-3 over long sequences), the recurrent steps as single-pass TF32 (cluster or per-step kernel, by shape)"""
     rng = np.random.default_rng(4)
     x = rng.standard_normal((B, T, in_size)).astype(np.float32)
     outs = []
@@ -68,11 +69,12 @@ def test_unaligned_shapes_fall_back_to_fp32_kernel(tf32, ref):
     assert_parity(c_new.apply_batch(x), np.stack([c_ref.apply(v) for v in x]), what="fallback")
 
 
-@pytest.mark.parametrize("cell,in_size,H,T,B,seq", [("gru", 64, 256, 12, 300, True), ("lstm", 96, 128, 40, 260, True),
-                                                    ("rnn", 40, 96, 12, 257, True), ("lstm", 64, 192, 7, 385, False),
-                                                    ("gru", 32, 64, 50, 270, False)])
+@pytest.mark.parametrize("cell,in_size,H,T,B,seq", [("gru", 64, 288, 12, 300, True), ("lstm", 96, 320, 40, 260, True),
+                                                    ("rnn", 40, 96, 12, 257, True), ("lstm", 64, 264, 7, 385, False),
+                                                    ("gru", 32, 68, 50, 270, False)])
 def test_recurrent_step_on_tensor_cores(tf32, port, cell, in_size, H, T, B, seq):
-    """batch > NNTK_CLUSTER_MAX_BATCH (256): every timestep is a tcgen05 GEMM with the cell fused into its epilogue
+    """batch > NNTK_CLUSTER_MAX_BATCH (256) and H not eligible for the persistent tensor-core cluster kernel (H > 256 or
+    H % 32 != 0): every timestep is a tcgen05 GEMM with the cell fused into its epilogue
     (csrc/recurrent_tc.cu); rows from the first, a middle and the last 128-row tile are checked against the oracle port
     (the reference's own RNNApplyInference is undefined for sequences, rnn.c:237-241).  The un-gated tanh RNN is the
     exception: with Glorot U its Jacobian does not contract, so TF32 rounding grows step by step (measured 1.06e-3 at
@@ -104,3 +106,81 @@ def test_lstm_c4_shape_long_sequence_tf32(tf32, port):
     helpers.fill_recurrent(r, 400)
     got = r.apply_batch(x)
     assert_parity(got[pick], np.stack(outs), tol=TF32_TOL, what="lstm C4 shape, T=500, tensor-core step")
+
+
+@pytest.mark.parametrize("cell,in_size,H,T,B,seq", [("gru", 64, 256, 12, 300, True), ("lstm", 96, 128, 40, 260, True),
+                                                    ("lstm", 64, 192, 7, 385, False), ("gru", 32, 64, 50, 270, False),
+                                                    ("gru", 40, 128, 100, 33, True), ("gru", 16, 32, 9, 128, True),
+                                                    ("gru", 256, 256, 300, 129, True)])
+def test_persistent_tensor_core_cluster_kernel(tf32, port, cell, in_size, H, T, B, seq):
+    """TF32 mode, H % 32 == 0, H <= 256, batch >= 32: ONE launch runs all T steps (csrc/recurrent_cluster_tc.cu) -- a cluster
+    of H/32 CTAs per 128 sequences keeps U resident in shared memory and exchanges h_t by DSMEM bulk copies.  Cluster sizes
+    1, 2, 4, 6, 8; ragged last slice; rows from the first, a middle and the last slice against the oracle port; the C5
+    GRU(256) shape over 300 steps checks that TF32 rounding of h does not accumulate beyond the stated 1e-3."""
+    import port_cases
+    rng = np.random.default_rng(16)
+    x = rng.standard_normal((B, T, in_size)).astype(np.float32)
+    pick = sorted({0, 1, min(127, B - 1), min(128, B - 1), B // 2, B - 2, B - 1})
+    w = port_cases.recurrent_weights(cell, in_size, H, 420)
+    outs = [port_cases.recurrent(port, cell, in_size, H, T, seq, True, w, x[i]) for i in pick]
+    r = L.Recurrent(tf32, cell, in_size, H, T, return_sequences=seq)
+    helpers.fill_recurrent(r, 420)
+    got = r.apply_batch(x)
+    err, l2 = assert_parity(got[pick], np.stack(outs), tol=TF32_TOL, what=f"{cell} tensor-core cluster kernel")
+    assert l2 > 1e-7, "suspiciously exact: the tensor-core path did not run"
+
+
+def test_cluster_kernel_streaming_state_matches_one_shot(tf32):
+    """carried state through the persistent kernel: two half-length calls with caller-owned h / c == one full-length call"""
+    rng = np.random.default_rng(17)
+    B, T, H = 140, 16, 128
+    x = rng.standard_normal((B, 2 * T, 64)).astype(np.float32)
+    full = L.Recurrent(tf32, "lstm", 64, H, 2 * T); helpers.fill_recurrent(full, 430)
+    half = L.Recurrent(tf32, "lstm", 64, H, T); helpers.copy_weights(half, full)
+    want = full.apply_batch(x)
+    h = np.zeros((B, H), np.float32); c = np.zeros((B, H), np.float32)
+    a = half.apply_batch(np.ascontiguousarray(x[:, :T]), h_state=h, c_state=c)
+    b = half.apply_batch(np.ascontiguousarray(x[:, T:]), h_state=h, c_state=c)
+    assert_parity(np.concatenate([a, b], 1), want, tol=1e-6, what="cluster kernel streaming state")
+
+
+# ---- NNTK_MATH_TF32X3: tcgen05 with hi/lo operand split (three passes in one K loop).  Operand error drops to ~2^-22, what
+# remains is the tensor core's truncating fp32 accumulate (grows with K): stated tolerance 3e-5 (the FFMA mode holds 1e-5).
+X3_TOL = 3e-5
+@pytest.fixture()
+def x3(cuda, product):
+    assert product.NNTKSetMathMode(2) == 0
+    yield product
+    product.NNTKSetMathMode(0)
+
+
+@pytest.mark.parametrize("cin,cout,k,s,T,B", [(128, 256, 5, 1, 300, 3), (64, 96, 3, 2, 257, 2), (256, 256, 5, 1, 130, 2),
+                                              (16, 8, 1, 1, 40, 1), (20, 40, 3, 1, 50, 2)])
+def test_conv1d_3xtf32(x3, ref, cin, cout, k, s, T, B):
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal((B, T, cin)).astype(np.float32)
+    c_ref, c_new = L.Conv1d(ref, cin, cout, k, s, T), L.Conv1d(x3, cin, cout, k, s, T)
+    helpers.fill_conv(c_ref, 300); helpers.copy_weights(c_new, c_ref)
+    t_out = c_ref.out_shape[0]
+    bn_ref, bn_new = L.BatchNorm(ref, cout, 1e-3, t_out), L.BatchNorm(x3, cout, 1e-3, t_out)
+    helpers.fill_bn(bn_ref, 302); helpers.copy_weights(bn_new, bn_ref)
+    r_ref, r_new = L.Activation(ref, L.ACT_RELU, t_out * cout), L.Activation(x3, L.ACT_RELU, t_out * cout)
+    want = np.stack([r_ref.apply(bn_ref.apply(c_ref.apply(v))) for v in x])
+    got = c_new.apply_batch(x, bn=bn_new, act=r_new)
+    assert_parity(got, want, tol=X3_TOL, what="conv 3xTF32")
+
+
+def test_dense_tdd_and_recurrent_3xtf32(x3, ref):
+    rng = np.random.default_rng(9)
+    x = rng.standard_normal((3, 200, 256)).astype(np.float32)
+    d_ref, d_new = L.Dense(ref, 256, 12, L.ACT_SOFTMAX, ts=200), L.Dense(x3, 256, 12, L.ACT_SOFTMAX, ts=200)
+    helpers.fill_dense(d_ref, 501); helpers.copy_weights(d_new, d_ref)
+    assert_parity(d_new.apply_batch(x), np.stack([d_ref.apply(v) for v in x]), tol=X3_TOL, what="tdd 3xTF32")
+    # recurrent: projection 3xTF32, steps on FFMA (no single-pass tensor-core step in this mode)
+    xs = rng.standard_normal((300, 20, 64)).astype(np.float32)
+    outs = []
+    for v in xs[:3]:
+        r = L.Recurrent(ref, "gru", 64, 128, 20); helpers.fill_recurrent(r, 440)
+        outs.append(r.apply(v)); r.close()
+    g = L.Recurrent(x3, "gru", 64, 128, 20); helpers.fill_recurrent(g, 440)
+    assert_parity(g.apply_batch(xs)[:3], np.stack(outs), tol=X3_TOL, what="gru 3xTF32 projection + fp32 steps")
