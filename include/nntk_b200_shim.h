@@ -110,6 +110,10 @@ typedef struct {
 int nntk_cuda_gemm(const nntk_gemm_args *g);
 /* conv weights W[Cout][Cin][K] -> B[(k*Cin + ci)][co]   (layers/conv_1d.c:128-140 order -> implicit-GEMM order) */
 int nntk_cuda_pack_conv_weights(const float *d_W, float *d_B, int cout, int cin, int k);
+/* the same with the channel dimension zero-padded to cin_pad (rows k*cin_pad + ci, ci >= cin are zero), and the matching
+ * activation repack [rows][C] -> [rows][Cpad]: give unaligned channel counts (Cin = 257) a 16-byte pitch for TMA */
+int nntk_cuda_pack_conv_weights_padded(const float *d_W, float *d_B, int cout, int cin, int cin_pad, int k);
+int nntk_cuda_pad_channels(const float *d_in, float *d_out, long long rows, int C, int Cpad);
 
 /* ---- K3+K4: recurrent layers ---------------------------------------------------------------------------------------- */
 typedef struct {

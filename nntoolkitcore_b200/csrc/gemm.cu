@@ -183,8 +183,19 @@ __global__ void __launch_bounds__(256, 2) gemm_fp32_kernel(GemmDev g) {
     }
 }
 
-// conv weights W[Cout][Cin][K] -> B[(k*Cin + ci)][co]
-__global__ void pack_conv_weights_kernel(const float *__restrict__ W, float *__restrict__ B, int cout, int cin, int ks) {
+// [rows][C] -> [rows][Cpad], zero filled: gives rows a 16-byte aligned pitch so TMA can address them (Cin = 257 -> 260)
+__global__ void pad_channels_kernel(const float *__restrict__ in, float *__restrict__ out, long long rows, int C, int Cpad) {
+    const long long total = rows * Cpad;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long r = i / Cpad;
+        const int c = (int)(i - r * Cpad);
+        out[i] = c < C ? __ldg(in + r * C + c) : 0.0f;
+    }
+}
+
+// conv weights W[Cout][Cin][K] -> B[(k*cin_pad + ci)][co], rows ci in [cin_src, cin) zero
+__global__ void pack_conv_weights_kernel(const float *__restrict__ W, float *__restrict__ B, int cout, int cin, int ks,
+                                         int cin_src) {
     const long long total = (long long)cout * cin * ks;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
@@ -193,7 +204,7 @@ __global__ void pack_conv_weights_kernel(const float *__restrict__ W, float *__r
         const long long rest = i / cout;
         const int ci = (int)(rest % cin);
         const int k = (int)(rest / cin);
-        B[i] = __ldg(W + ((long long)co * cin + ci) * ks + k);
+        B[i] = ci < cin_src ? __ldg(W + ((long long)co * cin_src + ci) * ks + k) : 0.0f;
     }
 }
 
@@ -240,14 +251,28 @@ extern "C" int nntk_cuda_gemm(const nntk_gemm_args *a) {
     return 0;
 }
 
-extern "C" int nntk_cuda_pack_conv_weights(const float *d_W, float *d_B, int cout, int cin, int k) {
+extern "C" int nntk_cuda_pack_conv_weights_padded(const float *d_W, float *d_B, int cout, int cin, int cin_pad, int k) {
     int rc = nntk_cuda_ensure_init();
     if (rc) return rc;
-    const long long total = (long long)cout * cin * k;
+    const long long total = (long long)cout * cin_pad * k;
     if (total <= 0) return 0;
     long long blocks = (total + 255) / 256;
     if (blocks > 4096) blocks = 4096;
-    pack_conv_weights_kernel<<<(unsigned)blocks, 256, 0, nntk_stream()>>>(d_W, d_B, cout, cin, k);
+    pack_conv_weights_kernel<<<(unsigned)blocks, 256, 0, nntk_stream()>>>(d_W, d_B, cout, cin_pad, k, cin);
     NNTK_LAUNCH_CHECK("pack_conv_weights_kernel");
+    return 0;
+}
+extern "C" int nntk_cuda_pack_conv_weights(const float *d_W, float *d_B, int cout, int cin, int k) {
+    return nntk_cuda_pack_conv_weights_padded(d_W, d_B, cout, cin, cin, k);
+}
+extern "C" int nntk_cuda_pad_channels(const float *d_in, float *d_out, long long rows, int C, int Cpad) {
+    int rc = nntk_cuda_ensure_init();
+    if (rc) return rc;
+    const long long total = rows * Cpad;
+    if (total <= 0) return 0;
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    pad_channels_kernel<<<(unsigned)blocks, 256, 0, nntk_stream()>>>(d_in, d_out, rows, C, Cpad);
+    NNTK_LAUNCH_CHECK("pad_channels_kernel");
     return 0;
 }

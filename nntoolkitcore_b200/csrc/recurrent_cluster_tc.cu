@@ -61,7 +61,14 @@ __device__ __forceinline__ void dsmem_bulk_copy(uint32_t dst_cluster, uint32_t s
 }
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
-template <int G>
+// DEF: the default gate activations (GRU sigmoid, sigmoid, tanh; LSTM sigmoid, sigmoid, tanh, sigmoid, tanh) compiled in --
+// the run-time kind switch per call cost ~3x the instructions of the gate math itself (ncu, r1).
+template <bool DEF, int KIND>
+__device__ __forceinline__ float ct_act(const CtParams &p, int slot, float x) {
+    return DEF ? act_fast(KIND, 1.0f, x) : act_fast(p.act[slot], p.act_a[slot], x);
+}
+
+template <int G, bool DEF>
 __global__ void __launch_bounds__(CT_THREADS, 1)
 recurrent_cluster_tc_kernel(const __grid_constant__ CUtensorMap map_u, CtParams p) {
     constexpr int N = 32 * G;
@@ -197,19 +204,17 @@ recurrent_cluster_tc_kernel(const __grid_constant__ CUtensorMap map_u, CtParams 
                     x[g] = (&xr[g][u >> 2].x)[u & 3];
                 }
                 if (G == 3) {
-                    const float z = act_fast(p.act[0], p.act_a[0], x[0] + hu[0]);
-                    const float rg = act_fast(p.act[1], p.act_a[1], x[1] + hu[1]);
-                    const float hh = act_fast(p.act[2], p.act_a[2], fmaf(rg, hu[2], x[2]));
+                    const float z = ct_act<DEF, NNTK_ACT_SIGMOID>(p, 0, x[0] + hu[0]);
+                    const float rg = ct_act<DEF, NNTK_ACT_SIGMOID>(p, 1, x[1] + hu[1]);
+                    const float hh = ct_act<DEF, NNTK_ACT_TANH>(p, 2, fmaf(rg, hu[2], x[2]));
                     h[u] = fmaf(z, h[u] - hh, hh);                    // (1 - z) hh + z h_{t-1}
                 } else if (G == 4) {
-                    const float ig = act_fast(p.act[0], p.act_a[0], x[0] + hu[0]);
-                    const float fg = act_fast(p.act[1], p.act_a[1], x[1] + hu[1]);
-                    const float gg = act_fast(p.act[2], p.act_a[2], x[2] + hu[2]);
-                    const float og = act_fast(p.act[3], p.act_a[3], x[3] + hu[3]);
+                    const float ig = ct_act<DEF, NNTK_ACT_SIGMOID>(p, 0, x[0] + hu[0]);
+                    const float fg = ct_act<DEF, NNTK_ACT_SIGMOID>(p, 1, x[1] + hu[1]);
+                    const float gg = ct_act<DEF, NNTK_ACT_TANH>(p, 2, x[2] + hu[2]);
+                    const float og = ct_act<DEF, NNTK_ACT_SIGMOID>(p, 3, x[3] + hu[3]);
                     c[u] = fmaf(fg, c[u], ig * gg);
-                    h[u] = og * act_fast(p.act[4], p.act_a[4], c[u]);
-                } else {
-                    h[u] = act_fast(p.act[0], p.act_a[0], hu[0] + x[0]);
+                    h[u] = og * ct_act<DEF, NNTK_ACT_TANH>(p, 4, c[u]);
                 }
             }
             if (p.return_sequences && row_ok) {
@@ -255,9 +260,9 @@ __global__ void pack_cluster_weights_kernel(const float *__restrict__ U, float *
 float *g_ct_scratch = nullptr;
 size_t g_ct_floats = 0;
 
-template <int G>
+template <int G, bool DEF>
 int launch_ct(const CUtensorMap &mu, const CtParams &p, int slices, size_t smem, cudaStream_t st) {
-    auto kern = recurrent_cluster_tc_kernel<G>;
+    auto kern = recurrent_cluster_tc_kernel<G, DEF>;
     static size_t attr_smem = 0;
     static bool attr_np = false;
     if (smem > attr_smem) {
@@ -337,7 +342,12 @@ extern "C" int nntk_cuda_recurrent_cluster_tc(const nntk_recurrent_args *r, int 
     p.xw = xw; p.h_state = h; p.c_state = c; p.out = out;
     for (int i = 0; i < 5; ++i) { p.act[i] = r->act[i]; p.act_a[i] = r->act_a[i]; }
     const int slices = (nb + CT_BM - 1) / CT_BM;
-    int rc = (G == 3) ? launch_ct<3>(mu, p, slices, smem, st) : launch_ct<4>(mu, p, slices, smem, st);
+    const int S = NNTK_ACT_SIGMOID, TH = NNTK_ACT_TANH;
+    const bool def = (G == 3) ? (p.act[0] == S && p.act[1] == S && p.act[2] == TH)
+                              : (p.act[0] == S && p.act[1] == S && p.act[2] == TH && p.act[3] == S && p.act[4] == TH);
+    int rc;
+    if (G == 3) rc = def ? launch_ct<3, true>(mu, p, slices, smem, st) : launch_ct<3, false>(mu, p, slices, smem, st);
+    else rc = def ? launch_ct<4, true>(mu, p, slices, smem, st) : launch_ct<4, false>(mu, p, slices, smem, st);
     if (rc) return rc;
     *used = 1;
     return 0;

@@ -12,7 +12,10 @@ struct Conv1dStruct {
     Conv1dConfig config;
     ConvWeights weights;
     float *d_packed; /* [K*Cin][Cout] */
+    float *d_packed_pad; /* [K*Cin_pad][Cout], only when Cin % 4 != 0 (tensor-core modes need 16-byte row pitch) */
 };
+
+static int cin_pad(const Conv1dConfig *c) { return (c->input_feature_channels + 3) & ~3; }
 
 Conv1dConfig Conv1dConfigCreate(int input_feature_channels, int output_feature_channels, int kernel_size, int stride,
                                 int inputSize) {
@@ -35,8 +38,17 @@ static int conv_repack(nntk_layer_hdr *h) {
         if (rc) return rc;
         f->d_packed = (float *)d;
     }
-    return nntk_cuda_pack_conv_weights(h->d_block, f->d_packed, c->output_feature_channels, c->input_feature_channels,
-                                       c->kernel_size);
+    int rc = nntk_cuda_pack_conv_weights(h->d_block, f->d_packed, c->output_feature_channels, c->input_feature_channels,
+                                         c->kernel_size);
+    if (rc || cin_pad(c) == c->input_feature_channels) return rc;
+    if (!f->d_packed_pad) {
+        void *d = NULL;
+        rc = nntk_cuda_malloc(&d, sizeof(float) * (size_t)c->output_feature_channels * cin_pad(c) * c->kernel_size);
+        if (rc) return rc;
+        f->d_packed_pad = (float *)d;
+    }
+    return nntk_cuda_pack_conv_weights_padded(h->d_block, f->d_packed_pad, c->output_feature_channels,
+                                              c->input_feature_channels, cin_pad(c), c->kernel_size);
 }
 
 Conv1d Conv1dCreateForInference(Conv1dConfig config) {
@@ -61,6 +73,7 @@ ConvWeights *Conv1dGetWeights(Conv1d filter) { return &filter->weights; }
 void Conv1dDestroy(Conv1d filter) {
     if (!filter) return;
     nntk_cuda_free(filter->d_packed);
+    nntk_cuda_free(filter->d_packed_pad);
     nntk_layer_release(&filter->hdr);
     free(filter);
 }
@@ -89,7 +102,31 @@ static int conv_launch(void *ctx, const float *d_in, float *d_out, long long fir
     g.d_C = d_out;
     g.c_slab_stride = (long long)c->output_size * c->output_feature_channels;
     g.ldc = c->output_feature_channels;
-    return nntk_cuda_gemm(&g);
+    const int cp = cin_pad(c);
+    if (cp == c->input_feature_channels || nntk_cuda_math_mode() == NNTK_MATH_FP32 || !cc->f->d_packed_pad)
+        return nntk_cuda_gemm(&g);
+    /* tensor-core modes, Cin % 4 != 0 (the C5 front-end: 257 frequency bins): TMA needs a 16-byte row pitch, so the input is
+     * re-laid [T][Cin] -> [T][Cin_pad] (zeros; the weights carry matching zero rows) in chunks that fit the workspace */
+    const size_t per_sample = sizeof(float) * (size_t)c->input_size * cp;
+    void *ws = NULL; size_t got = 0;
+    int rc = nntk_cuda_workspace(per_sample * (size_t)n, per_sample, &ws, &got);
+    if (rc) return rc;
+    const int chunk = (int)(got / per_sample < (size_t)n ? got / per_sample : (size_t)n);
+    g.a_slab_stride = (long long)c->input_size * cp;
+    g.lda = c->stride * cp;
+    g.K = c->kernel_size * cp;
+    g.d_B = cc->f->d_packed_pad;
+    for (int b0 = 0; b0 < n; b0 += chunk) {
+        const int nb = b0 + chunk <= n ? chunk : n - b0;
+        rc = nntk_cuda_pad_channels(d_in + (size_t)b0 * c->input_size * c->input_feature_channels, (float *)ws,
+                                    (long long)nb * c->input_size, c->input_feature_channels, cp);
+        if (rc) return rc;
+        g.d_A = (const float *)ws;
+        g.batch = nb;
+        g.d_C = d_out + (size_t)b0 * c->output_size * c->output_feature_channels;
+        if ((rc = nntk_cuda_gemm(&g))) return rc;
+    }
+    return 0;
 }
 
 int Conv1dBNActApplyInferenceBatch(Conv1d filter, BatchNorm bn, ActivationFunction act, const float *input,
