@@ -428,6 +428,9 @@ extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, cons
 extern "C" int nntk_cuda_recurrent_cluster_tc(const nntk_recurrent_args *r, int nb, const float *xw, float *h, float *c,
                                               float *out, int *used);   // recurrent_cluster_tc.cu
 
+extern "C" int nntk_cuda_recurrent_cluster_h16(const nntk_recurrent_args *r, int nb, const float *xw, float *h, float *c,
+                                               float *out, int *used);  // recurrent_cluster_h16.cu
+
 static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *work) {
     const int G = r->cell, H = r->H, T = r->T, GH = G * H;
     const float *x = r->d_x + (long long)b0 * T * r->in;
@@ -458,6 +461,14 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     if (mode == 1 && G != 1) {
         static int min_batch = -1;
         if (min_batch < 0) { const char *e = getenv("NNTK_CLUSTER_TC_MIN_BATCH"); min_batch = e ? atoi(e) : 32; }
+        static int use_h16 = -1;
+        if (use_h16 < 0) { const char *e = getenv("NNTK_CLUSTER_H16"); use_h16 = e ? atoi(e) : 1; }
+        if (nb >= min_batch && use_h16) {   // fp16-operand, two-slice variant first (default activations only)
+            int used = 0;
+            rc = nntk_cuda_recurrent_cluster_h16(r, nb, xw, h, c, out, &used);
+            if (rc) return rc;
+            if (used) return 0;
+        }
         if (nb >= min_batch) {
             int used = 0;
             rc = nntk_cuda_recurrent_cluster_tc(r, nb, xw, h, c, out, &used);

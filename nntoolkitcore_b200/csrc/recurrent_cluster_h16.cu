@@ -1,0 +1,390 @@
+// recurrent_cluster_h16.cu -- K4, persistent tensor-core recurrence, fp16-operand / two-slice variant (NNTK_MATH_TF32 mode,
+// default gate activations, H <= 256).  Same structure as recurrent_cluster_tc.cu (cluster of C = H/32 CTAs, U slice resident
+// in shared memory, h exchanged by DSMEM bulk copies, a_full / a_free mbarriers) with two changes that ncu asked for:
+//   * operands are fp16 (tcgen05.mma kind::f16, fp32 accumulate).  With the default activations h is bounded by 1, so fp16's
+//     10-bit mantissa is EXACTLY the TF32 operand precision (2^-11 relative) -- but the A tile, the U slice and above all the
+//     per-step DSMEM exchange (which bounded the TF32 kernel: 45 % of the step was the wait for copies + MMA) are half the
+//     bytes.  k-block = 32 units = 64-byte rows, SWIZZLE_64B, 8 KB per 128 sequences.
+//   * the halved A tile leaves room for TWO independent 128-sequence slices per cluster.  The step of one slice is a strict
+//     chain (MMA -> cell math -> exchange -> MMA ...); with two slices the epilogue warps do the cell math of one slice while
+//     the other slice's copies and MMA are in flight, so the exchange latency is hidden instead of added.
+// Not eligible (caller falls back to the TF32 cluster kernel, then to the per-step kernels): custom gate activations (h may
+// leave the fp16 range), H > 256.  fp16 overflow of a caller-supplied |h_0| > 65504 saturates to inf like any fp16 cast.
+
+#include <cuda_fp16.h>
+#include "tc_common.cuh"
+
+namespace {
+
+constexpr int HT_THREADS = 320;              // warp 0: a_free signalling, warp 1: MMA issuer, warps 2..9: epilogue
+constexpr int HT_BM = 128;                   // sequences per slice
+constexpr int HT_SLICES = 2;
+constexpr int HT_KB_BYTES = HT_BM * 64;      // one k-block of A: 128 rows x 32 halves
+
+struct HtParams {
+    int B, H, T, C;
+    int return_sequences;
+    const float *bh;                // [G*H] or null (not added)
+    const float *xw;                // [B][T][G*H], b_i already added
+    float *h_state, *c_state;       // [B][H] in/out
+    float *out;                     // [B][T][H] or [B][H]
+};
+
+__device__ __forceinline__ uint32_t ht_cluster_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void ht_cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t ht_map(uint32_t saddr, uint32_t rank) {
+    uint32_t d;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(d) : "r"(saddr), "r"(rank));
+    return d;
+}
+__device__ __forceinline__ void ht_arrive_remote(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void ht_bulk_copy(uint32_t dst_cluster, uint32_t src_cta, uint32_t bytes, uint32_t mbar_cluster) {
+    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst_cluster), "r"(src_cta), "r"(bytes), "r"(mbar_cluster) : "memory");
+}
+__device__ __forceinline__ void ht_mma_f16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+// K-major, SWIZZLE_64B shared-memory matrix descriptor: rows of 64 bytes, 8-row groups 512 bytes apart
+__device__ __forceinline__ uint64_t ht_desc(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3fff);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(512 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)4 << 61;                        // SWIZZLE_64B
+    return d;
+}
+__device__ __forceinline__ uint32_t ht_pack2(float a, float b) {
+    __half2 v = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&v);
+}
+
+template <int G>
+__global__ void __launch_bounds__(HT_THREADS, 1)
+recurrent_cluster_h16_kernel(const __grid_constant__ CUtensorMap map_u, HtParams p) {
+    constexpr int N = 32 * G;
+    constexpr uint32_t ACC_STRIDE = 128;                   // TMEM columns between the two slices' accumulators
+    constexpr uint32_t TMEM_COLS = 256;
+    constexpr int S_SIG = NNTK_ACT_SIGMOID, S_TANH = NNTK_ACT_TANH;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const int C = p.C, H = p.H, T = p.T, GH = G * H;
+    const int a_slice_bytes = C * HT_KB_BYTES;
+    uint8_t *sA = smem;                                              // [2 slices][C k-blocks][128 rows][32 halves]
+    uint8_t *sB = smem + (size_t)HT_SLICES * a_slice_bytes;          // [C k-blocks][N rows][32 halves]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sB + (size_t)C * N * 64);
+    uint64_t *b_full = bars, *a_full = bars + 1, *mma_done = bars + 3, *a_free = bars + 5, *h_ready = bars + 7;   // [2] each
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 9);
+    float *s_bh = reinterpret_cast<float *>(bars + 10);              // [G][32]
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t rank = ht_cluster_rank();
+    const int row0 = (blockIdx.x / C) * (HT_SLICES * HT_BM);
+    const uint32_t tx_bytes = (uint32_t)((C - 1) * HT_KB_BYTES);
+
+    if (tid == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_u) : "memory");
+        mbar_init(b_full, 1);
+        for (int s = 0; s < HT_SLICES; ++s) {
+            mbar_init(a_full + s, 2); mbar_init(mma_done + s, 1); mbar_init(a_free + s, (uint32_t)C); mbar_init(h_ready + s, 8);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        mbar_expect_tx(b_full, (uint32_t)(C * N * 64));
+        for (int kb = 0; kb < C; ++kb) tma_load_2d(sB + (size_t)kb * N * 64, &map_u, b_full, kb * 32, (int)rank * N);
+        for (int s = 0; s < HT_SLICES; ++s) mbar_expect_tx(a_full + s, tx_bytes);       // phase 0: the exchange of h_0
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (tid >= 64 && tid < 64 + N) {
+        const int i = tid - 64, g = i >> 5, u = i & 31;
+        s_bh[i] = p.bh ? __ldg(p.bh + g * H + (int)rank * 32 + u) : 0.0f;
+    }
+    tc_fence_before();
+    __syncthreads();
+    ht_cluster_sync();           // every CTA's barriers exist before anybody arrives on / copies into a peer
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== exchange engine: lane = 16 s + peer.  Two duties per (slice, peer), in time order:
+        //   h_ready[s] (the 8 epilogue warps have written the new h slice into my k-block)  -> push it to CTA `peer`
+        //   mma_done[s] (my MMA of step t has read my A tile)                              -> a_free arrival at CTA `peer`
+        // This warp has no global-memory traffic of its own, so the generic->async proxy fence it executes before the copy
+        // is cheap; in the epilogue threads the same fence waited for their outstanding xw loads (ncu: 12 % of the step).
+        const int s = lane >> 4, peer = lane & 15;
+        if (peer < C) {
+            const uint32_t my_kb = smem_u32(sA) + s * a_slice_bytes + rank * HT_KB_BYTES;
+            const uint32_t dst_kb = ht_map(my_kb, (uint32_t)peer);
+            const uint32_t dst_full = ht_map(smem_u32(a_full + s), (uint32_t)peer);
+            const uint32_t dst_free = ht_map(smem_u32(a_free + s), (uint32_t)peer);
+            for (int e = 0; e < T; ++e) {
+                mbar_wait(h_ready + s, (uint32_t)(e & 1));
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                if (peer == (int)rank) mbar_arrive(a_full + s);
+                else ht_bulk_copy(dst_kb, my_kb, HT_KB_BYTES, dst_full);
+                if (e + 1 < T) {
+                    mbar_wait(mma_done + s, (uint32_t)(e & 1));
+                    ht_arrive_remote(dst_free);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer: alternates between the two slices =====
+        if (lane == 0) {
+            // D = f32, A = B = f16, both K-major; N >> 3 at bit 17, M >> 4 at bit 24
+            constexpr uint32_t idesc = (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(HT_BM >> 4) << 24);
+            const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
+            mbar_wait(b_full, 0);
+            for (int t = 0; t < T; ++t) {
+#pragma unroll
+                for (int s = 0; s < HT_SLICES; ++s) {
+                    mbar_wait(a_full + s, (uint32_t)(t & 1));
+                    if (t + 1 < T) mbar_expect_tx(a_full + s, tx_bytes);     // arm the next phase
+                    tc_fence_after();
+                    const uint32_t tmem_d = tmem_base + s * ACC_STRIDE;
+                    for (int kb = 0; kb < C; ++kb) {
+                        const uint64_t da = ht_desc(a0 + s * a_slice_bytes + kb * HT_KB_BYTES), db = ht_desc(b0 + kb * N * 64);
+#pragma unroll
+                        for (int k = 0; k < 2; ++k) ht_mma_f16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                    }
+                    tc_commit(mma_done + s);
+                }
+            }
+        }
+    } else {
+        // ===== epilogue: thread = row r of BOTH slices x 16 hidden units =====
+        const int q = warp & 3, half = (warp - 2) >> 2;
+        const int r = q * 32 + lane;
+        const int ul = half * 16;                          // first unit inside the CTA's 32
+        const int unit0 = (int)rank * 32 + ul;             // first hidden unit (global index)
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + ul;
+        // own A k-block: this thread's two 16-byte chunks of row r (SWIZZLE_64B: chunk index ^ ((row >> 1) & 3))
+        const int sw = (r >> 1) & 3;
+        bool row_ok[HT_SLICES];
+        long long rr[HT_SLICES];
+        float h[HT_SLICES][16], c[HT_SLICES][G == 4 ? 16 : 1];
+#pragma unroll
+        for (int s = 0; s < HT_SLICES; ++s) {
+            const int row = row0 + s * HT_BM + r;
+            row_ok[s] = row < p.B;
+            rr[s] = row_ok[s] ? row : 0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float4 hv = row_ok[s] ? *reinterpret_cast<const float4 *>(p.h_state + rr[s] * H + unit0 + 4 * j)
+                                            : make_float4(0.f, 0.f, 0.f, 0.f);
+                h[s][4 * j] = hv.x; h[s][4 * j + 1] = hv.y; h[s][4 * j + 2] = hv.z; h[s][4 * j + 3] = hv.w;
+                if (G == 4) {
+                    const float4 cv = row_ok[s] ? *reinterpret_cast<const float4 *>(p.c_state + rr[s] * H + unit0 + 4 * j)
+                                                : make_float4(0.f, 0.f, 0.f, 0.f);
+                    c[s][4 * j] = cv.x; c[s][4 * j + 1] = cv.y; c[s][4 * j + 2] = cv.z; c[s][4 * j + 3] = cv.w;
+                }
+            }
+        }
+        float4 xr[G][4];           // ONE buffer: loaded for the other slice while this slice's exchange is in progress
+        auto load_xw = [&](int s, int t) {
+            const float *src = p.xw + (rr[s] * T + t) * (long long)GH + unit0;
+#pragma unroll
+            for (int g = 0; g < G; ++g)
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    xr[g][j] = row_ok[s] ? __ldg(reinterpret_cast<const float4 *>(src + g * H) + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+        };
+        // publishes the fp16-rounded h registers of slice s as k-block `rank` of every CTA's A tile; e = exchange index
+        auto exchange = [&](int s, int e) {
+            uint8_t *kb = sA + (size_t)s * a_slice_bytes + (size_t)rank * HT_KB_BYTES;
+            mbar_wait(a_free + s, (uint32_t)((e & 1) ^ 1));  // e = 0 passes at once; e = t+1 waits for every MMA of step t
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                uint4 v;
+                v.x = ht_pack2(h[s][8 * j + 0], h[s][8 * j + 1]); v.y = ht_pack2(h[s][8 * j + 2], h[s][8 * j + 3]);
+                v.z = ht_pack2(h[s][8 * j + 4], h[s][8 * j + 5]); v.w = ht_pack2(h[s][8 * j + 6], h[s][8 * j + 7]);
+                *reinterpret_cast<uint4 *>(kb + r * 64 + (((half * 2 + j) ^ sw) << 4)) = v;
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(h_ready + s);         // release: the exchange warp fences and pushes
+        };
+        exchange(0, 0);
+        exchange(1, 0);
+        load_xw(0, 0);
+        for (int t = 0; t < T; ++t) {
+#pragma unroll
+            for (int s = 0; s < HT_SLICES; ++s) {
+                mbar_wait(mma_done + s, (uint32_t)(t & 1));
+                tc_fence_after();
+                float acc[G][16];
+#pragma unroll
+                for (int g = 0; g < G; ++g) tc_ld_32x16(taddr + s * ACC_STRIDE + g * 32, acc[g]);
+#pragma unroll
+                for (int u = 0; u < 16; ++u) {
+                    float hu[G], x[G];
+#pragma unroll
+                    for (int g = 0; g < G; ++g) {
+                        hu[g] = acc[g][u] + s_bh[g * 32 + ul + u];
+                        x[g] = (&xr[g][u >> 2].x)[u & 3];
+                    }
+                    if (G == 3) {          // gru.c:156-186
+                        const float z = act_fast(S_SIG, 1.0f, x[0] + hu[0]);
+                        const float rg = act_fast(S_SIG, 1.0f, x[1] + hu[1]);
+                        const float hh = act_fast(S_TANH, 1.0f, fmaf(rg, hu[2], x[2]));
+                        h[s][u] = fmaf(z, h[s][u] - hh, hh);               // (1 - z) hh + z h_{t-1}
+                    } else {               // lstm.c:199-238
+                        const float ig = act_fast(S_SIG, 1.0f, x[0] + hu[0]);
+                        const float fg = act_fast(S_SIG, 1.0f, x[1] + hu[1]);
+                        const float gg = act_fast(S_TANH, 1.0f, x[2] + hu[2]);
+                        const float og = act_fast(S_SIG, 1.0f, x[3] + hu[3]);
+                        c[s][u] = fmaf(fg, c[s][u], ig * gg);
+                        h[s][u] = og * act_fast(S_TANH, 1.0f, c[s][u]);
+                    }
+                }
+                // xw of the NEXT slice-step goes in flight now (xr is dead), under this slice's exchange
+                if (s == 0) load_xw(1, t);
+                else if (t + 1 < T) load_xw(0, t + 1);
+                if (t + 1 < T) exchange(s, t + 1);
+                if (p.return_sequences && row_ok[s]) {
+                    float4 *o = reinterpret_cast<float4 *>(p.out + (rr[s] * T + t) * H + unit0);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) o[j] = make_float4(h[s][4 * j], h[s][4 * j + 1], h[s][4 * j + 2], h[s][4 * j + 3]);
+                }
+            }
+        }
+#pragma unroll
+        for (int s = 0; s < HT_SLICES; ++s) {
+            if (!row_ok[s]) continue;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float4 hv = make_float4(h[s][4 * j], h[s][4 * j + 1], h[s][4 * j + 2], h[s][4 * j + 3]);
+                *reinterpret_cast<float4 *>(p.h_state + rr[s] * H + unit0 + 4 * j) = hv;
+                if (!p.return_sequences) *reinterpret_cast<float4 *>(p.out + rr[s] * H + unit0 + 4 * j) = hv;
+                if (G == 4)
+                    *reinterpret_cast<float4 *>(p.c_state + rr[s] * H + unit0 + 4 * j) =
+                        make_float4(c[s][4 * j], c[s][4 * j + 1], c[s][4 * j + 2], c[s][4 * j + 3]);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    ht_cluster_sync();           // nobody leaves while a peer could still address this CTA's shared memory
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+    }
+}
+
+// Bt[(rank*G + g)*32 + u][k] = half(U[k][g*H + 32 rank + u])
+__global__ void pack_cluster_weights_h16_kernel(const float *__restrict__ U, __half *__restrict__ Bt, int H, int G) {
+    const long long total = (long long)G * H * H;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int n = (int)(i / H), k = (int)(i - (long long)n * H);
+        const int rank = n / (G * 32), rem = n - rank * G * 32, g = rem >> 5, u = rem & 31;
+        Bt[i] = __float2half_rn(__ldg(U + (long long)k * G * H + g * H + rank * 32 + u));
+    }
+}
+
+__half *g_ht_scratch = nullptr;
+size_t g_ht_halves = 0;
+
+template <int G>
+int launch_ht(const CUtensorMap &mu, const HtParams &p, int clusters, size_t smem, cudaStream_t st) {
+    auto kern = recurrent_cluster_h16_kernel<G>;
+    static size_t attr_smem = 0;
+    static bool attr_np = false;
+    if (smem > attr_smem) {
+        NNTK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_smem = smem;
+    }
+    if (p.C > 8 && !attr_np) {
+        NNTK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        attr_np = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(clusters * p.C));
+    cfg.blockDim = dim3(HT_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)p.C;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    NNTK_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mu, p));
+    return 0;
+}
+
+}  // namespace
+
+// Runs all T steps of one batch chunk in ONE launch.  *used = 0 when the shape / activations are not eligible.
+extern "C" int nntk_cuda_recurrent_cluster_h16(const nntk_recurrent_args *r, int nb, const float *xw, float *h, float *c,
+                                               float *out, int *used) {
+    *used = 0;
+    const int G = r->cell, H = r->H, T = r->T;
+    if ((G != 3 && G != 4) || (H & 31) || H > 256 || T < 1 || nb < 1) return 0;
+    const int SG = NNTK_ACT_SIGMOID, TH = NNTK_ACT_TANH;
+    const bool def = (G == 3) ? (r->act[0] == SG && r->act[1] == SG && r->act[2] == TH)
+                              : (r->act[0] == SG && r->act[1] == SG && r->act[2] == TH && r->act[3] == SG && r->act[4] == TH);
+    if (!def) return 0;
+    const int C = H / 32;
+    const size_t smem = (size_t)HT_SLICES * C * HT_KB_BYTES + (size_t)C * G * 32 * 64 + 96 + (size_t)G * 32 * 4 + 1024;
+    if (C > 16 || smem > 227 * 1024) return 0;
+    if ((((uintptr_t)h) | ((uintptr_t)out) | ((uintptr_t)xw) | ((uintptr_t)c)) & 15) return 0;
+    EncodeTiledFn encode = get_encode();
+    if (!encode) {
+        nntk_cuda_set_error(NNTK_ERR_CUDA_, "recurrent_cluster_h16: cuTensorMapEncodeTiled is not available from this driver");
+        return NNTK_ERR_CUDA_;
+    }
+    cudaStream_t st = nntk_stream();
+    const size_t need = (size_t)G * H * H;
+    if (need > g_ht_halves) {
+        NNTK_CUDA_TRY(cudaStreamSynchronize(st));
+        if (g_ht_scratch) cudaFree(g_ht_scratch);
+        g_ht_scratch = nullptr; g_ht_halves = 0;
+        NNTK_CUDA_TRY(cudaMalloc(&g_ht_scratch, need * sizeof(__half)));
+        g_ht_halves = need;
+    }
+    {
+        const long long total = (long long)need;
+        const int blocks = (int)((total + 255) / 256 < 1024 ? (total + 255) / 256 : 1024);
+        pack_cluster_weights_h16_kernel<<<blocks, 256, 0, st>>>(r->d_U, g_ht_scratch, H, G);
+        NNTK_LAUNCH_CHECK("pack_cluster_weights_h16_kernel");
+    }
+    CUtensorMap mu;
+    {
+        cuuint64_t dims[2] = {(cuuint64_t)H, (cuuint64_t)G * H};
+        cuuint64_t strides[1] = {(cuuint64_t)H * 2};
+        cuuint32_t box[2] = {32, (cuuint32_t)(G * 32)};
+        cuuint32_t estr[2] = {1, 1};
+        CUresult cr = encode(&mu, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (void *)g_ht_scratch, dims, strides, box, estr,
+                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (cr != CUDA_SUCCESS) {
+            nntk_cuda_set_error(NNTK_ERR_CUDA_, "recurrent_cluster_h16: tensor map for U rejected (CUresult %d)", (int)cr);
+            return NNTK_ERR_CUDA_;
+        }
+    }
+    HtParams p;
+    p.B = nb; p.H = H; p.T = T; p.C = C; p.return_sequences = r->return_sequences;
+    p.bh = ((G == 3) || r->v2) ? r->d_bh : nullptr;
+    p.xw = xw; p.h_state = h; p.c_state = c; p.out = out;
+    const int clusters = (nb + HT_SLICES * HT_BM - 1) / (HT_SLICES * HT_BM);
+    int rc = (G == 3) ? launch_ht<3>(mu, p, clusters, smem, st) : launch_ht<4>(mu, p, clusters, smem, st);
+    if (rc) return rc;
+    *used = 1;
+    return 0;
+}

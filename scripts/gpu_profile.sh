@@ -10,7 +10,8 @@ cap() { # name kernel-regex skip stage mode scale
 }
 cap conv_tc gemm_tf32_kernel 4 c3 tf32 0.25
 cap lstm_tc recurrent_tc_step 40 c4 tf32 0.25
-cap gru_cluster recurrent_cluster 1 c5 fp32 0.25
+cap gru_ctc recurrent_cluster_tc 1 c5 tf32 1.875
+cap gru_cluster recurrent_cluster_kernel 1 c5 fp32 0.25
 cap conv_fp32 gemm_fp32_kernel 4 c3 fp32 0.25
 cap lstm_fp32 recurrent_step_kernel 40 c4 fp32 0.25
 ls -la gpurun_out
