@@ -109,6 +109,41 @@ inline unsigned grid_for(long long work_items, int per_block) {
     return (unsigned)blocks;
 }
 
+
+// Any C (e.g. the 257 frequency bins of C5) with 16-byte accesses: float4 i covers elements 4i..4i+3 whose channels are
+// (4i + e) mod C, tracked by a running index.  gamma | beta | mean | sd sit in shared memory; sd = sqrtf(var + eps) is
+// evaluated once per channel -- the same fp32 value the reference recomputes for every row (batch_norm.c:153-156).
+__global__ void __launch_bounds__(256) batch_norm_any_kernel(const float *__restrict__ prm, int C, float eps,
+                                                             const float *__restrict__ in, float *__restrict__ out,
+                                                             long long total) {
+    extern __shared__ float tab[];       // [4][C]
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        tab[c] = prm[c]; tab[C + c] = prm[C + c]; tab[2 * C + c] = prm[2 * C + c];
+        tab[3 * C + c] = sqrtf(__fadd_rn(prm[3 * C + c], eps));
+    }
+    __syncthreads();
+    const float *gamma = tab, *beta = tab + C, *mean = tab + 2 * C, *sd = tab + 3 * C;
+    const long long stride = (long long)gridDim.x * blockDim.x, nvec = total >> 2;
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    int c = (int)((4 * i) % C);
+    const int step = (int)((4 * stride) % C);
+    for (; i < nvec; i += stride) {
+        float4 x = ld_stream(reinterpret_cast<const float4 *>(in) + i);
+        float *xe = &x.x;
+        int ce = c;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            xe[e] = __fadd_rn(__fmul_rn(__fdiv_rn(__fsub_rn(xe[e], mean[ce]), sd[ce]), gamma[ce]), beta[ce]);
+            if (++ce == C) ce = 0;
+        }
+        st_stream(reinterpret_cast<float4 *>(out) + i, x);
+        c += step; if (c >= C) c -= C;
+    }
+    for (long long t = (nvec << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += stride) {
+        const int ct = (int)(t % C);
+        out[t] = __fadd_rn(__fmul_rn(__fdiv_rn(__fsub_rn(in[t], mean[ct]), sd[ct]), gamma[ct]), beta[ct]);
+    }
+}
 }  // namespace
 
 extern "C" int nntk_cuda_batch_norm(const float *d_params, int C, float eps, const float *d_in, float *d_out,
@@ -122,8 +157,11 @@ extern "C" int nntk_cuda_batch_norm(const float *d_params, int C, float eps, con
     const long long total = rows * C;
     if (total == 0) return 0;
     const bool vec = (C % 4 == 0) && ((((uintptr_t)d_in) | ((uintptr_t)d_out) | ((uintptr_t)d_params)) & 15) == 0;
+    const bool aligned = ((((uintptr_t)d_in) | ((uintptr_t)d_out)) & 15) == 0;
     if (vec)
         batch_norm_kernel<true><<<grid_for(total >> 2, 256), 256, 0, nntk_stream()>>>(d_params, C, eps, d_in, d_out, total);
+    else if (aligned && C <= 2048 && total >= 4096)
+        batch_norm_any_kernel<<<grid_for(total >> 2, 256), 256, 4 * C * sizeof(float), nntk_stream()>>>(d_params, C, eps, d_in, d_out, total);
     else
         batch_norm_kernel<false><<<grid_for(total, 256), 256, 0, nntk_stream()>>>(d_params, C, eps, d_in, d_out, total);
     NNTK_LAUNCH_CHECK("batch_norm_kernel");

@@ -43,7 +43,8 @@ struct SmemLayout {
     static constexpr int B_BYTES = BN * BK * 4;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
-    static constexpr int TOTAL = BAR_OFFSET + (2 * STAGES + 4) * 8 + 16 + 1024;   // + alignment slack
+    static constexpr int STG_OFFSET = BAR_OFFSET + 256;                         // epilogue staging: 8 warps x 2 KB
+    static constexpr int TOTAL = STG_OFFSET + 8 * 2048 + 1024;                  // + alignment slack
 };
 
 template <int BN, int STAGES, bool FAST>
@@ -133,6 +134,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         const int q = warp & 3;
         const int half = (warp - 2) >> 2;
         const int row_in_tile = q * 32 + lane;
+        uint8_t *stg = smem + SL::STG_OFFSET + (warp - 2) * 2048;      // [32 rows][64 bytes], xor-swizzled 16-byte slots
         uint32_t it = 0;
         const bool vec_ok = ((p.ldc & 3) == 0) && ((p.c_slab & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
         for (long long tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
@@ -144,6 +146,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             const int row = m_t * BM + row_in_tile;
             const bool row_ok = row < p.rows;
             float *crow = p.C + slab * p.c_slab + (long long)row * p.ldc;
+            float *cwarp = p.C + slab * p.c_slab + (long long)(m_t * BM + q * 32) * p.ldc;   // first row of this warp's 32
             const uint32_t taddr = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16);
             mbar_wait(&tmem_full[buf], use & 1);
             tc_fence_after();
@@ -163,7 +166,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                         sh[j] = __ldg(reinterpret_cast<const float4 *>(p.shift + n0) + j);
                     }
                     tc_ld_wait();
-                    float4 *dst = reinterpret_cast<float4 *>(crow + n0);
+                    float4 vv[8];
                     if (p.act == NNTK_ACT_RELU) {
                         const float a = p.act_a;
 #pragma unroll
@@ -173,7 +176,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                             v.y = fmaxf(fmaf(__uint_as_float(r[4 * j + 1]), sc[j].y, sh[j].y), 0.0f) * a;
                             v.z = fmaxf(fmaf(__uint_as_float(r[4 * j + 2]), sc[j].z, sh[j].z), 0.0f) * a;
                             v.w = fmaxf(fmaf(__uint_as_float(r[4 * j + 3]), sc[j].w, sh[j].w), 0.0f) * a;
-                            if (row_ok) dst[j] = v;
+                            vv[j] = v;
                         }
                     } else if (p.act == NNTK_ACT_SIGMOID || p.act == NNTK_ACT_TANH) {
 #pragma unroll
@@ -183,7 +186,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                             v.y = nntk_act(p.act, 1.0f, fmaf(__uint_as_float(r[4 * j + 1]), sc[j].y, sh[j].y));
                             v.z = nntk_act(p.act, 1.0f, fmaf(__uint_as_float(r[4 * j + 2]), sc[j].z, sh[j].z));
                             v.w = nntk_act(p.act, 1.0f, fmaf(__uint_as_float(r[4 * j + 3]), sc[j].w, sh[j].w));
-                            if (row_ok) dst[j] = v;
+                            vv[j] = v;
                         }
                     } else {
 #pragma unroll
@@ -193,8 +196,26 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                             v.y = fmaf(__uint_as_float(r[4 * j + 1]), sc[j].y, sh[j].y);
                             v.z = fmaf(__uint_as_float(r[4 * j + 2]), sc[j].z, sh[j].z);
                             v.w = fmaf(__uint_as_float(r[4 * j + 3]), sc[j].w, sh[j].w);
-                            if (row_ok) dst[j] = v;
+                            vv[j] = v;
                         }
+                    }
+                    // Store through a per-warp 2 KB staging tile so that one store instruction covers 8 rows x 64 contiguous
+                    // bytes (8 wavefronts) instead of 32 rows x 16 bytes (32 wavefronts): the row-per-lane TMEM layout made the
+                    // LSU, not the tensor pipe, the limiter of short-K GEMMs (ncu r1: 42 % LSU wavefronts at K = 1280).
+#pragma unroll
+                    for (int hh = 0; hh < 2; ++hh) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            *reinterpret_cast<float4 *>(stg + lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4)) = vv[hh * 4 + j];
+                        __syncwarp();
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const int rw = (lane >> 2) + 8 * i, c4 = lane & 3;
+                            const float4 w = *reinterpret_cast<const float4 *>(stg + rw * 64 + ((c4 ^ ((rw >> 1) & 3)) << 4));
+                            if (m_t * BM + q * 32 + rw < p.rows)
+                                *reinterpret_cast<float4 *>(cwarp + (long long)rw * p.ldc + n0 + hh * 16 + c4 * 4) = w;
+                        }
+                        __syncwarp();
                     }
                 } else {
                     tc_ld_32x32(taddr + c0, r);
