@@ -1,5 +1,5 @@
 // recurrent_cluster_h16.cu -- K4, persistent tensor-core recurrence, fp16-operand / two-slice variant (NNTK_MATH_TF32 mode,
-// default gate activations, H <= 256).  Same structure as recurrent_cluster_tc.cu (cluster of C = H/32 CTAs, U slice resident
+// default gate activations, H <= 512).  Same structure as recurrent_cluster_tc.cu (cluster of C = H/32 CTAs, U slice resident
 // in shared memory, h exchanged by DSMEM bulk copies, a_full / a_free mbarriers) with two changes that ncu asked for:
 //   * operands are fp16 (tcgen05.mma kind::f16, fp32 accumulate).  With the default activations h is bounded by 1, so fp16's
 //     10-bit mantissa is EXACTLY the TF32 operand precision (2^-11 relative) -- but the A tile, the U slice and above all the
@@ -9,7 +9,8 @@
 //     chain (MMA -> cell math -> exchange -> MMA ...); with two slices the epilogue warps do the cell math of one slice while
 //     the other slice's copies and MMA are in flight, so the exchange latency is hidden instead of added.
 // Not eligible (caller falls back to the TF32 cluster kernel, then to the per-step kernels): custom gate activations (h may
-// leave the fp16 range), H > 256.  fp16 overflow of a caller-supplied |h_0| > 65504 saturates to inf like any fp16 cast.
+// leave the fp16 range), H > 512 or H % 32 != 0.  H = 512 (16-CTA non-portable clusters) runs with 64-sequence slices:
+// LSTM-512 (BASELINE config 4) one slice per cluster, GRU-512 two.  fp16 overflow of a caller-supplied |h_0| > 65504 saturates to inf like any fp16 cast.
 
 #include <cuda_fp16.h>
 #include "tc_common.cuh"
@@ -17,9 +18,8 @@
 namespace {
 
 constexpr int HT_THREADS = 320;              // warp 0: a_free signalling, warp 1: MMA issuer, warps 2..9: epilogue
-constexpr int HT_BM = 128;                   // sequences per slice
-constexpr int HT_SLICES = 2;
-constexpr int HT_KB_BYTES = HT_BM * 64;      // one k-block of A: 128 rows x 32 halves
+// Template parameters of the kernel: BM = sequences per slice (128, or 64 when the A tile must shrink: H = 512), SL = slices
+// per cluster (2, or 1 when shared memory holds only one A tile: LSTM-512).  One k-block of A = BM rows x 32 halves.
 
 struct HtParams {
     int B, H, T, C;
@@ -72,12 +72,13 @@ __device__ __forceinline__ uint32_t ht_pack2(float a, float b) {
     return *reinterpret_cast<uint32_t *>(&v);
 }
 
-template <int G>
+template <int G, int BM, int SL>
 __global__ void __launch_bounds__(HT_THREADS, 1)
 recurrent_cluster_h16_kernel(const __grid_constant__ CUtensorMap map_u, HtParams p) {
     constexpr int N = 32 * G;
+    constexpr int HT_BM = BM, HT_SLICES = SL, HT_KB_BYTES = BM * 64;
     constexpr uint32_t ACC_STRIDE = 128;                   // TMEM columns between the two slices' accumulators
-    constexpr uint32_t TMEM_COLS = 256;
+    constexpr uint32_t TMEM_COLS = SL == 2 ? 256 : 128;
     constexpr int S_SIG = NNTK_ACT_SIGMOID, S_TANH = NNTK_ACT_TANH;
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -127,7 +128,7 @@ recurrent_cluster_h16_kernel(const __grid_constant__ CUtensorMap map_u, HtParams
         // This warp has no global-memory traffic of its own, so the generic->async proxy fence it executes before the copy
         // is cheap; in the epilogue threads the same fence waited for their outstanding xw loads (ncu: 12 % of the step).
         const int s = lane >> 4, peer = lane & 15;
-        if (peer < C) {
+        if (peer < C && s < HT_SLICES) {
             const uint32_t my_kb = smem_u32(sA) + s * a_slice_bytes + rank * HT_KB_BYTES;
             const uint32_t dst_kb = ht_map(my_kb, (uint32_t)peer);
             const uint32_t dst_full = ht_map(smem_u32(a_full + s), (uint32_t)peer);
@@ -168,8 +169,11 @@ recurrent_cluster_h16_kernel(const __grid_constant__ CUtensorMap map_u, HtParams
         }
     } else {
         // ===== epilogue: thread = row r of BOTH slices x 16 hidden units =====
+        // BM = 128: TMEM lane = row.  BM = 64: row m sits in TMEM lane (m % 16) + 32 (m / 16), so each warp's lanes 0..15 own
+        // rows 16 q .. 16 q + 15 and lanes 16..31 idle (they still take part in the warp-wide TMEM loads).
         const int q = warp & 3, half = (warp - 2) >> 2;
-        const int r = q * 32 + lane;
+        const bool active = (BM == 128) || lane < 16;
+        const int r = (BM == 128) ? q * 32 + lane : q * 16 + (lane & 15);
         const int ul = half * 16;                          // first unit inside the CTA's 32
         const int unit0 = (int)rank * 32 + ul;             // first hidden unit (global index)
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + ul;
@@ -181,7 +185,7 @@ recurrent_cluster_h16_kernel(const __grid_constant__ CUtensorMap map_u, HtParams
 #pragma unroll
         for (int s = 0; s < HT_SLICES; ++s) {
             const int row = row0 + s * HT_BM + r;
-            row_ok[s] = row < p.B;
+            row_ok[s] = active && row < p.B;
             rr[s] = row_ok[s] ? row : 0;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -213,14 +217,14 @@ recurrent_cluster_h16_kernel(const __grid_constant__ CUtensorMap map_u, HtParams
                 uint4 v;
                 v.x = ht_pack2(h[s][8 * j + 0], h[s][8 * j + 1]); v.y = ht_pack2(h[s][8 * j + 2], h[s][8 * j + 3]);
                 v.z = ht_pack2(h[s][8 * j + 4], h[s][8 * j + 5]); v.w = ht_pack2(h[s][8 * j + 6], h[s][8 * j + 7]);
-                *reinterpret_cast<uint4 *>(kb + r * 64 + (((half * 2 + j) ^ sw) << 4)) = v;
+                if (active) *reinterpret_cast<uint4 *>(kb + r * 64 + (((half * 2 + j) ^ sw) << 4)) = v;
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(h_ready + s);         // release: the exchange warp fences and pushes
         };
-        exchange(0, 0);
-        exchange(1, 0);
+#pragma unroll
+        for (int s = 0; s < HT_SLICES; ++s) exchange(s, 0);
         load_xw(0, 0);
         for (int t = 0; t < T; ++t) {
 #pragma unroll
@@ -253,7 +257,7 @@ recurrent_cluster_h16_kernel(const __grid_constant__ CUtensorMap map_u, HtParams
                     }
                 }
                 // xw of the NEXT slice-step goes in flight now (xr is dead), under this slice's exchange
-                if (s == 0) load_xw(1, t);
+                if (s + 1 < HT_SLICES) load_xw(s + 1, t);
                 else if (t + 1 < T) load_xw(0, t + 1);
                 if (t + 1 < T) exchange(s, t + 1);
                 if (p.return_sequences && row_ok[s]) {
@@ -299,9 +303,9 @@ __global__ void pack_cluster_weights_h16_kernel(const float *__restrict__ U, __h
 __half *g_ht_scratch = nullptr;
 size_t g_ht_halves = 0;
 
-template <int G>
+template <int G, int BM, int SL>
 int launch_ht(const CUtensorMap &mu, const HtParams &p, int clusters, size_t smem, cudaStream_t st) {
-    auto kern = recurrent_cluster_h16_kernel<G>;
+    auto kern = recurrent_cluster_h16_kernel<G, BM, SL>;
     static size_t attr_smem = 0;
     static bool attr_np = false;
     if (smem > attr_smem) {
@@ -324,6 +328,11 @@ int launch_ht(const CUtensorMap &mu, const HtParams &p, int clusters, size_t sme
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
+    int max_clusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&max_clusters, kern, &cfg) != cudaSuccess || max_clusters < 1) {
+        (void)cudaGetLastError();
+        return 1;     // this cluster shape cannot be scheduled on this device: not eligible, the caller falls back
+    }
     NNTK_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mu, p));
     return 0;
 }
@@ -335,14 +344,30 @@ extern "C" int nntk_cuda_recurrent_cluster_h16(const nntk_recurrent_args *r, int
                                                float *out, int *used) {
     *used = 0;
     const int G = r->cell, H = r->H, T = r->T;
-    if ((G != 3 && G != 4) || (H & 31) || H > 256 || T < 1 || nb < 1) return 0;
+    if ((G != 3 && G != 4) || (H & 31) || H > 512 || T < 1 || nb < 1) return 0;
     const int SG = NNTK_ACT_SIGMOID, TH = NNTK_ACT_TANH;
     const bool def = (G == 3) ? (r->act[0] == SG && r->act[1] == SG && r->act[2] == TH)
                               : (r->act[0] == SG && r->act[1] == SG && r->act[2] == TH && r->act[3] == SG && r->act[4] == TH);
     if (!def) return 0;
     const int C = H / 32;
-    const size_t smem = (size_t)HT_SLICES * C * HT_KB_BYTES + (size_t)C * G * 32 * 64 + 96 + (size_t)G * 32 * 4 + 1024;
-    if (C > 16 || smem > 227 * 1024) return 0;
+    if (C > 16) return 0;
+    // largest configuration that fits 227 KB: (128 sequences x 2 slices), (64 x 2), (64 x 1)
+    int BM = 0, SL = 0;
+    size_t smem = 0;
+    const int cand[3][2] = {{128, 2}, {64, 2}, {64, 1}};
+    for (int i = 0; i < 3 && !BM; ++i) {
+        const size_t need_smem = (size_t)cand[i][1] * C * cand[i][0] * 64 + (size_t)C * G * 32 * 64 + 96 + (size_t)G * 32 * 4 + 1024;
+        if (need_smem <= 227 * 1024) { BM = cand[i][0]; SL = cand[i][1]; smem = need_smem; }
+    }
+    if (!BM) return 0;
+    // 64-sequence slices on 16-CTA clusters (H = 512) keep only ~7 x 64 sequences in flight: measured on C4 they beat the
+    // per-step tensor-core kernel up to ~1.5k sequences (B = 512: 19.2 vs 34.9 ms, B = 2048: 55.3 vs 52.6 ms) -- which is
+    // the 8-GPU share of C4 (512 per GPU) -- and lose beyond.
+    if (BM == 64) {
+        static int max64 = -1;
+        if (max64 < 0) { const char *e = getenv("NNTK_CLUSTER_H16_MAX_BATCH_64"); max64 = e ? atoi(e) : 1536; }
+        if (nb > max64) return 0;
+    }
     if ((((uintptr_t)h) | ((uintptr_t)out) | ((uintptr_t)xw) | ((uintptr_t)c)) & 15) return 0;
     EncodeTiledFn encode = get_encode();
     if (!encode) {
@@ -382,8 +407,13 @@ extern "C" int nntk_cuda_recurrent_cluster_h16(const nntk_recurrent_args *r, int
     p.B = nb; p.H = H; p.T = T; p.C = C; p.return_sequences = r->return_sequences;
     p.bh = ((G == 3) || r->v2) ? r->d_bh : nullptr;
     p.xw = xw; p.h_state = h; p.c_state = c; p.out = out;
-    const int clusters = (nb + HT_SLICES * HT_BM - 1) / (HT_SLICES * HT_BM);
-    int rc = (G == 3) ? launch_ht<3>(mu, p, clusters, smem, st) : launch_ht<4>(mu, p, clusters, smem, st);
+    const int clusters = (nb + SL * BM - 1) / (SL * BM);
+    int rc;
+#define NNTK_HT(GG) (BM == 128 ? launch_ht<GG, 128, 2>(mu, p, clusters, smem, st) \
+                    : SL == 2 ? launch_ht<GG, 64, 2>(mu, p, clusters, smem, st) : launch_ht<GG, 64, 1>(mu, p, clusters, smem, st))
+    rc = (G == 3) ? NNTK_HT(3) : NNTK_HT(4);
+#undef NNTK_HT
+    if (rc == 1) return 0;
     if (rc) return rc;
     *used = 1;
     return 0;

@@ -113,11 +113,12 @@ def test_lstm_c4_shape_long_sequence_tf32(tf32, port):
 @pytest.mark.parametrize("cell,in_size,H,T,B,seq", [("gru", 64, 256, 12, 300, True), ("lstm", 96, 128, 40, 260, True),
                                                     ("lstm", 64, 192, 7, 385, False), ("gru", 32, 64, 50, 270, False),
                                                     ("gru", 40, 128, 100, 33, True), ("gru", 16, 32, 9, 128, True),
-                                                    ("gru", 256, 256, 300, 129, True)])
+                                                    ("gru", 256, 256, 300, 129, True), ("gru", 48, 512, 20, 150, True),
+                                                    ("lstm", 64, 512, 12, 70, False), ("lstm", 32, 384, 9, 200, True)])
 def test_persistent_tensor_core_cluster_kernel(tf32, port, cell, in_size, H, T, B, seq):
     """TF32 mode, H % 32 == 0, H <= 256, batch >= 32: ONE launch runs all T steps (csrc/recurrent_cluster_tc.cu) -- a cluster
     of H/32 CTAs per 128 sequences keeps U resident in shared memory and exchanges h_t by DSMEM bulk copies.  Cluster sizes
-    1, 2, 4, 6, 8; ragged last slice; rows from the first, a middle and the last slice against the oracle port; the C5
+    1, 2, 4, 6, 8, 12, 16 (H = 512: 64-sequence slices, LSTM one slice per cluster, GRU two); ragged last slice; rows from the first, a middle and the last slice against the oracle port; the C5
     GRU(256) shape over 300 steps checks that TF32 rounding of h does not accumulate beyond the stated 1e-3."""
     import port_cases
     rng = np.random.default_rng(16)
