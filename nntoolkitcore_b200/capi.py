@@ -166,6 +166,7 @@ SHIM_SYMBOLS = [
     "nntk_cuda_host_free", "nntk_cuda_h2d", "nntk_cuda_d2h", "nntk_cuda_d2d", "nntk_cuda_memset",
     "nntk_cuda_is_device_ptr", "nntk_cuda_workspace", "nntk_cuda_staged_run", "nntk_cuda_spectrogram",
     "nntk_cuda_batch_norm", "nntk_cuda_activation", "nntk_cuda_gemm", "nntk_cuda_pack_conv_weights",
+    "nntk_cuda_pack_conv_weights_padded", "nntk_cuda_pad_channels",
     "nntk_cuda_recurrent_workspace", "nntk_cuda_recurrent",
 ]
 
