@@ -26,7 +26,8 @@ constexpr int EPI_WARPS = 8;
 struct TcParams {
     int N, n_tiles, m_tiles_per_slab, k_blocks;   // k_blocks: total over all passes (3x in split mode)
     int kb_pass;                                  // k-blocks per pass = ceil(K / 32)
-    int lo_slab;                                  // split mode: slab coordinate offset of the lo copy of A (= batch), else 0
+    int c_blocked;                                // 0: C row-major.  1: recurrent layout [slab][row/32][N/4][row%32][4] (see nntk_cuda_gemm_tf32_ex)
+    int row_blocks;                               // c_blocked: ceil(rows / 32)
     long long total_tiles;
     int rows;
     float *C;
@@ -95,7 +96,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                     // two small passes come FIRST: the tensor core's fp32 accumulate truncates (measured: error grows
                     // with the number of accumulation steps at full magnitude), so they run while the sum is still tiny.
                     const int pass = kb / p.kb_pass, akb = kb - pass * p.kb_pass;
-                    tma_load_3d(sa, &map_a, &full_bar[stage], akb * BK, m_t * BM, slab + (pass == 1 ? p.lo_slab : 0));
+                    tma_load_4d(sa, &map_a, &full_bar[stage], akb * BK, m_t * BM, slab, pass == 1 ? 1 : 0);
                     tma_load_2d(sa + SL::A_BYTES, &map_b, &full_bar[stage], kb * BK, n_t * BN);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -198,6 +199,15 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                             v.w = fmaf(__uint_as_float(r[4 * j + 3]), sc[j].w, sh[j].w);
                             vv[j] = v;
                         }
+                    }
+                    if (p.c_blocked) {
+                        // recurrent layout: lanes (consecutive rows) are contiguous 16-byte slots -> 512-byte stores, no staging
+                        float4 *dstb = reinterpret_cast<float4 *>(p.C) +
+                                       (((long long)slab * p.row_blocks + (m_t * (BM / 32) + q)) * (p.N >> 2) + (n0 >> 2)) * 32 + lane;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            if (row_ok) dstb[j * 32] = vv[j];
+                        continue;
                     }
                     // Store through a per-warp 2 KB staging tile so that one store instruction covers 8 rows x 64 contiguous
                     // bytes (8 wavefronts) instead of 32 rows x 16 bytes (32 wavefronts): the row-per-lane TMEM layout made the
@@ -329,7 +339,16 @@ static int launch_tc(const CUtensorMap &ma, const CUtensorMap &mb, TcParams &p, 
 
 // returns 0 done, 1 not eligible (caller runs the fp32 kernel), <0 error.  split != 0: 3xTF32 (hi/lo operand split, three
 // passes folded into ONE K loop of length 3K -- the kernel is unchanged), fp32-class accuracy at a third of the TF32 rate.
-extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *a, int split) {
+extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_blocked);
+extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *a, int split) { return nntk_cuda_gemm_tf32_ex(a, split, 0); }
+
+// c_blocked = 1 (internal, used by the hoisted recurrent projection): slabs are TIMESTEPS and rows are SEQUENCES
+// (a_slab_stride = in, lda = T*in -- interleaved slabs are fine for TMA), and C is written as
+//   C[slab][row / 32][N / 4][row % 32][4 floats]
+// so that a warp whose lanes are 32 consecutive sequences -- the TMEM row-per-lane layout here AND in the persistent recurrent
+// kernel that reads it back -- touches 512 contiguous bytes per 16-byte access instead of 32 different lines.  Needs N % 32 == 0.
+extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_blocked) {
+    if (c_blocked && (a->N % 32 != 0 || (((uintptr_t)a->d_C) & 15))) return 1;
     if ((a->lda & 3) || (a->a_slab_stride & 3) || (((uintptr_t)a->d_A) & 15) || a->rows < 1 || a->batch < 1) return 1;
     EncodeTiledFn encode = get_encode();
     if (!encode) {
@@ -361,10 +380,10 @@ extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *a, int split) {
     // slab stride of A as the tensor map sees it; in split mode the lo copy sits `batch` slabs behind the hi copy
     const long long slab_floats = a->batch > 1 ? a->a_slab_stride : (long long)a->rows * a->lda;
     const float *A = a->d_A;
+    long long lo_off = 4;
     if (split) {
-        if (a->batch > 1 && a->a_slab_stride < (long long)(a->rows - 1) * a->lda + K) return 1;   // slabs must not interleave
         const long long extent = (long long)(a->batch - 1) * slab_floats + (long long)(a->rows - 1) * a->lda + K;
-        const long long lo_off = (long long)a->batch * slab_floats;
+        lo_off = (extent + 63) & ~63LL;
         const size_t want = (size_t)(lo_off + extent + 64);
         if (want > g_split_floats) {
             NNTK_CUDA_TRY(cudaStreamSynchronize(st));
@@ -384,13 +403,14 @@ extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *a, int split) {
     const int BN = N > 128 ? 256 : 128;
     CUtensorMap ma, mb;
     {
-        cuuint64_t dims[3] = {(cuuint64_t)K, (cuuint64_t)a->rows, (cuuint64_t)a->batch * (split ? 2 : 1)};
+        // {K, rows, slabs, parts}: parts = hi / lo copies of A in split mode (lo_off floats apart)
+        cuuint64_t dims[4] = {(cuuint64_t)K, (cuuint64_t)a->rows, (cuuint64_t)a->batch, (cuuint64_t)(split ? 2 : 1)};
         cuuint64_t slab_bytes = (cuuint64_t)slab_floats * 4;
         if (slab_bytes == 0) slab_bytes = 16;
-        cuuint64_t strides[2] = {(cuuint64_t)a->lda * 4, slab_bytes};
-        cuuint32_t box[3] = {BK, BM, 1};
-        cuuint32_t estr[3] = {1, 1, 1};
-        CUresult r = encode(&ma, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void *)A, dims, strides, box, estr,
+        cuuint64_t strides[3] = {(cuuint64_t)a->lda * 4, slab_bytes, (cuuint64_t)lo_off * 4};
+        cuuint32_t box[4] = {BK, BM, 1, 1};
+        cuuint32_t estr[4] = {1, 1, 1, 1};
+        CUresult r = encode(&ma, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void *)A, dims, strides, box, estr,
                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) {
@@ -417,13 +437,13 @@ extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *a, int split) {
     p.m_tiles_per_slab = (a->rows + BM - 1) / BM;
     p.kb_pass = (K + BK - 1) / BK;
     p.k_blocks = parts * p.kb_pass;
-    p.lo_slab = split ? a->batch : 0;
+    p.c_blocked = c_blocked; p.row_blocks = (a->rows + 31) / 32;
     p.total_tiles = (long long)p.n_tiles * p.m_tiles_per_slab * a->batch;
     p.rows = a->rows;
     p.C = a->d_C; p.c_slab = a->c_slab_stride; p.ldc = a->ldc;
     p.scale = scale; p.shift = shift; p.act = a->act; p.act_a = a->act_a;
     // FAST epilogue: whole 32-column chunks and 16-byte aligned output rows (every BASELINE shape except the 12-wide TDD)
-    const bool fast = (N % 32 == 0) && (a->ldc % 4 == 0) && (a->c_slab_stride % 4 == 0) && ((((uintptr_t)a->d_C) & 15) == 0);
+    const bool fast = c_blocked || ((N % 32 == 0) && (a->ldc % 4 == 0) && (a->c_slab_stride % 4 == 0) && ((((uintptr_t)a->d_C) & 15) == 0));
     if (BN == 256) return fast ? launch_tc<256, 4, true>(ma, mb, p, st) : launch_tc<256, 4, false>(ma, mb, p, st);
     return fast ? launch_tc<128, 6, true>(ma, mb, p, st) : launch_tc<128, 6, false>(ma, mb, p, st);
 }

@@ -353,7 +353,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) recurrent_cluster_kernel(Cluste
 extern "C" size_t nntk_cuda_recurrent_workspace(const nntk_recurrent_args *r) {
     if (!r) return 0;
     const size_t G = (size_t)r->cell;
-    size_t xw = (size_t)r->batch * r->T * G * r->H * sizeof(float);
+    size_t xw = (size_t)((r->batch + 31) / 32 * 32) * r->T * G * r->H * sizeof(float);   // 32-sequence blocks
     size_t pp = (size_t)4 * r->batch * r->H * sizeof(float);   // exact + TF32-rounded h ping-pong
     return xw + pp + 256;
 }
@@ -428,8 +428,10 @@ extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, cons
 extern "C" int nntk_cuda_recurrent_cluster_tc(const nntk_recurrent_args *r, int nb, const float *xw, float *h, float *c,
                                               float *out, int *used);   // recurrent_cluster_tc.cu
 
-extern "C" int nntk_cuda_recurrent_cluster_h16(const nntk_recurrent_args *r, int nb, const float *xw, float *h, float *c,
-                                               float *out, int *used);  // recurrent_cluster_h16.cu
+extern "C" int nntk_cuda_recurrent_cluster_h16(const nntk_recurrent_args *r, int nb, const float *xw, int xw_blocked, float *h,
+                                               float *c, float *out, int *used);  // recurrent_cluster_h16.cu
+extern "C" int nntk_cuda_recurrent_cluster_h16_plan(const nntk_recurrent_args *r, int nb);
+extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_blocked);   // gemm_tc.cu
 
 static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *work) {
     const int G = r->cell, H = r->H, T = r->T, GH = G * H;
@@ -438,7 +440,7 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     float *c = r->d_c ? r->d_c + (long long)b0 * H : nullptr;
     float *out = r->d_out + (long long)b0 * (r->return_sequences ? (long long)T * H : H);
     float *xw = work;
-    float *pp = work + (size_t)nb * T * GH;
+    float *pp = work + (size_t)nb * T * GH;      // (a blocked xw may run into pp: the kernel that reads it does not use pp)
     // 1. hoisted input projection: xw = x*W + b_i over all timesteps
     nntk_gemm_args g = {};
     g.d_A = x; g.a_slab_stride = 0; g.lda = r->in; g.batch = 1; g.rows = nb * T; g.N = GH; g.K = r->in;
@@ -452,22 +454,39 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     // single-pass TF32 rounding of x and W in the PROJECTION alone costs 1.2e-3 (each operand ~7e-4), the recurrent TF32
     // rounding only 3.5e-4 -- and the projection is the cheap part.  The tensor-core STEP kernels stay single-pass TF32.
     const int proj_mode = (G == 1) ? 0 : (mode == 1 ? 2 : mode);
-    if (proj_mode != mode) nntk_cuda_set_math_mode(proj_mode);
-    int rc = nntk_cuda_gemm(&g);
-    if (proj_mode != mode) nntk_cuda_set_math_mode(mode);
-    if (rc) return rc;
+    static int min_batch = -1, use_h16 = -1;
+    if (min_batch < 0) { const char *e = getenv("NNTK_CLUSTER_TC_MIN_BATCH"); min_batch = e ? atoi(e) : 32; }
+    if (use_h16 < 0) { const char *e = getenv("NNTK_CLUSTER_H16"); use_h16 = e ? atoi(e) : 1; }
+    int rc;
+    // When the fp16 persistent cluster kernel will take this chunk, the projection is computed timestep-major and written in
+    // the 32-sequence-blocked layout that kernel reads with fully coalesced row-per-lane accesses (gemm_tc.cu, c_blocked).
+    int xw_blocked = 0;
+    const bool h16 = mode == 1 && G != 1 && use_h16 && nb >= min_batch && nntk_cuda_recurrent_cluster_h16_plan(r, nb);
+    if (h16 && (((uintptr_t)xw) & 15) == 0) {
+        nntk_gemm_args gb = g;
+        gb.batch = T; gb.rows = nb; gb.a_slab_stride = r->in; gb.lda = T * r->in;      // slab = timestep, row = sequence
+        rc = nntk_cuda_gemm_tf32_ex(&gb, 1, 1);
+        if (rc < 0) return rc;
+        xw_blocked = rc == 0;
+    }
+    if (!xw_blocked) {
+        if (proj_mode != mode) nntk_cuda_set_math_mode(proj_mode);
+        rc = nntk_cuda_gemm(&g);
+        if (proj_mode != mode) nntk_cuda_set_math_mode(mode);
+        if (rc) return rc;
+    }
     // 2a'. TF32 mode, H <= 256, batch >= NNTK_CLUSTER_TC_MIN_BATCH (default 32): ONE persistent tensor-core cluster kernel
     //      for all T steps (recurrent_cluster_tc.cu: U resident in shared memory, DSMEM bulk-copy h exchange)
     if (mode == 1 && G != 1) {
-        static int min_batch = -1;
-        if (min_batch < 0) { const char *e = getenv("NNTK_CLUSTER_TC_MIN_BATCH"); min_batch = e ? atoi(e) : 32; }
-        static int use_h16 = -1;
-        if (use_h16 < 0) { const char *e = getenv("NNTK_CLUSTER_H16"); use_h16 = e ? atoi(e) : 1; }
-        if (nb >= min_batch && use_h16) {   // fp16-operand, two-slice variant first (default activations only)
+        if (h16) {   // fp16-operand, two-slice variant first (default activations only)
             int used = 0;
-            rc = nntk_cuda_recurrent_cluster_h16(r, nb, xw, h, c, out, &used);
+            rc = nntk_cuda_recurrent_cluster_h16(r, nb, xw, xw_blocked, h, c, out, &used);
             if (rc) return rc;
             if (used) return 0;
+            if (xw_blocked) {
+                nntk_cuda_set_error(NNTK_ERR_CUDA_, "recurrent: the planned fp16 cluster kernel did not run");
+                return NNTK_ERR_CUDA_;
+            }
         }
         if (nb >= min_batch) {
             int used = 0;
@@ -555,7 +574,15 @@ extern "C" int nntk_cuda_recurrent(const nntk_recurrent_args *r) {
         nntk_cuda_set_error(NNTK_ERR_ARG_, "recurrent: workspace of %zu bytes holds no sequence (%zu needed each)", r->work_bytes, per_seq);
         return NNTK_ERR_ARG_;
     }
-    if (chunk > r->batch) chunk = r->batch;
+    if (chunk >= r->batch) {
+        chunk = r->batch;
+        // the blocked projection layout rounds the chunk up to 32 sequences: make sure that still fits
+        const size_t need = ((size_t)((chunk + 31) / 32 * 32) * r->T * r->cell * r->H + 4 * (size_t)chunk * r->H) * sizeof(float);
+        if (need > avail) chunk = chunk / 32 * 32;
+    } else {
+        chunk = chunk / 32 * 32;
+    }
+    if (chunk < 1) chunk = 1;      // tiny workspace: plain layout paths only (nb < 32 never plans the blocked layout)
     for (int b0 = 0; b0 < r->batch; b0 += (int)chunk) {
         const int nb = (int)((b0 + chunk <= r->batch) ? chunk : (r->batch - b0));
         rc = recurrent_chunk(r, b0, nb, r->d_work);

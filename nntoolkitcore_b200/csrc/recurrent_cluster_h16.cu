@@ -25,7 +25,8 @@ struct HtParams {
     int B, H, T, C;
     int return_sequences;
     const float *bh;                // [G*H] or null (not added)
-    const float *xw;                // [B][T][G*H], b_i already added
+    const float *xw;                // [B][T][G*H], b_i already added -- or, xw_blocked: [T][B/32][G*H/4][32][4] (gemm_tc.cu)
+    int xw_blocked, row_blocks;
     float *h_state, *c_state;       // [B][H] in/out
     float *out;                     // [B][T][H] or [B][H]
 };
@@ -179,6 +180,7 @@ recurrent_cluster_h16_kernel(const __grid_constant__ CUtensorMap map_u, HtParams
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + ul;
         // own A k-block: this thread's two 16-byte chunks of row r (SWIZZLE_64B: chunk index ^ ((row >> 1) & 3))
         const int sw = (r >> 1) & 3;
+        uint8_t *stg = reinterpret_cast<uint8_t *>(s_bh + G * 32) + (warp - 2) * 2048;   // output staging, 16-byte aligned
         bool row_ok[HT_SLICES];
         long long rr[HT_SLICES];
         float h[HT_SLICES][16], c[HT_SLICES][G == 4 ? 16 : 1];
@@ -201,6 +203,17 @@ recurrent_cluster_h16_kernel(const __grid_constant__ CUtensorMap map_u, HtParams
         }
         float4 xr[G][4];           // ONE buffer: loaded for the other slice while this slice's exchange is in progress
         auto load_xw = [&](int s, int t) {
+            if (p.xw_blocked) {
+                // lanes = 32 consecutive sequences -> every 16-byte load of the warp covers 512 contiguous bytes
+                const float4 *src = reinterpret_cast<const float4 *>(p.xw) +
+                                    (((long long)t * p.row_blocks + (rr[s] >> 5)) * (GH >> 2) + (unit0 >> 2)) * 32 + (rr[s] & 31);
+#pragma unroll
+                for (int g = 0; g < G; ++g)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        xr[g][j] = row_ok[s] ? __ldg(src + ((long long)g * (H >> 2) + j) * 32) : make_float4(0.f, 0.f, 0.f, 0.f);
+                return;
+            }
             const float *src = p.xw + (rr[s] * T + t) * (long long)GH + unit0;
 #pragma unroll
             for (int g = 0; g < G; ++g)
@@ -260,10 +273,26 @@ recurrent_cluster_h16_kernel(const __grid_constant__ CUtensorMap map_u, HtParams
                 if (s + 1 < HT_SLICES) load_xw(s + 1, t);
                 else if (t + 1 < T) load_xw(0, t + 1);
                 if (t + 1 < T) exchange(s, t + 1);
-                if (p.return_sequences && row_ok[s]) {
-                    float4 *o = reinterpret_cast<float4 *>(p.out + (rr[s] * T + t) * H + unit0);
+                if (p.return_sequences) {
+                    // h_t rows are 64-byte pieces of [B, T, H] rows: transposed through a 2 KB per-warp tile so that one store
+                    // instruction covers 8 sequences x 64 contiguous bytes instead of 32 sequences x 16 bytes
+                    constexpr int WROWS = (BM == 128) ? 32 : 16;
+                    if (active) {
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) o[j] = make_float4(h[s][4 * j], h[s][4 * j + 1], h[s][4 * j + 2], h[s][4 * j + 3]);
+                        for (int j = 0; j < 4; ++j)
+                            *reinterpret_cast<float4 *>(stg + (lane & 31) * 64 + ((j ^ ((lane >> 1) & 3)) << 4)) =
+                                make_float4(h[s][4 * j], h[s][4 * j + 1], h[s][4 * j + 2], h[s][4 * j + 3]);
+                    }
+                    __syncwarp();
+                    const long long wrow0 = (long long)row0 + s * HT_BM + q * WROWS;      // first sequence of this warp
+#pragma unroll
+                    for (int i = 0; i < WROWS / 8; ++i) {
+                        const int rw = (lane >> 2) + 8 * i, c4 = lane & 3;
+                        const float4 w = *reinterpret_cast<const float4 *>(stg + rw * 64 + ((c4 ^ ((rw >> 1) & 3)) << 4));
+                        if (wrow0 + rw < p.B)
+                            *reinterpret_cast<float4 *>(p.out + ((wrow0 + rw) * T + t) * H + unit0 + c4 * 4) = w;
+                    }
+                    __syncwarp();
                 }
             }
         }
@@ -304,7 +333,7 @@ __half *g_ht_scratch = nullptr;
 size_t g_ht_halves = 0;
 
 template <int G, int BM, int SL>
-int launch_ht(const CUtensorMap &mu, const HtParams &p, int clusters, size_t smem, cudaStream_t st) {
+int launch_ht(const CUtensorMap &mu, const HtParams &p, int clusters, size_t smem, cudaStream_t st, bool dry) {
     auto kern = recurrent_cluster_h16_kernel<G, BM, SL>;
     static size_t attr_smem = 0;
     static bool attr_np = false;
@@ -333,16 +362,15 @@ int launch_ht(const CUtensorMap &mu, const HtParams &p, int clusters, size_t sme
         (void)cudaGetLastError();
         return 1;     // this cluster shape cannot be scheduled on this device: not eligible, the caller falls back
     }
+    if (dry) return 0;
     NNTK_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mu, p));
     return 0;
 }
 
 }  // namespace
 
-// Runs all T steps of one batch chunk in ONE launch.  *used = 0 when the shape / activations are not eligible.
-extern "C" int nntk_cuda_recurrent_cluster_h16(const nntk_recurrent_args *r, int nb, const float *xw, float *h, float *c,
-                                               float *out, int *used) {
-    *used = 0;
+// static eligibility + configuration: the largest of (128 sequences x 2 slices), (64 x 2), (64 x 1) that fits 227 KB
+static int ht_config(const nntk_recurrent_args *r, int nb, int *BM_, int *SL_, size_t *smem_) {
     const int G = r->cell, H = r->H, T = r->T;
     if ((G != 3 && G != 4) || (H & 31) || H > 512 || T < 1 || nb < 1) return 0;
     const int SG = NNTK_ACT_SIGMOID, TH = NNTK_ACT_TANH;
@@ -351,12 +379,11 @@ extern "C" int nntk_cuda_recurrent_cluster_h16(const nntk_recurrent_args *r, int
     if (!def) return 0;
     const int C = H / 32;
     if (C > 16) return 0;
-    // largest configuration that fits 227 KB: (128 sequences x 2 slices), (64 x 2), (64 x 1)
     int BM = 0, SL = 0;
     size_t smem = 0;
     const int cand[3][2] = {{128, 2}, {64, 2}, {64, 1}};
     for (int i = 0; i < 3 && !BM; ++i) {
-        const size_t need_smem = (size_t)cand[i][1] * C * cand[i][0] * 64 + (size_t)C * G * 32 * 64 + 96 + (size_t)G * 32 * 4 + 1024;
+        const size_t need_smem = (size_t)cand[i][1] * C * cand[i][0] * 64 + (size_t)C * G * 32 * 64 + 96 + (size_t)G * 32 * 4 + 8 * 2048 + 1024;
         if (need_smem <= 227 * 1024) { BM = cand[i][0]; SL = cand[i][1]; smem = need_smem; }
     }
     if (!BM) return 0;
@@ -368,6 +395,35 @@ extern "C" int nntk_cuda_recurrent_cluster_h16(const nntk_recurrent_args *r, int
         if (max64 < 0) { const char *e = getenv("NNTK_CLUSTER_H16_MAX_BATCH_64"); max64 = e ? atoi(e) : 1536; }
         if (nb > max64) return 0;
     }
+    *BM_ = BM; *SL_ = SL; *smem_ = smem;
+    return 1;
+}
+
+#define NNTK_HT_DISPATCH(GG, DRY) (BM == 128 ? launch_ht<GG, 128, 2>(mu, p, clusters, smem, st, DRY) \
+                                  : SL == 2 ? launch_ht<GG, 64, 2>(mu, p, clusters, smem, st, DRY) : launch_ht<GG, 64, 1>(mu, p, clusters, smem, st, DRY))
+
+// 1 when nntk_cuda_recurrent_cluster_h16 WILL run this chunk (so the caller may lay the projection out for it), else 0
+extern "C" int nntk_cuda_recurrent_cluster_h16_plan(const nntk_recurrent_args *r, int nb) {
+    int BM, SL; size_t smem;
+    if (!ht_config(r, nb, &BM, &SL, &smem) || !get_encode()) return 0;
+    CUtensorMap mu = {};
+    HtParams p = {};
+    p.C = r->H / 32;
+    const int clusters = 1;
+    cudaStream_t st = nntk_stream();
+    const int rc = (r->cell == 3) ? NNTK_HT_DISPATCH(3, true) : NNTK_HT_DISPATCH(4, true);
+    return rc == 0;
+}
+
+// Runs all T steps of one batch chunk in ONE launch.  *used = 0 when the shape / activations are not eligible.
+// xw_blocked: the projection was written in the blocked recurrent layout of nntk_cuda_gemm_tf32_ex.
+extern "C" int nntk_cuda_recurrent_cluster_h16(const nntk_recurrent_args *r, int nb, const float *xw, int xw_blocked, float *h,
+                                               float *c, float *out, int *used) {
+    *used = 0;
+    const int G = r->cell, H = r->H, T = r->T;
+    int BM, SL; size_t smem;
+    if (!ht_config(r, nb, &BM, &SL, &smem)) return 0;
+    const int C = H / 32;
     if ((((uintptr_t)h) | ((uintptr_t)out) | ((uintptr_t)xw) | ((uintptr_t)c)) & 15) return 0;
     EncodeTiledFn encode = get_encode();
     if (!encode) {
@@ -407,12 +463,9 @@ extern "C" int nntk_cuda_recurrent_cluster_h16(const nntk_recurrent_args *r, int
     p.B = nb; p.H = H; p.T = T; p.C = C; p.return_sequences = r->return_sequences;
     p.bh = ((G == 3) || r->v2) ? r->d_bh : nullptr;
     p.xw = xw; p.h_state = h; p.c_state = c; p.out = out;
+    p.xw_blocked = xw_blocked; p.row_blocks = (nb + 31) / 32;
     const int clusters = (nb + SL * BM - 1) / (SL * BM);
-    int rc;
-#define NNTK_HT(GG) (BM == 128 ? launch_ht<GG, 128, 2>(mu, p, clusters, smem, st) \
-                    : SL == 2 ? launch_ht<GG, 64, 2>(mu, p, clusters, smem, st) : launch_ht<GG, 64, 1>(mu, p, clusters, smem, st))
-    rc = (G == 3) ? NNTK_HT(3) : NNTK_HT(4);
-#undef NNTK_HT
+    int rc = (G == 3) ? NNTK_HT_DISPATCH(3, false) : NNTK_HT_DISPATCH(4, false);
     if (rc == 1) return 0;
     if (rc) return rc;
     *used = 1;
