@@ -44,9 +44,6 @@ __device__ __forceinline__ uint32_t ht_map(uint32_t saddr, uint32_t rank) {
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(d) : "r"(saddr), "r"(rank));
     return d;
 }
-__device__ __forceinline__ void ht_arrive_remote(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
-}
 __device__ __forceinline__ void ht_bulk_copy(uint32_t dst_cluster, uint32_t src_cta, uint32_t bytes, uint32_t mbar_cluster) {
     asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst_cluster), "r"(src_cta), "r"(bytes), "r"(mbar_cluster) : "memory");
@@ -57,6 +54,12 @@ __device__ __forceinline__ void ht_mma_f16(uint32_t tmem_d, uint64_t da, uint64_
         "setp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+// tcgen05.commit that arrives on the mbarrier at the SAME offset in every CTA of `mask` once the MMAs issued so far complete:
+// the hardware tells all peers "my A tile has been read" -- no software hop between MMA completion and the a_free arrivals
+__device__ __forceinline__ void ht_commit_multicast(uint64_t *bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"(mask) : "memory");
 }
 // K-major, SWIZZLE_64B shared-memory matrix descriptor: rows of 64 bytes, 8-row groups 512 bytes apart
 __device__ __forceinline__ uint64_t ht_desc(uint32_t saddr) {
@@ -123,25 +126,21 @@ recurrent_cluster_h16_kernel(const __grid_constant__ CUtensorMap map_u, HtParams
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
-        // ===== exchange engine: lane = 16 s + peer.  Two duties per (slice, peer), in time order:
+        // ===== exchange engine: lane = peer.  For every exchange e and, in the order the epilogue produces them, every slice s:
         //   h_ready[s] (the 8 epilogue warps have written the new h slice into my k-block)  -> push it to CTA `peer`
-        //   mma_done[s] (my MMA of step t has read my A tile)                              -> a_free arrival at CTA `peer`
         // This warp has no global-memory traffic of its own, so the generic->async proxy fence it executes before the copy
         // is cheap; in the epilogue threads the same fence waited for their outstanding xw loads (ncu: 12 % of the step).
-        const int s = lane >> 4, peer = lane & 15;
-        if (peer < C && s < HT_SLICES) {
-            const uint32_t my_kb = smem_u32(sA) + s * a_slice_bytes + rank * HT_KB_BYTES;
-            const uint32_t dst_kb = ht_map(my_kb, (uint32_t)peer);
-            const uint32_t dst_full = ht_map(smem_u32(a_full + s), (uint32_t)peer);
-            const uint32_t dst_free = ht_map(smem_u32(a_free + s), (uint32_t)peer);
+        // (The a_free arrivals are not software at all: the MMA issuer's multicast tcgen05.commit delivers them.)
+        const int peer = lane;
+        if (peer < C) {
             for (int e = 0; e < T; ++e) {
-                mbar_wait(h_ready + s, (uint32_t)(e & 1));
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                if (peer == (int)rank) mbar_arrive(a_full + s);
-                else ht_bulk_copy(dst_kb, my_kb, HT_KB_BYTES, dst_full);
-                if (e + 1 < T) {
-                    mbar_wait(mma_done + s, (uint32_t)(e & 1));
-                    ht_arrive_remote(dst_free);
+#pragma unroll
+                for (int s = 0; s < HT_SLICES; ++s) {
+                    const uint32_t my_kb = smem_u32(sA) + s * a_slice_bytes + rank * HT_KB_BYTES;
+                    mbar_wait(h_ready + s, (uint32_t)(e & 1));
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    if (peer == (int)rank) mbar_arrive(a_full + s);
+                    else ht_bulk_copy(ht_map(my_kb, (uint32_t)peer), my_kb, HT_KB_BYTES, ht_map(smem_u32(a_full + s), (uint32_t)peer));
                 }
             }
         }
@@ -165,6 +164,7 @@ recurrent_cluster_h16_kernel(const __grid_constant__ CUtensorMap map_u, HtParams
                         for (int k = 0; k < 2; ++k) ht_mma_f16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
                     }
                     tc_commit(mma_done + s);
+                    if (t + 1 < T) ht_commit_multicast(a_free + s, (uint16_t)((1u << C) - 1));
                 }
             }
         }
@@ -269,10 +269,12 @@ recurrent_cluster_h16_kernel(const __grid_constant__ CUtensorMap map_u, HtParams
                         h[s][u] = og * act_fast(S_TANH, 1.0f, c[s][u]);
                     }
                 }
-                // xw of the NEXT slice-step goes in flight now (xr is dead), under this slice's exchange
+                // exchange first (the other CTAs are waiting for it), then put the xw of the NEXT slice-step in flight (xr is dead
+                // now); issuing the 12 loads BEFORE the barrier try_wait / shared stores of the exchange queued those behind
+                // them in the LSU (ncu: 18 % of the step on an a_free wait that never spun)
+                if (t + 1 < T) exchange(s, t + 1);
                 if (s + 1 < HT_SLICES) load_xw(s + 1, t);
                 else if (t + 1 < T) load_xw(0, t + 1);
-                if (t + 1 < T) exchange(s, t + 1);
                 if (p.return_sequences) {
                     // h_t rows are 64-byte pieces of [B, T, H] rows: transposed through a 2 KB per-warp tile so that one store
                     // instruction covers 8 sequences x 64 contiguous bytes instead of 32 sequences x 16 bytes
