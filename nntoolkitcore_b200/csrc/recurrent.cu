@@ -422,8 +422,8 @@ static int recurrent_cluster_try(const nntk_recurrent_args *r, int nb, const flo
     return 0;
 }
 
-extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, const float *xw, float *h, float *c, float *out,
-                                      float *pp, int *used);   // recurrent_tc.cu
+extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, const float *xw, int xw_blocked, float *h, float *c,
+                                      float *out, float *pp, int *used);   // recurrent_tc.cu
 
 extern "C" int nntk_cuda_recurrent_cluster_tc(const nntk_recurrent_args *r, int nb, const float *xw, float *h, float *c,
                                               float *out, int *used);   // recurrent_cluster_tc.cu
@@ -440,7 +440,7 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     float *c = r->d_c ? r->d_c + (long long)b0 * H : nullptr;
     float *out = r->d_out + (long long)b0 * (r->return_sequences ? (long long)T * H : H);
     float *xw = work;
-    float *pp = work + (size_t)nb * T * GH;      // (a blocked xw may run into pp: the kernel that reads it does not use pp)
+    float *pp = work + (size_t)nb * T * GH;
     // 1. hoisted input projection: xw = x*W + b_i over all timesteps
     nntk_gemm_args g = {};
     g.d_A = x; g.a_slab_stride = 0; g.lda = r->in; g.batch = 1; g.rows = nb * T; g.N = GH; g.K = r->in;
@@ -462,12 +462,17 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     // the 32-sequence-blocked layout that kernel reads with fully coalesced row-per-lane accesses (gemm_tc.cu, c_blocked).
     int xw_blocked = 0;
     const bool h16 = mode == 1 && G != 1 && use_h16 && nb >= min_batch && nntk_cuda_recurrent_cluster_h16_plan(r, nb);
-    if (h16 && (((uintptr_t)xw) & 15) == 0) {
+    // The per-step tensor-core kernel profits even more: with the plain [B, T, G*H] layout one step touches B pieces 4 MB
+    // apart (C4: 4096 different pages per step -- no operand-traffic change moved its 52 us/step, this is what bound it).
+    // It is the planned path when neither cluster kernel can hold the shape (H > 256 or H % 32 != 0) and the batch is large.
+    const bool step_tc = mode == 1 && G != 1 && !h16 && nb > 256 && (H > 256 || (H & 31)) && (H & 3) == 0 && (GH & 31) == 0;
+    if ((h16 || step_tc) && (((uintptr_t)xw) & 15) == 0) {
         nntk_gemm_args gb = g;
         gb.batch = T; gb.rows = nb; gb.a_slab_stride = r->in; gb.lda = T * r->in;      // slab = timestep, row = sequence
         rc = nntk_cuda_gemm_tf32_ex(&gb, 1, 1);
         if (rc < 0) return rc;
         xw_blocked = rc == 0;
+        if (xw_blocked) pp = work + (size_t)((nb + 31) / 32 * 32) * T * GH;      // the blocked xw is rounded up to 32 sequences
     }
     if (!xw_blocked) {
         if (proj_mode != mode) nntk_cuda_set_math_mode(proj_mode);
@@ -488,7 +493,7 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
                 return NNTK_ERR_CUDA_;
             }
         }
-        if (nb >= min_batch) {
+        if (nb >= min_batch && !xw_blocked) {
             int used = 0;
             rc = nntk_cuda_recurrent_cluster_tc(r, nb, xw, h, c, out, &used);
             if (rc) return rc;
@@ -496,7 +501,7 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
         }
     }
     // 2a. small / medium batch: ONE persistent cluster kernel for all T steps (U resident in shared memory, DSMEM exchange)
-    {
+    if (!xw_blocked) {
         int used = 0;
         rc = recurrent_cluster_try(r, nb, xw, h, c, out, &used);
         if (rc) return rc;
@@ -506,9 +511,13 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     // 2b. large batch, TF32 mode: T tensor-core step kernels with the cell fused into the GEMM epilogue (recurrent_tc.cu)
     if (mode == 1 && G != 1) {
         int used = 0;
-        rc = nntk_cuda_recurrent_tc(r, nb, xw, h, c, out, pp, &used);
+        rc = nntk_cuda_recurrent_tc(r, nb, xw, xw_blocked, h, c, out, pp, &used);
         if (rc) return rc;
         if (used) goto carry_state;
+    }
+    if (xw_blocked) {
+        nntk_cuda_set_error(NNTK_ERR_CUDA_, "recurrent: the planned tensor-core kernel did not run on the blocked projection");
+        return NNTK_ERR_CUDA_;
     }
     {
     // 2c. large batch, fp32 mode: T fused FFMA step kernels

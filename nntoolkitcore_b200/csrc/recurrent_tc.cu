@@ -15,6 +15,7 @@
 // Operands are TF32 (A truncated by the tensor core and bias-compensated, see tc_common.cuh), accumulation and all gate
 // math fp32: 1e-3 parity class.  The fp32 (1e-5) mode never comes here.
 #include <stdlib.h>
+#include <cuda_fp16.h>
 #include "tc_common.cuh"
 
 namespace {
@@ -28,6 +29,7 @@ struct RtcParams {
     int a_t;                           // TMA coordinate of h_{t-1} along the time axis of map_a
     const float *bh;                   // permuted like the columns of Bt, or null
     const float *xw; long long ld_xw;  // row b: xw + b*ld_xw, original column order g*H + unit
+    int xw_blocked, row_blocks;        // xw_blocked: xw points at this step's [B/32][G*H/4][32][4] block (gemm_tc.cu c_blocked)
     const float *h_prev; long long ld_prev;
     float *h_next; long long ld_next;
     float *hr_next;                    // [B, H]: h_t rounded to nearest TF32 = the A operand of step t+1
@@ -60,7 +62,10 @@ __device__ __forceinline__ void tc_ld_32x8(uint32_t taddr, float (&r)[8]) {
     for (int i = 0; i < 8; ++i) r[i] = __uint_as_float(u[i]);
 }
 
-template <int G, int STAGES>
+// H16: operands are fp16 (kind::f16; a 128-byte stage row holds 64 k-elements instead of 32): with the default activations h is
+// bounded by 1, so fp16's 10-bit mantissa is exactly the TF32 operand precision while U and h cost half the L2 traffic -- the
+// per-step kernel re-reads U once per 128-row tile and was bound by exactly that (C4, B = 4096: 196 MB of operands per step).
+template <int G, int STAGES, bool H16>
 __global__ void __launch_bounds__(R_THREADS, 1)
 recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, RtcParams p) {
     using SL = RtcSmem<G, STAGES>;
@@ -99,15 +104,15 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t *sa = smem + stage * SL::STAGE_BYTES;
                     mbar_expect_tx(&full_bar[stage], SL::STAGE_BYTES);
-                    tma_load_3d(sa, &map_a, &full_bar[stage], kb * R_BK, p.a_t, m_t * R_BM);
-                    tma_load_2d(sa + SL::A_BYTES, &map_b, &full_bar[stage], kb * R_BK, n_t * BN);
+                    tma_load_3d(sa, &map_a, &full_bar[stage], kb * (H16 ? 2 * R_BK : R_BK), p.a_t, m_t * R_BM);
+                    tma_load_2d(sa + SL::A_BYTES, &map_b, &full_bar[stage], kb * (H16 ? 2 * R_BK : R_BK), n_t * BN);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(R_BM >> 4) << 24);
+            constexpr uint32_t idesc = (1u << 4) | (H16 ? 0u : ((2u << 7) | (2u << 10))) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(R_BM >> 4) << 24);
             int stage = 0; uint32_t phase = 0, it = 0;
             for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
                 const uint32_t buf = it & 1, use = it >> 1;
@@ -120,7 +125,10 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
                     const uint32_t sa = smem_u32(smem + stage * SL::STAGE_BYTES);
                     const uint64_t da = make_desc(sa), db = make_desc(sa + SL::A_BYTES);
 #pragma unroll
-                    for (int k = 0; k < R_BK / 8; ++k) tc_mma_tf32(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                    for (int k = 0; k < R_BK / 8; ++k) {
+                        if (H16) tc_mma_f16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                        else tc_mma_tf32(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                    }
                     tc_commit(&empty_bar[stage]);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -146,6 +154,8 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
             const long long rr = row_ok ? row : 0;
             const int ubase = n_t * R_UT + half * 32;          // first hidden unit of this thread
             const float *xw = p.xw + rr * p.ld_xw + ubase;
+            // blocked layout: float4 slot of (row, column n) = ((row / 32) * (G*H/4) + n / 4) * 32 + row % 32
+            const float4 *xwb = reinterpret_cast<const float4 *>(p.xw) + ((rr >> 5) * (long long)((G * p.H) >> 2) + (ubase >> 2)) * 32 + (rr & 31);
             const float *stp = (G == 4) ? p.c + rr * p.H + ubase : p.h_prev + rr * p.ld_prev + ubase;
             float *hn = p.h_next + rr * p.ld_next + ubase;
             float *hr = p.hr_next + rr * p.H + ubase;
@@ -158,7 +168,9 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
                     const bool ok = row_ok && ubase + u < p.H && !(p.dbg & 1);
 #pragma unroll
                     for (int g = 0; g < G; ++g)
-                        P.xv[g][v] = ok ? *reinterpret_cast<const float4 *>(xw + (long long)g * p.H + u) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        P.xv[g][v] = !ok ? make_float4(0.f, 0.f, 0.f, 0.f)
+                                         : p.xw_blocked ? __ldg(xwb + ((long long)g * (p.H >> 2) + (u >> 2)) * 32)
+                                                        : *reinterpret_cast<const float4 *>(xw + (long long)g * p.H + u);
                     P.st[v] = (ok && G != 1) ? *reinterpret_cast<const float4 *>(stp + u) : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
             };
@@ -210,7 +222,13 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
                     }
                     if (p.dbg & 2) { if (out[0] == 123.456f) hn[u] = out[1] + out[2] + out[3] + cn[0] + cn[1] + cn[2] + cn[3]; continue; }
                     *reinterpret_cast<float4 *>(hn + u) = make_float4(out[0], out[1], out[2], out[3]);
-                    *reinterpret_cast<float4 *>(hr + u) = make_float4(round_tf32(out[0]), round_tf32(out[1]), round_tf32(out[2]), round_tf32(out[3]));
+                    if (H16) {
+                        __half2 lo = __floats2half2_rn(out[0], out[1]), hi = __floats2half2_rn(out[2], out[3]);
+                        uint2 pk = make_uint2(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi));
+                        *reinterpret_cast<uint2 *>(reinterpret_cast<__half *>(p.hr_next) + rr * p.H + ubase + u) = pk;
+                    } else {
+                        *reinterpret_cast<float4 *>(hr + u) = make_float4(round_tf32(out[0]), round_tf32(out[1]), round_tf32(out[2]), round_tf32(out[3]));
+                    }
                     if (G == 4) *reinterpret_cast<float4 *>(cw + u) = make_float4(cn[0], cn[1], cn[2], cn[3]);
                 }
                 cur = nxt;
@@ -242,31 +260,49 @@ __global__ void pack_recurrent_weights_kernel(const float *__restrict__ U, const
     }
 }
 
+__global__ void pack_recurrent_weights_h16_kernel(const float *__restrict__ U, const float *__restrict__ bh, __half *__restrict__ Bt,
+                                                  float *__restrict__ bhp, int H, int G, int ldbt, int n_rows) {
+    const long long total = (long long)n_rows * ldbt;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int n = (int)(i / ldbt), k = (int)(i - (long long)n * ldbt);
+        const int j = n / (G * R_UT), r = n - j * G * R_UT, g = r / R_UT, u = r - g * R_UT;
+        const int unit = j * R_UT + u;
+        const bool ok = unit < H && k < H;
+        Bt[i] = __float2half_rn(ok ? __ldg(U + (long long)k * G * H + g * H + unit) : 0.0f);
+        if (k == 0 && bhp) bhp[n] = (unit < H && bh) ? bh[g * H + unit] : 0.0f;
+    }
+}
+__global__ void to_half_kernel(const float *__restrict__ in, __half *__restrict__ out, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        out[i] = __float2half_rn(in[i]);
+}
+
 float *g_rtc_scratch = nullptr;
 size_t g_rtc_floats = 0;
 
 }  // namespace
 
-template <int G, int STAGES>
+template <int G, int STAGES, bool H16>
 static int launch_rtc(const CUtensorMap &ma, const CUtensorMap &mb, const RtcParams &p, cudaStream_t st) {
     using SL = RtcSmem<G, STAGES>;
     static bool attr_done = false;
     if (!attr_done) {
-        NNTK_CUDA_TRY(cudaFuncSetAttribute(recurrent_tc_step_kernel<G, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::TOTAL));
+        NNTK_CUDA_TRY(cudaFuncSetAttribute(recurrent_tc_step_kernel<G, STAGES, H16>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::TOTAL));
         attr_done = true;
     }
     const int grid = p.total_tiles < nntk_cuda_sm_count() ? p.total_tiles : nntk_cuda_sm_count();
-    recurrent_tc_step_kernel<G, STAGES><<<grid, R_THREADS, SL::TOTAL, st>>>(ma, mb, p);
+    recurrent_tc_step_kernel<G, STAGES, H16><<<grid, R_THREADS, SL::TOTAL, st>>>(ma, mb, p);
     return 0;
 }
 
-static int encode_h_map(EncodeTiledFn encode, CUtensorMap *m, const float *base, int H, int n_t, long long t_stride,
-                        int rows, long long row_stride) {
+static int encode_h_map(EncodeTiledFn encode, CUtensorMap *m, const void *base, int H, int n_t, long long t_stride,
+                        int rows, long long row_stride, bool h16 = false) {
+    const int es = h16 ? 2 : 4;
     cuuint64_t dims[3] = {(cuuint64_t)H, (cuuint64_t)n_t, (cuuint64_t)rows};
-    cuuint64_t strides[2] = {(cuuint64_t)t_stride * 4, (cuuint64_t)row_stride * 4};
-    cuuint32_t box[3] = {R_BK, 1, R_BM};
+    cuuint64_t strides[2] = {(cuuint64_t)t_stride * es, (cuuint64_t)row_stride * es};
+    cuuint32_t box[3] = {(cuuint32_t)(h16 ? 2 * R_BK : R_BK), 1, R_BM};
     cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void *)base, dims, strides, box, estr,
+    CUresult r = encode(m, h16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void *)base, dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
@@ -279,8 +315,8 @@ static int encode_h_map(EncodeTiledFn encode, CUtensorMap *m, const float *base,
 // Runs all T steps of one batch chunk on the tensor cores.  *used = 0 when the shape is not eligible (caller falls back to
 // the fp32 step kernels).  xw: hoisted projection [nb, T, G*H]; h/c: state [nb, H]; pp: [4, nb, H] (exact ping-pong, then
 // the TF32-rounded ping-pong).
-extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, const float *xw, float *h, float *c, float *out,
-                                      float *pp, int *used) {
+extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, const float *xw, int xw_blocked, float *h, float *c,
+                                      float *out, float *pp, int *used) {
     *used = 0;
     const int G = r->cell, H = r->H, T = r->T;
     if ((H & 3) || T < 1 || nb < 1) return 0;
@@ -306,23 +342,37 @@ extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, cons
     float *Bt = g_rtc_scratch;
     float *bhp = g_rtc_scratch + (((size_t)n_rows * ldbt + 3) & ~(size_t)3);
     const bool add_bh = (G == 3) || r->v2;
+    // fp16 operands when h is bounded (default activations) and rows of halves stay 16-byte aligned
+    static int want_h16 = -1;
+    if (want_h16 < 0) { const char *e = getenv("NNTK_RTC_H16"); want_h16 = e ? atoi(e) : 1; }
+    const int SG = NNTK_ACT_SIGMOID, TH = NNTK_ACT_TANH;
+    const bool def = (G == 3) ? (r->act[0] == SG && r->act[1] == SG && r->act[2] == TH)
+                              : (r->act[0] == SG && r->act[1] == SG && r->act[2] == TH && r->act[3] == SG && r->act[4] == TH);
+    const bool h16 = want_h16 && def && (H % 8 == 0);
+    const int es = h16 ? 2 : 4;
     {
         long long total = (long long)n_rows * ldbt;
         int blocks = (int)((total + 255) / 256 < 2048 ? (total + 255) / 256 : 2048);
-        pack_recurrent_weights_kernel<<<blocks, 256, 0, st>>>(r->d_U, add_bh ? r->d_bh : nullptr, Bt, bhp, H, G, ldbt, n_rows);
+        if (h16) pack_recurrent_weights_h16_kernel<<<blocks, 256, 0, st>>>(r->d_U, add_bh ? r->d_bh : nullptr, reinterpret_cast<__half *>(Bt), bhp, H, G, ldbt, n_rows);
+        else pack_recurrent_weights_kernel<<<blocks, 256, 0, st>>>(r->d_U, add_bh ? r->d_bh : nullptr, Bt, bhp, H, G, ldbt, n_rows);
         NNTK_LAUNCH_CHECK("pack_recurrent_weights_kernel");
     }
     CUtensorMap m_state, m_hr, mb;
     int rc;
-    float *hr = pp + (size_t)2 * nb * H;   // rounded ping-pong [2][nb][H] behind the exact one
-    if ((rc = encode_h_map(encode, &m_state, h, H, 1, H, nb, H))) return rc;
-    if ((rc = encode_h_map(encode, &m_hr, hr, H, 2, (long long)nb * H, nb, H))) return rc;
+    float *hr = pp + (size_t)2 * nb * H;   // rounded ping-pong [2][nb][H] behind the exact one (fp16 mode: halves, same region)
+    if (h16) {
+        // step 0 reads h_0 like every other step: converted into slot 1 of the ping-pong ((t - 1) & 1 for t = 0)
+        const long long n = (long long)nb * H;
+        to_half_kernel<<<(unsigned)((n + 255) / 256 < 2048 ? (n + 255) / 256 : 2048), 256, 0, st>>>(h, reinterpret_cast<__half *>(hr) + n, n);
+        NNTK_LAUNCH_CHECK("to_half_kernel");
+    } else if ((rc = encode_h_map(encode, &m_state, h, H, 1, H, nb, H))) return rc;
+    if ((rc = encode_h_map(encode, &m_hr, hr, H, 2, (long long)nb * H, nb, H, h16))) return rc;
     {
         cuuint64_t dims[2] = {(cuuint64_t)ldbt, (cuuint64_t)n_rows};
-        cuuint64_t strides[1] = {(cuuint64_t)ldbt * 4};
-        cuuint32_t box[2] = {R_BK, (cuuint32_t)(G * R_UT)};
+        cuuint64_t strides[1] = {(cuuint64_t)ldbt * es};
+        cuuint32_t box[2] = {(cuuint32_t)(h16 ? 2 * R_BK : R_BK), (cuuint32_t)(G * R_UT)};
         cuuint32_t estr[2] = {1, 1};
-        CUresult cr = encode(&mb, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)Bt, dims, strides, box, estr,
+        CUresult cr = encode(&mb, h16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)Bt, dims, strides, box, estr,
                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (cr != CUDA_SUCCESS) {
@@ -332,16 +382,18 @@ extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, cons
     }
     RtcParams p;
     p.B = nb; p.H = H; p.n_tiles = n_tiles; p.m_tiles = (nb + R_BM - 1) / R_BM;
-    p.k_blocks = (H + R_BK - 1) / R_BK;
+    p.k_blocks = h16 ? (H + 2 * R_BK - 1) / (2 * R_BK) : (H + R_BK - 1) / R_BK;
     p.total_tiles = p.n_tiles * p.m_tiles;
     p.bh = add_bh ? bhp : nullptr;
-    p.ld_xw = (long long)T * G * H;
+    p.ld_xw = xw_blocked ? 0 : (long long)T * G * H;
+    p.xw_blocked = xw_blocked; p.row_blocks = (nb + 31) / 32;
     { const char *e = getenv("NNTK_RTC_DBG"); p.dbg = e ? atoi(e) : 0; }
     p.c = c;
     for (int i = 0; i < 5; ++i) { p.act[i] = r->act[i]; p.act_a[i] = r->act_a[i]; }
     for (int t = 0; t < T; ++t) {
         const CUtensorMap *ma;
-        if (t == 0) { ma = &m_state; p.a_t = 0; p.h_prev = h; p.ld_prev = H; p.comp = 1.0f + TF32_TRUNC_BIAS; }
+        if (t == 0 && h16) { ma = &m_hr; p.a_t = 1; p.h_prev = h; p.ld_prev = H; p.comp = 1.0f; }
+        else if (t == 0) { ma = &m_state; p.a_t = 0; p.h_prev = h; p.ld_prev = H; p.comp = 1.0f + TF32_TRUNC_BIAS; }
         else {
             ma = &m_hr; p.a_t = (t - 1) & 1; p.comp = 1.0f;
             if (r->return_sequences) { p.h_prev = out + (long long)(t - 1) * H; p.ld_prev = (long long)T * H; }
@@ -349,11 +401,12 @@ extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, cons
         }
         if (r->return_sequences) { p.h_next = out + (long long)t * H; p.ld_next = (long long)T * H; }
         else { p.h_next = pp + (size_t)(t & 1) * nb * H; p.ld_next = H; }
-        p.hr_next = hr + (size_t)(t & 1) * nb * H;
-        p.xw = xw + (long long)t * G * H;
-        if (G == 1) rc = launch_rtc<1, 6>(*ma, mb, p, st);
-        else if (G == 3) rc = launch_rtc<3, 4>(*ma, mb, p, st);
-        else rc = launch_rtc<4, 4>(*ma, mb, p, st);
+        p.hr_next = h16 ? reinterpret_cast<float *>(reinterpret_cast<__half *>(hr) + (size_t)(t & 1) * nb * H)
+                        : hr + (size_t)(t & 1) * nb * H;
+        p.xw = xw_blocked ? xw + (long long)t * p.row_blocks * 32 * G * H : xw + (long long)t * G * H;
+        if (G == 1) rc = launch_rtc<1, 6, false>(*ma, mb, p, st);
+        else if (G == 3) rc = h16 ? launch_rtc<3, 4, true>(*ma, mb, p, st) : launch_rtc<3, 4, false>(*ma, mb, p, st);
+        else rc = h16 ? launch_rtc<4, 4, true>(*ma, mb, p, st) : launch_rtc<4, 4, false>(*ma, mb, p, st);
         if (rc) return rc;
     }
     NNTK_LAUNCH_CHECK("recurrent_tc_step_kernel");
