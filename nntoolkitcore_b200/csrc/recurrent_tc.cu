@@ -62,7 +62,14 @@ __device__ __forceinline__ void tc_ld_32x8(uint32_t taddr, float (&r)[8]) {
     for (int i = 0; i < 8; ++i) r[i] = __uint_as_float(u[i]);
 }
 
-// H16: operands are fp16 (kind::f16; a 128-byte stage row holds 64 k-elements instead of 32): with the default activations h is
+// default gate activations compiled in when DEF (the run-time kind switch per call tripled the epilogue's instruction count;
+// ncu r1: the per-step kernel ran at 0.53 IPC on ~5000 instructions per thread per tile -- the epilogue, not TMA or MMA)
+template <bool DEF, int KIND>
+__device__ __forceinline__ float rt_act(const RtcParams &p, int slot, float x) {
+    return DEF ? act_fast(KIND, 1.0f, x) : act_fast(p.act[slot], p.act_a[slot], x);
+}
+
+// H16 (implies the default activations): operands are fp16 (kind::f16; a 128-byte stage row holds 64 k-elements instead of 32): with the default activations h is
 // bounded by 1, so fp16's 10-bit mantissa is exactly the TF32 operand precision while U and h cost half the L2 traffic -- the
 // per-step kernel re-reads U once per 128-row tile and was bound by exactly that (C4, B = 4096: 196 MB of operands per step).
 template <int G, int STAGES, bool H16>
@@ -205,17 +212,17 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
                         }
                         const float sv = (&cur.st[v].x)[e];
                         if (G == 3) {
-                            const float z = act_fast(p.act[0], p.act_a[0], x[0] + hu[0]);
-                            const float r = act_fast(p.act[1], p.act_a[1], x[1] + hu[1]);
-                            const float hh = act_fast(p.act[2], p.act_a[2], fmaf(r, hu[2], x[2]));
+                            const float z = rt_act<H16, NNTK_ACT_SIGMOID>(p, 0, x[0] + hu[0]);
+                            const float r = rt_act<H16, NNTK_ACT_SIGMOID>(p, 1, x[1] + hu[1]);
+                            const float hh = rt_act<H16, NNTK_ACT_TANH>(p, 2, fmaf(r, hu[2], x[2]));
                             out[e] = fmaf(z, sv - hh, hh);                   // (1 - z) hh + z h_{t-1}
                         } else if (G == 4) {
-                            const float ig = act_fast(p.act[0], p.act_a[0], x[0] + hu[0]);
-                            const float fg = act_fast(p.act[1], p.act_a[1], x[1] + hu[1]);
-                            const float gg = act_fast(p.act[2], p.act_a[2], x[2] + hu[2]);
-                            const float og = act_fast(p.act[3], p.act_a[3], x[3] + hu[3]);
+                            const float ig = rt_act<H16, NNTK_ACT_SIGMOID>(p, 0, x[0] + hu[0]);
+                            const float fg = rt_act<H16, NNTK_ACT_SIGMOID>(p, 1, x[1] + hu[1]);
+                            const float gg = rt_act<H16, NNTK_ACT_TANH>(p, 2, x[2] + hu[2]);
+                            const float og = rt_act<H16, NNTK_ACT_SIGMOID>(p, 3, x[3] + hu[3]);
                             cn[e] = fmaf(fg, sv, ig * gg);
-                            out[e] = og * act_fast(p.act[4], p.act_a[4], cn[e]);
+                            out[e] = og * rt_act<H16, NNTK_ACT_TANH>(p, 4, cn[e]);
                         } else {
                             out[e] = act_fast(p.act[0], p.act_a[0], hu[0] + x[0]);
                         }
