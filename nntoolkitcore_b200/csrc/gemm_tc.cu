@@ -14,6 +14,7 @@
 // Conv1d needs no im2col: with channels-last input the im2col row x is the contiguous span in[x*stride : x*stride+K, :],
 // so A is a 3-D TMA tensor {K*Cin, T_out, batch} with OVERLAPPING rows (row stride = stride*Cin floats).
 // Weights are re-laid K-major (Bt[N][K]) per call -- they may legally change between Applies.
+#include <cuda_bf16.h>
 #include "tc_common.cuh"
 
 namespace {
@@ -48,7 +49,9 @@ struct SmemLayout {
     static constexpr int TOTAL = STG_OFFSET + 8 * 2048 + 1024;                  // + alignment slack
 };
 
-template <int BN, int STAGES, bool FAST>
+// BF16 = true: the operands are bf16 (kind::f16, K = 16 per MMA, 64 elements per 128-byte k-block) -- the 3xbf16 split mode
+// of the hoisted recurrent projection.  Byte-wise the stages, swizzle and descriptors are the same as for tf32.
+template <int BN, int STAGES, bool FAST, bool BF16>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, TcParams p) {
     using SL = SmemLayout<BN, STAGES>;
@@ -62,6 +65,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     constexpr uint32_t TMEM_COLS = 2 * BN;        // two accumulator buffers (256 or 512 columns: powers of two)
+    constexpr int BKE = BF16 ? 2 * BK : BK;       // elements per 128-byte k-block
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
@@ -96,8 +100,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                     // two small passes come FIRST: the tensor core's fp32 accumulate truncates (measured: error grows
                     // with the number of accumulation steps at full magnitude), so they run while the sum is still tiny.
                     const int pass = kb / p.kb_pass, akb = kb - pass * p.kb_pass;
-                    tma_load_4d(sa, &map_a, &full_bar[stage], akb * BK, m_t * BM, slab, pass == 1 ? 1 : 0);
-                    tma_load_2d(sa + SL::A_BYTES, &map_b, &full_bar[stage], kb * BK, n_t * BN);
+                    tma_load_4d(sa, &map_a, &full_bar[stage], akb * BKE, m_t * BM, slab, pass == 1 ? 1 : 0);
+                    tma_load_2d(sa + SL::A_BYTES, &map_b, &full_bar[stage], kb * BKE, n_t * BN);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -106,7 +110,9 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         // ===== MMA issuer =====
         if (lane == 0) {
             // instruction descriptor: D=f32, A=B=tf32, both K-major, N>>3 at bit 17, M>>4 at bit 24
-            constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+            // (bf16: a/b format 1, kind::f16)
+            constexpr uint32_t fmt = BF16 ? 1u : 2u;
+            constexpr uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
             int stage = 0; uint32_t phase = 0;
             uint32_t it = 0;
             for (long long tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
@@ -122,7 +128,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k) {
                         // advance 32 bytes along K inside the 128-byte swizzle atom: +2 in the (addr >> 4) field
-                        tc_mma_tf32(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                        if (BF16) tc_mma_f16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                        else tc_mma_tf32(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
                     }
                     tc_commit(&empty_bar[stage]);               // smem stage free once these MMAs have read it
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -300,6 +307,42 @@ __global__ void split_tf32_kernel(const float *__restrict__ x, float *__restrict
     }
 }
 
+// 3xbf16 split: hi = rn_bf16(x), lo = rn_bf16(x - hi) (x - hi is exact in fp32; what is dropped is below 2^-17 |x|).
+__device__ __forceinline__ void bf16_split(float v, __nv_bfloat16 &h, __nv_bfloat16 &l) {
+    h = __float2bfloat16_rn(v);
+    l = __float2bfloat16_rn(v - __bfloat162float(h));
+}
+__global__ void split_bf16_kernel(const float *__restrict__ x, __nv_bfloat16 *__restrict__ hi, __nv_bfloat16 *__restrict__ lo, long long n) {
+    const long long n4 = n >> 2, stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        const float4 v = __ldg(reinterpret_cast<const float4 *>(x) + i);
+        __nv_bfloat16 h[4], l[4];
+        bf16_split(v.x, h[0], l[0]); bf16_split(v.y, h[1], l[1]); bf16_split(v.z, h[2], l[2]); bf16_split(v.w, h[3], l[3]);
+        reinterpret_cast<uint2 *>(hi)[i] = *reinterpret_cast<const uint2 *>(h);
+        reinterpret_cast<uint2 *>(lo)[i] = *reinterpret_cast<const uint2 *>(l);
+    }
+    for (long long i = (n4 << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) bf16_split(x[i], hi[i], lo[i]);
+}
+// Bt[n] = [lo | hi | hi] of B[:, n] in bf16, each part kpad (multiple of 64) wide, zero tail
+__global__ void transpose_weights_bf16_kernel(const float *__restrict__ B, __nv_bfloat16 *__restrict__ Bt, int K, int N, int kpad, int ldbt) {
+    __shared__ float tile[32][33];
+    const int k0 = blockIdx.x * 32, n0 = blockIdx.y * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int k = k0 + i, n = n0 + threadIdx.x;
+        tile[i][threadIdx.x] = (k < K && n < N) ? B[(long long)k * N + n] : 0.0f;
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int n = n0 + i, k = k0 + threadIdx.x;
+        if (n < N && k < kpad) {
+            __nv_bfloat16 h, l;
+            bf16_split(tile[threadIdx.x][i], h, l);
+            __nv_bfloat16 *row = Bt + (long long)n * ldbt;
+            row[k] = l; row[kpad + k] = h; row[2 * kpad + k] = h;
+        }
+    }
+}
+
 // scale[n], shift[n] such that act(acc*scale + shift) == act(BN(acc + bias)) up to rounding; the scale also carries the
 // compensation of the A-operand truncation bias (see TF32_TRUNC_BIAS).
 __global__ void fold_epilogue_kernel(const float *bias, const float *bn, float eps, int N, float *scale, float *shift, float comp) {
@@ -323,16 +366,16 @@ size_t g_split_floats = 0;
 
 }  // namespace
 
-template <int BN, int STAGES, bool FAST>
+template <int BN, int STAGES, bool FAST, bool BF16 = false>
 static int launch_tc(const CUtensorMap &ma, const CUtensorMap &mb, TcParams &p, cudaStream_t st) {
     using SL = SmemLayout<BN, STAGES>;
     static bool attr_done = false;
     if (!attr_done) {
-        NNTK_CUDA_TRY(cudaFuncSetAttribute(gemm_tf32_kernel<BN, STAGES, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::TOTAL));
+        NNTK_CUDA_TRY(cudaFuncSetAttribute(gemm_tf32_kernel<BN, STAGES, FAST, BF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::TOTAL));
         attr_done = true;
     }
     long long grid = p.total_tiles < nntk_cuda_sm_count() ? p.total_tiles : nntk_cuda_sm_count();
-    gemm_tf32_kernel<BN, STAGES, FAST><<<(unsigned)grid, NUM_THREADS, SL::TOTAL, st>>>(ma, mb, p);
+    gemm_tf32_kernel<BN, STAGES, FAST, BF16><<<(unsigned)grid, NUM_THREADS, SL::TOTAL, st>>>(ma, mb, p);
     NNTK_LAUNCH_CHECK("gemm_tf32_kernel");
     return 0;
 }
@@ -357,8 +400,15 @@ extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_
     }
     cudaStream_t st = nntk_stream();
     const int K = a->K, N = a->N;
+    // split: 0 single TF32 pass, 1 3xTF32 (fp32 operands split into tf32 hi/lo), 2 3xbf16 (bf16 hi/lo at twice the tensor
+    // rate and half the operand bytes; ~2^-16 relative operand error, used by the recurrent projection of the TF32 mode)
+    const bool bf = split == 2;
+    const bool fast = c_blocked || ((N % 32 == 0) && (a->ldc % 4 == 0) && (a->c_slab_stride % 4 == 0) && ((((uintptr_t)a->d_C) & 15) == 0));
+    if (bf && (!fast || (a->lda & 7) || (a->a_slab_stride & 7))) return 1;
+    const int BKE = bf ? 2 * BK : BK;           // elements per k-block
+    const size_t esz = bf ? 2 : 4;
     const int parts = split ? 3 : 1;
-    const int kpad = split ? ((K + BK - 1) / BK) * BK : ((K + 3) & ~3);
+    const int kpad = split ? ((K + BKE - 1) / BKE) * BKE : ((K + 3) & ~3);
     const int ldbt = parts * kpad;
     const size_t need = (size_t)N * ldbt + 2 * (size_t)N + 64;
     if (need > g_scratch_floats) {
@@ -372,19 +422,20 @@ extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_
     float *scale = g_scratch + (((size_t)N * ldbt + 3) & ~(size_t)3);
     float *shift = scale + N;
     dim3 tb(32, 8), tg((kpad + 31) / 32, (N + 31) / 32);
-    transpose_weights_kernel<<<tg, tb, 0, st>>>(a->d_B, Bt, K, N, kpad, ldbt, parts);
+    if (bf) transpose_weights_bf16_kernel<<<tg, tb, 0, st>>>(a->d_B, reinterpret_cast<__nv_bfloat16 *>(Bt), K, N, kpad, ldbt);
+    else transpose_weights_kernel<<<tg, tb, 0, st>>>(a->d_B, Bt, K, N, kpad, ldbt, parts);
     fold_epilogue_kernel<<<(N + 127) / 128, 128, 0, st>>>(a->d_bias, a->d_bn, a->bn_eps, N, scale, shift,
                                                           split ? 1.0f : 1.0f + TF32_TRUNC_BIAS);
     NNTK_LAUNCH_CHECK("gemm_tf32 prologue");
 
-    // slab stride of A as the tensor map sees it; in split mode the lo copy sits `batch` slabs behind the hi copy
+    // slab stride of A as the tensor map sees it (elements); in split mode the lo copy sits lo_off elements behind the hi copy
     const long long slab_floats = a->batch > 1 ? a->a_slab_stride : (long long)a->rows * a->lda;
-    const float *A = a->d_A;
-    long long lo_off = 4;
+    const void *A = a->d_A;
+    long long lo_off = 8;
     if (split) {
         const long long extent = (long long)(a->batch - 1) * slab_floats + (long long)(a->rows - 1) * a->lda + K;
         lo_off = (extent + 63) & ~63LL;
-        const size_t want = (size_t)(lo_off + extent + 64);
+        const size_t want = ((size_t)(lo_off + extent + 64) * esz + 3) / 4;
         if (want > g_split_floats) {
             NNTK_CUDA_TRY(cudaStreamSynchronize(st));
             if (g_split) cudaFree(g_split);
@@ -395,22 +446,28 @@ extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_
         long long blocks = (extent / 4 + 255) / 256;
         if (blocks > 148 * 16) blocks = 148 * 16;
         if (blocks < 1) blocks = 1;
-        split_tf32_kernel<<<(unsigned)blocks, 256, 0, st>>>(a->d_A, g_split, g_split + lo_off, extent);
-        NNTK_LAUNCH_CHECK("split_tf32_kernel");
+        if (bf) {
+            __nv_bfloat16 *hi = reinterpret_cast<__nv_bfloat16 *>(g_split);
+            split_bf16_kernel<<<(unsigned)blocks, 256, 0, st>>>(a->d_A, hi, hi + lo_off, extent);
+        } else {
+            split_tf32_kernel<<<(unsigned)blocks, 256, 0, st>>>(a->d_A, g_split, g_split + lo_off, extent);
+        }
+        NNTK_LAUNCH_CHECK("split kernel");
         A = g_split;
     }
 
     const int BN = N > 128 ? 256 : 128;
+    const CUtensorMapDataType dt = bf ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
     CUtensorMap ma, mb;
     {
-        // {K, rows, slabs, parts}: parts = hi / lo copies of A in split mode (lo_off floats apart)
+        // {K, rows, slabs, parts}: parts = hi / lo copies of A in split mode (lo_off elements apart)
         cuuint64_t dims[4] = {(cuuint64_t)K, (cuuint64_t)a->rows, (cuuint64_t)a->batch, (cuuint64_t)(split ? 2 : 1)};
-        cuuint64_t slab_bytes = (cuuint64_t)slab_floats * 4;
+        cuuint64_t slab_bytes = (cuuint64_t)slab_floats * esz;
         if (slab_bytes == 0) slab_bytes = 16;
-        cuuint64_t strides[3] = {(cuuint64_t)a->lda * 4, slab_bytes, (cuuint64_t)lo_off * 4};
-        cuuint32_t box[4] = {BK, BM, 1, 1};
+        cuuint64_t strides[3] = {(cuuint64_t)a->lda * esz, slab_bytes, (cuuint64_t)lo_off * esz};
+        cuuint32_t box[4] = {(cuuint32_t)BKE, BM, 1, 1};
         cuuint32_t estr[4] = {1, 1, 1, 1};
-        CUresult r = encode(&ma, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void *)A, dims, strides, box, estr,
+        CUresult r = encode(&ma, dt, 4, const_cast<void *>(A), dims, strides, box, estr,
                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) {
@@ -420,10 +477,10 @@ extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_
     }
     {
         cuuint64_t dims[2] = {(cuuint64_t)ldbt, (cuuint64_t)N};
-        cuuint64_t strides[1] = {(cuuint64_t)ldbt * 4};
-        cuuint32_t box[2] = {BK, (cuuint32_t)BN};
+        cuuint64_t strides[1] = {(cuuint64_t)ldbt * esz};
+        cuuint32_t box[2] = {(cuuint32_t)BKE, (cuuint32_t)BN};
         cuuint32_t estr[2] = {1, 1};
-        CUresult r = encode(&mb, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)Bt, dims, strides, box, estr,
+        CUresult r = encode(&mb, dt, 2, (void *)Bt, dims, strides, box, estr,
                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) {
@@ -435,7 +492,7 @@ extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_
     p.N = N;
     p.n_tiles = (N + BN - 1) / BN;
     p.m_tiles_per_slab = (a->rows + BM - 1) / BM;
-    p.kb_pass = (K + BK - 1) / BK;
+    p.kb_pass = (K + BKE - 1) / BKE;
     p.k_blocks = parts * p.kb_pass;
     p.c_blocked = c_blocked; p.row_blocks = (a->rows + 31) / 32;
     p.total_tiles = (long long)p.n_tiles * p.m_tiles_per_slab * a->batch;
@@ -443,7 +500,7 @@ extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_
     p.C = a->d_C; p.c_slab = a->c_slab_stride; p.ldc = a->ldc;
     p.scale = scale; p.shift = shift; p.act = a->act; p.act_a = a->act_a;
     // FAST epilogue: whole 32-column chunks and 16-byte aligned output rows (every BASELINE shape except the 12-wide TDD)
-    const bool fast = c_blocked || ((N % 32 == 0) && (a->ldc % 4 == 0) && (a->c_slab_stride % 4 == 0) && ((((uintptr_t)a->d_C) & 15) == 0));
+    if (bf) return BN == 256 ? launch_tc<256, 4, true, true>(ma, mb, p, st) : launch_tc<128, 6, true, true>(ma, mb, p, st);
     if (BN == 256) return fast ? launch_tc<256, 4, true>(ma, mb, p, st) : launch_tc<256, 4, false>(ma, mb, p, st);
     return fast ? launch_tc<128, 6, true>(ma, mb, p, st) : launch_tc<128, 6, false>(ma, mb, p, st);
 }

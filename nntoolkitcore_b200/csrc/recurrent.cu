@@ -469,7 +469,12 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     if ((h16 || step_tc) && (((uintptr_t)xw) & 15) == 0) {
         nntk_gemm_args gb = g;
         gb.batch = T; gb.rows = nb; gb.a_slab_stride = r->in; gb.lda = T * r->in;      // slab = timestep, row = sequence
-        rc = nntk_cuda_gemm_tf32_ex(&gb, 1, 1);
+        // 3xbf16 first (bf16 hi/lo split: ~2^-16 operand error, twice the tensor rate and half the operand bytes of 3xTF32);
+        // shapes its 2-byte pitch rules exclude fall back to 3xTF32
+        static int proj_bf16 = -1;
+        if (proj_bf16 < 0) { const char *e = getenv("NNTK_PROJ_BF16X3"); proj_bf16 = e ? atoi(e) : 1; }
+        rc = proj_bf16 ? nntk_cuda_gemm_tf32_ex(&gb, 2, 1) : 1;
+        if (rc == 1) rc = nntk_cuda_gemm_tf32_ex(&gb, 1, 1);
         if (rc < 0) return rc;
         xw_blocked = rc == 0;
         if (xw_blocked) pp = work + (size_t)((nb + 31) / 32 * 32) * T * GH;      // the blocked xw is rounded up to 32 sequences
