@@ -81,6 +81,24 @@ typedef struct {
 /* d_in [n_clips, input_size] -> d_out [n_clips, ntime, nfreq] */
 int nntk_cuda_spectrogram(const nntk_spectrogram_args *a, const float *d_in, float *d_out, int n_clips);
 
+/* K1 with the log-mel epilogue (signal/log_mel_spectrogram.c:33-38 in one kernel).
+ * The mel table is passed as a per-lane work list: entry (iter, lane) = {packed, weight}; packed = 8 * slot(bin) |
+ * band << 15 | last << 31 with slot(k) = k + k / 16 (the kernel's conflict-free parking order of the spectrum).  A lane
+ * accumulates weight * spectrum[bin] over consecutive entries and, at an entry flagged `last`, emits its sum as mel band
+ * `band` and restarts.  The host balances the ~2 non-zeros per bin over the 32 lanes and orders them against bank conflicts. */
+typedef struct {
+    int n_mels;
+    int n_iter;             /* entries per lane */
+    const void *d_entries;  /* [n_iter][32] x 8 bytes */
+    float log_offset;       /* 1.5849e-13f, log_mel_spectrogram.c:36 */
+} nntk_mel_args;
+/* d_in [n_clips, input_size] -> d_out [n_clips, ntime, n_mels].  Returns 1 (nothing enqueued) when the fused kernel does not
+ * cover the shape (nfft != 512, more than 384 bands): the caller then runs spectrogram -> GEMM -> nntk_cuda_log_offset. */
+int nntk_cuda_log_mel_spectrogram(const nntk_spectrogram_args *a, const nntk_mel_args *m, const float *d_in, float *d_out,
+                                  int n_clips);
+/* d_out[i] = logf(d_in[i] + offset)   (op_vec_add_sc + op_vec_log, log_mel_spectrogram.c:36-37) */
+int nntk_cuda_log_offset(const float *d_in, float *d_out, long long n, float offset);
+
 /* ---- K5: element-wise --------------------------------------------------------------------------------------------- */
 /* d_params = gamma|beta|mean|var (4*C floats); rows x C elements; layers/batch_norm.c:140-163 */
 int nntk_cuda_batch_norm(const float *d_params, int C, float eps, const float *d_in, float *d_out, long long rows);

@@ -18,6 +18,7 @@
 
 #include <stddef.h>
 #include "signal/spectrogram.h"
+#include "signal/log_mel_spectrogram.h"
 #include "layers/activation_default.h"
 #include "layers/batch_norm.h"
 #include "layers/conv_1d.h"
@@ -82,6 +83,8 @@ int NNTKResetState(void *recurrent_layer);
 /* ---- batched forwards ------------------------------------------------------------------------------------------- */
 /* [n_clips, input_size] -> [n_clips, ntime_series, nfreq] */
 int SpectrogramApplyBatch(Spectrogram filter, const float *input, float *output, int n_clips);
+/* [n_clips, input_size] -> [n_clips, ntime_series, n_mels]; one fused kernel for nfft == 512 */
+int LogMelSpectrogramApplyBatch(LogMelSpectrogram filter, const float *input, float *output, int n_clips);
 /* [batch, count, C] -> same */
 int BatchNormApplyInferenceBatch(BatchNorm filter, const float *input, float *output, int batch);
 /* `batch` repetitions of the activation's own size */

@@ -18,6 +18,10 @@ class SpectrogramConfig(C.Structure):
                 ("nfreq", c_int), ("ntime_series", c_int), ("fft_normalization_factor", c_float)]
 
 
+class MelFilterBankConfig(C.Structure):
+    _fields_ = [("n_mels", c_int), ("n_fft", c_int), ("sample_rate", c_int), ("lower_hz", c_float), ("upper_hz", c_float)]
+
+
 class BatchNormWeights(C.Structure):
     _fields_ = [("gamma", FP), ("beta", FP), ("moving_mean", FP), ("moving_variance", FP)]
 
@@ -91,6 +95,14 @@ REFERENCE_API = {
     "SpectrogramSetScaleFactor": (None, [H, c_float]),
     "SpectrogramApply": (None, [H, c_void_p, c_void_p]),
     "SpectrogramDestroy": (None, [H]),
+    # signal/mel_filterbank.h, signal/log_mel_spectrogram.h
+    "MelFilterBankConfigCreate": (MelFilterBankConfig, [c_int, c_int, c_int, c_float, c_float]),
+    "MelFilterBankCreate": (H, [MelFilterBankConfig]),
+    "MelFilterBankApply": (None, [H, c_void_p, c_void_p, c_int]),
+    "MelFilterBankDestroy": (None, [H]),
+    "LogMelSpectrogramCreate": (H, [H, MelFilterBankConfig]),
+    "LogMelSpectrogramApply": (None, [H, c_void_p, c_void_p]),
+    "LogMelSpectrogramDestroy": (None, [H]),
     # layers/activation*.h
     "ActivationFunctionCreate": (H, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "ActivationFunctionCreateIdentity": (H, [c_int]), "ActivationFunctionCreateSigmoid": (H, [c_int]),
@@ -144,6 +156,7 @@ EXT_API = {
     "NNTKWeightsFreeze": (c_int, [c_void_p]), "NNTKWeightsUnfreeze": (c_int, [c_void_p]),
     "NNTKResetState": (c_int, [c_void_p]),
     "SpectrogramApplyBatch": (c_int, [H, c_void_p, c_void_p, c_int]),
+    "LogMelSpectrogramApplyBatch": (c_int, [H, c_void_p, c_void_p, c_int]),
     "BatchNormApplyInferenceBatch": (c_int, [H, c_void_p, c_void_p, c_int]),
     "ActivationFunctionApplyBatch": (c_int, [H, c_void_p, c_void_p, c_int]),
     "Conv1dApplyInferenceBatch": (c_int, [H, c_void_p, c_void_p, c_int]),
@@ -165,6 +178,7 @@ SHIM_SYMBOLS = [
     "nntk_cuda_math_mode", "nntk_cuda_sm_count", "nntk_cuda_malloc", "nntk_cuda_free", "nntk_cuda_host_alloc",
     "nntk_cuda_host_free", "nntk_cuda_h2d", "nntk_cuda_d2h", "nntk_cuda_d2d", "nntk_cuda_memset",
     "nntk_cuda_is_device_ptr", "nntk_cuda_workspace", "nntk_cuda_staged_run", "nntk_cuda_spectrogram",
+    "nntk_cuda_log_mel_spectrogram", "nntk_cuda_log_offset",
     "nntk_cuda_batch_norm", "nntk_cuda_activation", "nntk_cuda_gemm", "nntk_cuda_pack_conv_weights",
     "nntk_cuda_pack_conv_weights_padded", "nntk_cuda_pad_channels",
     "nntk_cuda_recurrent_workspace", "nntk_cuda_recurrent",

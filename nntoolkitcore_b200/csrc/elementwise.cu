@@ -202,3 +202,25 @@ extern "C" int nntk_cuda_activation(int kind, float relu_a, int vector_size, con
     NNTK_LAUNCH_CHECK("activation_kernel");
     return 0;
 }
+
+// out = logf(in + offset): the tail of the unfused log-mel chain (signal/log_mel_spectrogram.c:36-37)
+namespace {
+__global__ void __launch_bounds__(256) log_offset_kernel(const float *__restrict__ in, float *__restrict__ out, long long n,
+                                                         float offset) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = logf(in[i] + offset);
+}
+}  // namespace
+
+extern "C" int nntk_cuda_log_offset(const float *d_in, float *d_out, long long n, float offset) {
+    int rc = nntk_cuda_ensure_init();
+    if (rc) return rc;
+    if (!d_in || !d_out || n < 0) {
+        nntk_cuda_set_error(NNTK_ERR_ARG_, "log_offset: bad arguments");
+        return NNTK_ERR_ARG_;
+    }
+    if (n == 0) return 0;
+    log_offset_kernel<<<grid_for(n, 256), 256, 0, nntk_stream()>>>(d_in, d_out, n, offset);
+    NNTK_LAUNCH_CHECK("log_offset_kernel");
+    return 0;
+}

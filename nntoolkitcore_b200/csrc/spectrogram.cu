@@ -35,6 +35,8 @@ struct SpecParams {
     float psd_edge;     // PSD bins 0, nfreq-1: norm^2 * 0.25 / scale
     int mode;           // 0 magnitude, 1 PSD (generic kernel only; the 512 kernel is templated on it)
     int in_vec_ok;      // input base pointer 16-byte aligned
+    int n_mels, mel_iter;   // log-mel epilogue (MEL kernels only): bands, work-list entries per lane
+    float log_offset;
 };
 
 __device__ __forceinline__ float sqrt_approx(float x) {
@@ -110,10 +112,14 @@ __device__ __forceinline__ void tile_load_async(const SpecParams &p, const TileG
 // buffer, walks tiles (gw, gw + n_warps, ...) of SPEC_FW frames and never meets a CTA-wide barrier, so the warps of an SM
 // drift apart and one warp's shared-memory exchange overlaps another's butterflies.
 // Shared memory layout: [SPEC_WARPS][2][in_cap] floats | SPEC_WARPS x 656 float2 | [SPEC_WARPS][2] mbarriers.
-template <bool FULLWIN, int MODE>
+// MEL = true (row f1, signal/log_mel_spectrogram.c:33-38): instead of storing the 257 bins, the warp parks the two frames'
+// spectra in its (idle) exchange buffer as (a, b) pairs, every lane walks its share of the mel table's non-zeros
+// (`mel`: [mel_iter][32] entries {bin | last << 9 | band << 10, weight}, balanced on the host), emits
+// log(sum + log_offset) per band, and the warp stores 2 x n_mels contiguous floats.  The spectrogram never reaches HBM.
+template <bool FULLWIN, int MODE, bool MEL>
 __global__ void __launch_bounds__(SPEC_THREADS, 2)
 spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const float2 *__restrict__ tw512,
-                      const float *__restrict__ in, float *__restrict__ out) {
+                      const float *__restrict__ in, float *__restrict__ out, const uint2 *__restrict__ mel) {
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     float *s_in = smem + warp * 2 * p.in_cap;
@@ -221,6 +227,49 @@ spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const floa
 #pragma unroll
                 for (int slot = 0; slot < 9; ++slot) { pa[slot] = -pa[slot]; pb[slot] = -pb[slot]; }
             }
+            if (MEL) {
+                // the exchange buffer is idle here (its last readers passed the __syncwarp after spec_xchg2_load)
+                // parked spectra: bin k at slot k + k / 16 as (frame a, frame b) -- with the skew the lanes' bins c + 64 j hit
+                // 16 different bank pairs per half-warp (c1 is the identity up to the swaps 1 <-> 16, 9 <-> 24)
+                float2 *mg = sx;
+                float2 *so = sx + 280;                                  // [n_mels] raw band sums (a, b)
+#pragma unroll
+                for (int slot = 0; slot < 8; ++slot) {
+                    const int k = 64 * (slot & 3) + (slot < 4 ? c1 : c2);
+                    mg[k + (k >> 4)] = make_float2(pa[slot], pb[slot]);
+                }
+                if (l0) mg[256 + 16] = make_float2(pa[8], pb[8]);
+                __syncwarp();
+                float acc_a = 0.0f, acc_b = 0.0f;
+                const uint2 *e = mel + lane;
+                const char *mgb = reinterpret_cast<const char *>(mg);
+                char *sob = reinterpret_cast<char *>(so);
+                // The walk only accumulates and parks raw band sums (a flagged entry is one predicated store): the lanes'
+                // bands end at different iterations, so a logf inside the loop would run -- for the whole warp -- on nearly
+                // every iteration (first version: 31 iterations cost 2.3x the FFT itself).  The log is taken in the store loop.
+#pragma unroll 4
+                for (int i = 0; i < p.mel_iter; ++i) {
+                    const uint2 en = __ldg(e + 32 * i);
+                    const float2 m = *reinterpret_cast<const float2 *>(mgb + (en.x & 0xff8u));
+                    acc_a = fmaf(__uint_as_float(en.y), m.x, acc_a);
+                    acc_b = fmaf(__uint_as_float(en.y), m.y, acc_b);
+                    if ((int)en.x < 0) {
+                        *reinterpret_cast<float2 *>(sob + ((en.x >> 12) & 0x7fff8u)) = make_float2(acc_a, acc_b);
+                        acc_a = acc_b = 0.0f;
+                    }
+                }
+                __syncwarp();
+                float *dst = out + ((long long)g.clip * p.ntime + f0 + fa) * p.n_mels;
+                for (int i = lane; i < p.n_mels; i += 32) {
+                    const float2 v = so[i];
+                    // MUFU log2 (2 instructions; absolute error < 6e-6 on |log| <= 30, inside the 1e-5 contract) -- logf's
+                    // ~22-instruction expansion was 200 of the epilogue's ~550 instructions per frame pair
+                    dst[i] = __logf(v.x + p.log_offset);
+                    if (has_b) dst[p.n_mels + i] = __logf(v.y + p.log_offset);
+                }
+                __syncwarp();   // before the next pair's exchange-1 stores overwrite mg / so
+                continue;
+            }
 #pragma unroll
             for (int slot = 0; slot < 8; ++slot) {
                 float *dst = (slot < 4 ? ra1 : ra2) + 64 * (slot & 3);
@@ -307,7 +356,24 @@ spectrogram_generic_kernel(SpecParams p, int nfft, int log2n, const float *__res
 
 }  // namespace
 
+static int spectrogram_run(const nntk_spectrogram_args *a, const nntk_mel_args *m, const float *d_in, float *d_out, int n_clips);
+
 extern "C" int nntk_cuda_spectrogram(const nntk_spectrogram_args *a, const float *d_in, float *d_out, int n_clips) {
+    return spectrogram_run(a, nullptr, d_in, d_out, n_clips);
+}
+
+extern "C" int nntk_cuda_log_mel_spectrogram(const nntk_spectrogram_args *a, const nntk_mel_args *m, const float *d_in,
+                                             float *d_out, int n_clips) {
+    if (!m || !m->d_entries || m->n_mels < 1 || m->n_iter < 1) {
+        nntk_cuda_set_error(NNTK_ERR_ARG_, "log_mel_spectrogram: bad mel arguments");
+        return NNTK_ERR_ARG_;
+    }
+    // the staged band results of a frame pair share the warp's exchange buffer with the parked spectra
+    if (!a || a->nfft != NNTK_SPEC_N || m->n_mels > NNTK_SPEC_SMEM_F2 - 280 || m->n_iter > 4096) return 1;
+    return spectrogram_run(a, m, d_in, d_out, n_clips);
+}
+
+static int spectrogram_run(const nntk_spectrogram_args *a, const nntk_mel_args *m, const float *d_in, float *d_out, int n_clips) {
     int rc = nntk_cuda_ensure_init();
     if (rc) return rc;
     if (!a || !d_in || !d_out || n_clips < 0 || a->nfft < 1 || a->window_size < 1 || a->window_size > a->nfft ||
@@ -333,6 +399,9 @@ extern "C" int nntk_cuda_spectrogram(const nntk_spectrogram_args *a, const float
     p.psd_mid = an * an * 0.25f * (2.0f / a->scale);
     p.psd_edge = an * an * 0.25f / a->scale;
     p.in_vec_ok = (((uintptr_t)d_in) & 15) == 0;
+    p.n_mels = m ? m->n_mels : 0;
+    p.mel_iter = m ? m->n_iter : 0;
+    p.log_offset = m ? m->log_offset : 0.0f;
     cudaStream_t st = nntk_stream();
 
     if (a->nfft == NNTK_SPEC_N) {
@@ -356,11 +425,15 @@ extern "C" int nntk_cuda_spectrogram(const nntk_spectrogram_args *a, const float
         p.in_cap = in_cap;
         p.n_clips = n_clips;
         const bool fullwin = a->window_size == NNTK_SPEC_N;
-        void (*kern)(SpecParams, const float *, const float2 *, const float *, float *) =
-            a->mode == 0 ? (fullwin ? spectrogram512_kernel<true, 0> : spectrogram512_kernel<false, 0>)
-                         : (fullwin ? spectrogram512_kernel<true, 1> : spectrogram512_kernel<false, 1>);
-        static size_t attr_bytes[4] = {0, 0, 0, 0};
-        const int ki = (a->mode ? 2 : 0) + (fullwin ? 1 : 0);
+        typedef void (*SpecKernel)(SpecParams, const float *, const float2 *, const float *, float *, const uint2 *);
+        static const SpecKernel kernels[8] = {
+            spectrogram512_kernel<false, 0, false>, spectrogram512_kernel<true, 0, false>,
+            spectrogram512_kernel<false, 1, false>, spectrogram512_kernel<true, 1, false>,
+            spectrogram512_kernel<false, 0, true>,  spectrogram512_kernel<true, 0, true>,
+            spectrogram512_kernel<false, 1, true>,  spectrogram512_kernel<true, 1, true>};
+        static size_t attr_bytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        const int ki = (m ? 4 : 0) + (a->mode ? 2 : 0) + (fullwin ? 1 : 0);
+        const SpecKernel kern = kernels[ki];
         if (bytes > attr_bytes[ki]) {
             NNTK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
             attr_bytes[ki] = bytes;
@@ -374,10 +447,11 @@ extern "C" int nntk_cuda_spectrogram(const nntk_spectrogram_args *a, const float
         const long long need = (p.total_tiles + SPEC_WARPS - 1) / SPEC_WARPS;
         if (grid > need) grid = need;
         kern<<<(unsigned)grid, SPEC_THREADS, bytes, st>>>(p, a->d_window, reinterpret_cast<const float2 *>(a->d_twiddle),
-                                                          d_in, d_out);
+                                                          d_in, d_out, m ? reinterpret_cast<const uint2 *>(m->d_entries) : nullptr);
         NNTK_LAUNCH_CHECK("spectrogram512_kernel");
         return 0;
     }
+    if (m) return 1;   // only the 512-point kernel has the mel epilogue
     int log2n = -1;
     if ((a->nfft & (a->nfft - 1)) == 0) {
         log2n = 0;

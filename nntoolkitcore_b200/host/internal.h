@@ -43,6 +43,21 @@ struct ActivationFunctionStruct {
     ActivationFunctionDerivative derivative, cached_derivative;
 };
 
+/* spectrogram.c: makes the device tables of `s` current and fills the kernel arguments (used by the log-mel front-end) */
+int nntk_spectrogram_prepare(Spectrogram s, nntk_spectrogram_args *a);
+
+/* mel_filterbank.c */
+struct MelFilterBankStruct {
+    MelFilterBankConfig config;
+    float *weights;    /* host [n_fft/2+1][n_mels] */
+    void *entries;     /* host per-lane work list of the fused kernel, [n_iter][32] x 8 bytes (NULL: not expressible) */
+    int n_iter;
+    float *d_weights;  /* device mirrors, uploaded at the first Apply */
+    void *d_entries;
+};
+int nntk_mel_stage(MelFilterBank b);
+int nntk_mel_gemm(MelFilterBank b, const float *d_in, float *d_out, long long rows);
+
 static inline int nntk_act_kind(ActivationFunction f) { return f ? f->kind : NNTK_ACT_NONE; }
 static inline float nntk_act_a(ActivationFunction f) { return f ? f->a : 1.0f; }
 

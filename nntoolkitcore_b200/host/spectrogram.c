@@ -119,9 +119,23 @@ static int spectrogram_stage(Spectrogram s) {
     return 0;
 }
 
+static void spectrogram_args(Spectrogram s, nntk_spectrogram_args *out);
+
+int nntk_spectrogram_prepare(Spectrogram s, nntk_spectrogram_args *a) {
+    int rc = spectrogram_stage(s);
+    if (rc) return rc;
+    spectrogram_args(s, a);
+    return 0;
+}
+
 static int spectrogram_launch(void *ctx, const float *d_in, float *d_out, long long first, int n) {
     (void)first;
-    Spectrogram s = (Spectrogram)ctx;
+    nntk_spectrogram_args a;
+    spectrogram_args((Spectrogram)ctx, &a);
+    return nntk_cuda_spectrogram(&a, d_in, d_out, n);
+}
+
+static void spectrogram_args(Spectrogram s, nntk_spectrogram_args *out) {
     nntk_spectrogram_args a;
     a.nfft = s->config.nfft;
     a.window_size = s->config.window_size;
@@ -134,7 +148,7 @@ static int spectrogram_launch(void *ctx, const float *d_in, float *d_out, long l
     a.scale = s->scale_factor;
     a.d_window = s->d_window;
     a.d_twiddle = s->d_twiddle;
-    return nntk_cuda_spectrogram(&a, d_in, d_out, n);
+    *out = a;
 }
 
 int SpectrogramApplyBatch(Spectrogram filter, const float *input, float *output, int n_clips) {

@@ -127,6 +127,59 @@ class Spectrogram:
             self.handle = None
 
 
+class MelFilterBank:
+    """signal/mel_filterbank.h: [rows, n_fft/2+1] spectra -> [rows, n_mels]"""
+
+    def __init__(self, lib, n_mels, n_fft, sample_rate, lower_hz, upper_hz):
+        self.lib, self.n_mels, self.n_bins = lib, n_mels, n_fft // 2 + 1
+        self.config = lib.MelFilterBankConfigCreate(n_mels, n_fft, sample_rate, lower_hz, upper_hz)
+        self.handle = lib.MelFilterBankCreate(self.config)
+        if not self.handle:
+            raise NNTKError("MelFilterBankCreate failed")
+
+    def apply(self, spec, out=None):
+        rows = int(np.prod(spec.shape[:-1]))
+        out = _new_out(spec, tuple(spec.shape[:-1]) + (self.n_mels,)) if out is None else out
+        self.lib.MelFilterBankApply(self.handle, _ptr(spec), _ptr(out), rows)
+        return out
+
+    def close(self):
+        if self.handle:
+            self.lib.MelFilterBankDestroy(self.handle)
+            self.handle = None
+
+
+class LogMelSpectrogram:
+    """signal/log_mel_spectrogram.h on top of a `Spectrogram` (borrowed: close this object first)"""
+
+    def __init__(self, lib, spectrogram, n_mels, sample_rate, lower_hz, upper_hz, n_fft=None):
+        self.lib, self.spectrogram, self.n_mels = lib, spectrogram, n_mels
+        self.mel_config = lib.MelFilterBankConfigCreate(n_mels, n_fft or spectrogram.config.nfft, sample_rate, lower_hz, upper_hz)
+        self.handle = lib.LogMelSpectrogramCreate(spectrogram.handle, self.mel_config)
+        if not self.handle:
+            raise NNTKError("LogMelSpectrogramCreate failed")
+
+    @property
+    def out_shape(self):
+        return (self.spectrogram.config.ntime_series, self.n_mels)
+
+    def apply(self, x, out=None):
+        out = _new_out(x, self.out_shape) if out is None else out
+        self.lib.LogMelSpectrogramApply(self.handle, _ptr(x), _ptr(out))
+        return out
+
+    def apply_batch(self, x, out=None):
+        n = x.shape[0]
+        out = _new_out(x, (n,) + self.out_shape) if out is None else out
+        _check(self.lib, self.lib.LogMelSpectrogramApplyBatch(self.handle, _ptr(x), _ptr(out), n), "LogMelSpectrogramApplyBatch")
+        return out
+
+    def close(self):
+        if self.handle:
+            self.lib.LogMelSpectrogramDestroy(self.handle)
+            self.handle = None
+
+
 class BatchNorm:
     def __init__(self, lib, channels, eps, count):
         self.lib, self.C, self.count = lib, channels, count

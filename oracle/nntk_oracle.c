@@ -283,6 +283,64 @@ void oracle_spectrogram(int nfft, int window_size, int noverlap, int input_size,
     plan_destroy(pl);
 }
 
+/* ------------------------------------------------------------------------------------------------ mel / log-mel */
+
+/* signal/mel_filterbank.c:11-23: HTK mel scale as four fp32 vector passes each way */
+static float oracle_hz_to_mel(float hz) { float m = hz / 700.0f; m = m + 1.0f; m = logf(m); return m * 1127.0f; }
+static float oracle_mel_to_hz(float mel) { float h = mel / 1127.0f; h = expf(h); h = h + -1.0f; return h * 700.0f; }
+
+/* weights [n_fft/2+1][n_mels]: band edges equally spaced in mel between lower_hz and upper_hz (mel_filterbank.c:43-54),
+ * bin frequencies k*sr/n_fft (:57-65), triangle = max(min(falling, rising), 0) evaluated in Hz (:68-93), bin 0 zeroed
+ * (:93), stored transposed (:96). */
+void oracle_mel_weights(int n_mels, int n_fft, int sample_rate, float lower_hz, float upper_hz, float *weights) {
+    int n_bins = n_fft / 2 + 1;
+    float *band = (float *)malloc(sizeof(float) * (size_t)(n_mels + 2));
+    float e0 = oracle_hz_to_mel(lower_hz), e1 = oracle_hz_to_mel(upper_hz);
+    float step = (e1 - e0) / (float)(n_mels + 1);
+    for (int i = 0; i < n_mels + 2; ++i) band[i] = oracle_mel_to_hz(e0 + (step * i));
+    float fstep = (float)sample_rate / (float)n_fft;
+    for (int i = 0; i < n_mels; ++i) {
+        float lower = band[i], center = band[i + 1], upper = band[i + 2];
+        for (int k = 0; k < n_bins; ++k) {
+            float f = fstep * (float)k;
+            float rising = (f + -1.0f * lower) / (center - lower);
+            float falling = (-f + upper) / (upper - center);
+            float w = fmaxf(fminf(falling, rising), 0.0f);
+            weights[(size_t)k * n_mels + i] = k == 0 ? 0.0f : w;
+        }
+    }
+    free(band);
+}
+
+/* MelFilterBankApply = op_mat_mul(spec, weights, mel, rows, n_mels, n_bins) (mel_filterbank.c:114-116); k-ascending sums
+ * here, Eigen's blocked order in the reference -> tolerance, not bit-equality */
+void oracle_mel_apply(int n_mels, int n_bins, const float *weights, const float *spec, float *mel, int rows) {
+    for (int r = 0; r < rows; ++r)
+        for (int m = 0; m < n_mels; ++m) {
+            float acc = 0.0f;
+            for (int k = 0; k < n_bins; ++k) acc += spec[(size_t)r * n_bins + k] * weights[(size_t)k * n_mels + m];
+            mel[(size_t)r * n_mels + m] = acc;
+        }
+}
+
+/* signal/log_mel_spectrogram.c:33-38: spectrogram -> mel -> + 1.5849e-13 -> logf */
+void oracle_log_mel_spectrogram(int nfft, int window_size, int noverlap, int input_size, float norm_factor,
+                                const float *window, int mode, int fs, int n_mels, int sample_rate, float lower_hz,
+                                float upper_hz, const float *input, float *output, int n_clips) {
+    int nfreq = nfft / 2 + 1, ntime = (input_size - noverlap) / (window_size - noverlap);
+    float *w = (float *)malloc(sizeof(float) * (size_t)nfreq * n_mels);
+    float *spec = (float *)malloc(sizeof(float) * (size_t)ntime * nfreq);
+    oracle_mel_weights(n_mels, nfft, sample_rate, lower_hz, upper_hz, w);
+    for (int c = 0; c < n_clips; ++c) {
+        float *o = output + (size_t)c * ntime * n_mels;
+        oracle_spectrogram(nfft, window_size, noverlap, input_size, norm_factor, window, mode, fs, 0.0f,
+                           input + (size_t)c * input_size, spec, 1);
+        oracle_mel_apply(n_mels, nfreq, w, spec, o, ntime);
+        for (int i = 0; i < ntime * n_mels; ++i) { float v = o[i] + 1.5849e-13f; o[i] = logf(v); }
+    }
+    free(w); free(spec);
+}
+
 /* ------------------------------------------------------------------------------------------------ activations */
 
 /* layers/activation_default.c: sigmoid :28-33 (neg, expf, +1, 1/x), tanh :65-67 (tanhf), identity :98-103,

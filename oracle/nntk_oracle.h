@@ -39,6 +39,14 @@ void oracle_spectrogram(int nfft, int window_size, int noverlap, int input_size,
                         const float *window, int mode, int fs, float scale_override,
                         const float *input, float *output, int n_clips);
 
+/* mel filter bank table [n_fft/2+1][n_mels] (signal/mel_filterbank.c:43-100), its apply (:114-116) and the log-mel chain
+ * (signal/log_mel_spectrogram.c:33-38) */
+void oracle_mel_weights(int n_mels, int n_fft, int sample_rate, float lower_hz, float upper_hz, float *weights);
+void oracle_mel_apply(int n_mels, int n_bins, const float *weights, const float *spec, float *mel, int rows);
+void oracle_log_mel_spectrogram(int nfft, int window_size, int noverlap, int input_size, float norm_factor,
+                                const float *window, int mode, int fs, int n_mels, int sample_rate, float lower_hz,
+                                float upper_hz, const float *input, float *output, int n_clips);
+
 void oracle_activation(int kind, float relu_a, int vector_size, const float *in, float *out, int n);
 
 void oracle_batch_norm(int channels, float eps, int count, const float *gamma, const float *beta,

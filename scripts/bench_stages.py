@@ -2,7 +2,7 @@
 """Per-stage timing of the hot path at the BASELINE.json config shapes (C1, C3, C4, C5), CUDA events on the library
 stream, device-resident buffers, weights frozen.  One JSON line per stage.  Development tool -- bench.py is the contract.
 
-    python scripts/bench_stages.py [--stage c1|c3|c4|c5|all] [--mode fp32|tf32] [--batch-scale 0.25] [--iters 3]
+    python scripts/bench_stages.py [--stage c1|c3|c4|c5|f1|all] [--mode fp32|tf32] [--batch-scale 0.25] [--iters 3]
 """
 from __future__ import annotations
 
@@ -115,6 +115,30 @@ def c5(lib, args):
     emit(stage=f"C5 chain B{B}", mode=args.mode, ms=total, audio_s_per_s=B * 10.0 / (total * 1e-3))
 
 
+def f1(lib, args):
+    """fused log-mel front-end at the C2 shape (4096 x 10 s clips x batch-scale), against the same
+    three stages run separately (spectrogram -> MelFilterBankApply -> the log lives only in the fused / chained C call)"""
+    B = max(1, int(4096 * args.batch_scale)); n = 160000
+    pool = torch.from_numpy(np.stack([helpers.audio_clip(i, n) for i in range(min(B, 64))])).to(dev)
+    x = pool[torch.arange(B, device=dev) % pool.shape[0]].contiguous()
+    spec = L.Spectrogram(lib, 512, 512, 352, n, 1.0, "hann_window")
+    T0, F = spec.out_shape
+    for n_mels in (40, 80, 128):
+        lm = L.LogMelSpectrogram(lib, spec, n_mels, 16000, 20.0, 8000.0)
+        out = torch.empty(B, T0, n_mels, device=dev)
+        ms = timeit(lambda: lm.apply_batch(x, out), max(args.iters, 5), 2)
+        alg = 4.0 * B * (n + T0 * n_mels)
+        emit(stage=f"F1 log-mel fused n_mels={n_mels} B{B}", ms=ms, gbs=alg / ms / 1e6, audio_s_per_s=B * 10.0 / (ms * 1e-3))
+        lm.close()
+    s = torch.empty(B, T0, F, device=dev)
+    bank = L.MelFilterBank(lib, 80, 512, 16000, 20.0, 8000.0)
+    m = torch.empty(B, T0, 80, device=dev)
+    ms_s = timeit(lambda: spec.apply_batch(x, s), max(args.iters, 5), 2)
+    ms_m = timeit(lambda: bank.apply(s, m), max(args.iters, 5), 2)
+    emit(stage=f"F1 unfused spectrogram + mel GEMM n_mels=80 B{B} (log not included)", ms=ms_s + ms_m, spectrogram_ms=ms_s, mel_ms=ms_m,
+         audio_s_per_s=B * 10.0 / ((ms_s + ms_m) * 1e-3))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--stage", default="all")
@@ -126,8 +150,8 @@ def main():
     assert lib.NNTKInit(0) == 0, lib.NNTKLastError()
     lib.NNTKSetStream(torch.cuda.current_stream().cuda_stream)
     assert lib.NNTKSetMathMode(1 if args.mode == "tf32" else 0) == 0
-    for name, fn in (("c1", c1), ("c3", c3), ("c4", c4), ("c5", c5)):
-        if args.stage in ("all", name):
+    for name, fn in (("c1", c1), ("c3", c3), ("c4", c4), ("c5", c5), ("f1", f1)):
+        if args.stage == name or (args.stage == "all" and name[0] == "c"):
             fn(lib, args)
 
 

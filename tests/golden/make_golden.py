@@ -1,4 +1,4 @@
-"""Generates tests/golden/golden_v1.npz from the UNMODIFIED reference (oracle/_ref/libnntk_ref.so, built from
+"""Generates tests/golden/golden_v1.npz (hot path) and golden_v2.npz from the UNMODIFIED reference (oracle/_ref/libnntk_ref.so, built from
 /root/reference by oracle/Makefile).  The reference ships no tests or golden vectors of its own (README.md:25), so these
 outputs of the reference itself are the pin.  Run in the build container (needs /root/reference once, to build _ref):
 
@@ -23,3 +23,8 @@ if __name__ == "__main__":
         out[name] = case(ref)
         print(f"{name:32s} {out[name].shape} mean {out[name].mean():+.6f}")
     np.savez_compressed(Path(__file__).parent / "golden_v1.npz", **out)
+    nxt = {}
+    for name, case in golden_cases.NEXT_CASES.items():
+        nxt[name] = case(ref)
+        print(f"{name:32s} {nxt[name].shape} mean {nxt[name].mean():+.6f}")
+    np.savez_compressed(Path(__file__).parent / "golden_v2.npz", **nxt)

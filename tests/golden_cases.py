@@ -62,6 +62,26 @@ def _dense(i, o, act, ts, seed):
     return run
 
 
+def _logmel(nfft, win, nov, n, window, n_mels, sr, lo, hi, fs=None, clip=0):
+    def run(lib):
+        s = L.Spectrogram(lib, nfft, win, nov, n, 1.0, window, fs)
+        f = L.LogMelSpectrogram(lib, s, n_mels, sr, lo, hi)
+        out = f.apply(helpers.audio_clip(clip, n))
+        f.close(); s.close()
+        return out
+    return run
+
+
+def _mel(n_mels, n_fft, sr, lo, hi, rows, seed):
+    def run(lib):
+        m = L.MelFilterBank(lib, n_mels, n_fft, sr, lo, hi)
+        x = np.abs(np.random.Generator(np.random.PCG64(seed)).standard_normal((rows, n_fft // 2 + 1))).astype(np.float32)
+        out = m.apply(x)
+        m.close()
+        return out
+    return run
+
+
 CASES = {
     "spec_c2_1s_hann": _spec(512, 512, 352, 16000, "hann_window"),
     "spec_c5_1s_hann400": _spec(512, 400, 240, 16000, "hann_window", clip=1),
@@ -78,4 +98,13 @@ CASES = {
     "bn_257": _bn(257, 20, 170),
     "dense_relu": _dense(256, 12, L.ACT_RELU, None, 180),
     "tdd_softmax": _dense(256, 12, L.ACT_SOFTMAX, 10, 190),
+}
+
+# SURVEY.md section 8(f) "next" rows, stored in tests/golden/golden_v2.npz
+NEXT_CASES = {
+    "logmel_40_c2": _logmel(512, 512, 352, 16000, "hann_window", 40, 16000, 20.0, 8000.0),
+    "logmel_80_win400": _logmel(512, 400, 240, 16000, "hann_window", 80, 16000, 0.0, 8000.0, clip=1),
+    "logmel_128_psd": _logmel(512, 512, 352, 8000, "hamming_window", 128, 16000, 0.0, 8000.0, fs=16000, clip=2),
+    "logmel_nfft256": _logmel(256, 256, 128, 4096, "hann_window", 20, 16000, 100.0, 7600.0, clip=3),
+    "mel_23_rows7": _mel(23, 512, 8000, 100.0, 3800.0, 7, 200),
 }

@@ -131,3 +131,44 @@ def run_case(port, name):
         out = dense(port, 256, 12, sh.W, sh.b, act, 1.0, x)
         return out[0] if ts is None else out
     raise KeyError(name)
+
+
+# ---- SURVEY.md section 8(f) rows ---------------------------------------------------------------------------------------
+def mel_weights(port, n_mels, n_fft, sr, lo, hi):
+    w = np.zeros((n_fft // 2 + 1, n_mels), np.float32)
+    port.oracle_mel_weights(n_mels, n_fft, sr, C.c_float(lo), C.c_float(hi), fptr(w))
+    return w
+
+
+def mel_apply(port, n_mels, n_fft, sr, lo, hi, spec):
+    spec = np.ascontiguousarray(spec, np.float32)
+    w = mel_weights(port, n_mels, n_fft, sr, lo, hi)
+    out = np.zeros(spec.shape[:-1] + (n_mels,), np.float32)
+    port.oracle_mel_apply(n_mels, n_fft // 2 + 1, fptr(w), fptr(spec), fptr(out), int(np.prod(spec.shape[:-1])))
+    return out
+
+
+def log_mel(port, nfft, win, nov, n, window, n_mels, sr, lo, hi, fs=None, x=None):
+    w = np.zeros(win, np.float32)
+    port.oracle_window(WIN[window], fptr(w), win)
+    x = np.ascontiguousarray(x, np.float32).reshape(-1, n)
+    ntime = (n - nov) // (win - nov)
+    out = np.zeros((x.shape[0], ntime, n_mels), np.float32)
+    port.oracle_log_mel_spectrogram(nfft, win, nov, n, C.c_float(1.0), fptr(w), 0 if fs is None else 1, int(fs or 0),
+                                    n_mels, sr, C.c_float(lo), C.c_float(hi), fptr(x), fptr(out), x.shape[0])
+    return out
+
+
+def run_next_case(port, name):
+    """the golden_v2 case `name` evaluated by the port (same table as golden_cases.NEXT_CASES)"""
+    logmel = {"logmel_40_c2": (512, 512, 352, 16000, "hann_window", 40, 16000, 20.0, 8000.0, None, 0),
+              "logmel_80_win400": (512, 400, 240, 16000, "hann_window", 80, 16000, 0.0, 8000.0, None, 1),
+              "logmel_128_psd": (512, 512, 352, 8000, "hamming_window", 128, 16000, 0.0, 8000.0, 16000, 2),
+              "logmel_nfft256": (256, 256, 128, 4096, "hann_window", 20, 16000, 100.0, 7600.0, None, 3)}
+    if name in logmel:
+        nfft, win, nov, n, window, n_mels, sr, lo, hi, fs, clip = logmel[name]
+        return log_mel(port, nfft, win, nov, n, window, n_mels, sr, lo, hi, fs, helpers.audio_clip(clip, n))[0]
+    if name == "mel_23_rows7":
+        x = np.abs(_rng(200).standard_normal((7, 257))).astype(np.float32)
+        return mel_apply(port, 23, 512, 8000, 100.0, 3800.0, x)
+    raise KeyError(name)

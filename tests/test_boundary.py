@@ -131,3 +131,48 @@ def test_custom_activation_runs_callers_callback_on_host_buffers(product):
     product.ActivationFunctionApply(act, x.ctypes.data, y.ctypes.data)
     assert seen == [6] and np.array_equal(x, y)
     product.ActivationFunctionDestroy(act)
+
+
+@pytest.mark.parametrize("args", [(40, 512, 16000, 20.0, 8000.0), (80, 512, 16000, 0.0, 8000.0), (128, 512, 16000, 0.0, 8000.0),
+                                  (23, 512, 8000, 100.0, 3800.0), (376, 512, 16000, 0.0, 8000.0), (1, 512, 16000, 0.0, 8000.0)])
+def test_mel_work_list_reproduces_the_table(product, args):
+    """host logic of the fused log-mel kernel (include/nntk_b200_shim.h, nntk_mel_args): walking the per-lane work list the
+    way the kernel does -- accumulate weight * spectrum[slot], emit at flagged entries -- gives the dense table product for
+    every band exactly once, and the list is balanced and nearly free of shared-memory bank conflicts"""
+    n_mels, n_fft = args[0], args[1]
+    nb = n_fft // 2 + 1
+
+    class Head(C.Structure):   # leading fields of the product's private struct (host/internal.h)
+        _fields_ = [("cfg", capi.MelFilterBankConfig), ("weights", C.POINTER(C.c_float)), ("entries", C.c_void_p),
+                    ("n_iter", C.c_int)]
+    m = L.MelFilterBank(product, *args)
+    head = C.cast(m.handle, C.POINTER(Head)).contents
+    w = np.ctypeslib.as_array(head.weights, shape=(nb, n_mels)).copy()
+    n_iter = head.n_iter
+    ent = np.ctypeslib.as_array(C.cast(head.entries, C.POINTER(C.c_uint32)), shape=(n_iter, 32, 2)).copy()
+    m.close()
+    packed, weight = ent[..., 0], ent[..., 1].copy().view(np.float32)
+    spec = np.abs(np.random.default_rng(1).standard_normal(nb)).astype(np.float64) + 0.1
+    parked = np.zeros(nb + nb // 16 + 16)
+    k = np.arange(nb)
+    parked[k + k // 16] = spec
+    got = np.full(n_mels, np.nan)
+    for lane in range(32):
+        acc = 0.0
+        for it in range(n_iter):
+            p = int(packed[it, lane])
+            acc += float(weight[it, lane]) * parked[(p & 0xff8) // 8]
+            if p & 0x80000000:
+                band = (p >> 15) & 0xffff
+                assert np.isnan(got[band]), f"band {band} emitted twice"
+                got[band] = acc
+                acc = 0.0
+    assert not np.isnan(got).any(), "a band was never emitted"
+    np.testing.assert_allclose(got, spec @ w.astype(np.float64), rtol=1e-12, atol=1e-12)
+    work = int(np.maximum((w != 0).sum(0), 1).sum())                                       # an empty band still costs one entry
+    assert n_iter <= max(int(np.ceil(work / 32)) + 2, int((w != 0).sum(0).max()))         # longest-first balance
+    # 8-byte accesses: a half-warp is conflict-free when its 16 slots differ mod 16
+    slots = (packed & 0xff8) // 8
+    waves = sum(np.bincount(slots[it, h * 16:(h + 1) * 16] % 16, minlength=16).max() for it in range(n_iter) for h in (0, 1))
+    if n_mels <= 128:   # (hundreds of 1-4 bin bands leave the ordering no choice)
+        assert waves <= 2.2 * 2 * n_iter, f"{waves} wavefronts for {n_iter} iterations"

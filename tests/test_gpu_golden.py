@@ -15,3 +15,12 @@ GOLDEN = np.load(Path(__file__).parent / "golden" / "golden_v1.npz")
 def test_product_matches_golden(cuda, product, name):
     got = golden_cases.CASES[name](product)
     assert_parity(got, GOLDEN[name], what=name)
+
+
+GOLDEN_NEXT = np.load(Path(__file__).parent / "golden" / "golden_v2.npz")
+
+
+@pytest.mark.parametrize("name", sorted(golden_cases.NEXT_CASES))
+def test_product_matches_golden_next_rows(cuda, product, name):
+    got = golden_cases.NEXT_CASES[name](product)
+    assert_parity(got, GOLDEN_NEXT[name], what=name)

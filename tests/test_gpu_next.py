@@ -1,0 +1,110 @@
+"""GPU parity tests of the SURVEY.md section 8(f) rows (log-mel front-end, ...): the CUDA path through the C-ABI against
+the unmodified reference (oracle/_ref) on the same seeded inputs, fp32 contract (1e-5 on helpers.parity)."""
+import numpy as np
+import pytest
+
+import helpers
+from helpers import assert_parity
+from nntoolkitcore_b200 import layers as L
+
+pytestmark = pytest.mark.gpu
+
+
+def _to_dev(cuda, a):
+    import torch
+    return torch.from_numpy(a).to(cuda)
+
+
+# ------------------------------------------------------------------------------------------------ f1: log-mel
+LOGMEL_CASES = [
+    # nfft, win, noverlap, n, window, psd_fs, n_mels, sample_rate, lower_hz, upper_hz
+    (512, 512, 352, 16000, "hann_window", None, 40, 16000, 20.0, 8000.0),      # C2 framing, fused kernel
+    (512, 400, 240, 16000, "hann_window", None, 80, 16000, 0.0, 8000.0),       # C5 framing (window < nfft)
+    (512, 512, 352, 8000, "hamming_window", 16000, 128, 16000, 0.0, 8000.0),   # PSD input, one empty band
+    (512, 300, 17, 4001, "periodic_hamming_window", None, 23, 8000, 100.0, 3800.0),  # ragged sizes, odd frame count
+    (512, 512, 0, 5120, "ones", None, 1, 16000, 0.0, 8000.0),                  # a single band
+    (512, 512, 256, 4096, "hann_window", None, 376, 16000, 0.0, 8000.0),       # most bands the fused kernel stages
+    (512, 512, 256, 4096, "hann_window", None, 377, 16000, 0.0, 8000.0),       # one more: unfused chain
+    (256, 256, 128, 4096, "hann_window", None, 20, 16000, 100.0, 7600.0),      # nfft != 512: unfused chain
+    (1024, 1024, 512, 8192, "hann_window", None, 64, 22050, 50.0, 11025.0),
+]
+
+
+@pytest.mark.parametrize("nfft,win,nov,n,window,fs,n_mels,sr,lo,hi", LOGMEL_CASES)
+def test_log_mel_matches_reference(cuda, product, ref, nfft, win, nov, n, window, fs, n_mels, sr, lo, hi):
+    clips = np.stack([helpers.audio_clip(i, n) for i in range(3)])
+    s_ref = L.Spectrogram(ref, nfft, win, nov, n, 1.0, window, fs)
+    f_ref = L.LogMelSpectrogram(ref, s_ref, n_mels, sr, lo, hi)
+    want = np.stack([f_ref.apply(c) for c in clips])
+    s = L.Spectrogram(product, nfft, win, nov, n, 1.0, window, fs)
+    f = L.LogMelSpectrogram(product, s, n_mels, sr, lo, hi)
+    assert f.out_shape == f_ref.out_shape
+    got_host = f.apply_batch(clips)
+    got_dev = f.apply_batch(_to_dev(cuda, clips)).cpu().numpy()
+    assert_parity(got_host, want, what="log-mel host path")
+    assert np.array_equal(got_host, got_dev)
+    assert np.array_equal(f.apply(clips[2]), got_host[2])           # the reference's own single-clip call
+    for x in (f, s, f_ref, s_ref):
+        x.close()
+
+
+def test_log_mel_of_silence_is_the_log_offset(cuda, product):
+    s = L.Spectrogram(product, 512, 512, 352, 4000, 1.0, "hann_window")
+    f = L.LogMelSpectrogram(product, s, 40, 16000, 20.0, 8000.0)
+    out = f.apply_batch(np.zeros((2, 4000), np.float32))
+    assert_parity(out, np.full_like(out, np.log(np.float32(1.5849e-13))), what="log-mel of silence")
+    f.close(); s.close()
+
+
+def test_log_mel_follows_a_window_change(cuda, product, ref):
+    """the filter borrows the Spectrogram: SpectrogramSetWindowFunc after LogMelSpectrogramCreate must take effect"""
+    n = 8000
+    x = helpers.audio_clip(5, n)
+    outs = []
+    for lib in (product, ref):
+        s = L.Spectrogram(lib, 512, 512, 352, n, 1.0, "hann_window")
+        f = L.LogMelSpectrogram(lib, s, 40, 16000, 20.0, 8000.0)
+        f.apply(x)
+        s.set_window("blackman_window")
+        outs.append(f.apply(x))
+        f.close(); s.close()
+    assert_parity(outs[0], outs[1], what="log-mel after SetWindowFunc")
+
+
+def test_log_mel_refuses_a_mismatched_filter_bank(product):
+    s = L.Spectrogram(product, 512, 512, 352, 4000, 1.0, "hann_window")
+    with pytest.raises(L.NNTKError):
+        L.LogMelSpectrogram(product, s, 40, 16000, 20.0, 8000.0, n_fft=256)
+    s.close()
+
+
+@pytest.mark.parametrize("args,rows", [((40, 512, 16000, 20.0, 8000.0), 97), ((128, 512, 16000, 0.0, 8000.0), 1),
+                                       ((64, 1024, 22050, 50.0, 11025.0), 33), ((10, 100, 16000, 300.0, 7000.0), 250)])
+def test_mel_filter_bank_matches_reference(cuda, product, ref, args, rows):
+    x = np.abs(np.random.default_rng(rows).standard_normal((rows, args[1] // 2 + 1))).astype(np.float32)
+    m_ref, m = L.MelFilterBank(ref, *args), L.MelFilterBank(product, *args)
+    want = m_ref.apply(x)
+    got = m.apply(x)
+    assert_parity(got, want, what="mel filter bank")
+    assert np.array_equal(got, m.apply(_to_dev(cuda, x)).cpu().numpy())
+    m.close(); m_ref.close()
+
+
+def test_log_mel_full_size_equals_the_unfused_chain(cuda, product):
+    """BASELINE C2 clip length (10 s), 64 clips: the fused kernel against the product's own spectrogram -> mel GEMM chain
+    followed by log(x + 1.5849e-13) in numpy -- a size-independent consistency property (the per-stage kernels are pinned
+    to the reference separately)"""
+    import torch
+    n, B = 160000, 64
+    pool = np.stack([helpers.audio_clip(i, n) for i in range(8)])
+    x = torch.from_numpy(pool[np.arange(B) % 8]).to(cuda)
+    s = L.Spectrogram(product, 512, 512, 352, n, 1.0, "hann_window")
+    f = L.LogMelSpectrogram(product, s, 80, 16000, 20.0, 8000.0)
+    bank = L.MelFilterBank(product, 80, 512, 16000, 20.0, 8000.0)
+    got = f.apply_batch(x).cpu().numpy()
+    mel = bank.apply(s.apply_batch(x)).cpu().numpy()
+    want = np.log(mel + np.float32(1.5849e-13))
+    assert got.shape == (B, 997, 80)
+    assert_parity(got, want, what="fused log-mel vs unfused chain")
+    for o in (f, bank, s):
+        o.close()

@@ -26,9 +26,41 @@ def test_port_matches_golden(port, name):
         assert_parity(got, want, what=name)
 
 
+GOLDEN_NEXT = np.load(Path(__file__).parent / "golden" / "golden_v2.npz")
+
+
+@pytest.mark.parametrize("name", sorted(GOLDEN_NEXT.files))
+def test_port_matches_golden_next_rows(port, name):
+    """summation order of the mel products differs from Eigen's -> tolerance"""
+    assert_parity(port_cases.run_next_case(port, name), GOLDEN_NEXT[name], what=name)
+
+
 def test_golden_covers_every_case():
     import golden_cases
     assert sorted(GOLDEN.files) == sorted(golden_cases.CASES)
+    assert sorted(GOLDEN_NEXT.files) == sorted(golden_cases.NEXT_CASES)
+
+
+@pytest.mark.parametrize("args", [(40, 512, 16000, 20.0, 8000.0), (80, 512, 16000, 0.0, 8000.0), (128, 512, 16000, 0.0, 8000.0),
+                                  (23, 512, 8000, 100.0, 3800.0), (64, 1024, 22050, 50.0, 11025.0), (10, 100, 16000, 300.0, 7000.0)])
+def test_mel_tables_bit_exact(port, ref, product, args):
+    """the mel table of the port AND of the product's host set-up code equal the reference's bit for bit
+    (reference table read back through MelFilterBankApply on an identity matrix)"""
+    from nntoolkitcore_b200 import capi, layers as L
+    import ctypes as C
+    n_mels, n_fft = args[0], args[1]
+    nb = n_fft // 2 + 1
+    m = L.MelFilterBank(ref, *args)
+    want = m.apply(np.eye(nb, dtype=np.float32))
+    m.close()
+    assert np.array_equal(port_cases.mel_weights(port, *args), want)
+
+    class Head(C.Structure):   # leading fields of the product's private struct (host/internal.h)
+        _fields_ = [("cfg", capi.MelFilterBankConfig), ("weights", C.POINTER(C.c_float))]
+    pm = L.MelFilterBank(product, *args)
+    got = np.ctypeslib.as_array(C.cast(pm.handle, C.POINTER(Head)).contents.weights, shape=(nb, n_mels)).copy()
+    pm.close()
+    assert np.array_equal(got, want)
 
 
 def test_port_windows_bit_exact_vs_reference(port, ref):
