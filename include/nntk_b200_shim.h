@@ -99,6 +99,13 @@ int nntk_cuda_log_mel_spectrogram(const nntk_spectrogram_args *a, const nntk_mel
 /* d_out[i] = logf(d_in[i] + offset)   (op_vec_add_sc + op_vec_log, log_mel_spectrogram.c:36-37) */
 int nntk_cuda_log_offset(const float *d_in, float *d_out, long long n, float offset);
 
+/* Standalone complex DFT on planar buffers (signal/dft.c:34-47).  d_twiddle is the FORWARD table
+ * [nfft][2] of nntk_spectrogram_args; inverse != 0 conjugates it.  [batch, nfft] planes, in-place allowed. */
+int nntk_cuda_dft(int nfft, int inverse, const float *d_twiddle, const float *d_in_re, const float *d_in_im, float *d_out_re,
+                  float *d_out_im, long long batch);
+/* strided element copies behind split_complex / join_complex_split on device pointers: dst[i * dst_stride] = src[i * src_stride] */
+int nntk_cuda_copy_strided(float *d_dst, int dst_stride, const float *d_src, int src_stride, long long n);
+
 /* ---- K5: element-wise --------------------------------------------------------------------------------------------- */
 /* d_params = gamma|beta|mean|var (4*C floats); rows x C elements; layers/batch_norm.c:140-163 */
 int nntk_cuda_batch_norm(const float *d_params, int C, float eps, const float *d_in, float *d_out, long long rows);
@@ -132,6 +139,13 @@ int nntk_cuda_pack_conv_weights(const float *d_W, float *d_B, int cout, int cin,
  * activation repack [rows][C] -> [rows][Cpad]: give unaligned channel counts (Cin = 257) a 16-byte pitch for TMA */
 int nntk_cuda_pack_conv_weights_padded(const float *d_W, float *d_B, int cout, int cin, int cin_pad, int k);
 int nntk_cuda_pad_channels(const float *d_in, float *d_out, long long rows, int C, int Cpad);
+
+/* bidirectional helpers (layers/bidirectional.c:10-85) */
+/* d_out[b][t][:] = d_in[b][T-1-t][:], rows of `vec` floats; not in-place */
+int nntk_cuda_bd_reverse(const float *d_in, float *d_out, int vec, int T, long long batch);
+/* d_out[row] = d_fwd[row] | d_bwd[row], rows of `cols` floats each */
+int nntk_cuda_bd_concat(const float *d_fwd, const float *d_bwd, float *d_out, int cols, long long rows);
+int nntk_cuda_bd_sum(const float *d_a, const float *d_b, float *d_out, long long n);
 
 /* ---- K3+K4: recurrent layers ---------------------------------------------------------------------------------------- */
 typedef struct {

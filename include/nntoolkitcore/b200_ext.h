@@ -19,6 +19,7 @@
 #include <stddef.h>
 #include "signal/spectrogram.h"
 #include "signal/log_mel_spectrogram.h"
+#include "signal/dft.h"
 #include "layers/activation_default.h"
 #include "layers/batch_norm.h"
 #include "layers/conv_1d.h"
@@ -27,6 +28,7 @@
 #include "layers/rnn.h"
 #include "layers/gru.h"
 #include "layers/lstm.h"
+#include "layers/bidirectional.h"
 
 #ifdef __cplusplus
 extern "C" {
@@ -85,6 +87,8 @@ int NNTKResetState(void *recurrent_layer);
 int SpectrogramApplyBatch(Spectrogram filter, const float *input, float *output, int n_clips);
 /* [n_clips, input_size] -> [n_clips, ntime_series, n_mels]; one fused kernel for nfft == 512 */
 int LogMelSpectrogramApplyBatch(LogMelSpectrogram filter, const float *input, float *output, int n_clips);
+/* `batch` nfft-point signals stored back to back in each plane: [batch, nfft] -> [batch, nfft] */
+int DFTPerformBatch(DFTSetup setup, const ComplexFloatSplit *input, const ComplexFloatSplit *output, int batch);
 /* [batch, count, C] -> same */
 int BatchNormApplyInferenceBatch(BatchNorm filter, const float *input, float *output, int batch);
 /* `batch` repetitions of the activation's own size */

@@ -22,6 +22,14 @@ class MelFilterBankConfig(C.Structure):
     _fields_ = [("n_mels", c_int), ("n_fft", c_int), ("sample_rate", c_int), ("lower_hz", c_float), ("upper_hz", c_float)]
 
 
+class DFTConfig(C.Structure):
+    _fields_ = [("nfft", c_int), ("forward", c_bool), ("complex", c_bool)]
+
+
+class ComplexFloatSplit(C.Structure):
+    _fields_ = [("real_p", c_void_p), ("imag_p", c_void_p)]
+
+
 class BatchNormWeights(C.Structure):
     _fields_ = [("gamma", FP), ("beta", FP), ("moving_mean", FP), ("moving_variance", FP)]
 
@@ -103,6 +111,17 @@ REFERENCE_API = {
     "LogMelSpectrogramCreate": (H, [H, MelFilterBankConfig]),
     "LogMelSpectrogramApply": (None, [H, c_void_p, c_void_p]),
     "LogMelSpectrogramDestroy": (None, [H]),
+    # signal/dft.h
+    "DFTConfigCreate": (DFTConfig, [c_int, c_bool, c_bool]), "DFTSetupCreate": (H, [DFTConfig]),
+    "DFTPerform": (None, [H, POINTER(ComplexFloatSplit), POINTER(ComplexFloatSplit)]), "DFTSetupDestroy": (None, [H]),
+    "split_complex": (None, [c_void_p, POINTER(ComplexFloatSplit), c_int]),
+    "join_complex_split": (None, [POINTER(ComplexFloatSplit), c_void_p, c_int]),
+    # layers/bidirectional.h (inference half)
+    "bd_reverse_input_batch": (None, [c_void_p, c_void_p, RecurrentConfig, c_int]),
+    "bd_reverse_backward_batch": (None, [c_void_p, c_void_p, RecurrentConfig, c_int]),
+    "bd_merge_concat_buffer_size": (c_int, [RecurrentConfig]),
+    "bd_merge_concat": (None, [c_void_p, c_void_p, c_void_p, RecurrentConfig, c_int, c_void_p]),
+    "bd_merge_sum": (None, [c_void_p, c_void_p, c_void_p, RecurrentConfig, c_int]),
     # layers/activation*.h
     "ActivationFunctionCreate": (H, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "ActivationFunctionCreateIdentity": (H, [c_int]), "ActivationFunctionCreateSigmoid": (H, [c_int]),
@@ -157,6 +176,7 @@ EXT_API = {
     "NNTKResetState": (c_int, [c_void_p]),
     "SpectrogramApplyBatch": (c_int, [H, c_void_p, c_void_p, c_int]),
     "LogMelSpectrogramApplyBatch": (c_int, [H, c_void_p, c_void_p, c_int]),
+    "DFTPerformBatch": (c_int, [H, POINTER(ComplexFloatSplit), POINTER(ComplexFloatSplit), c_int]),
     "BatchNormApplyInferenceBatch": (c_int, [H, c_void_p, c_void_p, c_int]),
     "ActivationFunctionApplyBatch": (c_int, [H, c_void_p, c_void_p, c_int]),
     "Conv1dApplyInferenceBatch": (c_int, [H, c_void_p, c_void_p, c_int]),
@@ -178,7 +198,8 @@ SHIM_SYMBOLS = [
     "nntk_cuda_math_mode", "nntk_cuda_sm_count", "nntk_cuda_malloc", "nntk_cuda_free", "nntk_cuda_host_alloc",
     "nntk_cuda_host_free", "nntk_cuda_h2d", "nntk_cuda_d2h", "nntk_cuda_d2d", "nntk_cuda_memset",
     "nntk_cuda_is_device_ptr", "nntk_cuda_workspace", "nntk_cuda_staged_run", "nntk_cuda_spectrogram",
-    "nntk_cuda_log_mel_spectrogram", "nntk_cuda_log_offset",
+    "nntk_cuda_log_mel_spectrogram", "nntk_cuda_log_offset", "nntk_cuda_dft", "nntk_cuda_copy_strided",
+    "nntk_cuda_bd_reverse", "nntk_cuda_bd_concat", "nntk_cuda_bd_sum",
     "nntk_cuda_batch_norm", "nntk_cuda_activation", "nntk_cuda_gemm", "nntk_cuda_pack_conv_weights",
     "nntk_cuda_pack_conv_weights_padded", "nntk_cuda_pad_channels",
     "nntk_cuda_recurrent_workspace", "nntk_cuda_recurrent",

@@ -224,3 +224,84 @@ extern "C" int nntk_cuda_log_offset(const float *d_in, float *d_out, long long n
     NNTK_LAUNCH_CHECK("log_offset_kernel");
     return 0;
 }
+
+// ---- bidirectional helpers (layers/bidirectional.c:10-85): pure data movement at 8 B/element --
+namespace {
+// out[b][t][:] = in[b][T - 1 - t][:]; V = float4 when the row length and the pointers allow, else float
+template <typename V>
+__global__ void __launch_bounds__(256) bd_reverse_kernel(const V *__restrict__ in, V *__restrict__ out, int vec, int T, long long total) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long per_seq = (long long)vec * T;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        const long long b = i / per_seq;
+        const int r = (int)(i - b * per_seq), t = r / vec, c = r - t * vec;
+        out[i] = in[b * per_seq + (long long)(T - 1 - t) * vec + c];
+    }
+}
+// out[row][0:cols] = fwd[row][:], out[row][cols:2 cols] = bwd[row][:]
+template <typename V>
+__global__ void __launch_bounds__(256) bd_concat_kernel(const V *__restrict__ fwd, const V *__restrict__ bwd, V *__restrict__ out, int cols,
+                                                        long long total) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        const long long row = i / (2 * cols);
+        const int c = (int)(i - row * 2 * cols);
+        out[i] = c < cols ? fwd[row * cols + c] : bwd[row * cols + (c - cols)];
+    }
+}
+__global__ void __launch_bounds__(256) bd_sum_kernel(const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ out, long long n) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = a[i] + b[i];
+}
+inline bool aligned16(const void *p) { return (((uintptr_t)p) & 15) == 0; }
+}  // namespace
+
+extern "C" int nntk_cuda_bd_reverse(const float *d_in, float *d_out, int vec, int T, long long batch) {
+    int rc = nntk_cuda_ensure_init();
+    if (rc) return rc;
+    if (!d_in || !d_out || d_in == d_out || vec < 1 || T < 0 || batch < 0) {
+        nntk_cuda_set_error(NNTK_ERR_ARG_, "bd_reverse: bad arguments (in-place is not supported)");
+        return NNTK_ERR_ARG_;
+    }
+    const long long total = batch * (long long)T * vec;
+    if (total == 0) return 0;
+    if (vec % 4 == 0 && aligned16(d_in) && aligned16(d_out))
+        bd_reverse_kernel<float4><<<grid_for(total >> 2, 256), 256, 0, nntk_stream()>>>(
+            reinterpret_cast<const float4 *>(d_in), reinterpret_cast<float4 *>(d_out), vec >> 2, T, total >> 2);
+    else
+        bd_reverse_kernel<float><<<grid_for(total, 256), 256, 0, nntk_stream()>>>(d_in, d_out, vec, T, total);
+    NNTK_LAUNCH_CHECK("bd_reverse_kernel");
+    return 0;
+}
+
+extern "C" int nntk_cuda_bd_concat(const float *d_fwd, const float *d_bwd, float *d_out, int cols, long long rows) {
+    int rc = nntk_cuda_ensure_init();
+    if (rc) return rc;
+    if (!d_fwd || !d_bwd || !d_out || cols < 1 || rows < 0) {
+        nntk_cuda_set_error(NNTK_ERR_ARG_, "bd_concat: bad arguments");
+        return NNTK_ERR_ARG_;
+    }
+    const long long total = rows * 2 * cols;
+    if (total == 0) return 0;
+    if (cols % 4 == 0 && aligned16(d_fwd) && aligned16(d_bwd) && aligned16(d_out))
+        bd_concat_kernel<float4><<<grid_for(total >> 2, 256), 256, 0, nntk_stream()>>>(
+            reinterpret_cast<const float4 *>(d_fwd), reinterpret_cast<const float4 *>(d_bwd), reinterpret_cast<float4 *>(d_out),
+            cols >> 2, total >> 2);
+    else
+        bd_concat_kernel<float><<<grid_for(total, 256), 256, 0, nntk_stream()>>>(d_fwd, d_bwd, d_out, cols, total);
+    NNTK_LAUNCH_CHECK("bd_concat_kernel");
+    return 0;
+}
+
+extern "C" int nntk_cuda_bd_sum(const float *d_a, const float *d_b, float *d_out, long long n) {
+    int rc = nntk_cuda_ensure_init();
+    if (rc) return rc;
+    if (!d_a || !d_b || !d_out || n < 0) {
+        nntk_cuda_set_error(NNTK_ERR_ARG_, "bd_sum: bad arguments");
+        return NNTK_ERR_ARG_;
+    }
+    if (n == 0) return 0;
+    bd_sum_kernel<<<grid_for(n, 256), 256, 0, nntk_stream()>>>(d_a, d_b, d_out, n);
+    NNTK_LAUNCH_CHECK("bd_sum_kernel");
+    return 0;
+}

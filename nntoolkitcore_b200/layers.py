@@ -367,3 +367,69 @@ class Recurrent:
 def freeze(lib, *layers):
     for l in layers:
         _check(lib, lib.NNTKWeightsFreeze(l.handle), "NNTKWeightsFreeze")
+
+
+class DFT:
+    """signal/dft.h: complex DFT on planar buffers; `perform` takes [nfft] or [batch, nfft] real / imaginary planes"""
+
+    def __init__(self, lib, nfft, forward=True):
+        self.lib, self.nfft = lib, nfft
+        self.handle = lib.DFTSetupCreate(lib.DFTConfigCreate(nfft, forward, True))
+        if not self.handle:
+            raise NNTKError("DFTSetupCreate failed")
+
+    def perform(self, re, im, out_re=None, out_im=None):
+        out_re = _new_out(re, re.shape) if out_re is None else out_re
+        out_im = _new_out(im, im.shape) if out_im is None else out_im
+        src = capi.ComplexFloatSplit(_ptr(re), _ptr(im))
+        dst = capi.ComplexFloatSplit(_ptr(out_re), _ptr(out_im))
+        if re.ndim == 1:
+            self.lib.DFTPerform(self.handle, C.byref(src), C.byref(dst))
+        else:
+            _check(self.lib, self.lib.DFTPerformBatch(self.handle, C.byref(src), C.byref(dst), re.shape[0]), "DFTPerformBatch")
+        return out_re, out_im
+
+    def close(self):
+        if self.handle:
+            self.lib.DFTSetupDestroy(self.handle)
+            self.handle = None
+
+
+# ---- layers/bidirectional.h (inference half): x [batch, T, in], results [batch, rows, out] -------------------------------
+def _rcfg(lib, in_size, out_size, return_sequences, timesteps):
+    return lib.RecurrentConfigCreate(in_size, out_size, return_sequences, timesteps)
+
+
+def bd_reverse_input(lib, x, out=None):
+    b, t, c = x.shape
+    out = _new_out(x, x.shape) if out is None else out
+    lib.bd_reverse_input_batch(_ptr(x), _ptr(out), _rcfg(lib, c, c, True, t), b)
+    return out
+
+
+def bd_reverse_backward(lib, y, out=None):
+    b, t, c = y.shape
+    out = _new_out(y, y.shape) if out is None else out
+    lib.bd_reverse_backward_batch(_ptr(y), _ptr(out), _rcfg(lib, c, c, True, t), b)
+    return out
+
+
+def _bd_cfg(lib, r):
+    if r.ndim == 3:
+        return _rcfg(lib, r.shape[2], r.shape[2], True, r.shape[1]), r.shape[0]
+    return _rcfg(lib, r.shape[1], r.shape[1], False, 1), r.shape[0]
+
+
+def bd_merge_concat(lib, fwd, bwd, out=None):
+    cfg, b = _bd_cfg(lib, fwd)
+    out = _new_out(fwd, tuple(fwd.shape[:-1]) + (2 * fwd.shape[-1],)) if out is None else out
+    scratch = np.zeros(lib.bd_merge_concat_buffer_size(cfg), np.float32)   # the reference needs it; ours ignores it
+    lib.bd_merge_concat(_ptr(fwd), _ptr(bwd), _ptr(out), cfg, b, scratch.ctypes.data)
+    return out
+
+
+def bd_merge_sum(lib, fwd, bwd, out=None):
+    cfg, b = _bd_cfg(lib, fwd)
+    out = _new_out(fwd, fwd.shape) if out is None else out
+    lib.bd_merge_sum(_ptr(fwd), _ptr(bwd), _ptr(out), cfg, b)
+    return out

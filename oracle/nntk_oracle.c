@@ -537,3 +537,25 @@ void oracle_lstm(int in, int H, int T, int return_sequences, int v2,
     }
     free(Z);
 }
+
+/* ------------------------------------------------------------------------------------------------ bidirectional helpers */
+
+/* layers/bidirectional.c:10-32: per sequence, row t of the output is row T-1-t of the input */
+void oracle_bd_reverse(const float *in, float *out, int vec, int T, int batch) {
+    for (int b = 0; b < batch; ++b)
+        for (int t = 0; t < T; ++t)
+            memcpy(out + ((size_t)b * T + t) * vec, in + ((size_t)b * T + (T - 1 - t)) * vec, sizeof(float) * (size_t)vec);
+}
+
+/* layers/bidirectional.c:39-55: the three transposes amount to out[b][r] = fwd[b][r] | bwd[b][r] */
+void oracle_bd_concat(const float *fwd, const float *bwd, float *out, int cols, int rows, int batch) {
+    for (size_t r = 0; r < (size_t)batch * rows; ++r) {
+        memcpy(out + r * 2 * cols, fwd + r * cols, sizeof(float) * (size_t)cols);
+        memcpy(out + r * 2 * cols + cols, bwd + r * cols, sizeof(float) * (size_t)cols);
+    }
+}
+
+/* layers/bidirectional.c:75-85: op_vec_add over batch * rows * cols elements */
+void oracle_bd_sum(const float *fwd, const float *bwd, float *out, long long n) {
+    for (long long i = 0; i < n; ++i) out[i] = fwd[i] + bwd[i];
+}

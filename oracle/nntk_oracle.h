@@ -72,6 +72,11 @@ void oracle_lstm(int in, int H, int T, int return_sequences, int v2,
                  const float *W, const float *U, const float *b_i, const float *b_h,
                  const float *x, float *h, float *c, float *out);
 
+/* bidirectional helpers (layers/bidirectional.c:10-85) */
+void oracle_bd_reverse(const float *in, float *out, int vec, int T, int batch);
+void oracle_bd_concat(const float *fwd, const float *bwd, float *out, int cols, int rows, int batch);
+void oracle_bd_sum(const float *fwd, const float *bwd, float *out, long long n);
+
 #ifdef __cplusplus
 }
 #endif

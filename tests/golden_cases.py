@@ -100,6 +100,34 @@ CASES = {
     "tdd_softmax": _dense(256, 12, L.ACT_SOFTMAX, 10, 190),
 }
 
+def _dft(nfft, forward, batch, seed):
+    def run(lib):
+        rng = np.random.Generator(np.random.PCG64(seed))
+        re = rng.standard_normal((batch, nfft)).astype(np.float32)
+        im = rng.standard_normal((batch, nfft)).astype(np.float32)
+        d = L.DFT(lib, nfft, forward)
+        if getattr(lib, "has_ext", False):
+            o_re, o_im = d.perform(re, im)
+        else:   # the reference transforms one signal per call
+            outs = [d.perform(re[b], im[b]) for b in range(batch)]
+            o_re, o_im = np.stack([o[0] for o in outs]), np.stack([o[1] for o in outs])
+        d.close()
+        return np.stack([o_re, o_im])
+    return run
+
+
+def _bd(which, batch, T, C_, seed, seq=True):
+    def run(lib):
+        rng = np.random.Generator(np.random.PCG64(seed))
+        shape = (batch, T, C_) if seq else (batch, C_)
+        a = rng.standard_normal(shape).astype(np.float32)
+        b = rng.standard_normal(shape).astype(np.float32)
+        if which == "reverse":
+            return L.bd_reverse_input(lib, a)
+        return (L.bd_merge_concat if which == "concat" else L.bd_merge_sum)(lib, a, b)
+    return run
+
+
 # SURVEY.md section 8(f) "next" rows, stored in tests/golden/golden_v2.npz
 NEXT_CASES = {
     "logmel_40_c2": _logmel(512, 512, 352, 16000, "hann_window", 40, 16000, 20.0, 8000.0),
@@ -107,4 +135,12 @@ NEXT_CASES = {
     "logmel_128_psd": _logmel(512, 512, 352, 8000, "hamming_window", 128, 16000, 0.0, 8000.0, fs=16000, clip=2),
     "logmel_nfft256": _logmel(256, 256, 128, 4096, "hann_window", 20, 16000, 100.0, 7600.0, clip=3),
     "mel_23_rows7": _mel(23, 512, 8000, 100.0, 3800.0, 7, 200),
+    "dft_512_fwd": _dft(512, True, 3, 210),
+    "dft_512_inv": _dft(512, False, 2, 211),
+    "dft_128_fwd": _dft(128, True, 2, 212),
+    "dft_100_inv": _dft(100, False, 2, 213),
+    "bd_reverse": _bd("reverse", 3, 7, 5, 220),
+    "bd_concat_seq": _bd("concat", 2, 6, 8, 221),
+    "bd_concat_last": _bd("concat", 4, 1, 6, 222, seq=False),
+    "bd_sum": _bd("sum", 2, 5, 7, 223),
 }

@@ -171,4 +171,33 @@ def run_next_case(port, name):
     if name == "mel_23_rows7":
         x = np.abs(_rng(200).standard_normal((7, 257))).astype(np.float32)
         return mel_apply(port, 23, 512, 8000, 100.0, 3800.0, x)
+    dft = {"dft_512_fwd": (512, True, 3, 210), "dft_512_inv": (512, False, 2, 211), "dft_128_fwd": (128, True, 2, 212),
+           "dft_100_inv": (100, False, 2, 213)}
+    if name in dft:
+        nfft, forward, batch, seed = dft[name]
+        rng = _rng(seed)
+        re = rng.standard_normal((batch, nfft)).astype(np.float32)
+        im = rng.standard_normal((batch, nfft)).astype(np.float32)
+        out = np.zeros((2, batch, nfft), np.float32)
+        for b in range(batch):
+            port.oracle_dft(nfft, int(not forward), fptr(re[b]), fptr(im[b]), fptr(out[0, b]), fptr(out[1, b]))
+        return out
+    bd = {"bd_reverse": ("reverse", 3, 7, 5, 220, True), "bd_concat_seq": ("concat", 2, 6, 8, 221, True),
+          "bd_concat_last": ("concat", 4, 1, 6, 222, False), "bd_sum": ("sum", 2, 5, 7, 223, True)}
+    if name in bd:
+        which, batch, T, C_, seed, seq = bd[name]
+        rng = _rng(seed)
+        shape = (batch, T, C_) if seq else (batch, C_)
+        a = rng.standard_normal(shape).astype(np.float32)
+        b = rng.standard_normal(shape).astype(np.float32)
+        if which == "reverse":
+            out = np.zeros_like(a)
+            port.oracle_bd_reverse(fptr(a), fptr(out), C_, T, batch)
+        elif which == "concat":
+            out = np.zeros(shape[:-1] + (2 * C_,), np.float32)
+            port.oracle_bd_concat(fptr(a), fptr(b), fptr(out), C_, T if seq else 1, batch)
+        else:
+            out = np.zeros_like(a)
+            port.oracle_bd_sum(fptr(a), fptr(b), fptr(out), C.c_longlong(a.size))
+        return out
     raise KeyError(name)

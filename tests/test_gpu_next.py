@@ -108,3 +108,109 @@ def test_log_mel_full_size_equals_the_unfused_chain(cuda, product):
     assert_parity(got, want, what="fused log-mel vs unfused chain")
     for o in (f, bank, s):
         o.close()
+
+
+# ------------------------------------------------------------------------------------------------ f4: standalone DFT
+@pytest.mark.parametrize("nfft", [1, 8, 60, 100, 128, 512, 1000, 2048])
+@pytest.mark.parametrize("forward", [True, False])
+def test_dft_matches_reference(cuda, product, ref, nfft, forward):
+    rng = np.random.default_rng(nfft + int(forward))
+    batch = 5
+    re = rng.standard_normal((batch, nfft)).astype(np.float32)
+    im = rng.standard_normal((batch, nfft)).astype(np.float32)
+    d_ref, d = L.DFT(ref, nfft, forward), L.DFT(product, nfft, forward)
+    want = [d_ref.perform(re[b], im[b]) for b in range(batch)]
+    want = np.stack([np.stack([w[0] for w in want]), np.stack([w[1] for w in want])])
+    g_re, g_im = d.perform(re, im)                                   # host planes, batched
+    got = np.stack([g_re, g_im])
+    assert_parity(got, want, what=f"dft {nfft}")
+    t_re, t_im = d.perform(_to_dev(cuda, re), _to_dev(cuda, im))     # device planes
+    assert np.array_equal(np.stack([t_re.cpu().numpy(), t_im.cpu().numpy()]), got)
+    one = d.perform(re[3], im[3])                                    # the reference's own single-signal call
+    assert np.array_equal(one[0], g_re[3]) and np.array_equal(one[1], g_im[3])
+    a, b = _to_dev(cuda, re), _to_dev(cuda, im)                      # in place, like dft.c:41-45 allows
+    d.perform(a, b, a, b)
+    assert np.array_equal(np.stack([a.cpu().numpy(), b.cpu().numpy()]), got)
+    d.close(); d_ref.close()
+
+
+def test_dft_round_trip_at_scale(cuda, product):
+    """size-independent property at 65 536 x 512 points: inverse(forward(x)) == N x (neither direction normalises)"""
+    import torch
+    g = torch.Generator(device="cuda").manual_seed(5)
+    re = torch.randn(65536, 512, device=cuda, generator=g); im = torch.randn(65536, 512, device=cuda, generator=g)
+    f, i = L.DFT(product, 512, True), L.DFT(product, 512, False)
+    a, b = f.perform(re, im)
+    want = torch.fft.fft(torch.complex(re[:64].double(), im[:64].double()))
+    assert_parity(torch.stack([a[:64], b[:64]]).cpu().numpy(), torch.stack([want.real, want.imag]).cpu().numpy(), what="fft vs torch")
+    a, b = i.perform(a, b)
+    assert_parity((a / 512).cpu().numpy(), re.cpu().numpy(), what="round trip re")
+    assert_parity((b / 512).cpu().numpy(), im.cpu().numpy(), what="round trip im")
+    f.close(); i.close()
+
+
+def test_split_and_join_complex(cuda, product):
+    import ctypes as C
+    import torch
+    from nntoolkitcore_b200 import capi
+    z = np.random.default_rng(3).standard_normal((37, 2)).astype(np.float32)
+    re, im = np.zeros(37, np.float32), np.zeros(37, np.float32)
+    sp = capi.ComplexFloatSplit(re.ctypes.data, im.ctypes.data)
+    product.split_complex(z.ctypes.data, C.byref(sp), 37)
+    assert np.array_equal(re, z[:, 0]) and np.array_equal(im, z[:, 1])
+    back = np.zeros_like(z)
+    product.join_complex_split(C.byref(sp), back.ctypes.data, 37)
+    assert np.array_equal(back, z)
+    dz = torch.from_numpy(z).to(cuda); dre = torch.zeros(37, device=cuda); dim_ = torch.zeros(37, device=cuda)
+    dsp = capi.ComplexFloatSplit(dre.data_ptr(), dim_.data_ptr())
+    product.split_complex(dz.data_ptr(), C.byref(dsp), 37)
+    dback = torch.zeros_like(dz)
+    product.join_complex_split(C.byref(dsp), dback.data_ptr(), 37)
+    assert product.NNTKSynchronize() == 0
+    assert np.array_equal(dre.cpu().numpy(), z[:, 0]) and np.array_equal(dback.cpu().numpy(), z)
+
+
+# ------------------------------------------------------------------------------------------------ f2: bidirectional helpers
+@pytest.mark.parametrize("batch,T,C_", [(3, 7, 5), (2, 100, 256), (1, 1, 4), (5, 33, 12), (0, 4, 4)])
+def test_bidirectional_helpers_match_reference(cuda, product, ref, batch, T, C_):
+    rng = np.random.default_rng(batch * 1000 + T)
+    a = rng.standard_normal((batch, T, C_)).astype(np.float32)
+    b = rng.standard_normal((batch, T, C_)).astype(np.float32)
+    for fn in (L.bd_reverse_input, L.bd_reverse_backward):
+        want = fn(ref, a) if batch else a.copy()
+        got = fn(product, a)
+        assert np.array_equal(got, want) and np.array_equal(got, a[:, ::-1])
+        if batch:
+            assert np.array_equal(fn(product, _to_dev(cuda, a)).cpu().numpy(), want)
+    for fn in (L.bd_merge_concat, L.bd_merge_sum):
+        for x, y in ((a, b), (a[:, 0].copy(), b[:, 0].copy())):         # return_sequences true / false
+            if not batch:
+                continue
+            want = fn(ref, x, y)
+            assert np.array_equal(fn(product, x, y), want)
+            assert np.array_equal(fn(product, _to_dev(cuda, x), _to_dev(cuda, y)).cpu().numpy(), want)
+
+
+def test_bidirectional_gru_chain_matches_reference(cuda, product, ref):
+    """the helpers in their place: reverse -> backward GRU -> reverse back -> concat with the forward GRU"""
+    B, T, I, H = 4, 20, 16, 32
+    x = np.random.default_rng(9).standard_normal((B, T, I)).astype(np.float32)
+    outs = []
+    for lib in (product, ref):
+        fw, bw = L.Recurrent(lib, "gru", I, H, T), L.Recurrent(lib, "gru", I, H, T)
+        helpers.fill_recurrent(fw, 900); helpers.fill_recurrent(bw, 901)
+        xr = L.bd_reverse_input(lib, x)
+        if lib is product:
+            yf, yb = fw.apply_batch(x), bw.apply_batch(xr)
+        else:   # fresh handles per sequence: the reference call is stateful
+            yf, yb = [], []
+            for b in range(B):
+                f1, b1 = L.Recurrent(lib, "gru", I, H, T), L.Recurrent(lib, "gru", I, H, T)
+                helpers.copy_weights(f1, fw); helpers.copy_weights(b1, bw)
+                yf.append(f1.apply(x[b])); yb.append(b1.apply(xr[b]))
+                f1.close(); b1.close()
+            yf, yb = np.stack(yf), np.stack(yb)
+        outs.append(L.bd_merge_concat(lib, yf, L.bd_reverse_backward(lib, yb)))
+        fw.close(); bw.close()
+    assert outs[0].shape == (B, T, 2 * H)
+    assert_parity(outs[0], outs[1], what="bidirectional GRU chain")
