@@ -2,7 +2,7 @@
 """Per-stage timing of the hot path at the BASELINE.json config shapes (C1, C3, C4, C5), CUDA events on the library
 stream, device-resident buffers, weights frozen.  One JSON line per stage.  Development tool -- bench.py is the contract.
 
-    python scripts/bench_stages.py [--stage c1|c3|c4|c5|f1|all] [--mode fp32|tf32] [--batch-scale 0.25] [--iters 3]
+    python scripts/bench_stages.py [--stage c1|c3|c4|c5|f1|f2|f4|all] [--mode fp32|tf32] [--batch-scale 0.25] [--iters 3]
 """
 from __future__ import annotations
 
@@ -139,6 +139,31 @@ def f1(lib, args):
          audio_s_per_s=B * 10.0 / ((ms_s + ms_m) * 1e-3))
 
 
+def f4(lib, args):
+    """row f4: batched 512-point complex DFT, planar planes, 16 algorithmic bytes per point"""
+    B = max(1, int((1 << 20) * args.batch_scale))
+    for nfft in (512, 256, 100):
+        re = torch.randn(B, nfft, device=dev); im = torch.randn(B, nfft, device=dev)
+        o_re = torch.empty_like(re); o_im = torch.empty_like(im)
+        d = L.DFT(lib, nfft, True)
+        ms = timeit(lambda: d.perform(re, im, o_re, o_im), max(args.iters, 5), 2)
+        emit(stage=f"F4 DFT nfft={nfft} forward B{B}", ms=ms, gbs=16.0 * B * nfft / ms / 1e6, transforms_per_s=B / (ms * 1e-3))
+        d.close()
+
+
+def f2(lib, args):
+    """row f2: bidirectional helpers at the C5 GRU shape [B, 994, 256], 8 bytes per element moved"""
+    B = max(1, int(1024 * args.batch_scale)); T, H = 994, 256
+    a = torch.randn(B, T, H, device=dev); b = torch.randn(B, T, H, device=dev)
+    o1 = torch.empty_like(a); o2 = torch.empty(B, T, 2 * H, device=dev)
+    n = a.numel()
+    for name, fn, byts in (("reverse", lambda: L.bd_reverse_input(lib, a, o1), 8.0 * n),
+                           ("merge_concat", lambda: L.bd_merge_concat(lib, a, b, o2), 16.0 * n),
+                           ("merge_sum", lambda: L.bd_merge_sum(lib, a, b, o1), 12.0 * n)):
+        ms = timeit(fn, max(args.iters, 5), 2)
+        emit(stage=f"F2 bd_{name} [B{B},{T},{H}]", ms=ms, gbs=byts / ms / 1e6)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--stage", default="all")
@@ -150,7 +175,7 @@ def main():
     assert lib.NNTKInit(0) == 0, lib.NNTKLastError()
     lib.NNTKSetStream(torch.cuda.current_stream().cuda_stream)
     assert lib.NNTKSetMathMode(1 if args.mode == "tf32" else 0) == 0
-    for name, fn in (("c1", c1), ("c3", c3), ("c4", c4), ("c5", c5), ("f1", f1)):
+    for name, fn in (("c1", c1), ("c3", c3), ("c4", c4), ("c5", c5), ("f1", f1), ("f2", f2), ("f4", f4)):
         if args.stage == name or (args.stage == "all" and name[0] == "c"):
             fn(lib, args)
 
