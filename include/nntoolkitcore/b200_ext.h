@@ -58,7 +58,9 @@ void NNTKClearError(void);
 /* GEMM-shaped stages (Conv1d, Dense/TDD, recurrent projections and steps) can run in three math modes. */
 #define NNTK_MATH_FP32 0    /* FFMA on CUDA cores; matches the reference within 1e-5 (default) */
 #define NNTK_MATH_TF32 1    /* tcgen05 kind::tf32, operands rounded to 10-bit mantissa; 1e-3 */
-#define NNTK_MATH_TF32X3 2  /* tcgen05, hi/lo operand split, 3 MMAs per product; 3e-5 (truncating fp32 accumulate) */
+#define NNTK_MATH_TF32X3 2  /* tcgen05, hi/lo operand split, 3 MMAs per product, accumulate truncation compensated: holds the
+                               fp32 contract (1e-5) at ~1/3 of the TF32 rate (recurrent steps too, for batches above
+                               256); reduction lengths above 3 072 stay on FFMA */
 int NNTKSetMathMode(int mode);
 int NNTKGetMathMode(void);
 

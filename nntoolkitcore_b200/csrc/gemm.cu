@@ -211,6 +211,7 @@ __global__ void pack_conv_weights_kernel(const float *__restrict__ W, float *__r
 }  // namespace
 
 extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *g, int split);   // gemm_tc.cu
+#define NNTK_X3_MAX_K 3072
 
 extern "C" int nntk_cuda_gemm(const nntk_gemm_args *a) {
     int rc = nntk_cuda_ensure_init();
@@ -225,8 +226,12 @@ extern "C" int nntk_cuda_gemm(const nntk_gemm_args *a) {
     }
     const long long M = (long long)a->batch * a->rows;
     if (M == 0) return 0;
-    if (nntk_cuda_math_mode() != 0) {
-        rc = nntk_cuda_gemm_tf32(a, nntk_cuda_math_mode() == 2);
+    // TF32X3 promises the fp32 contract (1e-5).  The part of the tensor core's truncating accumulate that the epilogue cannot
+    // compensate grows linearly with the reduction length (measured rel-L2 1.5e-6 at K = 1 280, 3.0e-6 at 2 560, 8.0e-6 at
+    // 7 168): beyond NNTK_X3_MAX_K the mode runs the FFMA kernel.  Every BASELINE shape has K <= 1 285.
+    const int mode = nntk_cuda_math_mode();
+    if (mode == 1 || (mode == 2 && a->K <= NNTK_X3_MAX_K)) {
+        rc = nntk_cuda_gemm_tf32(a, mode == 2);
         if (rc != 1) return rc;   // 1 = shape not eligible for the tensor-core kernel: use the fp32 kernel
     }
     GemmDev g;

@@ -359,6 +359,8 @@ __global__ void fold_epilogue_kernel(const float *bias, const float *bn, float e
     }
 }
 
+constexpr float X3_ACC_TRUNC_PER_K = 2.06e-9f;
+
 float *g_scratch = nullptr;      // Bt | scale | shift
 size_t g_scratch_floats = 0;
 float *g_split = nullptr;        // split mode: hi | lo copies of A
@@ -424,8 +426,11 @@ extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_
     dim3 tb(32, 8), tg((kpad + 31) / 32, (N + 31) / 32);
     if (bf) transpose_weights_bf16_kernel<<<tg, tb, 0, st>>>(a->d_B, reinterpret_cast<__nv_bfloat16 *>(Bt), K, N, kpad, ldbt);
     else transpose_weights_kernel<<<tg, tb, 0, st>>>(a->d_B, Bt, K, N, kpad, ldbt, parts);
-    fold_epilogue_kernel<<<(N + 127) / 128, 128, 0, st>>>(a->d_bias, a->d_bn, a->bn_eps, N, scale, shift,
-                                                          split ? 1.0f : 1.0f + TF32_TRUNC_BIAS);
+    // 3xTF32: the operands are exact to ~2^-22, what is left is the tensor core's TRUNCATING fp32 accumulate -- a systematic
+    // shrink of every output, linear in the number of accumulation steps (measured on conv shapes K = 192 .. 1280 against the
+    // reference: least-squares slope -(2.05..2.16)e-9 * K, residual rel-L2 <= 1.6e-6 once removed).  Compensated here.
+    const float comp = split == 1 ? 1.0f + X3_ACC_TRUNC_PER_K * (float)K : (split ? 1.0f : 1.0f + TF32_TRUNC_BIAS);
+    fold_epilogue_kernel<<<(N + 127) / 128, 128, 0, st>>>(a->d_bias, a->d_bn, a->bn_eps, N, scale, shift, comp);
     NNTK_LAUNCH_CHECK("gemm_tf32 prologue");
 
     // slab stride of A as the tensor map sees it (elements); in split mode the lo copy sits lo_off elements behind the hi copy

@@ -354,7 +354,7 @@ extern "C" size_t nntk_cuda_recurrent_workspace(const nntk_recurrent_args *r) {
     if (!r) return 0;
     const size_t G = (size_t)r->cell;
     size_t xw = (size_t)((r->batch + 31) / 32 * 32) * r->T * G * r->H * sizeof(float);   // 32-sequence blocks
-    size_t pp = (size_t)4 * r->batch * r->H * sizeof(float);   // exact + TF32-rounded h ping-pong
+    size_t pp = (size_t)6 * r->batch * r->H * sizeof(float);   // exact h ping-pong + operand ping-pong (3xTF32: hi and lo parts)
     return xw + pp + 256;
 }
 
@@ -423,7 +423,7 @@ static int recurrent_cluster_try(const nntk_recurrent_args *r, int nb, const flo
 }
 
 extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, const float *xw, int xw_blocked, float *h, float *c,
-                                      float *out, float *pp, int *used);   // recurrent_tc.cu
+                                      float *out, float *pp, int x3, int *used);   // recurrent_tc.cu
 
 extern "C" int nntk_cuda_recurrent_cluster_tc(const nntk_recurrent_args *r, int nb, const float *xw, float *h, float *c,
                                               float *out, int *used);   // recurrent_cluster_tc.cu
@@ -466,14 +466,16 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     // apart (C4: 4096 different pages per step -- no operand-traffic change moved its 52 us/step, this is what bound it).
     // It is the planned path when neither cluster kernel can hold the shape (H > 256 or H % 32 != 0) and the batch is large.
     const bool step_tc = mode == 1 && G != 1 && !h16 && nb > 256 && (H > 256 || (H & 31)) && (H & 3) == 0 && (GH & 31) == 0;
-    if ((h16 || step_tc) && (((uintptr_t)xw) & 15) == 0) {
+    // TF32X3 mode (fp32 contract on the tensor cores): large batches run the same per-step kernel with hi/lo split operands
+    const bool step_x3 = mode == 2 && G != 1 && nb > 256 && (H & 3) == 0 && (GH & 31) == 0 && H <= 3072 && r->in <= 3072;
+    if ((h16 || step_tc || step_x3) && (((uintptr_t)xw) & 15) == 0) {
         nntk_gemm_args gb = g;
         gb.batch = T; gb.rows = nb; gb.a_slab_stride = r->in; gb.lda = T * r->in;      // slab = timestep, row = sequence
         // 3xbf16 first (bf16 hi/lo split: ~2^-16 operand error, twice the tensor rate and half the operand bytes of 3xTF32);
         // shapes its 2-byte pitch rules exclude fall back to 3xTF32
         static int proj_bf16 = -1;
         if (proj_bf16 < 0) { const char *e = getenv("NNTK_PROJ_BF16X3"); proj_bf16 = e ? atoi(e) : 1; }
-        rc = proj_bf16 ? nntk_cuda_gemm_tf32_ex(&gb, 2, 1) : 1;
+        rc = (proj_bf16 && !step_x3) ? nntk_cuda_gemm_tf32_ex(&gb, 2, 1) : 1;
         if (rc == 1) rc = nntk_cuda_gemm_tf32_ex(&gb, 1, 1);
         if (rc < 0) return rc;
         xw_blocked = rc == 0;
@@ -514,9 +516,9 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     }
     cudaStream_t st = nntk_stream();
     // 2b. large batch, TF32 mode: T tensor-core step kernels with the cell fused into the GEMM epilogue (recurrent_tc.cu)
-    if (mode == 1 && G != 1) {
+    if ((mode == 1 || step_x3) && G != 1) {
         int used = 0;
-        rc = nntk_cuda_recurrent_tc(r, nb, xw, xw_blocked, h, c, out, pp, &used);
+        rc = nntk_cuda_recurrent_tc(r, nb, xw, xw_blocked, h, c, out, pp, step_x3 ? 1 : 0, &used);
         if (rc) return rc;
         if (used) goto carry_state;
     }
@@ -581,7 +583,7 @@ extern "C" int nntk_cuda_recurrent(const nntk_recurrent_args *r) {
         }
     if (r->batch == 0 || r->T == 0) return 0;
     // batch chunks that fit the workspace
-    const size_t per_seq = ((size_t)r->T * r->cell * r->H + 4 * (size_t)r->H) * sizeof(float);
+    const size_t per_seq = ((size_t)r->T * r->cell * r->H + 6 * (size_t)r->H) * sizeof(float);
     size_t avail = r->work_bytes > 256 ? r->work_bytes - 256 : 0;
     long long chunk = (long long)(avail / per_seq);
     if (chunk < 1) {
@@ -591,7 +593,7 @@ extern "C" int nntk_cuda_recurrent(const nntk_recurrent_args *r) {
     if (chunk >= r->batch) {
         chunk = r->batch;
         // the blocked projection layout rounds the chunk up to 32 sequences: make sure that still fits
-        const size_t need = ((size_t)((chunk + 31) / 32 * 32) * r->T * r->cell * r->H + 4 * (size_t)chunk * r->H) * sizeof(float);
+        const size_t need = ((size_t)((chunk + 31) / 32 * 32) * r->T * r->cell * r->H + 6 * (size_t)chunk * r->H) * sizeof(float);
         if (need > avail) chunk = chunk / 32 * 32;
     } else {
         chunk = chunk / 32 * 32;

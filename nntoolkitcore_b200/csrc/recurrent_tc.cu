@@ -26,6 +26,8 @@ constexpr int R_EPI_WARPS = 8;
 
 struct RtcParams {
     int B, H, n_tiles, m_tiles, k_blocks, total_tiles;
+    int kb_pass;                       // X3: k-blocks per pass (k_blocks = 3 * kb_pass)
+    long long part_stride;             // X3: floats between the hi and the lo copy of h in the operand ping-pong
     int a_t;                           // TMA coordinate of h_{t-1} along the time axis of map_a
     const float *bh;                   // permuted like the columns of Bt, or null
     const float *xw; long long ld_xw;  // row b: xw + b*ld_xw, original column order g*H + unit
@@ -64,15 +66,20 @@ __device__ __forceinline__ void tc_ld_32x8(uint32_t taddr, float (&r)[8]) {
 
 // default gate activations compiled in when DEF (the run-time kind switch per call tripled the epilogue's instruction count;
 // ncu r1: the per-step kernel ran at 0.53 IPC on ~5000 instructions per thread per tile -- the epilogue, not TMA or MMA)
-template <bool DEF, int KIND>
+// X3 (the fp32-contract mode): expf / tanhf / IEEE division like the FFMA kernels (common.cuh), never the MUFU forms.
+template <bool DEF, int KIND, bool X3>
 __device__ __forceinline__ float rt_act(const RtcParams &p, int slot, float x) {
+    if (X3) return nntk_act(p.act[slot], p.act_a[slot], x);
     return DEF ? act_fast(KIND, 1.0f, x) : act_fast(p.act[slot], p.act_a[slot], x);
 }
 
 // H16 (implies the default activations): operands are fp16 (kind::f16; a 128-byte stage row holds 64 k-elements instead of 32): with the default activations h is
 // bounded by 1, so fp16's 10-bit mantissa is exactly the TF32 operand precision while U and h cost half the L2 traffic -- the
 // per-step kernel re-reads U once per 128-row tile and was bound by exactly that (C4, B = 4096: 196 MB of operands per step).
-template <int G, int STAGES, bool H16>
+// X3 (NNTK_MATH_TF32X3, never together with H16): 3xTF32 -- h is kept as tf32 hi + lo parts (h - hi is exact), U as
+// [lo | hi | hi] along K, three passes hi*Ulo, lo*Uhi, hi*Uhi in one K loop (small passes first); the accumulate truncation is
+// compensated through p.comp like in gemm_tc.cu.  Operand error ~2^-22: the recurrence holds the fp32 contract (1e-5).
+template <int G, int STAGES, bool H16, bool X3>
 __global__ void __launch_bounds__(R_THREADS, 1)
 recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, RtcParams p) {
     using SL = RtcSmem<G, STAGES>;
@@ -111,7 +118,8 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t *sa = smem + stage * SL::STAGE_BYTES;
                     mbar_expect_tx(&full_bar[stage], SL::STAGE_BYTES);
-                    tma_load_3d(sa, &map_a, &full_bar[stage], kb * (H16 ? 2 * R_BK : R_BK), p.a_t, m_t * R_BM);
+                    const int pass = X3 ? kb / p.kb_pass : 0, akb = kb - pass * p.kb_pass;
+                    tma_load_3d(sa, &map_a, &full_bar[stage], akb * (H16 ? 2 * R_BK : R_BK), X3 ? 2 * p.a_t + (pass == 1 ? 1 : 0) : p.a_t, m_t * R_BM);
                     tma_load_2d(sa + SL::A_BYTES, &map_b, &full_bar[stage], kb * (H16 ? 2 * R_BK : R_BK), n_t * BN);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -212,17 +220,17 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
                         }
                         const float sv = (&cur.st[v].x)[e];
                         if (G == 3) {
-                            const float z = rt_act<H16, NNTK_ACT_SIGMOID>(p, 0, x[0] + hu[0]);
-                            const float r = rt_act<H16, NNTK_ACT_SIGMOID>(p, 1, x[1] + hu[1]);
-                            const float hh = rt_act<H16, NNTK_ACT_TANH>(p, 2, fmaf(r, hu[2], x[2]));
+                            const float z = rt_act<H16, NNTK_ACT_SIGMOID, X3>(p, 0, x[0] + hu[0]);
+                            const float r = rt_act<H16, NNTK_ACT_SIGMOID, X3>(p, 1, x[1] + hu[1]);
+                            const float hh = rt_act<H16, NNTK_ACT_TANH, X3>(p, 2, fmaf(r, hu[2], x[2]));
                             out[e] = fmaf(z, sv - hh, hh);                   // (1 - z) hh + z h_{t-1}
                         } else if (G == 4) {
-                            const float ig = rt_act<H16, NNTK_ACT_SIGMOID>(p, 0, x[0] + hu[0]);
-                            const float fg = rt_act<H16, NNTK_ACT_SIGMOID>(p, 1, x[1] + hu[1]);
-                            const float gg = rt_act<H16, NNTK_ACT_TANH>(p, 2, x[2] + hu[2]);
-                            const float og = rt_act<H16, NNTK_ACT_SIGMOID>(p, 3, x[3] + hu[3]);
+                            const float ig = rt_act<H16, NNTK_ACT_SIGMOID, X3>(p, 0, x[0] + hu[0]);
+                            const float fg = rt_act<H16, NNTK_ACT_SIGMOID, X3>(p, 1, x[1] + hu[1]);
+                            const float gg = rt_act<H16, NNTK_ACT_TANH, X3>(p, 2, x[2] + hu[2]);
+                            const float og = rt_act<H16, NNTK_ACT_SIGMOID, X3>(p, 3, x[3] + hu[3]);
                             cn[e] = fmaf(fg, sv, ig * gg);
-                            out[e] = og * rt_act<H16, NNTK_ACT_TANH>(p, 4, cn[e]);
+                            out[e] = og * rt_act<H16, NNTK_ACT_TANH, X3>(p, 4, cn[e]);
                         } else {
                             out[e] = act_fast(p.act[0], p.act_a[0], hu[0] + x[0]);
                         }
@@ -234,7 +242,11 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
                         uint2 pk = make_uint2(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi));
                         *reinterpret_cast<uint2 *>(reinterpret_cast<__half *>(p.hr_next) + rr * p.H + ubase + u) = pk;
                     } else {
-                        *reinterpret_cast<float4 *>(hr + u) = make_float4(round_tf32(out[0]), round_tf32(out[1]), round_tf32(out[2]), round_tf32(out[3]));
+                        const float4 hi = make_float4(round_tf32(out[0]), round_tf32(out[1]), round_tf32(out[2]), round_tf32(out[3]));
+                        *reinterpret_cast<float4 *>(hr + u) = hi;
+                        if (X3)
+                            *reinterpret_cast<float4 *>(hr + p.part_stride + u) =
+                                make_float4(round_tf32(out[0] - hi.x), round_tf32(out[1] - hi.y), round_tf32(out[2] - hi.z), round_tf32(out[3] - hi.w));
                     }
                     if (G == 4) *reinterpret_cast<float4 *>(cw + u) = make_float4(cn[0], cn[1], cn[2], cn[3]);
                 }
@@ -267,6 +279,29 @@ __global__ void pack_recurrent_weights_kernel(const float *__restrict__ U, const
     }
 }
 
+// X3: row n holds [lo | hi | hi], each kpad wide
+__global__ void pack_recurrent_weights_x3_kernel(const float *__restrict__ U, const float *__restrict__ bh, float *__restrict__ Bt,
+                                                 float *__restrict__ bhp, int H, int G, int kpad, int n_rows) {
+    const long long total = (long long)n_rows * kpad;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int n = (int)(i / kpad), k = (int)(i - (long long)n * kpad);
+        const int j = n / (G * R_UT), r = n - j * G * R_UT, g = r / R_UT, u = r - g * R_UT;
+        const int unit = j * R_UT + u;
+        const float v = (unit < H && k < H) ? __ldg(U + (long long)k * G * H + g * H + unit) : 0.0f;
+        const float hi = round_tf32(v);
+        float *row = Bt + (long long)n * 3 * kpad;
+        row[k] = round_tf32(v - hi); row[kpad + k] = hi; row[2 * kpad + k] = hi;
+        if (k == 0 && bhp) bhp[n] = (unit < H && bh) ? bh[g * H + unit] : 0.0f;
+    }
+}
+// X3: the caller's h_0 split into the operand ping-pong slot that step 0 reads
+__global__ void split_state_kernel(const float *__restrict__ in, float *__restrict__ hi, float *__restrict__ lo, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float v = in[i], h = round_tf32(v);
+        hi[i] = h; lo[i] = round_tf32(v - h);
+    }
+}
+
 __global__ void pack_recurrent_weights_h16_kernel(const float *__restrict__ U, const float *__restrict__ bh, __half *__restrict__ Bt,
                                                   float *__restrict__ bhp, int H, int G, int ldbt, int n_rows) {
     const long long total = (long long)n_rows * ldbt;
@@ -289,16 +324,16 @@ size_t g_rtc_floats = 0;
 
 }  // namespace
 
-template <int G, int STAGES, bool H16>
+template <int G, int STAGES, bool H16, bool X3 = false>
 static int launch_rtc(const CUtensorMap &ma, const CUtensorMap &mb, const RtcParams &p, cudaStream_t st) {
     using SL = RtcSmem<G, STAGES>;
     static bool attr_done = false;
     if (!attr_done) {
-        NNTK_CUDA_TRY(cudaFuncSetAttribute(recurrent_tc_step_kernel<G, STAGES, H16>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::TOTAL));
+        NNTK_CUDA_TRY(cudaFuncSetAttribute(recurrent_tc_step_kernel<G, STAGES, H16, X3>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::TOTAL));
         attr_done = true;
     }
     const int grid = p.total_tiles < nntk_cuda_sm_count() ? p.total_tiles : nntk_cuda_sm_count();
-    recurrent_tc_step_kernel<G, STAGES, H16><<<grid, R_THREADS, SL::TOTAL, st>>>(ma, mb, p);
+    recurrent_tc_step_kernel<G, STAGES, H16, X3><<<grid, R_THREADS, SL::TOTAL, st>>>(ma, mb, p);
     return 0;
 }
 
@@ -323,7 +358,7 @@ static int encode_h_map(EncodeTiledFn encode, CUtensorMap *m, const void *base, 
 // the fp32 step kernels).  xw: hoisted projection [nb, T, G*H]; h/c: state [nb, H]; pp: [4, nb, H] (exact ping-pong, then
 // the TF32-rounded ping-pong).
 extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, const float *xw, int xw_blocked, float *h, float *c,
-                                      float *out, float *pp, int *used) {
+                                      float *out, float *pp, int x3, int *used) {
     *used = 0;
     const int G = r->cell, H = r->H, T = r->T;
     if ((H & 3) || T < 1 || nb < 1) return 0;
@@ -337,7 +372,8 @@ extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, cons
     cudaStream_t st = nntk_stream();
     const int n_tiles = (H + R_UT - 1) / R_UT;
     const int n_rows = n_tiles * G * R_UT;
-    const int ldbt = H;   // multiple of 4
+    const int kpad = (H + R_BK - 1) / R_BK * R_BK;
+    const int ldbt = x3 ? 3 * kpad : H;   // multiple of 4
     const size_t need = (size_t)n_rows * ldbt + n_rows + 64;
     if (need > g_rtc_floats) {
         NNTK_CUDA_TRY(cudaStreamSynchronize(st));
@@ -355,12 +391,13 @@ extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, cons
     const int SG = NNTK_ACT_SIGMOID, TH = NNTK_ACT_TANH;
     const bool def = (G == 3) ? (r->act[0] == SG && r->act[1] == SG && r->act[2] == TH)
                               : (r->act[0] == SG && r->act[1] == SG && r->act[2] == TH && r->act[3] == SG && r->act[4] == TH);
-    const bool h16 = want_h16 && def && (H % 8 == 0);
+    const bool h16 = !x3 && want_h16 && def && (H % 8 == 0);
     const int es = h16 ? 2 : 4;
     {
         long long total = (long long)n_rows * ldbt;
         int blocks = (int)((total + 255) / 256 < 2048 ? (total + 255) / 256 : 2048);
-        if (h16) pack_recurrent_weights_h16_kernel<<<blocks, 256, 0, st>>>(r->d_U, add_bh ? r->d_bh : nullptr, reinterpret_cast<__half *>(Bt), bhp, H, G, ldbt, n_rows);
+        if (x3) pack_recurrent_weights_x3_kernel<<<blocks, 256, 0, st>>>(r->d_U, add_bh ? r->d_bh : nullptr, Bt, bhp, H, G, kpad, n_rows);
+        else if (h16) pack_recurrent_weights_h16_kernel<<<blocks, 256, 0, st>>>(r->d_U, add_bh ? r->d_bh : nullptr, reinterpret_cast<__half *>(Bt), bhp, H, G, ldbt, n_rows);
         else pack_recurrent_weights_kernel<<<blocks, 256, 0, st>>>(r->d_U, add_bh ? r->d_bh : nullptr, Bt, bhp, H, G, ldbt, n_rows);
         NNTK_LAUNCH_CHECK("pack_recurrent_weights_kernel");
     }
@@ -372,8 +409,13 @@ extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, cons
         const long long n = (long long)nb * H;
         to_half_kernel<<<(unsigned)((n + 255) / 256 < 2048 ? (n + 255) / 256 : 2048), 256, 0, st>>>(h, reinterpret_cast<__half *>(hr) + n, n);
         NNTK_LAUNCH_CHECK("to_half_kernel");
+    } else if (x3) {
+        // operand ping-pong [2 steps][hi, lo][nb][H]; step 0 reads slot pair 1 like every odd step
+        const long long n = (long long)nb * H;
+        split_state_kernel<<<(unsigned)((n + 255) / 256 < 2048 ? (n + 255) / 256 : 2048), 256, 0, st>>>(h, hr + 2 * n, hr + 3 * n, n);
+        NNTK_LAUNCH_CHECK("split_state_kernel");
     } else if ((rc = encode_h_map(encode, &m_state, h, H, 1, H, nb, H))) return rc;
-    if ((rc = encode_h_map(encode, &m_hr, hr, H, 2, (long long)nb * H, nb, H, h16))) return rc;
+    if ((rc = encode_h_map(encode, &m_hr, hr, H, x3 ? 4 : 2, (long long)nb * H, nb, H, h16))) return rc;
     {
         cuuint64_t dims[2] = {(cuuint64_t)ldbt, (cuuint64_t)n_rows};
         cuuint64_t strides[1] = {(cuuint64_t)ldbt * es};
@@ -389,7 +431,9 @@ extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, cons
     }
     RtcParams p;
     p.B = nb; p.H = H; p.n_tiles = n_tiles; p.m_tiles = (nb + R_BM - 1) / R_BM;
-    p.k_blocks = h16 ? (H + 2 * R_BK - 1) / (2 * R_BK) : (H + R_BK - 1) / R_BK;
+    p.kb_pass = h16 ? (H + 2 * R_BK - 1) / (2 * R_BK) : (H + R_BK - 1) / R_BK;
+    p.k_blocks = x3 ? 3 * p.kb_pass : p.kb_pass;
+    p.part_stride = (long long)nb * H;
     p.total_tiles = p.n_tiles * p.m_tiles;
     p.bh = add_bh ? bhp : nullptr;
     p.ld_xw = xw_blocked ? 0 : (long long)T * G * H;
@@ -399,21 +443,23 @@ extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, cons
     for (int i = 0; i < 5; ++i) { p.act[i] = r->act[i]; p.act_a[i] = r->act_a[i]; }
     for (int t = 0; t < T; ++t) {
         const CUtensorMap *ma;
-        if (t == 0 && h16) { ma = &m_hr; p.a_t = 1; p.h_prev = h; p.ld_prev = H; p.comp = 1.0f; }
+        const float x3_comp = 1.0f + 2.06e-9f * (float)H;   // truncating accumulate, see gemm_tc.cu (X3_ACC_TRUNC_PER_K)
+        if (t == 0 && x3) { ma = &m_hr; p.a_t = 1; p.h_prev = h; p.ld_prev = H; p.comp = x3_comp; }
+        else if (t == 0 && h16) { ma = &m_hr; p.a_t = 1; p.h_prev = h; p.ld_prev = H; p.comp = 1.0f; }
         else if (t == 0) { ma = &m_state; p.a_t = 0; p.h_prev = h; p.ld_prev = H; p.comp = 1.0f + TF32_TRUNC_BIAS; }
         else {
-            ma = &m_hr; p.a_t = (t - 1) & 1; p.comp = 1.0f;
+            ma = &m_hr; p.a_t = (t - 1) & 1; p.comp = x3 ? x3_comp : 1.0f;
             if (r->return_sequences) { p.h_prev = out + (long long)(t - 1) * H; p.ld_prev = (long long)T * H; }
             else { p.h_prev = pp + (size_t)((t - 1) & 1) * nb * H; p.ld_prev = H; }
         }
         if (r->return_sequences) { p.h_next = out + (long long)t * H; p.ld_next = (long long)T * H; }
         else { p.h_next = pp + (size_t)(t & 1) * nb * H; p.ld_next = H; }
         p.hr_next = h16 ? reinterpret_cast<float *>(reinterpret_cast<__half *>(hr) + (size_t)(t & 1) * nb * H)
-                        : hr + (size_t)(t & 1) * nb * H;
+                        : hr + (size_t)(t & 1) * (x3 ? 2 : 1) * nb * H;
         p.xw = xw_blocked ? xw + (long long)t * p.row_blocks * 32 * G * H : xw + (long long)t * G * H;
         if (G == 1) rc = launch_rtc<1, 6, false>(*ma, mb, p, st);
-        else if (G == 3) rc = h16 ? launch_rtc<3, 4, true>(*ma, mb, p, st) : launch_rtc<3, 4, false>(*ma, mb, p, st);
-        else rc = h16 ? launch_rtc<4, 4, true>(*ma, mb, p, st) : launch_rtc<4, 4, false>(*ma, mb, p, st);
+        else if (G == 3) rc = x3 ? launch_rtc<3, 4, false, true>(*ma, mb, p, st) : h16 ? launch_rtc<3, 4, true>(*ma, mb, p, st) : launch_rtc<3, 4, false>(*ma, mb, p, st);
+        else rc = x3 ? launch_rtc<4, 4, false, true>(*ma, mb, p, st) : h16 ? launch_rtc<4, 4, true>(*ma, mb, p, st) : launch_rtc<4, 4, false>(*ma, mb, p, st);
         if (rc) return rc;
     }
     NNTK_LAUNCH_CHECK("recurrent_tc_step_kernel");

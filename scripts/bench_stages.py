@@ -2,7 +2,7 @@
 """Per-stage timing of the hot path at the BASELINE.json config shapes (C1, C3, C4, C5), CUDA events on the library
 stream, device-resident buffers, weights frozen.  One JSON line per stage.  Development tool -- bench.py is the contract.
 
-    python scripts/bench_stages.py [--stage c1|c3|c4|c5|f1|f2|f4|all] [--mode fp32|tf32] [--batch-scale 0.25] [--iters 3]
+    python scripts/bench_stages.py [--stage c1|c3|c4|c5|f1|f2|f4|all] [--mode fp32|tf32|x3] [--batch-scale 0.25] [--iters 3]
 """
 from __future__ import annotations
 
@@ -167,14 +167,14 @@ def f2(lib, args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--stage", default="all")
-    ap.add_argument("--mode", default="fp32", choices=["fp32", "tf32"])
+    ap.add_argument("--mode", default="fp32", choices=["fp32", "tf32", "x3"])
     ap.add_argument("--batch-scale", type=float, default=1.0)
     ap.add_argument("--iters", type=int, default=3)
     args = ap.parse_args()
     lib = nn.lib()
     assert lib.NNTKInit(0) == 0, lib.NNTKLastError()
     lib.NNTKSetStream(torch.cuda.current_stream().cuda_stream)
-    assert lib.NNTKSetMathMode(1 if args.mode == "tf32" else 0) == 0
+    assert lib.NNTKSetMathMode({"fp32": 0, "tf32": 1, "x3": 2}[args.mode]) == 0
     for name, fn in (("c1", c1), ("c3", c3), ("c4", c4), ("c5", c5), ("f1", f1), ("f2", f2), ("f4", f4)):
         if args.stage == name or (args.stage == "all" and name[0] == "c"):
             fn(lib, args)

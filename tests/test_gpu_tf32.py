@@ -147,9 +147,10 @@ def test_cluster_kernel_streaming_state_matches_one_shot(tf32):
     assert_parity(np.concatenate([a, b], 1), want, tol=1e-6, what="cluster kernel streaming state")
 
 
-# ---- NNTK_MATH_TF32X3: tcgen05 with hi/lo operand split (three passes in one K loop).  Operand error drops to ~2^-22, what
-# remains is the tensor core's truncating fp32 accumulate (grows with K): stated tolerance 3e-5 (the FFMA mode holds 1e-5).
-X3_TOL = 3e-5
+# ---- NNTK_MATH_TF32X3: tcgen05 with hi/lo operand split (three passes in one K loop).  Operand error drops to ~2^-22; the
+# tensor core's truncating fp32 accumulate (a shrink linear in K) is compensated in the epilogue: the mode holds the fp32
+# contract, 1e-5.
+X3_TOL = helpers.FP32_TOL
 @pytest.fixture()
 def x3(cuda, product):
     assert product.NNTKSetMathMode(2) == 0
@@ -158,7 +159,8 @@ def x3(cuda, product):
 
 
 @pytest.mark.parametrize("cin,cout,k,s,T,B", [(128, 256, 5, 1, 300, 3), (64, 96, 3, 2, 257, 2), (256, 256, 5, 1, 130, 2),
-                                              (16, 8, 1, 1, 40, 1), (20, 40, 3, 1, 50, 2), (257, 64, 5, 1, 60, 2)])
+                                              (16, 8, 1, 1, 40, 1), (20, 40, 3, 1, 50, 2), (257, 64, 5, 1, 60, 2),
+                                              (512, 256, 5, 1, 40, 2), (1024, 128, 7, 1, 30, 1)])   # K = 2 560; 7 168 (> 3 072: FFMA)
 def test_conv1d_3xtf32(x3, ref, cin, cout, k, s, T, B):
     rng = np.random.default_rng(3)
     x = rng.standard_normal((B, T, cin)).astype(np.float32)
@@ -187,3 +189,20 @@ def test_dense_tdd_and_recurrent_3xtf32(x3, ref):
         outs.append(r.apply(v)); r.close()
     g = L.Recurrent(x3, "gru", 64, 128, 20); helpers.fill_recurrent(g, 440)
     assert_parity(g.apply_batch(xs)[:3], np.stack(outs), tol=X3_TOL, what="gru 3xTF32 projection + fp32 steps")
+
+
+@pytest.mark.parametrize("cell,in_size,H,T,B,rs", [("gru", 64, 128, 40, 300, True), ("lstm", 96, 256, 120, 260, True),
+                                                   ("lstm", 512, 512, 200, 257, True), ("gru", 40, 264, 60, 290, False),
+                                                   ("lstm", 32, 68, 300, 270, True)])
+def test_recurrent_steps_3xtf32_hold_the_fp32_contract(x3, ref, cell, in_size, H, T, B, rs):
+    """TF32X3 mode, batch > 256: projection AND per-step GEMM run on the tensor cores with hi/lo split operands
+    (csrc/recurrent_tc.cu, X3), gate math with expf / tanhf -- checked at the fp32 tolerance, 1e-5"""
+    rng = np.random.default_rng(T)
+    xs = rng.standard_normal((B, T, in_size)).astype(np.float32)
+    g = L.Recurrent(x3, cell, in_size, H, T, rs); helpers.fill_recurrent(g, 470)
+    got = g.apply_batch(xs)
+    for b in (0, B // 2, B - 1):
+        r = L.Recurrent(ref, cell, in_size, H, T, rs); helpers.copy_weights(r, g)
+        assert_parity(got[b], r.apply(xs[b]), tol=X3_TOL, what=f"{cell} 3xTF32 steps, sequence {b}")
+        r.close()
+    g.close()
