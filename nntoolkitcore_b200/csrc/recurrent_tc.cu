@@ -13,7 +13,8 @@
 //     warpgroups (each thread owns one batch row and 32 of the tile's 64 units); two TMEM accumulator buffers let the
 //     epilogue of tile i overlap the MMAs of tile i+1.  Persistent over the (B/128) x (H/64) tiles of the step.
 // Operands are TF32 (A truncated by the tensor core and bias-compensated, see tc_common.cuh), accumulation and all gate
-// math fp32: 1e-3 parity class.  The fp32 (1e-5) mode never comes here.
+// math fp32: 1e-3 parity class.  The X3 variant (NNTK_MATH_TF32X3: hi/lo split operands, three passes, expf / tanhf gate
+// math) holds the fp32 contract, 1e-5; the plain FP32 mode never comes here.
 #include <stdlib.h>
 #include <cuda_fp16.h>
 #include "tc_common.cuh"
