@@ -40,38 +40,84 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """SM clock + throttle reasons DURING the timed region (B200_PROFILING.md recipe).  Sampled in-process through NVML --
+    the library nvidia-smi itself queries -- every 2 ms, because the timed region of the default run is ~20 ms and an
+    `nvidia-smi -lms 100` child does not even start that fast on an 8-GPU box (it produced no sample there); the
+    nvidia-smi child is kept as the fallback when NVML cannot be imported.  Only samples between mark_start() and
+    mark_end() are summarised."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.h, self.stop = index, [], None, None, False
+        self.t0 = self.t1 = None
+        self.source = None
 
     def __enter__(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE, text=True)
-            threading.Thread(target=self._read, daemon=True).start()
-        except OSError:
-            self.proc = None
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[self.index]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else self.index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nv = pynvml
+            self.mx = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.source = "nvml"
+            threading.Thread(target=self._poll, daemon=True).start()
+        except Exception:
+            self.h = None
+            try:
+                self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                              "--format=csv,noheader,nounits", "-lms", "20"], stdout=subprocess.PIPE, text=True)
+                self.source = "nvidia-smi"
+                threading.Thread(target=self._read, daemon=True).start()
+            except OSError:
+                self.proc = None
         return self
 
+    def _poll(self):
+        nv = self.nv
+        bits = [("hw_slowdown", nv.nvmlClocksEventReasonHwSlowdown if hasattr(nv, "nvmlClocksEventReasonHwSlowdown") else 0x8),
+                ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4)]
+        while not self.stop:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                get = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+                mask = int(get(self.h))
+                self.rows.append((time.perf_counter(), sm, self.mx, [n for n, b in bits if mask & b]))
+            except Exception:
+                pass
+            time.sleep(0.002)
+
     def _read(self):
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            c = [v.strip() for v in line.split(",")]
+            if len(c) >= 6 and c[0].isdigit() and c[1].isdigit():
+                self.rows.append((time.perf_counter(), int(c[0]), int(c[1]),
+                                  [n for n, v in zip(names, c[2:6]) if v.lower().startswith("active")]))
+
+    def mark_start(self):
+        self.t0 = time.perf_counter()
+
+    def mark_end(self):
+        self.t1 = time.perf_counter()
 
     def __exit__(self, *a):
+        self.stop = True
         if self.proc:
-            time.sleep(0.15)
             self.proc.terminate()
 
     def summary(self):
-        sm = [int(r[0]) for r in self.rows if len(r) >= 6 and r[0].isdigit()]
-        mx = [int(r[1]) for r in self.rows if len(r) >= 6 and r[1].isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
-        return {"sm_mhz": int(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(sm)}
+        t0, t1 = self.t0 or 0.0, self.t1 or float("inf")
+        rows = [r for r in self.rows if t0 <= r[0] <= t1]
+        window = "timed region"
+        if not rows:   # region shorter than one sampling period: the samples taken under the same load just around it
+            rows = [r for r in self.rows if t0 - 0.05 <= r[0] <= t1 + 0.05]
+            window = "timed region +-50 ms"
+        sm = [r[1] for r in rows]
+        return {"sm_mhz": int(np.median(sm)) if sm else None, "sm_max_mhz": max(r[2] for r in rows) if rows else None,
+                "reasons": sorted({n for r in rows for n in r[3]}), "samples": len(sm), "source": self.source, "window": window}
 
 
 def c2_pool(n_pool, n):
@@ -131,6 +177,15 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # one process per GPU: keep this rank's threads (and so its pinned host buffers, first touch) on the GPU's own
+        # NUMA node -- the e2e leg moves 6.8 GB per step per GPU through host memory
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local))
+        except Exception:
+            pass
+    if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     lib = nn.lib()      # raises if the CUDA library is not built: there is no fallback
     assert lib.NNTKInit(local) == 0, lib.NNTKLastError()
@@ -178,12 +233,16 @@ def run_ours(args):
     barrier()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     with ClockSampler(local) as clk:
+        for _ in range(2):      # the sampler thread is already polling while the GPU runs the same load
+            step()
         barrier()
+        clk.mark_start()
         ev[0].record(stream)
         for i in range(args.steps):
             step()
             ev[i + 1].record(stream)
         barrier()
+        clk.mark_end()
     total_ms = ev[0].elapsed_time(ev[-1])
     per_launch_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
     t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
