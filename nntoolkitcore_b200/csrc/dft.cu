@@ -10,6 +10,7 @@
 //   every nfft the reference accepts, not tuned).
 // HBM roofline: 16 bytes per complex point (read re, im; write re, im).
 #include "common.cuh"
+#define NNTK_SPEC_PACKED 1   // complex adds / subtracts of the butterflies as sm_100 FADD2 / FFMA2 (spectrogram_core.h)
 #include "spectrogram_core.h"
 
 namespace {

@@ -18,6 +18,7 @@
 //
 // HBM roofline: algorithmic bytes per clip = 4*input_size + 4*ntime*nfreq.
 #include "common.cuh"
+#define NNTK_SPEC_PACKED 1   // complex adds / subtracts of the butterflies as sm_100 FADD2 / FFMA2 (spectrogram_core.h)
 #include "spectrogram_core.h"
 
 namespace {
@@ -116,7 +117,10 @@ __device__ __forceinline__ void tile_load_async(const SpecParams &p, const TileG
 // spectra in its (idle) exchange buffer as (a, b) pairs, every lane walks its share of the mel table's non-zeros
 // (`mel`: [mel_iter][32] entries {bin | last << 9 | band << 10, weight}, balanced on the host), emits
 // log(sum + log_offset) per band, and the warp stores 2 x n_mels contiguous floats.  The spectrogram never reaches HBM.
-template <bool FULLWIN, int MODE, bool MEL>
+// HOP5 = step / 32 when the hop is 160 (the BASELINE framing), else 0: lane L reads x[L + 32 j], so with a hop of 5 * 32 the
+// second frame's element j IS the first frame's element j + 5 -- 21 shared-memory loads per frame pair instead of 32 (the
+// kernel is LSU-wavefront bound: 180 wavefronts per pair, ncu r1).
+template <bool FULLWIN, int MODE, bool MEL, int HOP5>
 __global__ void __launch_bounds__(SPEC_THREADS, 2)
 spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const float2 *__restrict__ tw512,
                       const float *__restrict__ in, float *__restrict__ out, const uint2 *__restrict__ mel) {
@@ -191,14 +195,31 @@ spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const floa
             const float *xa = buf + fa * p.step;
             const float *xb = has_b ? xa + p.step : xa;
             float2 v[16];
+            if (HOP5 > 0) {
+                float r[16 + HOP5];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                float a = 0.0f, b = 0.0f;
-                if (FULLWIN || lane + 32 * j < p.window_size) {
-                    a = xa[32 * j];
-                    b = xb[32 * j];
+                for (int k = 0; k < 16 + HOP5; ++k) {
+                    const bool as_a = k < 16 && (FULLWIN || lane + 32 * k < p.window_size);
+                    const bool as_b = k >= HOP5 && has_b && (FULLWIN || lane + 32 * (k - HOP5) < p.window_size);
+                    r[k] = (as_a || as_b) ? xa[32 * k] : 0.0f;
                 }
-                v[j] = make_float2(w[j] * a, w[j] * b);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const bool in_win = FULLWIN || lane + 32 * j < p.window_size;
+                    const float a = in_win ? r[j] : 0.0f;
+                    const float b = has_b ? (in_win ? r[j + HOP5] : 0.0f) : a;
+                    v[j] = make_float2(w[j] * a, w[j] * b);
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    float a = 0.0f, b = 0.0f;
+                    if (FULLWIN || lane + 32 * j < p.window_size) {
+                        a = xa[32 * j];
+                        b = xb[32 * j];
+                    }
+                    v[j] = make_float2(w[j] * a, w[j] * b);
+                }
             }
             spec_pass1(v, lc);
             spec_xchg1_store(v, x1_st);
@@ -426,13 +447,17 @@ static int spectrogram_run(const nntk_spectrogram_args *a, const nntk_mel_args *
         p.n_clips = n_clips;
         const bool fullwin = a->window_size == NNTK_SPEC_N;
         typedef void (*SpecKernel)(SpecParams, const float *, const float2 *, const float *, float *, const uint2 *);
-        static const SpecKernel kernels[8] = {
-            spectrogram512_kernel<false, 0, false>, spectrogram512_kernel<true, 0, false>,
-            spectrogram512_kernel<false, 1, false>, spectrogram512_kernel<true, 1, false>,
-            spectrogram512_kernel<false, 0, true>,  spectrogram512_kernel<true, 0, true>,
-            spectrogram512_kernel<false, 1, true>,  spectrogram512_kernel<true, 1, true>};
-        static size_t attr_bytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        const int ki = (m ? 4 : 0) + (a->mode ? 2 : 0) + (fullwin ? 1 : 0);
+        static const SpecKernel kernels[16] = {
+            spectrogram512_kernel<false, 0, false, 0>, spectrogram512_kernel<true, 0, false, 0>,
+            spectrogram512_kernel<false, 1, false, 0>, spectrogram512_kernel<true, 1, false, 0>,
+            spectrogram512_kernel<false, 0, true, 0>,  spectrogram512_kernel<true, 0, true, 0>,
+            spectrogram512_kernel<false, 1, true, 0>,  spectrogram512_kernel<true, 1, true, 0>,
+            spectrogram512_kernel<false, 0, false, 5>, spectrogram512_kernel<true, 0, false, 5>,
+            spectrogram512_kernel<false, 1, false, 5>, spectrogram512_kernel<true, 1, false, 5>,
+            spectrogram512_kernel<false, 0, true, 5>,  spectrogram512_kernel<true, 0, true, 5>,
+            spectrogram512_kernel<false, 1, true, 5>,  spectrogram512_kernel<true, 1, true, 5>};
+        static size_t attr_bytes[16] = {0};
+        const int ki = (a->step == 160 ? 8 : 0) + (m ? 4 : 0) + (a->mode ? 2 : 0) + (fullwin ? 1 : 0);
         const SpecKernel kern = kernels[ki];
         if (bytes > attr_bytes[ki]) {
             NNTK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
