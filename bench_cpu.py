@@ -48,6 +48,22 @@ def _c2_units(first, count, cfg):
     return dt
 
 
+def _f1_units(first, count, cfg):
+    """row f1: LogMelSpectrogram (80 bands, 20 Hz .. 8 kHz) on the C2 framing, one 10-s clip per unit"""
+    from nntoolkitcore_b200 import layers as L
+    ref = _ref()
+    s = L.Spectrogram(ref, cfg["nfft"], cfg["window_size"], cfg["noverlap"], cfg["input_size"], 1.0, "hann_window")
+    f = L.LogMelSpectrogram(ref, s, 80, 16000, 20.0, 8000.0)
+    clips = [_audio(first + i, cfg["input_size"]) for i in range(count)]
+    out = np.empty(f.out_shape, np.float32)
+    t0 = time.perf_counter()
+    for c in clips:
+        f.apply(c, out)
+    dt = time.perf_counter() - t0
+    f.close(); s.close()
+    return dt
+
+
 def _timed(fn, count):
     t0 = time.perf_counter()
     for i in range(count):
@@ -126,8 +142,8 @@ def _c5_units(first, count, cfg):
     return _timed(lambda i: tdd.apply(grus[i][1].apply(grus[i][0].apply(relu.apply(conv.apply(bn.apply(spec.apply(clips[i]))))))), count)
 
 
-UNIT_FNS = {"c1": _c1_units, "c2": _c2_units, "c3": _c3_units, "c4": _c4_units, "c5": _c5_units}
-AUDIO_SEC_PER_UNIT = {"c1": 1.0, "c2": 10.0, "c3": 10.0, "c4": 5.0, "c5": 10.0}
+UNIT_FNS = {"c1": _c1_units, "c2": _c2_units, "c3": _c3_units, "c4": _c4_units, "c5": _c5_units, "f1": _f1_units}
+AUDIO_SEC_PER_UNIT = {"c1": 1.0, "c2": 10.0, "c3": 10.0, "c4": 5.0, "c5": 10.0, "f1": 10.0}
 
 
 def _worker(args):
@@ -158,7 +174,7 @@ if __name__ == "__main__":
     # python bench_cpu.py c1 c3 c4 c5 [--units-per-core K]: one JSON line per config (reference CPU path, all host cores)
     import json
     names = [a for a in sys.argv[1:] if a in UNIT_FNS] or list(UNIT_FNS)
-    per_core = {"c1": 64, "c2": 8, "c3": 1, "c4": 1, "c5": 1}
+    per_core = {"c1": 64, "c2": 8, "c3": 1, "c4": 1, "c5": 1, "f1": 8}
     for nm in names:
         procs = host_cores()
         units = per_core[nm] * procs

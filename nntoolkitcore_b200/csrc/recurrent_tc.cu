@@ -22,8 +22,12 @@
 namespace {
 
 constexpr int R_BM = 128, R_BK = 32, R_UT = 64;     // rows, k per stage, hidden units per N tile
-constexpr int R_THREADS = 320;                      // 10 warps
-constexpr int R_EPI_WARPS = 8;
+// Epilogue warps (plus the TMA warp and the MMA warp): EW / 4 per TMEM lane quarter, each owning 64 / (EW / 4) units of the tile.
+// The fp16 / TF32 variants run 8 (32 units per thread, 8-unit chunks: more warps did not help them, 54.1 -> 55.9 ms on C4);
+// the X3 variant's expf / tanhf / IEEE-divide gate math is several times longer, and 16 warps (16 units per thread, 4-unit
+// chunks to fit 96 registers) took C4 from 159 to 110 ms.
+__host__ __device__ constexpr int rtc_epi_warps(bool x3) { return x3 ? 16 : 8; }
+__host__ __device__ constexpr int rtc_threads(bool x3) { return 64 + 32 * rtc_epi_warps(x3); }
 
 struct RtcParams {
     int B, H, n_tiles, m_tiles, k_blocks, total_tiles;
@@ -65,6 +69,16 @@ __device__ __forceinline__ void tc_ld_32x8(uint32_t taddr, float (&r)[8]) {
     for (int i = 0; i < 8; ++i) r[i] = __uint_as_float(u[i]);
 }
 
+__device__ __forceinline__ void tc_ld_chunk(uint32_t taddr, float (&r)[8]) { tc_ld_32x8(taddr, r); }
+__device__ __forceinline__ void tc_ld_chunk(uint32_t taddr, float (&r)[4]) {
+    uint32_t u[4];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]) : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 4; ++i) r[i] = __uint_as_float(u[i]);
+}
+
 // default gate activations compiled in when DEF (the run-time kind switch per call tripled the epilogue's instruction count;
 // ncu r1: the per-step kernel ran at 0.53 IPC on ~5000 instructions per thread per tile -- the epilogue, not TMA or MMA)
 // X3 (the fp32-contract mode): expf / tanhf / IEEE division like the FFMA kernels (common.cuh), never the MUFU forms.
@@ -81,7 +95,7 @@ __device__ __forceinline__ float rt_act(const RtcParams &p, int slot, float x) {
 // [lo | hi | hi] along K, three passes hi*Ulo, lo*Uhi, hi*Uhi in one K loop (small passes first); the accumulate truncation is
 // compensated through p.comp like in gemm_tc.cu.  Operand error ~2^-22: the recurrence holds the fp32 contract (1e-5).
 template <int G, int STAGES, bool H16, bool X3>
-__global__ void __launch_bounds__(R_THREADS, 1)
+__global__ void __launch_bounds__(rtc_threads(X3), 1)
 recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, RtcParams p) {
     using SL = RtcSmem<G, STAGES>;
     constexpr int BN = SL::BN;
@@ -93,6 +107,7 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
     uint64_t *tmem_empty = tmem_full + 2;         // [2]
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_empty + 2);
 
+    constexpr int R_EPI_WARPS = rtc_epi_warps(X3), R_EPI_UNITS = R_UT / (R_EPI_WARPS / 4);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
@@ -156,11 +171,11 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
         // from HBM (xw, c, h_{t-1}) is independent of the accumulator, so it is loaded one chunk AHEAD -- the first chunk
         // even before the tile's MMAs have finished -- and the load latency hides behind the previous chunk's gate math.
         const int q = warp & 3;                       // TMEM lane quarter this warp may read
-        const int half = (warp - 2) >> 2;             // which 32 units of the tile's 64
+        const int half = (warp - 2) >> 2;             // which R_EPI_UNITS units of the tile's 64
         const int row_in_tile = q * 32 + lane;
         const float comp = p.comp;
-        constexpr int CH = 8, NCH = 32 / CH;
-        struct Pre { float4 xv[G][2]; float4 st[2]; };    // st: c (LSTM) or h_{t-1} (GRU)
+        constexpr int CH = X3 ? 4 : 8, NCH = R_EPI_UNITS / CH, NV = CH / 4;
+        struct Pre { float4 xv[G][NV]; float4 st[NV]; };    // st: c (LSTM) or h_{t-1} (GRU)
         uint32_t it = 0;
         for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
             const int n_t = tile % p.n_tiles, m_t = tile / p.n_tiles;
@@ -168,7 +183,7 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
             const int row = m_t * R_BM + row_in_tile;
             const bool row_ok = row < p.B;
             const long long rr = row_ok ? row : 0;
-            const int ubase = n_t * R_UT + half * 32;          // first hidden unit of this thread
+            const int ubase = n_t * R_UT + half * R_EPI_UNITS; // first hidden unit of this thread
             const float *xw = p.xw + rr * p.ld_xw + ubase;
             // blocked layout: float4 slot of (row, column n) = ((row / 32) * (G*H/4) + n / 4) * 32 + row % 32
             const float4 *xwb = reinterpret_cast<const float4 *>(p.xw) + ((rr >> 5) * (long long)((G * p.H) >> 2) + (ubase >> 2)) * 32 + (rr & 31);
@@ -176,10 +191,10 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
             float *hn = p.h_next + rr * p.ld_next + ubase;
             float *hr = p.hr_next + rr * p.H + ubase;
             float *cw = (G == 4) ? p.c + rr * p.H + ubase : nullptr;
-            const float *bh = p.bh ? p.bh + n_t * BN + half * 32 : nullptr;
+            const float *bh = p.bh ? p.bh + n_t * BN + half * R_EPI_UNITS : nullptr;
             auto prefetch = [&](int ch, Pre &P) {
 #pragma unroll
-                for (int v = 0; v < 2; ++v) {
+                for (int v = 0; v < NV; ++v) {
                     const int u = ch * CH + 4 * v;
                     const bool ok = row_ok && ubase + u < p.H && !(p.dbg & 1);
 #pragma unroll
@@ -194,16 +209,16 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
             prefetch(0, cur);
             mbar_wait(&tmem_full[buf], use & 1);
             tc_fence_after();
-            const uint32_t taddr = tmem_base + buf * SL::ACC_STRIDE + ((uint32_t)(q * 32) << 16) + half * 32;
+            const uint32_t taddr = tmem_base + buf * SL::ACC_STRIDE + ((uint32_t)(q * 32) << 16) + half * R_EPI_UNITS;
 #pragma unroll
             for (int ch = 0; ch < NCH; ++ch) {
                 Pre nxt;
                 if (ch + 1 < NCH) prefetch(ch + 1, nxt);
                 float acc[G][CH];
 #pragma unroll
-                for (int g = 0; g < G; ++g) tc_ld_32x8(taddr + g * R_UT + ch * CH, acc[g]);
+                for (int g = 0; g < G; ++g) tc_ld_chunk(taddr + g * R_UT + ch * CH, acc[g]);
 #pragma unroll
-                for (int v = 0; v < 2; ++v) {
+                for (int v = 0; v < NV; ++v) {
                     const int u = ch * CH + 4 * v;
                     if (!(row_ok && ubase + u < p.H)) continue;          // H is a multiple of 4
                     float4 bv[G];
@@ -334,7 +349,7 @@ static int launch_rtc(const CUtensorMap &ma, const CUtensorMap &mb, const RtcPar
         attr_done = true;
     }
     const int grid = p.total_tiles < nntk_cuda_sm_count() ? p.total_tiles : nntk_cuda_sm_count();
-    recurrent_tc_step_kernel<G, STAGES, H16, X3><<<grid, R_THREADS, SL::TOTAL, st>>>(ma, mb, p);
+    recurrent_tc_step_kernel<G, STAGES, H16, X3><<<grid, rtc_threads(X3), SL::TOTAL, st>>>(ma, mb, p);
     return 0;
 }
 

@@ -202,7 +202,15 @@ extern "C" int nntk_cuda_staged_run(const void *h_in, void *h_out, size_t unit_i
     if (rc) return rc;
     Stage &s = g_stage;
     cudaStream_t saved = g_stream;
-    // the caller's stream may hold work that produced nothing we depend on (host inputs), so no cross-stream wait
+    // The inputs come from the host, but the layer's WEIGHTS were just staged (H2D + repack kernels) on the caller's stream,
+    // and the pipeline streams are non-blocking: without this edge the first chunk's kernels could run before the weights
+    // had landed (seen once in ~30 runs of the GPU tests as an all-zero conv output: weights, bias and BatchNorm table still
+    // zero).  One event on the caller's stream, waited for by the compute stream.
+    {
+        cudaError_t e = cudaEventRecord(s.in_free[0], saved);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(s.s_run, s.in_free[0], 0);
+        if (e != cudaSuccess) { nntk_cuda_set_error(NNTK_ERR_CUDA_, "staged pipeline: %s", cudaGetErrorString(e)); return NNTK_ERR_CUDA_; }
+    }
     int result = 0;
     long long n_chunks = (n_units + chunk - 1) / chunk;
     for (long long i = 0; i < n_chunks && result == 0; ++i) {
