@@ -12,6 +12,7 @@ int g_device = -1;            // -1: not initialised
 int g_sm_count = 0;
 cudaStream_t g_stream = 0;    // legacy default stream unless the caller sets one
 int g_math_mode = 0;
+bool g_math_mode_set = false;
 thread_local char t_err[512] = {0};
 thread_local int t_err_code = 0;
 
@@ -84,9 +85,18 @@ extern "C" int nntk_cuda_sync(void) {
 extern "C" int nntk_cuda_set_math_mode(int mode) {
     if (mode < 0 || mode > 2) { nntk_cuda_set_error(NNTK_ERR_ARG_, "math mode %d unknown", mode); return NNTK_ERR_ARG_; }
     g_math_mode = mode;
+    g_math_mode_set = true;
     return 0;
 }
-extern "C" int nntk_cuda_math_mode(void) { return g_math_mode; }
+// The process-wide default comes from NNTK_MATH_MODE (0 FP32, 1 TF32, 2 TF32X3) until NNTKSetMathMode is called.
+extern "C" int nntk_cuda_math_mode(void) {
+    static bool env_read = false;
+    if (!env_read) {
+        env_read = true;
+        if (const char *e = getenv("NNTK_MATH_MODE")) { const int m = atoi(e); if (m >= 0 && m <= 2 && !g_math_mode_set) g_math_mode = m; }
+    }
+    return g_math_mode;
+}
 
 extern "C" int nntk_cuda_malloc(void **d_ptr, size_t bytes) {
     *d_ptr = nullptr;
