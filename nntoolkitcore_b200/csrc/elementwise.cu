@@ -110,11 +110,13 @@ inline unsigned grid_for(long long work_items, int per_block) {
 }
 
 
-// Any C (e.g. the 257 frequency bins of C5) with 16-byte accesses: float4 i covers elements 4i..4i+3 whose channels are
-// (4i + e) mod C, tracked by a running index.  gamma | beta | mean | sd sit in shared memory; sd = sqrtf(var + eps) is
+// Any C (e.g. the 257 frequency bins of C5).  gamma | beta | mean | sd sit in shared memory; sd = sqrtf(var + eps) is
 // evaluated once per channel -- the same fp32 value the reference recomputes for every row (batch_norm.c:153-156).
+// Lane = consecutive element: a warp instruction moves 128 contiguous bytes AND reads 32 consecutive table entries
+// (conflict-free).  (The first version gave each thread a float4: lanes were 4 channels apart, every table read was a
+// 4-way bank conflict and the kernel ran at 0.64 of the HBM peak.)  Four independent elements per thread and iteration.
 __global__ void __launch_bounds__(256) batch_norm_any_kernel(const float *__restrict__ prm, int C, float eps,
-                                                             const float *__restrict__ in, float *__restrict__ out,
+                                                             const float *in, float *out,   // in == out is legal
                                                              long long total) {
     extern __shared__ float tab[];       // [4][C]
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
@@ -123,25 +125,26 @@ __global__ void __launch_bounds__(256) batch_norm_any_kernel(const float *__rest
     }
     __syncthreads();
     const float *gamma = tab, *beta = tab + C, *mean = tab + 2 * C, *sd = tab + 3 * C;
-    const long long stride = (long long)gridDim.x * blockDim.x, nvec = total >> 2;
-    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    int c = (int)((4 * i) % C);
-    const int step = (int)((4 * stride) % C);
-    for (; i < nvec; i += stride) {
-        float4 x = ld_stream(reinterpret_cast<const float4 *>(in) + i);
-        float *xe = &x.x;
-        int ce = c;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int step = (int)(stride % C);
+    int c = (int)(t % C);
+    for (; t + 3 * stride < total; t += 4 * stride) {
+        float x[4];
+        int ce[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-            xe[e] = __fadd_rn(__fmul_rn(__fdiv_rn(__fsub_rn(xe[e], mean[ce]), sd[ce]), gamma[ce]), beta[ce]);
-            if (++ce == C) ce = 0;
+            x[e] = in[t + e * stride];
+            ce[e] = c;
+            c += step; if (c >= C) c -= C;
         }
-        st_stream(reinterpret_cast<float4 *>(out) + i, x);
-        c += step; if (c >= C) c -= C;
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+            out[t + e * stride] = __fadd_rn(__fmul_rn(__fdiv_rn(__fsub_rn(x[e], mean[ce[e]]), sd[ce[e]]), gamma[ce[e]]), beta[ce[e]]);
     }
-    for (long long t = (nvec << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += stride) {
-        const int ct = (int)(t % C);
-        out[t] = __fadd_rn(__fmul_rn(__fdiv_rn(__fsub_rn(in[t], mean[ct]), sd[ct]), gamma[ct]), beta[ct]);
+    for (; t < total; t += stride) {
+        out[t] = __fadd_rn(__fmul_rn(__fdiv_rn(__fsub_rn(in[t], mean[c]), sd[c]), gamma[c]), beta[c]);
+        c += step; if (c >= C) c -= C;
     }
 }
 }  // namespace

@@ -184,12 +184,26 @@ __global__ void __launch_bounds__(256, 2) gemm_fp32_kernel(GemmDev g) {
 }
 
 // [rows][C] -> [rows][Cpad], zero filled: gives rows a 16-byte aligned pitch so TMA can address them (Cin = 257 -> 260)
-__global__ void pad_channels_kernel(const float *__restrict__ in, float *__restrict__ out, long long rows, int C, int Cpad) {
-    const long long total = rows * Cpad;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const long long r = i / Cpad;
-        const int c = (int)(i - r * Cpad);
-        out[i] = c < C ? __ldg(in + r * C + c) : 0.0f;
+__global__ void __launch_bounds__(256) pad_channels_kernel(const float *__restrict__ in, float *__restrict__ out, long long rows, int C, int Cpad) {
+    // one 16-byte store per thread and iteration (Cpad % 4 == 0, out 16-byte aligned); (row, column) advance incrementally
+    const int cp4 = Cpad >> 2;
+    const long long total4 = rows * cp4, stride = (long long)gridDim.x * blockDim.x;
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    long long r = i / cp4;
+    int c4 = (int)(i - r * cp4);
+    const long long dr = stride / cp4;
+    const int dc = (int)(stride - dr * cp4);
+    for (; i < total4; i += stride) {
+        const int c = 4 * c4;
+        const float *src = in + r * C + c;
+        float4 v;
+        v.x = c < C ? __ldg(src) : 0.0f;
+        v.y = c + 1 < C ? __ldg(src + 1) : 0.0f;
+        v.z = c + 2 < C ? __ldg(src + 2) : 0.0f;
+        v.w = c + 3 < C ? __ldg(src + 3) : 0.0f;
+        reinterpret_cast<float4 *>(out)[i] = v;
+        r += dr; c4 += dc;
+        if (c4 >= cp4) { c4 -= cp4; ++r; }
     }
 }
 
@@ -275,8 +289,12 @@ extern "C" int nntk_cuda_pad_channels(const float *d_in, float *d_out, long long
     if (rc) return rc;
     const long long total = rows * Cpad;
     if (total <= 0) return 0;
-    long long blocks = (total + 255) / 256;
-    if (blocks > 148 * 32) blocks = 148 * 32;
+    if ((Cpad & 3) || C > Cpad || (((uintptr_t)d_out) & 15)) {
+        nntk_cuda_set_error(NNTK_ERR_ARG_, "pad_channels: Cpad %d must be a multiple of 4 >= C %d, output 16-byte aligned", Cpad, C);
+        return NNTK_ERR_ARG_;
+    }
+    long long blocks = (total / 4 + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
     pad_channels_kernel<<<(unsigned)blocks, 256, 0, nntk_stream()>>>(d_in, d_out, rows, C, Cpad);
     NNTK_LAUNCH_CHECK("pad_channels_kernel");
     return 0;
