@@ -159,7 +159,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             mbar_wait(&tmem_full[buf], use & 1);
             tc_fence_after();
 #pragma unroll 1
-            for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 32) {
+            constexpr int HALF_COLS = BN >= 64 ? BN / 2 : BN;      // BN = 32: one 32-column chunk, drained by column-half 0 alone
+            for (int c0 = half * HALF_COLS; c0 < (half + 1) * HALF_COLS && c0 < BN; c0 += 32) {
                 const int n0 = n_t * BN + c0;
                 if (n0 >= p.N) break;                       // warp-uniform
                 uint32_t r[32];
@@ -461,7 +462,9 @@ extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_
         A = g_split;
     }
 
-    const int BN = N > 128 ? 256 : 128;
+    // narrow outputs (the 12-wide TDD of C5): a 32-column tile keeps the B stage at 4 KB instead of 16 KB -- with BN = 128 the
+    // zero-padded weight tile was as many bytes per stage as the activations and halved the HBM-bound kernel's input rate
+    const int BN = N > 128 ? 256 : (N > 32 || bf) ? 128 : 32;
     const CUtensorMapDataType dt = bf ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
     CUtensorMap ma, mb;
     {
@@ -506,6 +509,7 @@ extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_
     p.scale = scale; p.shift = shift; p.act = a->act; p.act_a = a->act_a;
     // FAST epilogue: whole 32-column chunks and 16-byte aligned output rows (every BASELINE shape except the 12-wide TDD)
     if (bf) return BN == 256 ? launch_tc<256, 4, true, true>(ma, mb, p, st) : launch_tc<128, 6, true, true>(ma, mb, p, st);
+    if (BN == 32) return fast ? launch_tc<32, 8, true>(ma, mb, p, st) : launch_tc<32, 8, false>(ma, mb, p, st);
     if (BN == 256) return fast ? launch_tc<256, 4, true>(ma, mb, p, st) : launch_tc<256, 4, false>(ma, mb, p, st);
     return fast ? launch_tc<128, 6, true>(ma, mb, p, st) : launch_tc<128, 6, false>(ma, mb, p, st);
 }
