@@ -62,6 +62,12 @@ class ClockSampler:
             self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
             self.nv = pynvml
             self.mx = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            # the first queries after nvmlInit can take tens of ms (seen: no sample at all inside a 17 ms timed region):
+            # pay that here, synchronously, before the polling thread and the timed region start
+            get = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+            for _ in range(3):
+                pynvml.nvmlDeviceGetClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+                get(self.h)
             self.source = "nvml"
             threading.Thread(target=self._poll, daemon=True).start()
         except Exception:
@@ -87,7 +93,7 @@ class ClockSampler:
                 self.rows.append((time.perf_counter(), sm, self.mx, [n for n, b in bits if mask & b]))
             except Exception:
                 pass
-            time.sleep(0.002)
+            time.sleep(0.001)
 
     def _read(self):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
