@@ -335,7 +335,7 @@ __half *g_ht_scratch = nullptr;
 size_t g_ht_halves = 0;
 
 template <int G, int BM, int SL>
-int launch_ht(const CUtensorMap &mu, const HtParams &p, int clusters, size_t smem, cudaStream_t st, bool dry) {
+int launch_ht(const CUtensorMap &mu, const HtParams &p, int clusters, size_t smem, cudaStream_t st, bool dry, int *max_out = nullptr) {
     auto kern = recurrent_cluster_h16_kernel<G, BM, SL>;
     static size_t attr_smem = 0;
     static bool attr_np = false;
@@ -364,6 +364,7 @@ int launch_ht(const CUtensorMap &mu, const HtParams &p, int clusters, size_t sme
         (void)cudaGetLastError();
         return 1;     // this cluster shape cannot be scheduled on this device: not eligible, the caller falls back
     }
+    if (max_out) *max_out = max_clusters;
     if (dry) return 0;
     NNTK_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mu, p));
     return 0;
@@ -383,8 +384,15 @@ static int ht_config(const nntk_recurrent_args *r, int nb, int *BM_, int *SL_, s
     if (C > 16) return 0;
     int BM = 0, SL = 0;
     size_t smem = 0;
-    const int cand[3][2] = {{128, 2}, {64, 2}, {64, 1}};
+    int cand[4][2] = {{128, 2}, {64, 2}, {64, 1}, {0, 0}};
+    static int force_bm = -1, force_sl = 0;
+    if (force_bm < 0) {
+        force_bm = 0;
+        if (const char *e = getenv("NNTK_CLUSTER_H16_FORCE")) { if (sscanf(e, "%d,%d", &force_bm, &force_sl) != 2) force_bm = 0; }
+    }
+    if (force_bm) { cand[0][0] = force_bm; cand[0][1] = force_sl; cand[1][0] = cand[2][0] = 0; }
     for (int i = 0; i < 3 && !BM; ++i) {
+        if (!cand[i][0]) continue;
         const size_t need_smem = (size_t)cand[i][1] * C * cand[i][0] * 64 + (size_t)C * G * 32 * 64 + 96 + (size_t)G * 32 * 4 + 8 * 2048 + 1024;
         if (need_smem <= 227 * 1024) { BM = cand[i][0]; SL = cand[i][1]; smem = need_smem; }
     }
@@ -401,7 +409,7 @@ static int ht_config(const nntk_recurrent_args *r, int nb, int *BM_, int *SL_, s
     return 1;
 }
 
-#define NNTK_HT_DISPATCH(GG, DRY) (BM == 128 ? launch_ht<GG, 128, 2>(mu, p, clusters, smem, st, DRY) \
+#define NNTK_HT_DISPATCH(GG, DRY) (BM == 128 ? (SL == 2 ? launch_ht<GG, 128, 2>(mu, p, clusters, smem, st, DRY) : launch_ht<GG, 128, 1>(mu, p, clusters, smem, st, DRY)) \
                                   : SL == 2 ? launch_ht<GG, 64, 2>(mu, p, clusters, smem, st, DRY) : launch_ht<GG, 64, 1>(mu, p, clusters, smem, st, DRY))
 
 // 1 when nntk_cuda_recurrent_cluster_h16 WILL run this chunk (so the caller may lay the projection out for it), else 0
@@ -466,10 +474,55 @@ extern "C" int nntk_cuda_recurrent_cluster_h16(const nntk_recurrent_args *r, int
     p.bh = ((G == 3) || r->v2) ? r->d_bh : nullptr;
     p.xw = xw; p.h_state = h; p.c_state = c; p.out = out;
     p.xw_blocked = xw_blocked; p.row_blocks = (nb + 31) / 32;
-    const int clusters = (nb + SL * BM - 1) / (SL * BM);
-    int rc = (G == 3) ? NNTK_HT_DISPATCH(3, false) : NNTK_HT_DISPATCH(4, false);
-    if (rc == 1) return 0;
-    if (rc) return rc;
+    // One launch covers `rows` sequences starting at row0 (a multiple of 32) with slices of bm x sl sequences per cluster.
+    auto run = [&](int bm, int sl, int row0, int rows, bool dry, int *max_out) -> int {
+        HtParams q = p;
+        q.B = rows;
+        q.h_state = h + (size_t)row0 * H;
+        q.c_state = c ? c + (size_t)row0 * H : nullptr;
+        q.out = out + (size_t)row0 * (r->return_sequences ? (size_t)T * H : (size_t)H);
+        q.xw = xw_blocked ? xw + (size_t)(row0 / 32) * G * H * 32 : xw + (size_t)row0 * T * G * H;
+        const size_t sm = (size_t)sl * C * bm * 64 + (size_t)C * G * 32 * 64 + 96 + (size_t)G * 32 * 4 + 8 * 2048 + 1024;
+        const int cl = (rows + sl * bm - 1) / (sl * bm);
+        if (bm == 128 && sl == 2) return G == 3 ? launch_ht<3, 128, 2>(mu, q, cl, sm, st, dry, max_out) : launch_ht<4, 128, 2>(mu, q, cl, sm, st, dry, max_out);
+        if (bm == 128) return G == 3 ? launch_ht<3, 128, 1>(mu, q, cl, sm, st, dry, max_out) : launch_ht<4, 128, 1>(mu, q, cl, sm, st, dry, max_out);
+        if (sl == 2) return G == 3 ? launch_ht<3, 64, 2>(mu, q, cl, sm, st, dry, max_out) : launch_ht<4, 64, 2>(mu, q, cl, sm, st, dry, max_out);
+        return G == 3 ? launch_ht<3, 64, 1>(mu, q, cl, sm, st, dry, max_out) : launch_ht<4, 64, 1>(mu, q, cl, sm, st, dry, max_out);
+    };
+    int rc;
+    int main_rows = nb, tail_rows = 0;
+    static int split_tail = -1;
+    if (split_tail < 0) { const char *e = getenv("NNTK_CLUSTER_H16_SPLIT_TAIL"); split_tail = e ? atoi(e) : 1; }
+    if (BM == 128 && SL == 2 && split_tail) {
+        // Waves: only `maxc` clusters are resident, and a wave costs the same whether it is full or not (the step is a latency
+        // chain).  Two-slice clusters (256 sequences, 6.9 us per step at GRU-256) are the densest; one-slice clusters
+        // (128 sequences, 3.8 us) finish a small remainder in ~0.55 of a wave.  Measured at GRU-256, T = 994: 512 sequences
+        // 7.6 -> 4.5 ms, 1 920 sequences 9.7 -> 6.7 ms.
+        int maxc = 0;
+        rc = run(128, 2, 0, nb, true, &maxc);
+        if (rc == 1) return 0;
+        if (rc) return rc;
+        const int wave = maxc * 256;
+        const int rem = nb % wave;
+        if (rem) {
+            const double two = (double)((rem + 255) / 256 + maxc - 1) / maxc >= 1.0 ? (double)(((rem + 255) / 256 + maxc - 1) / maxc) : 1.0;
+            const double one = 0.55 * (double)(((rem + 127) / 128 + maxc - 1) / maxc);
+            if (one < two) { tail_rows = rem; main_rows = nb - rem; }
+        }
+    }
+    if (main_rows > 0) {
+        rc = run(BM, SL, 0, main_rows, false, nullptr);
+        if (rc == 1) return 0;
+        if (rc) return rc;
+    }
+    if (tail_rows > 0) {
+        rc = run(128, 1, main_rows, tail_rows, false, nullptr);
+        if (rc == 1) {
+            if (main_rows > 0) { nntk_cuda_set_error(NNTK_ERR_CUDA_, "recurrent_cluster_h16: the one-slice tail launch is not schedulable"); return NNTK_ERR_CUDA_; }
+            return 0;
+        }
+        if (rc) return rc;
+    }
     *used = 1;
     return 0;
 }
