@@ -1,6 +1,8 @@
 // gemm_tc.cu -- K2/K3, tensor-core path (NNTK_MATH_TF32): (implicit) GEMM on tcgen05 with TMA-staged tiles and TMEM
 // accumulators, bias + BatchNorm + activation fused in the epilogue.  Same contract as csrc/gemm.cu (nntk_gemm_args);
 // operands are rounded to TF32 by the tensor core, accumulation is fp32, so parity with the reference is 1e-3, not 1e-5.
+// Split-operand variants of the same kernel: 3xTF32 (NNTK_MATH_TF32X3: hi/lo tf32 parts, three passes in one K loop, the
+// truncating accumulate compensated -- holds 1e-5) and 3xbf16 (kind::f16, the hoisted recurrent projection of the TF32 mode).
 //
 // Structure (persistent, warp specialised, one CTA per SM):
 //   warp 0      TMA producer: A tile [128 rows x 32 k] and B tile [BN x 32 k] per stage, SWIZZLE_128B, mbarrier tx-count

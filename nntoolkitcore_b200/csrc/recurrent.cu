@@ -450,7 +450,7 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     // The un-gated RNN amplifies operand rounding step by step (its Jacobian ~ U does not contract): measured 1.2e-3 at
     // T = 12 with only the PROJECTION in TF32.  It has no BASELINE config, so it simply stays fp32 in every math mode.
     const int mode = nntk_cuda_math_mode();
-    // TF32 mode runs the projection as 3xTF32 (split operands): emulation of the C5 GRU over 300 steps showed that the
+    // TF32 mode runs the projection with split operands (3xbf16 below, 3xTF32 where that does not fit): emulation of the C5 GRU over 300 steps showed that the
     // single-pass TF32 rounding of x and W in the PROJECTION alone costs 1.2e-3 (each operand ~7e-4), the recurrent TF32
     // rounding only 3.5e-4 -- and the projection is the cheap part.  The tensor-core STEP kernels stay single-pass TF32.
     const int proj_mode = (G == 1) ? 0 : (mode == 1 ? 2 : mode);

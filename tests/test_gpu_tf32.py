@@ -45,7 +45,7 @@ def test_dense_and_tdd_tf32(tf32, ref):
 
 @pytest.mark.parametrize("cell,in_size,H,T,B", [("gru", 256, 256, 10, 200), ("lstm", 512, 512, 6, 130)])
 def test_recurrent_projection_tf32(tf32, ref, cell, in_size, H, T, B):
-    """TF32 mode: the hoisted x*W projection runs on the tensor cores as 3xTF32 (its single-pass rounding alone would cost
+    """TF32 mode: the hoisted x*W projection runs on the tensor cores with split operands -- 3xbf16, or 3xTF32 where the 2-byte pitch rules do not fit (its single-pass rounding alone would cost
     ~1e-3 over long sequences), the recurrent steps as single-pass TF32 (cluster or per-step kernel, by shape)"""
     rng = np.random.default_rng(4)
     x = rng.standard_normal((B, T, in_size)).astype(np.float32)
@@ -181,7 +181,7 @@ def test_dense_tdd_and_recurrent_3xtf32(x3, ref):
     d_ref, d_new = L.Dense(ref, 256, 12, L.ACT_SOFTMAX, ts=200), L.Dense(x3, 256, 12, L.ACT_SOFTMAX, ts=200)
     helpers.fill_dense(d_ref, 501); helpers.copy_weights(d_new, d_ref)
     assert_parity(d_new.apply_batch(x), np.stack([d_ref.apply(v) for v in x]), tol=X3_TOL, what="tdd 3xTF32")
-    # recurrent: projection 3xTF32, steps on FFMA (no single-pass tensor-core step in this mode)
+    # recurrent: projection 3xTF32; at this batch (<= 256 per chunk rule aside) the steps run on FFMA kernels
     xs = rng.standard_normal((300, 20, 64)).astype(np.float32)
     outs = []
     for v in xs[:3]:
