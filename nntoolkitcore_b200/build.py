@@ -21,7 +21,7 @@ LIB = PKG / "lib" / "libnntoolkitcore_b200.so"
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 CC = os.environ.get("CC", "gcc")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
-              f"-I{INC}", f"-I{PKG / 'csrc'}"]
+              f"-I{INC}", f"-I{PKG / 'csrc'}", *os.environ.get("NNTK_NVCC_EXTRA", "").split()]
 CC_FLAGS = ["-O2", "-std=gnu11", "-fPIC", "-Wall", "-Wextra", "-Wno-unused-parameter", f"-I{INC}", f"-I{PKG / 'host'}"]
 
 

@@ -26,6 +26,18 @@ constexpr int R_BM = 128, R_BK = 32, R_UT = 64;     // rows, k per stage, hidden
 // The fp16 / TF32 variants run 8 (32 units per thread, 8-unit chunks: more warps did not help them, 54.1 -> 55.9 ms on C4);
 // the X3 variant's expf / tanhf / IEEE-divide gate math is several times longer, and 16 warps (16 units per thread, 4-unit
 // chunks to fit 96 registers) took C4 from 159 to 110 ms.
+#ifndef RTC_CH
+#define RTC_CH 8    // hidden units per epilogue chunk of the TF32/fp16 step kernel
+#endif
+#ifndef RTC_STG
+#define RTC_STG 0   // 1: stage h_t / c_t through shared memory so every store instruction writes 64-byte row pieces.
+                    // Measured on C4 (B = 4096): 56.5 ms against 52.7-54.4 ms with the direct 16-byte stores -- the stores'
+                    // cost (NNTK_RTC_DBG=4/8/16: 2.6 + 1.2 + 1.2 ms per layer) is not a coalescing problem.  Off.
+#endif
+#ifndef RTC_PD
+#define RTC_PD 1    // chunks whose xw / state loads are in flight ahead of the gate math.  CH=4 with PD=1, 2 or 3 all time
+                    // within 0.5 % of CH=8/PD=1 on C4 and C5 (scripts/rtc_variants.sh): load latency is not the limiter
+#endif
 __host__ __device__ constexpr int rtc_epi_warps(bool x3) { return x3 ? 16 : 8; }
 __host__ __device__ constexpr int rtc_threads(bool x3) { return 64 + 32 * rtc_epi_warps(x3); }
 
@@ -36,11 +48,12 @@ struct RtcParams {
     int a_t;                           // TMA coordinate of h_{t-1} along the time axis of map_a
     const float *bh;                   // permuted like the columns of Bt, or null
     const float *xw; long long ld_xw;  // row b: xw + b*ld_xw, original column order g*H + unit
+    const float *xw_next; long long pf_lines;  // next step's blocked projection slab (128-byte lines) to pull into L2, or null
     int xw_blocked, row_blocks;        // xw_blocked: xw points at this step's [B/32][G*H/4][32][4] block (gemm_tc.cu c_blocked)
     const float *h_prev; long long ld_prev;
     float *h_next; long long ld_next;
     float *hr_next;                    // [B, H]: h_t rounded to nearest TF32 = the A operand of step t+1
-    int dbg;                           // development switches (NNTK_RTC_DBG): 1 no loads, 2 no stores
+    int dbg;                           // development switches (NNTK_RTC_DBG): 1 no loads, 2 no stores, 4 no h_t store, 8 no operand-copy store, 16 no c store
     float comp;                        // 1 + truncation-bias compensation when A is raw fp32 (step 0), else 1
     float *c;                          // [B, H] LSTM
     int act[5];
@@ -54,7 +67,10 @@ struct RtcSmem {
     static constexpr int B_BYTES = BN * R_BK * 4;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
-    static constexpr int TOTAL = BAR_OFFSET + (2 * STAGES + 4) * 8 + 16 + 1024;
+    // store staging of the non-X3 epilogue: per warp a [32 rows][16 units] fp32 tile of h_t and one of c_t (2 KB each)
+    static constexpr int STG_OFFSET = BAR_OFFSET + (((2 * STAGES + 4) * 8 + 16 + 127) & ~127);
+    static constexpr int STG_WARP_BYTES = 4096;
+    static constexpr int TOTAL = STG_OFFSET + (RTC_STG ? 8 * STG_WARP_BYTES : 0) + 1024;
     static constexpr int ACC_STRIDE = BN <= 64 ? 64 : 256;       // TMEM columns between the two accumulators
     static constexpr int TMEM_COLS = 2 * ACC_STRIDE;
 };
@@ -109,6 +125,7 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
 
     constexpr int R_EPI_WARPS = rtc_epi_warps(X3), R_EPI_UNITS = R_UT / (R_EPI_WARPS / 4);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");     // the next step may queue behind this one right away
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
@@ -124,6 +141,7 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    asm volatile("griddepcontrol.wait;" ::: "memory");                  // everything the previous step wrote is visible from here
 
     if (warp == 0) {
         if (lane == 0) {
@@ -174,8 +192,17 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
         const int half = (warp - 2) >> 2;             // which R_EPI_UNITS units of the tile's 64
         const int row_in_tile = q * 32 + lane;
         const float comp = p.comp;
-        constexpr int CH = X3 ? 4 : 8, NCH = R_EPI_UNITS / CH, NV = CH / 4;
+        constexpr int CH = X3 ? 4 : RTC_CH, NCH = R_EPI_UNITS / CH, NV = CH / 4;
+        constexpr int PD = X3 ? 1 : RTC_PD, NS = PD + 1;        // chunks prefetched ahead; ring slots
+        constexpr bool STG = !X3 && CH == 8 && RTC_STG;          // stores go through the per-warp staging tile
+        float4 *stg = reinterpret_cast<float4 *>(smem + SL::STG_OFFSET + (STG ? (warp - 2) * SL::STG_WARP_BYTES : 0));
         struct Pre { float4 xv[G][NV]; float4 st[NV]; };    // st: c (LSTM) or h_{t-1} (GRU)
+        // optional (NNTK_RTC_PF, off by default -- see the host loop): pull the NEXT step's projection slab into L2
+        if (p.xw_next) {
+            constexpr int N_ET = R_EPI_WARPS * 32;
+            for (long long i = (long long)blockIdx.x * N_ET + (threadIdx.x - 64); i < p.pf_lines; i += (long long)gridDim.x * N_ET)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(p.xw_next + i * 32));
+        }
         uint32_t it = 0;
         for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
             const int n_t = tile % p.n_tiles, m_t = tile / p.n_tiles;
@@ -205,22 +232,24 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
                     P.st[v] = (ok && G != 1) ? *reinterpret_cast<const float4 *>(stp + u) : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
             };
-            Pre cur;
-            prefetch(0, cur);
+            Pre ring[NS];
+#pragma unroll
+            for (int i = 0; i < PD; ++i)
+                if (i < NCH) prefetch(i, ring[i]);
             mbar_wait(&tmem_full[buf], use & 1);
             tc_fence_after();
             const uint32_t taddr = tmem_base + buf * SL::ACC_STRIDE + ((uint32_t)(q * 32) << 16) + half * R_EPI_UNITS;
 #pragma unroll
             for (int ch = 0; ch < NCH; ++ch) {
-                Pre nxt;
-                if (ch + 1 < NCH) prefetch(ch + 1, nxt);
+                if (ch + PD < NCH) prefetch(ch + PD, ring[(ch + PD) % NS]);
+                const Pre &cur = ring[ch % NS];
                 float acc[G][CH];
 #pragma unroll
                 for (int g = 0; g < G; ++g) tc_ld_chunk(taddr + g * R_UT + ch * CH, acc[g]);
 #pragma unroll
                 for (int v = 0; v < NV; ++v) {
                     const int u = ch * CH + 4 * v;
-                    if (!(row_ok && ubase + u < p.H)) continue;          // H is a multiple of 4
+                    if (!(row_ok && ubase + u < p.H)) continue;          // H is a multiple of 4 (no warp-level sync below this line inside the v loop)
                     float4 bv[G];
 #pragma unroll
                     for (int g = 0; g < G; ++g)
@@ -252,8 +281,16 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
                         }
                     }
                     if (p.dbg & 2) { if (out[0] == 123.456f) hn[u] = out[1] + out[2] + out[3] + cn[0] + cn[1] + cn[2] + cn[3]; continue; }
-                    *reinterpret_cast<float4 *>(hn + u) = make_float4(out[0], out[1], out[2], out[3]);
-                    if (H16) {
+                    if (STG) {
+                        // park the 4 units in this warp's staging tile; the flush below writes whole 64-byte row pieces
+                        const int jj = (u >> 2) & 3, slot = lane * 4 + (jj ^ ((lane >> 1) & 3));
+                        stg[slot] = make_float4(out[0], out[1], out[2], out[3]);
+                        if (G == 4) stg[128 + slot] = make_float4(cn[0], cn[1], cn[2], cn[3]);
+                        continue;
+                    }
+                    if (!(p.dbg & 4)) *reinterpret_cast<float4 *>(hn + u) = make_float4(out[0], out[1], out[2], out[3]);
+                    if (p.dbg & 8) {
+                    } else if (H16) {
                         __half2 lo = __floats2half2_rn(out[0], out[1]), hi = __floats2half2_rn(out[2], out[3]);
                         uint2 pk = make_uint2(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi));
                         *reinterpret_cast<uint2 *>(reinterpret_cast<__half *>(p.hr_next) + rr * p.H + ubase + u) = pk;
@@ -264,9 +301,35 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
                             *reinterpret_cast<float4 *>(hr + p.part_stride + u) =
                                 make_float4(round_tf32(out[0] - hi.x), round_tf32(out[1] - hi.y), round_tf32(out[2] - hi.z), round_tf32(out[3] - hi.w));
                     }
-                    if (G == 4) *reinterpret_cast<float4 *>(cw + u) = make_float4(cn[0], cn[1], cn[2], cn[3]);
+                    if (G == 4 && !(p.dbg & 16)) *reinterpret_cast<float4 *>(cw + u) = make_float4(cn[0], cn[1], cn[2], cn[3]);
                 }
-                cur = nxt;
+                if (STG && (ch & 1) && !(p.dbg & 2)) {
+                    // 16 units of 32 rows are parked: lane -> (row it*8 + lane/4, 16-byte piece lane%4), so one store
+                    // instruction covers 8 rows x 64 contiguous bytes instead of 32 rows x 16 bytes
+                    __syncwarp();
+#pragma unroll
+                    for (int it = 0; it < 4; ++it) {
+                        const int r = it * 8 + (lane >> 2), j = lane & 3;
+                        const long long grow = (long long)m_t * R_BM + q * 32 + r;
+                        const int uu = ubase + (ch >> 1) * 16 + 4 * j;
+                        if (grow < p.B && uu < p.H) {
+                            const int slot = r * 4 + (j ^ ((r >> 1) & 3));
+                            const float4 hv = stg[slot];
+                            if (!(p.dbg & 4)) *reinterpret_cast<float4 *>(p.h_next + grow * p.ld_next + uu) = hv;
+                            if (p.dbg & 8) {
+                            } else if (H16) {
+                                __half2 lo = __floats2half2_rn(hv.x, hv.y), hi = __floats2half2_rn(hv.z, hv.w);
+                                *reinterpret_cast<uint2 *>(reinterpret_cast<__half *>(p.hr_next) + grow * p.H + uu) =
+                                    make_uint2(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi));
+                            } else {
+                                *reinterpret_cast<float4 *>(p.hr_next + grow * p.H + uu) =
+                                    make_float4(round_tf32(hv.x), round_tf32(hv.y), round_tf32(hv.z), round_tf32(hv.w));
+                            }
+                            if (G == 4 && !(p.dbg & 16)) *reinterpret_cast<float4 *>(p.c + grow * p.H + uu) = stg[128 + slot];
+                        }
+                    }
+                    __syncwarp();
+                }
             }
             tc_fence_before();
             __syncwarp();
@@ -349,7 +412,17 @@ static int launch_rtc(const CUtensorMap &ma, const CUtensorMap &mb, const RtcPar
         attr_done = true;
     }
     const int grid = p.total_tiles < nntk_cuda_sm_count() ? p.total_tiles : nntk_cuda_sm_count();
-    recurrent_tc_step_kernel<G, STAGES, H16, X3><<<grid, rtc_threads(X3), SL::TOTAL, st>>>(ma, mb, p);
+    // programmatic dependent launch: step t+1's CTAs may start (barrier init, TMEM allocation, descriptor prefetch) on SMs
+    // that step t has already left; they wait for all of step t in griddepcontrol.wait before touching h, c or xw
+    static int pdl = -1;
+    if (pdl < 0) { const char *e = getenv("NNTK_RTC_PDL"); pdl = e ? atoi(e) : 1; }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(rtc_threads(X3)); cfg.dynamicSmemBytes = SL::TOTAL; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    NNTK_CUDA_TRY(cudaLaunchKernelEx(&cfg, recurrent_tc_step_kernel<G, STAGES, H16, X3>, ma, mb, p));
     return 0;
 }
 
@@ -457,6 +530,10 @@ extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, cons
     { const char *e = getenv("NNTK_RTC_DBG"); p.dbg = e ? atoi(e) : 0; }
     p.c = c;
     for (int i = 0; i < 5; ++i) { p.act[i] = r->act[i]; p.act_a[i] = r->act_a[i]; }
+    static int pf = -1;
+    // NNTK_RTC_PF=1: each step pulls the next step's projection slab into L2 while its first MMAs run.  Measured on C4:
+    // B = 4096 50.6-51.4 -> 53.6-54.4 ms (the 33 MB slab competes with this step's own reads), B = 2048 28.0 -> 27.7 ms.  Off.
+    if (pf < 0) { const char *e = getenv("NNTK_RTC_PF"); pf = e ? atoi(e) : 0; }
     for (int t = 0; t < T; ++t) {
         const CUtensorMap *ma;
         const float x3_comp = 1.0f + 2.06e-9f * (float)H;   // truncating accumulate, see gemm_tc.cu (X3_ACC_TRUNC_PER_K)
@@ -473,6 +550,8 @@ extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, cons
         p.hr_next = h16 ? reinterpret_cast<float *>(reinterpret_cast<__half *>(hr) + (size_t)(t & 1) * nb * H)
                         : hr + (size_t)(t & 1) * (x3 ? 2 : 1) * nb * H;
         p.xw = xw_blocked ? xw + (long long)t * p.row_blocks * 32 * G * H : xw + (long long)t * G * H;
+        p.xw_next = (xw_blocked && pf && t + 1 < T) ? p.xw + (long long)p.row_blocks * 32 * G * H : nullptr;
+        p.pf_lines = (long long)p.row_blocks * 32 * G * H / 32;
         if (G == 1) rc = launch_rtc<1, 6, false>(*ma, mb, p, st);
         else if (G == 3) rc = x3 ? launch_rtc<3, 4, false, true>(*ma, mb, p, st) : h16 ? launch_rtc<3, 4, true>(*ma, mb, p, st) : launch_rtc<3, 4, false>(*ma, mb, p, st);
         else rc = x3 ? launch_rtc<4, 4, false, true>(*ma, mb, p, st) : h16 ? launch_rtc<4, 4, true>(*ma, mb, p, st) : launch_rtc<4, 4, false>(*ma, mb, p, st);
