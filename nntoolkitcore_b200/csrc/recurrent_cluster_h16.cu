@@ -15,6 +15,15 @@
 #include <cuda_fp16.h>
 #include "tc_common.cuh"
 
+#ifndef HT_MUFU_TANH
+#define HT_MUFU_TANH 1
+#endif
+#if HT_MUFU_TANH
+#define HT_ACT(kind, x) act_mufu(kind, x)
+#else
+#define HT_ACT(kind, x) act_fast(kind, 1.0f, x)
+#endif
+
 namespace {
 
 constexpr int HT_THREADS = 320;              // warp 0: a_free signalling, warp 1: MMA issuer, warps 2..9: epilogue
@@ -256,17 +265,17 @@ recurrent_cluster_h16_kernel(const __grid_constant__ CUtensorMap map_u, HtParams
                         x[g] = (&xr[g][u >> 2].x)[u & 3];
                     }
                     if (G == 3) {          // gru.c:156-186
-                        const float z = act_fast(S_SIG, 1.0f, x[0] + hu[0]);
-                        const float rg = act_fast(S_SIG, 1.0f, x[1] + hu[1]);
-                        const float hh = act_fast(S_TANH, 1.0f, fmaf(rg, hu[2], x[2]));
+                        const float z = HT_ACT(S_SIG, x[0] + hu[0]);
+                        const float rg = HT_ACT(S_SIG, x[1] + hu[1]);
+                        const float hh = HT_ACT(S_TANH, fmaf(rg, hu[2], x[2]));
                         h[s][u] = fmaf(z, h[s][u] - hh, hh);               // (1 - z) hh + z h_{t-1}
                     } else {               // lstm.c:199-238
-                        const float ig = act_fast(S_SIG, 1.0f, x[0] + hu[0]);
-                        const float fg = act_fast(S_SIG, 1.0f, x[1] + hu[1]);
-                        const float gg = act_fast(S_TANH, 1.0f, x[2] + hu[2]);
-                        const float og = act_fast(S_SIG, 1.0f, x[3] + hu[3]);
+                        const float ig = HT_ACT(S_SIG, x[0] + hu[0]);
+                        const float fg = HT_ACT(S_SIG, x[1] + hu[1]);
+                        const float gg = HT_ACT(S_TANH, x[2] + hu[2]);
+                        const float og = HT_ACT(S_SIG, x[3] + hu[3]);
                         c[s][u] = fmaf(fg, c[s][u], ig * gg);
-                        h[s][u] = og * act_fast(S_TANH, 1.0f, c[s][u]);
+                        h[s][u] = og * HT_ACT(S_TANH, c[s][u]);
                     }
                 }
                 // exchange first (the other CTAs are waiting for it), then put the xw of the NEXT slice-step in flight (xr is dead

@@ -34,6 +34,9 @@ constexpr int R_BM = 128, R_BK = 32, R_UT = 64;     // rows, k per stage, hidden
                     // Measured on C4 (B = 4096): 56.5 ms against 52.7-54.4 ms with the direct 16-byte stores -- the stores'
                     // cost (NNTK_RTC_DBG=4/8/16: 2.6 + 1.2 + 1.2 ms per layer) is not a coalescing problem.  Off.
 #endif
+#ifndef RTC_MUFU_TANH
+#define RTC_MUFU_TANH 1   // fp16-operand variant: MUFU.TANH gate activations (tc_common.cuh act_mufu); C4 51.7 -> 50.1 ms
+#endif
 #ifndef RTC_PD
 #define RTC_PD 1    // chunks whose xw / state loads are in flight ahead of the gate math.  CH=4 with PD=1, 2 or 3 all time
                     // within 0.5 % of CH=8/PD=1 on C4 and C5 (scripts/rtc_variants.sh): load latency is not the limiter
@@ -85,6 +88,17 @@ __device__ __forceinline__ void tc_ld_32x8(uint32_t taddr, float (&r)[8]) {
     for (int i = 0; i < 8; ++i) r[i] = __uint_as_float(u[i]);
 }
 
+// TMA tile load delivered to the same stage offset (and signalled on the same barrier offset) in both CTAs of a pair
+__device__ __forceinline__ void tma_load_2d_mc2(void *dst, const CUtensorMap *map, uint64_t *bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
+                 ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"((uint16_t)3) : "memory");
+}
+// tcgen05.commit arriving on the barrier at this offset in both CTAs of a pair
+__device__ __forceinline__ void tc_commit_mc2(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+
 __device__ __forceinline__ void tc_ld_chunk(uint32_t taddr, float (&r)[8]) { tc_ld_32x8(taddr, r); }
 __device__ __forceinline__ void tc_ld_chunk(uint32_t taddr, float (&r)[4]) {
     uint32_t u[4];
@@ -101,6 +115,9 @@ __device__ __forceinline__ void tc_ld_chunk(uint32_t taddr, float (&r)[4]) {
 template <bool DEF, int KIND, bool X3>
 __device__ __forceinline__ float rt_act(const RtcParams &p, int slot, float x) {
     if (X3) return nntk_act(p.act[slot], p.act_a[slot], x);
+#if RTC_MUFU_TANH
+    if (DEF) return act_mufu(KIND, x);
+#endif
     return DEF ? act_fast(KIND, 1.0f, x) : act_fast(p.act[slot], p.act_a[slot], x);
 }
 
@@ -110,7 +127,10 @@ __device__ __forceinline__ float rt_act(const RtcParams &p, int slot, float x) {
 // X3 (NNTK_MATH_TF32X3, never together with H16): 3xTF32 -- h is kept as tf32 hi + lo parts (h - hi is exact), U as
 // [lo | hi | hi] along K, three passes hi*Ulo, lo*Uhi, hi*Uhi in one K loop (small passes first); the accumulate truncation is
 // compensated through p.comp like in gemm_tc.cu.  Operand error ~2^-22: the recurrence holds the fp32 contract (1e-5).
-template <int G, int STAGES, bool H16, bool X3>
+// CL2 (H16 only): CTAs run as clusters of two on vertically adjacent tiles (same hidden units, rows m and m+1).  Each CTA loads
+// its own h tile and HALF of the shared U slice, multicast into both CTAs' stage buffers: the U traffic from L2 halves
+// (256 -> 128 KB per tile).  A stage is free once BOTH MMA issuers have committed it (multicast tcgen05.commit, count 2).
+template <int G, int STAGES, bool H16, bool X3, bool CL2 = false>
 __global__ void __launch_bounds__(rtc_threads(X3), 1)
 recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, RtcParams p) {
     using SL = RtcSmem<G, STAGES>;
@@ -129,7 +149,7 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
-        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], CL2 ? 2 : 1); }
         for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], R_EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -139,22 +159,29 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
     }
     tc_fence_before();
     __syncthreads();
+    if (CL2) asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // work item w -> tile: alone, w is the tile; in a pair, w names (n_t, pair of m tiles) and the cluster rank picks the row tile
+    uint32_t crank = 0;
+    if (CL2) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
+    const int w_first = CL2 ? blockIdx.x >> 1 : blockIdx.x, w_step = CL2 ? gridDim.x >> 1 : gridDim.x;
+    const int w_total = CL2 ? p.n_tiles * ((p.m_tiles + 1) >> 1) : p.total_tiles;
     asm volatile("griddepcontrol.wait;" ::: "memory");                  // everything the previous step wrote is visible from here
 
     if (warp == 0) {
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-                const int n_t = tile % p.n_tiles, m_t = tile / p.n_tiles;
+            for (int tile = w_first; tile < w_total; tile += w_step) {
+                const int n_t = tile % p.n_tiles, m_t = CL2 ? 2 * (tile / p.n_tiles) + (int)crank : tile / p.n_tiles;
                 for (int kb = 0; kb < p.k_blocks; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t *sa = smem + stage * SL::STAGE_BYTES;
                     mbar_expect_tx(&full_bar[stage], SL::STAGE_BYTES);
                     const int pass = X3 ? kb / p.kb_pass : 0, akb = kb - pass * p.kb_pass;
                     tma_load_3d(sa, &map_a, &full_bar[stage], akb * (H16 ? 2 * R_BK : R_BK), X3 ? 2 * p.a_t + (pass == 1 ? 1 : 0) : p.a_t, m_t * R_BM);
-                    tma_load_2d(sa + SL::A_BYTES, &map_b, &full_bar[stage], kb * (H16 ? 2 * R_BK : R_BK), n_t * BN);
+                    if (CL2) tma_load_2d_mc2(sa + SL::A_BYTES + crank * (SL::B_BYTES / 2), &map_b, &full_bar[stage], kb * 2 * R_BK, n_t * BN + (int)crank * (BN / 2));
+                    else tma_load_2d(sa + SL::A_BYTES, &map_b, &full_bar[stage], kb * (H16 ? 2 * R_BK : R_BK), n_t * BN);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -163,7 +190,7 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
         if (lane == 0) {
             constexpr uint32_t idesc = (1u << 4) | (H16 ? 0u : ((2u << 7) | (2u << 10))) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(R_BM >> 4) << 24);
             int stage = 0; uint32_t phase = 0, it = 0;
-            for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+            for (int tile = w_first; tile < w_total; tile += w_step, ++it) {
                 const uint32_t buf = it & 1, use = it >> 1;
                 mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);
                 tc_fence_after();
@@ -178,7 +205,8 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
                         if (H16) tc_mma_f16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
                         else tc_mma_tf32(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
                     }
-                    tc_commit(&empty_bar[stage]);
+                    if (CL2) tc_commit_mc2(&empty_bar[stage]);     // the peer's producer multicasts into this stage as well
+                    else tc_commit(&empty_bar[stage]);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
                 tc_commit(&tmem_full[buf]);
@@ -204,8 +232,8 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(p.xw_next + i * 32));
         }
         uint32_t it = 0;
-        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-            const int n_t = tile % p.n_tiles, m_t = tile / p.n_tiles;
+        for (int tile = w_first; tile < w_total; tile += w_step, ++it) {
+            const int n_t = tile % p.n_tiles, m_t = CL2 ? 2 * (tile / p.n_tiles) + (int)crank : tile / p.n_tiles;
             const uint32_t buf = it & 1, use = it >> 1;
             const int row = m_t * R_BM + row_in_tile;
             const bool row_ok = row < p.B;
@@ -338,6 +366,8 @@ recurrent_tc_step_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
     }
     tc_fence_before();
     __syncthreads();
+    // neither CTA of a pair may leave while the other can still multicast into its stages or arrive on its barriers
+    if (CL2) asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(SL::TMEM_COLS) : "memory");
@@ -403,26 +433,39 @@ size_t g_rtc_floats = 0;
 
 }  // namespace
 
-template <int G, int STAGES, bool H16, bool X3 = false>
+template <int G, int STAGES, bool H16, bool X3 = false, bool CL2 = false>
 static int launch_rtc(const CUtensorMap &ma, const CUtensorMap &mb, const RtcParams &p, cudaStream_t st) {
     using SL = RtcSmem<G, STAGES>;
     static bool attr_done = false;
+    static int max_pairs = 0;
     if (!attr_done) {
-        NNTK_CUDA_TRY(cudaFuncSetAttribute(recurrent_tc_step_kernel<G, STAGES, H16, X3>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::TOTAL));
+        NNTK_CUDA_TRY(cudaFuncSetAttribute(recurrent_tc_step_kernel<G, STAGES, H16, X3, CL2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::TOTAL));
+        if (CL2) {
+            cudaLaunchConfig_t q = {};
+            q.gridDim = dim3(2 * (nntk_cuda_sm_count() / 2)); q.blockDim = dim3(rtc_threads(X3)); q.dynamicSmemBytes = SL::TOTAL;
+            cudaLaunchAttribute ca[1];
+            ca[0].id = cudaLaunchAttributeClusterDimension; ca[0].val.clusterDim.x = 2; ca[0].val.clusterDim.y = 1; ca[0].val.clusterDim.z = 1;
+            q.attrs = ca; q.numAttrs = 1;
+            NNTK_CUDA_TRY(cudaOccupancyMaxActiveClusters(&max_pairs, recurrent_tc_step_kernel<G, STAGES, H16, X3, CL2>, &q));
+            if (max_pairs < 1) { nntk_cuda_set_error(NNTK_ERR_CUDA_, "recurrent_tc: no 2-CTA cluster fits"); return NNTK_ERR_CUDA_; }
+        }
         attr_done = true;
     }
-    const int grid = p.total_tiles < nntk_cuda_sm_count() ? p.total_tiles : nntk_cuda_sm_count();
+    const int pairs = p.n_tiles * ((p.m_tiles + 1) / 2);
+    const int grid = CL2 ? 2 * (pairs < max_pairs ? pairs : max_pairs)
+                         : (p.total_tiles < nntk_cuda_sm_count() ? p.total_tiles : nntk_cuda_sm_count());
     // programmatic dependent launch: step t+1's CTAs may start (barrier init, TMEM allocation, descriptor prefetch) on SMs
     // that step t has already left; they wait for all of step t in griddepcontrol.wait before touching h, c or xw
     static int pdl = -1;
     if (pdl < 0) { const char *e = getenv("NNTK_RTC_PDL"); pdl = e ? atoi(e) : 1; }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(rtc_threads(X3)); cfg.dynamicSmemBytes = SL::TOTAL; cfg.stream = st;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
-    NNTK_CUDA_TRY(cudaLaunchKernelEx(&cfg, recurrent_tc_step_kernel<G, STAGES, H16, X3>, ma, mb, p));
+    cudaLaunchAttribute at[2];
+    int na = 0;
+    if (CL2) { at[na].id = cudaLaunchAttributeClusterDimension; at[na].val.clusterDim.x = 2; at[na].val.clusterDim.y = 1; at[na].val.clusterDim.z = 1; ++na; }
+    if (pdl) { at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[na].val.programmaticStreamSerializationAllowed = 1; ++na; }
+    cfg.attrs = at; cfg.numAttrs = na;
+    NNTK_CUDA_TRY(cudaLaunchKernelEx(&cfg, recurrent_tc_step_kernel<G, STAGES, H16, X3, CL2>, ma, mb, p));
     return 0;
 }
 
@@ -492,6 +535,10 @@ extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, cons
     }
     CUtensorMap m_state, m_hr, mb;
     int rc;
+    // NNTK_RTC_CL2: 2-CTA clusters with the U slice multicast (fp16 operands, at least two row tiles)
+    static int want_cl2 = -1;
+    if (want_cl2 < 0) { const char *e = getenv("NNTK_RTC_CL2"); want_cl2 = e ? atoi(e) : 0; }
+    const bool cl2 = want_cl2 && h16 && !x3 && G != 1 && nb > R_BM;
     float *hr = pp + (size_t)2 * nb * H;   // rounded ping-pong [2][nb][H] behind the exact one (fp16 mode: halves, same region)
     if (h16) {
         // step 0 reads h_0 like every other step: converted into slot 1 of the ping-pong ((t - 1) & 1 for t = 0)
@@ -508,7 +555,8 @@ extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, cons
     {
         cuuint64_t dims[2] = {(cuuint64_t)ldbt, (cuuint64_t)n_rows};
         cuuint64_t strides[1] = {(cuuint64_t)ldbt * es};
-        cuuint32_t box[2] = {(cuuint32_t)(h16 ? 2 * R_BK : R_BK), (cuuint32_t)(G * R_UT)};
+        // pair mode: each CTA of a 2-CTA cluster loads half of the U slice (and multicasts it), so the box is half as tall
+        cuuint32_t box[2] = {(cuuint32_t)(h16 ? 2 * R_BK : R_BK), (cuuint32_t)(cl2 ? G * R_UT / 2 : G * R_UT)};
         cuuint32_t estr[2] = {1, 1};
         CUresult cr = encode(&mb, h16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)Bt, dims, strides, box, estr,
                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -553,8 +601,8 @@ extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, cons
         p.xw_next = (xw_blocked && pf && t + 1 < T) ? p.xw + (long long)p.row_blocks * 32 * G * H : nullptr;
         p.pf_lines = (long long)p.row_blocks * 32 * G * H / 32;
         if (G == 1) rc = launch_rtc<1, 6, false>(*ma, mb, p, st);
-        else if (G == 3) rc = x3 ? launch_rtc<3, 4, false, true>(*ma, mb, p, st) : h16 ? launch_rtc<3, 4, true>(*ma, mb, p, st) : launch_rtc<3, 4, false>(*ma, mb, p, st);
-        else rc = x3 ? launch_rtc<4, 4, false, true>(*ma, mb, p, st) : h16 ? launch_rtc<4, 4, true>(*ma, mb, p, st) : launch_rtc<4, 4, false>(*ma, mb, p, st);
+        else if (G == 3) rc = x3 ? launch_rtc<3, 4, false, true>(*ma, mb, p, st) : cl2 ? launch_rtc<3, 4, true, false, true>(*ma, mb, p, st) : h16 ? launch_rtc<3, 4, true>(*ma, mb, p, st) : launch_rtc<3, 4, false>(*ma, mb, p, st);
+        else rc = x3 ? launch_rtc<4, 4, false, true>(*ma, mb, p, st) : cl2 ? launch_rtc<4, 4, true, false, true>(*ma, mb, p, st) : h16 ? launch_rtc<4, 4, true>(*ma, mb, p, st) : launch_rtc<4, 4, false>(*ma, mb, p, st);
         if (rc) return rc;
     }
     NNTK_LAUNCH_CHECK("recurrent_tc_step_kernel");

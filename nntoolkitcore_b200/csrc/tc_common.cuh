@@ -111,6 +111,16 @@ __device__ __forceinline__ float act_fast(int kind, float a, float x) {
     }
 }
 
+// Gate activations of the fp16-operand recurrent kernels: one MUFU.TANH per activation (sigmoid(x) = 0.5 tanh(x/2) + 0.5)
+// instead of ex2 + rcp.  tanh.approx has 2^-11 relative error -- the same class as the fp16 operands of those kernels;
+// measured against the CPU reference at T = 500, H = 512: LSTM 1.5-2.0e-4 (exp forms: 1.5-1.7e-4), GRU 2.8-3.6e-4 (2.6-3.3e-4),
+// profiles/r1_rtc_step_experiments.txt.  KIND is a compile-time constant at every call site.
+__device__ __forceinline__ float act_mufu(int kind, float x) {
+    float t;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(kind == NNTK_ACT_SIGMOID ? 0.5f * x : x));
+    return kind == NNTK_ACT_SIGMOID ? fmaf(0.5f, t, 0.5f) : t;
+}
+
 // K-major, SWIZZLE_128B shared-memory matrix descriptor: rows of 128 bytes, 8-row groups 1024 bytes apart.
 __device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
     uint64_t d = 0;
