@@ -23,6 +23,8 @@ from pathlib import Path
 
 import numpy as np
 
+_OUT = sys.stdout
+
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 sys.path.insert(0, str(ROOT / "tests"))
@@ -158,7 +160,7 @@ def run_reference_arm(args):
         "e2e": {"value": value, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_OUT, flush=True)
 
 
 def workload_config(name, cfg, n_gpus):
@@ -306,9 +308,17 @@ def run_ours(args):
             "config": workload_config("c2", cfg, world), "clocks": clk.summary(), "roofline": roofline,
             "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": args.steps,
         }
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_OUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def _claim_stdout():
+    """Keep the JSON line alone on stdout: libraries that write to fd 1 (NCCL's version banner) go to stderr."""
+    global _OUT
+    sys.stdout.flush()
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
 
 
 def main():
@@ -324,6 +334,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
+    _claim_stdout()
     if args.impl == "reference":
         run_reference_arm(args)
     else:
