@@ -170,6 +170,63 @@ def run_reference(workload: str, cfg: dict, units: int, procs: int | None = None
     return max(times), procs, wall_all
 
 
+def _pool_worker(conn, workload, cfg):
+    """persistent worker: imports and library load happen once; every request builds fresh (zero-state) handles for its
+    units outside the timed loop, exactly like run_reference's one-shot workers"""
+    _ref()
+    while True:
+        msg = conn.recv()
+        if msg is None:
+            break
+        first, count = msg
+        try:
+            conn.send(UNIT_FNS[workload](first, count, cfg) if count > 0 else 0.0)
+        except Exception as e:      # surfaced by Pool.run
+            conn.send(e)
+
+
+class Pool:
+    """`procs` long-lived worker processes (one per host core) for the --impl reference arm and the cpu_baseline leg, so that a
+    K-step run does not pay process start-up K times.  run(units) -> seconds of the slowest worker's timed Apply loop."""
+
+    def __init__(self, workload: str, cfg: dict, procs: int | None = None):
+        import multiprocessing as mp
+        ctx = mp.get_context("spawn")
+        self.procs = procs or host_cores()
+        self.workers = []
+        for _ in range(self.procs):
+            a, b = ctx.Pipe()
+            pr = ctx.Process(target=_pool_worker, args=(b, workload, cfg), daemon=True)
+            pr.start()
+            self.workers.append((pr, a))
+        self.next_first = 0
+
+    def run(self, units: int) -> float:
+        n = min(self.procs, max(1, units))
+        per = [units // n + (1 if i < units % n else 0) for i in range(n)]
+        for (_, conn), c in zip(self.workers, per):
+            conn.send((self.next_first, c))
+            self.next_first += c
+        times = []
+        for (_, conn), _c in zip(self.workers, per):
+            t = conn.recv()
+            if isinstance(t, Exception):
+                raise t
+            times.append(t)
+        return max(times)
+
+    def close(self):
+        for pr, conn in self.workers:
+            try:
+                conn.send(None)
+            except Exception:
+                pass
+        for pr, _ in self.workers:
+            pr.join(timeout=10)
+            if pr.is_alive():
+                pr.terminate()
+
+
 if __name__ == "__main__":
     # python bench_cpu.py c1 c3 c4 c5 [--units-per-core K]: one JSON line per config (reference CPU path, all host cores)
     import json

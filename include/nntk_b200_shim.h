@@ -45,6 +45,15 @@ void nntk_cuda_set_error(int code, const char *fmt, ...);
 int nntk_cuda_set_math_mode(int mode);
 int nntk_cuda_math_mode(void);
 int nntk_cuda_sm_count(void);
+/* kernel launches enqueued by this library since load (every launch site counts itself; bench.py's `gpu_launches`) */
+void nntk_cuda_count_launch(int n);
+long long nntk_cuda_launch_count(void);
+/* Process-wide recursive API lock.  The runtime state behind the shim (library stream, math mode, shared workspace, packed-
+ * operand scratch, the host-buffer staging pipeline) is per process, so every public Apply / Freeze entry of host/*.c holds
+ * this lock for the duration of its enqueue: calls from different host threads on different handles serialise instead of
+ * racing (the reference keeps all scratch per handle, SURVEY.md section 8b "Threading"). */
+void nntk_cuda_api_lock(void);
+void nntk_cuda_api_unlock(void);
 
 int nntk_cuda_malloc(void **d_ptr, size_t bytes);
 void nntk_cuda_free(void *d_ptr);
@@ -55,6 +64,11 @@ int nntk_cuda_h2d(void *d_dst, const void *h_src, size_t bytes);
 int nntk_cuda_d2h(void *h_dst, const void *d_src, size_t bytes);
 int nntk_cuda_d2d(void *d_dst, const void *d_src, size_t bytes);
 int nntk_cuda_memset(void *d_dst, int value, size_t bytes);
+/* events on the library stream (weight-snapshot reuse, host/common.c) */
+int nntk_cuda_event_create(void **ev);
+int nntk_cuda_event_record(void *ev);
+int nntk_cuda_event_sync(void *ev);
+void nntk_cuda_event_destroy(void *ev);
 /* 1 = device (or managed) pointer, 0 = host pointer */
 int nntk_cuda_is_device_ptr(const void *ptr);
 
@@ -167,6 +181,9 @@ typedef struct {
     size_t work_bytes;
 } nntk_recurrent_args;
 size_t nntk_cuda_recurrent_workspace(const nntk_recurrent_args *r);
+/* name of the kernel family that ran the most recent recurrent chunk: "fused_tc", "cluster_h16", "cluster_tf32", "cluster_fp32",
+ * "step_tc_f16", "step_tc_x3", "step_fp32" (diagnostics; tests pin the dispatch at the BASELINE shapes with it) */
+const char *nntk_cuda_last_recurrent_path(void);
 int nntk_cuda_recurrent(const nntk_recurrent_args *r);
 
 #ifdef __cplusplus

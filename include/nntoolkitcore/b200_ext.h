@@ -54,6 +54,10 @@ int NNTKSynchronize(void);
  * ActivationFunctionApply) report failures only here and on stderr. */
 const char *NNTKLastError(void);
 void NNTKClearError(void);
+/* Kernel launches enqueued by the library since it was loaded (diagnostics / benchmark accounting). */
+long long NNTKDebugLaunchCount(void);
+/* Which recurrent kernel family served the most recent RNN/GRU/LSTM Apply (see nntk_b200_shim.h). */
+const char *NNTKDebugLastRecurrentPath(void);
 
 /* GEMM-shaped stages (Conv1d, Dense/TDD, recurrent projections and steps) can run in three math modes. */
 #define NNTK_MATH_FP32 0    /* FFMA on CUDA cores; matches the reference within 1e-5 (default) */

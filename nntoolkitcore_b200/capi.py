@@ -167,6 +167,7 @@ REFERENCE_API = {
 EXT_API = {
     "NNTKInit": (c_int, [c_int]), "NNTKSetStream": (c_int, [c_void_p]), "NNTKGetStream": (c_void_p, []),
     "NNTKSynchronize": (c_int, []), "NNTKLastError": (c_char_p, []), "NNTKClearError": (None, []),
+    "NNTKDebugLaunchCount": (C.c_longlong, []), "NNTKDebugLastRecurrentPath": (c_char_p, []),
     "NNTKSetMathMode": (c_int, [c_int]), "NNTKGetMathMode": (c_int, []),
     "NNTKDeviceAlloc": (c_void_p, [c_size_t]), "NNTKDeviceFree": (None, [c_void_p]),
     "NNTKHostAlloc": (c_void_p, [c_size_t]), "NNTKHostFree": (None, [c_void_p]),
@@ -195,14 +196,16 @@ EXT_API = {
 SHIM_SYMBOLS = [
     "nntk_cuda_init", "nntk_cuda_ensure_init", "nntk_cuda_set_stream", "nntk_cuda_stream", "nntk_cuda_sync",
     "nntk_cuda_last_error", "nntk_cuda_clear_error", "nntk_cuda_set_error", "nntk_cuda_set_math_mode",
-    "nntk_cuda_math_mode", "nntk_cuda_sm_count", "nntk_cuda_malloc", "nntk_cuda_free", "nntk_cuda_host_alloc",
+    "nntk_cuda_math_mode", "nntk_cuda_sm_count", "nntk_cuda_count_launch", "nntk_cuda_launch_count",
+    "nntk_cuda_api_lock", "nntk_cuda_api_unlock", "nntk_cuda_malloc", "nntk_cuda_free", "nntk_cuda_host_alloc",
     "nntk_cuda_host_free", "nntk_cuda_h2d", "nntk_cuda_d2h", "nntk_cuda_d2d", "nntk_cuda_memset",
-    "nntk_cuda_is_device_ptr", "nntk_cuda_workspace", "nntk_cuda_staged_run", "nntk_cuda_spectrogram",
+    "nntk_cuda_is_device_ptr", "nntk_cuda_event_create", "nntk_cuda_event_record", "nntk_cuda_event_sync",
+    "nntk_cuda_event_destroy", "nntk_cuda_workspace", "nntk_cuda_staged_run", "nntk_cuda_spectrogram",
     "nntk_cuda_log_mel_spectrogram", "nntk_cuda_log_offset", "nntk_cuda_dft", "nntk_cuda_copy_strided",
     "nntk_cuda_bd_reverse", "nntk_cuda_bd_concat", "nntk_cuda_bd_sum",
     "nntk_cuda_batch_norm", "nntk_cuda_activation", "nntk_cuda_gemm", "nntk_cuda_pack_conv_weights",
     "nntk_cuda_pack_conv_weights_padded", "nntk_cuda_pad_channels",
-    "nntk_cuda_recurrent_workspace", "nntk_cuda_recurrent",
+    "nntk_cuda_recurrent_workspace", "nntk_cuda_recurrent", "nntk_cuda_last_recurrent_path",
 ]
 
 

@@ -20,9 +20,12 @@
         }                                                                                              \
     } while (0)
 
-// After a kernel launch: catches launch-configuration errors (asynchronous faults surface at the next sync).
-#define NNTK_LAUNCH_CHECK(name)                                                                        \
+// After a kernel launch: catches launch-configuration errors (asynchronous faults surface at the next sync) and counts
+// the launch (nntk_cuda_launch_count(): bench.py's `gpu_launches`).  NNTK_LAUNCH_CHECK_N: `n` launches behind one check.
+#define NNTK_LAUNCH_CHECK(name) NNTK_LAUNCH_CHECK_N(name, 1)
+#define NNTK_LAUNCH_CHECK_N(name, n)                                                                   \
     do {                                                                                               \
+        nntk_cuda_count_launch(n);                                                                     \
         cudaError_t e__ = cudaGetLastError();                                                          \
         if (e__ != cudaSuccess) {                                                                      \
             nntk_cuda_set_error(NNTK_ERR_CUDA_, "launch %s failed: %s", name, cudaGetErrorString(e__)); \

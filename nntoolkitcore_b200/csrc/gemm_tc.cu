@@ -434,7 +434,7 @@ extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_
     // reference: least-squares slope -(2.05..2.16)e-9 * K, residual rel-L2 <= 1.6e-6 once removed).  Compensated here.
     const float comp = split == 1 ? 1.0f + X3_ACC_TRUNC_PER_K * (float)K : (split ? 1.0f : 1.0f + TF32_TRUNC_BIAS);
     fold_epilogue_kernel<<<(N + 127) / 128, 128, 0, st>>>(a->d_bias, a->d_bn, a->bn_eps, N, scale, shift, comp);
-    NNTK_LAUNCH_CHECK("gemm_tf32 prologue");
+    NNTK_LAUNCH_CHECK_N("gemm_tf32 prologue", 2);
 
     // slab stride of A as the tensor map sees it (elements); in split mode the lo copy sits lo_off elements behind the hi copy
     const long long slab_floats = a->batch > 1 ? a->a_slab_stride : (long long)a->rows * a->lda;

@@ -384,6 +384,7 @@ static int launch_cluster(const ClusterDev &p, int groups, size_t smem, cudaStre
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     NNTK_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, p));
+    nntk_cuda_count_launch(1);
     return 0;
 }
 
@@ -433,7 +434,11 @@ extern "C" int nntk_cuda_recurrent_cluster_h16(const nntk_recurrent_args *r, int
 extern "C" int nntk_cuda_recurrent_cluster_h16_plan(const nntk_recurrent_args *r, int nb);
 extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_blocked);   // gemm_tc.cu
 
-static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *work) {
+// which kernel family ran the most recent recurrent chunk (tests pin the config-shape dispatch with it)
+static const char *g_last_path = "none";
+extern "C" const char *nntk_cuda_last_recurrent_path(void) { return g_last_path; }
+
+static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *work, size_t work_bytes) {
     const int G = r->cell, H = r->H, T = r->T, GH = G * H;
     const float *x = r->d_x + (long long)b0 * T * r->in;
     float *h = r->d_h + (long long)b0 * H;
@@ -455,7 +460,9 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     // rounding only 3.5e-4 -- and the projection is the cheap part.  The tensor-core STEP kernels stay single-pass TF32.
     const int proj_mode = (G == 1) ? 0 : (mode == 1 ? 2 : mode);
     static int min_batch = -1, use_h16 = -1;
-    if (min_batch < 0) { const char *e = getenv("NNTK_CLUSTER_TC_MIN_BATCH"); min_batch = e ? atoi(e) : 32; }
+    // never below 32: the blocked projection layout rounds the chunk up to 32 sequences and the chunker only reserves that
+    // rounding for chunks of at least 32 (nntk_cuda_recurrent below)
+    if (min_batch < 0) { const char *e = getenv("NNTK_CLUSTER_TC_MIN_BATCH"); min_batch = e ? atoi(e) : 32; if (min_batch < 32) min_batch = 32; }
     if (use_h16 < 0) { const char *e = getenv("NNTK_CLUSTER_H16"); use_h16 = e ? atoi(e) : 1; }
     int rc;
     // When the fp16 persistent cluster kernel will take this chunk, the projection is computed timestep-major and written in
@@ -468,7 +475,9 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     const bool step_tc = mode == 1 && G != 1 && !h16 && nb > 256 && (H > 256 || (H & 31)) && (H & 3) == 0 && (GH & 31) == 0;
     // TF32X3 mode (fp32 contract on the tensor cores): large batches run the same per-step kernel with hi/lo split operands
     const bool step_x3 = mode == 2 && G != 1 && nb > 256 && (H & 3) == 0 && (GH & 31) == 0 && H <= 3072 && r->in <= 3072;
-    if ((h16 || step_tc || step_x3) && (((uintptr_t)xw) & 15) == 0) {
+    // the blocked layout rounds the chunk up to 32 sequences: only when that (plus the ping-pong buffers) fits this workspace
+    const bool blocked_fits = ((size_t)((nb + 31) / 32 * 32) * T * GH + (size_t)6 * nb * H) * sizeof(float) <= work_bytes;
+    if ((h16 || step_tc || step_x3) && blocked_fits && (((uintptr_t)xw) & 15) == 0) {
         nntk_gemm_args gb = g;
         gb.batch = T; gb.rows = nb; gb.a_slab_stride = r->in; gb.lda = T * r->in;      // slab = timestep, row = sequence
         // 3xbf16 first (bf16 hi/lo split: ~2^-16 operand error, twice the tensor rate and half the operand bytes of 3xTF32);
@@ -494,7 +503,7 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
             int used = 0;
             rc = nntk_cuda_recurrent_cluster_h16(r, nb, xw, xw_blocked, h, c, out, &used);
             if (rc) return rc;
-            if (used) return 0;
+            if (used) { g_last_path = "cluster_h16"; return 0; }
             if (xw_blocked) {
                 nntk_cuda_set_error(NNTK_ERR_CUDA_, "recurrent: the planned fp16 cluster kernel did not run");
                 return NNTK_ERR_CUDA_;
@@ -504,7 +513,7 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
             int used = 0;
             rc = nntk_cuda_recurrent_cluster_tc(r, nb, xw, h, c, out, &used);
             if (rc) return rc;
-            if (used) return 0;
+            if (used) { g_last_path = "cluster_tf32"; return 0; }
         }
     }
     // 2a. small / medium batch: ONE persistent cluster kernel for all T steps (U resident in shared memory, DSMEM exchange)
@@ -512,7 +521,7 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
         int used = 0;
         rc = recurrent_cluster_try(r, nb, xw, h, c, out, &used);
         if (rc) return rc;
-        if (used) return 0;
+        if (used) { g_last_path = "cluster_fp32"; return 0; }
     }
     cudaStream_t st = nntk_stream();
     // 2b. large batch, TF32 mode: T tensor-core step kernels with the cell fused into the GEMM epilogue (recurrent_tc.cu)
@@ -520,7 +529,7 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
         int used = 0;
         rc = nntk_cuda_recurrent_tc(r, nb, xw, xw_blocked, h, c, out, pp, step_x3 ? 1 : 0, &used);
         if (rc) return rc;
-        if (used) goto carry_state;
+        if (used) { g_last_path = step_x3 ? "step_tc_x3" : "step_tc_f16"; goto carry_state; }
     }
     if (xw_blocked) {
         nntk_cuda_set_error(NNTK_ERR_CUDA_, "recurrent: the planned tensor-core kernel did not run on the blocked projection");
@@ -549,7 +558,8 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
         else if (G == 3) recurrent_step_kernel<3><<<grid, 256, 0, st>>>(p);
         else recurrent_step_kernel<4><<<grid, 256, 0, st>>>(p);
     }
-    NNTK_LAUNCH_CHECK("recurrent_step_kernel");
+    NNTK_LAUNCH_CHECK_N("recurrent_step_kernel", T);
+    g_last_path = "step_fp32";
     }
 carry_state:
     // 3. carry the final state back (reference: f_copy(filter->h, h_t), gru.c:201 / lstm.c:264-265 / rnn.c:241)
@@ -601,7 +611,7 @@ extern "C" int nntk_cuda_recurrent(const nntk_recurrent_args *r) {
     if (chunk < 1) chunk = 1;      // tiny workspace: plain layout paths only (nb < 32 never plans the blocked layout)
     for (int b0 = 0; b0 < r->batch; b0 += (int)chunk) {
         const int nb = (int)((b0 + chunk <= r->batch) ? chunk : (r->batch - b0));
-        rc = recurrent_chunk(r, b0, nb, r->d_work);
+        rc = recurrent_chunk(r, b0, nb, r->d_work, avail);
         if (rc) return rc;
     }
     return 0;

@@ -376,6 +376,7 @@ int launch_ht(const CUtensorMap &mu, const HtParams &p, int clusters, size_t sme
     if (max_out) *max_out = max_clusters;
     if (dry) return 0;
     NNTK_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mu, p));
+    nntk_cuda_count_launch(1);
     return 0;
 }
 

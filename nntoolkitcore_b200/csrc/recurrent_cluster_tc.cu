@@ -286,6 +286,7 @@ int launch_ct(const CUtensorMap &mu, const CtParams &p, int slices, size_t smem,
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     NNTK_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mu, p));
+    nntk_cuda_count_launch(1);
     return 0;
 }
 

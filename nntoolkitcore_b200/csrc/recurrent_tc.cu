@@ -605,7 +605,7 @@ extern "C" int nntk_cuda_recurrent_tc(const nntk_recurrent_args *r, int nb, cons
         else rc = x3 ? launch_rtc<4, 4, false, true>(*ma, mb, p, st) : cl2 ? launch_rtc<4, 4, true, false, true>(*ma, mb, p, st) : h16 ? launch_rtc<4, 4, true>(*ma, mb, p, st) : launch_rtc<4, 4, false>(*ma, mb, p, st);
         if (rc) return rc;
     }
-    NNTK_LAUNCH_CHECK("recurrent_tc_step_kernel");
+    NNTK_LAUNCH_CHECK_N("recurrent_tc_step_kernel", T);
     *used = 1;
     return 0;
 }

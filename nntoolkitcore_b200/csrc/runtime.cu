@@ -3,11 +3,13 @@
 #include <stdarg.h>
 #include <stdlib.h>
 #include <string.h>
+#include <atomic>
 #include <mutex>
 #include "common.cuh"
 
 namespace {
-std::mutex g_mu;
+std::recursive_mutex g_mu;          // the API lock (nntk_cuda_api_lock) -- also taken by init / staged_run / workspace
+std::atomic<long long> g_launches{0};
 int g_device = -1;            // -1: not initialised
 int g_sm_count = 0;
 cudaStream_t g_stream = 0;    // legacy default stream unless the caller sets one
@@ -38,7 +40,7 @@ extern "C" const char *nntk_cuda_last_error(void) { return t_err; }
 extern "C" void nntk_cuda_clear_error(void) { t_err[0] = 0; t_err_code = 0; }
 
 extern "C" int nntk_cuda_init(int device) {
-    std::lock_guard<std::mutex> lk(g_mu);
+    std::lock_guard<std::recursive_mutex> lk(g_mu);
     int count = 0;
     cudaError_t e = cudaGetDeviceCount(&count);
     if (e != cudaSuccess || count == 0) {
@@ -74,12 +76,18 @@ extern "C" int nntk_cuda_ensure_init(void) {
     return nntk_cuda_init(-1);
 }
 
+extern "C" void nntk_cuda_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+extern "C" long long nntk_cuda_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+extern "C" void nntk_cuda_api_lock(void) { g_mu.lock(); }
+extern "C" void nntk_cuda_api_unlock(void) { g_mu.unlock(); }
 extern "C" int nntk_cuda_sm_count(void) { return g_sm_count > 0 ? g_sm_count : 148; }
 extern "C" int nntk_cuda_set_stream(void *stream) { g_stream = (cudaStream_t)stream; return 0; }
 extern "C" void *nntk_cuda_stream(void) { return (void *)g_stream; }
 extern "C" int nntk_cuda_sync(void) {
     if (g_device < 0) return 0;
-    NNTK_CUDA_TRY(cudaStreamSynchronize(g_stream));
+    cudaStream_t s;
+    { std::lock_guard<std::recursive_mutex> lk(g_mu); s = g_stream; }   // never the pipeline stream a host-buffer Apply swapped in
+    NNTK_CUDA_TRY(cudaStreamSynchronize(s));
     return 0;
 }
 extern "C" int nntk_cuda_set_math_mode(int mode) {
@@ -155,6 +163,15 @@ extern "C" int nntk_cuda_memset(void *d, int v, size_t bytes) {
     NNTK_CUDA_TRY(cudaMemsetAsync(d, v, bytes, g_stream));
     return 0;
 }
+extern "C" int nntk_cuda_event_create(void **ev) {
+    cudaEvent_t e;
+    NNTK_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    *ev = (void *)e;
+    return 0;
+}
+extern "C" int nntk_cuda_event_record(void *ev) { NNTK_CUDA_TRY(cudaEventRecord((cudaEvent_t)ev, g_stream)); return 0; }
+extern "C" int nntk_cuda_event_sync(void *ev) { NNTK_CUDA_TRY(cudaEventSynchronize((cudaEvent_t)ev)); return 0; }
+extern "C" void nntk_cuda_event_destroy(void *ev) { if (ev) cudaEventDestroy((cudaEvent_t)ev); }
 extern "C" int nntk_cuda_is_device_ptr(const void *ptr) {
     if (!ptr || g_device < 0) {
         int count = 0;
@@ -200,7 +217,7 @@ extern "C" int nntk_cuda_staged_run(const void *h_in, void *h_out, size_t unit_i
     int rc = nntk_cuda_ensure_init();
     if (rc) return rc;
     if (n_units <= 0) return 0;
-    std::lock_guard<std::mutex> lk(g_mu);
+    std::lock_guard<std::recursive_mutex> lk(g_mu);
     // chunk so that one slot moves ~256 MiB of (in + out): large enough for PCIe efficiency, small enough to overlap
     const size_t target = (size_t)256 << 20;
     size_t per_unit = unit_in_bytes + unit_out_bytes;

@@ -51,6 +51,7 @@ static int act_launch(void *ctx, const float *d_in, float *d_out, long long firs
 }
 
 int ActivationFunctionApplyBatch(ActivationFunction filter, const float *input, float *output, int batch) {
+    NNTK_API_GUARD();
     if (!filter || batch < 0) {
         nntk_cuda_set_error(NNTK_ERR_ARG, "ActivationFunctionApply: bad arguments");
         return NNTK_ERR_ARG;
@@ -74,5 +75,6 @@ int ActivationFunctionApplyBatch(ActivationFunction filter, const float *input, 
 }
 
 void ActivationFunctionApply(ActivationFunction filter, const float *input, float *output) {
+    NNTK_API_GUARD();
     (void)ActivationFunctionApplyBatch(filter, input, output, 1);
 }

@@ -58,6 +58,7 @@ static int bn_launch(void *ctx, const float *d_in, float *d_out, long long first
 }
 
 int BatchNormApplyInferenceBatch(BatchNorm filter, const float *input, float *output, int batch) {
+    NNTK_API_GUARD();
     if (!filter || batch < 0) {
         nntk_cuda_set_error(NNTK_ERR_ARG, "BatchNormApplyInference: bad arguments");
         return NNTK_ERR_ARG;
@@ -72,5 +73,6 @@ int BatchNormApplyInferenceBatch(BatchNorm filter, const float *input, float *ou
 }
 
 int BatchNormApplyInference(BatchNorm filter, const float *input, float *output) {
+    NNTK_API_GUARD();
     return BatchNormApplyInferenceBatch(filter, input, output, 1);
 }

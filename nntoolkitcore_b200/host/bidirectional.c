@@ -46,9 +46,11 @@ static void reverse_batch(const float *in, float *out, int vec, int T, int batch
     bd_run(in, NULL, out, n, 0, n, batch, rev_launch, &c, who);
 }
 void bd_reverse_input_batch(const float *input, float *output, RecurrentConfig config, int batch) {
+    NNTK_API_GUARD();
     reverse_batch(input, output, config.input_feature_channels, config.timesteps, batch, "bd_reverse_input_batch");
 }
 void bd_reverse_backward_batch(const float *input, float *output, RecurrentConfig config, int batch) {
+    NNTK_API_GUARD();
     reverse_batch(input, output, config.output_feature_channels, config.timesteps, batch, "bd_reverse_backward_batch");
 }
 
@@ -63,6 +65,7 @@ static int cat_launch(const float *d_a, const float *d_b, float *d_out, const vo
 }
 void bd_merge_concat(const float *forward_result, const float *backward_result, float *output, RecurrentConfig config,
                      int batch, float *buffer) {
+    NNTK_API_GUARD();
     (void)buffer; /* the reference's transpose scratch (bidirectional.c:50-53) */
     cat_ctx c = {config.output_feature_channels, bd_rows(config)};
     if (c.cols < 1 || c.rows < 0 || !backward_result) { nntk_cuda_set_error(NNTK_ERR_ARG, "bd_merge_concat: bad arguments"); return; }
@@ -74,6 +77,7 @@ static int sum_launch(const float *d_a, const float *d_b, float *d_out, const vo
     return nntk_cuda_bd_sum(d_a, d_b, d_out, units * *(const long long *)ctx);
 }
 void bd_merge_sum(const float *forward_result, const float *backward_result, float *output, RecurrentConfig config, int batch) {
+    NNTK_API_GUARD();
     long long n = (long long)config.output_feature_channels * bd_rows(config);
     if (n < 0 || !backward_result) { nntk_cuda_set_error(NNTK_ERR_ARG, "bd_merge_sum: bad arguments"); return; }
     bd_run(forward_result, backward_result, output, (size_t)n, (size_t)n, (size_t)n, batch, sum_launch, &n, "bd_merge_sum");

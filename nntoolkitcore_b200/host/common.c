@@ -16,9 +16,12 @@ int nntk_layer_init(nntk_layer_hdr *h, int kind, size_t n_floats) {
 
 void nntk_layer_release(nntk_layer_hdr *h) {
     if (!h) return;
+    if (h->snap_ev) { nntk_cuda_event_sync(h->snap_ev); nntk_cuda_event_destroy(h->snap_ev); }
+    nntk_cuda_host_free(h->h_snap);
     nntk_cuda_host_free(h->h_block);
     nntk_cuda_free(h->d_block);
-    h->h_block = h->d_block = NULL;
+    h->h_block = h->d_block = h->h_snap = NULL;
+    h->snap_ev = NULL;
     h->magic = 0;
 }
 
@@ -30,7 +33,18 @@ int nntk_layer_stage(nntk_layer_hdr *h) {
         if ((rc = nntk_cuda_malloc(&d, h->n_floats * sizeof(float)))) return rc;
         h->d_block = (float *)d;
     }
-    if ((rc = nntk_cuda_h2d(h->d_block, h->h_block, h->n_floats * sizeof(float)))) return rc;
+    /* snapshot first (synchronous host copy), then the asynchronous H2D reads the snapshot: a caller that rewrites its weights
+     * right after a device-pointer Apply returned cannot race with the copy engine.  The previous restage's H2D must have
+     * drained before the snapshot is overwritten (one event, normally long complete). */
+    if (!h->h_snap) {
+        void *p = NULL;
+        if (nntk_cuda_host_alloc(&p, h->n_floats * sizeof(float))) return NNTK_ERR_ARG;
+        h->h_snap = (float *)p;
+        if ((rc = nntk_cuda_event_create(&h->snap_ev))) return rc;
+    } else if ((rc = nntk_cuda_event_sync(h->snap_ev))) return rc;
+    memcpy(h->h_snap, h->h_block, h->n_floats * sizeof(float));
+    if ((rc = nntk_cuda_h2d(h->d_block, h->h_snap, h->n_floats * sizeof(float)))) return rc;
+    if ((rc = nntk_cuda_event_record(h->snap_ev))) return rc;
     if (h->after_stage && (rc = h->after_stage(h))) return rc;
     h->staged = 1;
     return 0;
@@ -61,22 +75,25 @@ static nntk_layer_hdr *as_layer(void *layer, const char *who) {
 }
 
 int NNTKInit(int device) { return nntk_cuda_init(device); }
-int NNTKSetStream(void *s) { return nntk_cuda_set_stream(s); }
+int NNTKSetStream(void *s) { NNTK_API_GUARD(); return nntk_cuda_set_stream(s); }
 void *NNTKGetStream(void) { return nntk_cuda_stream(); }
 int NNTKSynchronize(void) { return nntk_cuda_sync(); }
 const char *NNTKLastError(void) { return nntk_cuda_last_error(); }
 void NNTKClearError(void) { nntk_cuda_clear_error(); }
-int NNTKSetMathMode(int mode) { return nntk_cuda_set_math_mode(mode); }
+long long NNTKDebugLaunchCount(void) { return nntk_cuda_launch_count(); }
+const char *NNTKDebugLastRecurrentPath(void) { return nntk_cuda_last_recurrent_path(); }
+int NNTKSetMathMode(int mode) { NNTK_API_GUARD(); return nntk_cuda_set_math_mode(mode); }
 int NNTKGetMathMode(void) { return nntk_cuda_math_mode(); }
 void *NNTKDeviceAlloc(size_t bytes) { void *p = NULL; return nntk_cuda_malloc(&p, bytes) ? NULL : p; }
 void NNTKDeviceFree(void *p) { nntk_cuda_free(p); }
 void *NNTKHostAlloc(size_t bytes) { void *p = NULL; return nntk_cuda_host_alloc(&p, bytes) ? NULL : p; }
 void NNTKHostFree(void *p) { nntk_cuda_host_free(p); }
-int NNTKCopyToDevice(void *d, const void *h, size_t n) { int rc = nntk_cuda_ensure_init(); return rc ? rc : nntk_cuda_h2d(d, h, n); }
-int NNTKCopyToHost(void *h, const void *d, size_t n) { int rc = nntk_cuda_ensure_init(); return rc ? rc : nntk_cuda_d2h(h, d, n); }
+int NNTKCopyToDevice(void *d, const void *h, size_t n) { NNTK_API_GUARD(); int rc = nntk_cuda_ensure_init(); return rc ? rc : nntk_cuda_h2d(d, h, n); }
+int NNTKCopyToHost(void *h, const void *d, size_t n) { NNTK_API_GUARD(); int rc = nntk_cuda_ensure_init(); return rc ? rc : nntk_cuda_d2h(h, d, n); }
 int NNTKIsDevicePointer(const void *p) { return nntk_cuda_is_device_ptr(p); }
 
 int NNTKWeightsFreeze(void *layer) {
+    NNTK_API_GUARD();
     nntk_layer_hdr *h = as_layer(layer, "NNTKWeightsFreeze");
     if (!h) return NNTK_ERR_ARG;
     h->frozen = 0;
@@ -87,6 +104,7 @@ int NNTKWeightsFreeze(void *layer) {
     return 0;
 }
 int NNTKWeightsUnfreeze(void *layer) {
+    NNTK_API_GUARD();
     nntk_layer_hdr *h = as_layer(layer, "NNTKWeightsUnfreeze");
     if (!h) return NNTK_ERR_ARG;
     h->frozen = 0;

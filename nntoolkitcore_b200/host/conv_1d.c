@@ -139,6 +139,7 @@ static int conv_launch(void *ctx, const float *d_in, float *d_out, long long fir
 
 int Conv1dBNActApplyInferenceBatch(Conv1d filter, BatchNorm bn, ActivationFunction act, const float *input,
                                    float *output, int batch) {
+    NNTK_API_GUARD();
     if (!filter || batch < 0) {
         nntk_cuda_set_error(NNTK_ERR_ARG, "Conv1dApplyInference: bad arguments");
         return NNTK_ERR_ARG;
@@ -173,8 +174,10 @@ int Conv1dBNActApplyInferenceBatch(Conv1d filter, BatchNorm bn, ActivationFuncti
 }
 
 int Conv1dApplyInferenceBatch(Conv1d filter, const float *input, float *output, int batch) {
+    NNTK_API_GUARD();
     return Conv1dBNActApplyInferenceBatch(filter, NULL, NULL, input, output, batch);
 }
 int Conv1dApplyInference(Conv1d filter, const float *input, float *output) {
+    NNTK_API_GUARD();
     return Conv1dBNActApplyInferenceBatch(filter, NULL, NULL, input, output, 1);
 }

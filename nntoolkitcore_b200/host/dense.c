@@ -91,9 +91,11 @@ static int dense_apply(struct DenseStruct *f, int rows_per_unit, const float *in
 }
 
 int DenseApplyInferenceBatch(Dense filter, const float *input, float *output, int batch) {
+    NNTK_API_GUARD();
     return dense_apply(filter, 1, input, output, batch, "DenseApplyInference");
 }
 int DenseApplyInference(Dense filter, const float *input, float *output) {
+    NNTK_API_GUARD();
     return dense_apply(filter, 1, input, output, 1, "DenseApplyInference");
 }
 
@@ -124,9 +126,11 @@ void TimeDistributedDenseDestroy(TimeDistributedDense filter) {
     free(filter);
 }
 int TimeDistributedDenseApplyInferenceBatch(TimeDistributedDense filter, const float *input, float *output, int batch) {
+    NNTK_API_GUARD();
     if (!filter) { nntk_cuda_set_error(NNTK_ERR_ARG, "TimeDistributedDenseApplyInference: NULL handle"); return NNTK_ERR_ARG; }
     return dense_apply(&filter->dense, filter->config.ts, input, output, batch, "TimeDistributedDenseApplyInference");
 }
 int TimeDistributedDenseApplyInference(TimeDistributedDense filter, const float *input, float *output) {
+    NNTK_API_GUARD();
     return TimeDistributedDenseApplyInferenceBatch(filter, input, output, 1);
 }

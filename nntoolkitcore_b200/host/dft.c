@@ -53,6 +53,7 @@ static int dft_stage(DFTSetup s) {
 }
 
 int DFTPerformBatch(DFTSetup setup, const ComplexFloatSplit *input, const ComplexFloatSplit *output, int batch) {
+    NNTK_API_GUARD();
     if (!setup || !input || !output || batch < 0) {
         nntk_cuda_set_error(NNTK_ERR_ARG, "DFTPerform: bad arguments");
         return NNTK_ERR_ARG;
@@ -93,11 +94,13 @@ int DFTPerformBatch(DFTSetup setup, const ComplexFloatSplit *input, const Comple
 
 /* void like the reference (dft.c:34): failures land in NNTKLastError() and on stderr */
 void DFTPerform(DFTSetup setup, ComplexFloatSplit *input, ComplexFloatSplit *output) {
+    NNTK_API_GUARD();
     (void)DFTPerformBatch(setup, input, output, 1);
 }
 
 /* dft.c:60-71 / :80-84: plain element loops on host buffers; strided device copies on device buffers */
 void split_complex(const ComplexFloat *complex, ComplexFloatSplit *split, int size) {
+    NNTK_API_GUARD();
     if (!complex || !split || size < 0) return;
     if (nntk_cuda_is_device_ptr(complex)) {
         (void)nntk_cuda_copy_strided(split->real_p, 1, &complex->real, 2, size);
@@ -111,6 +114,7 @@ void split_complex(const ComplexFloat *complex, ComplexFloatSplit *split, int si
 }
 
 void join_complex_split(const ComplexFloatSplit *split, ComplexFloat *complex, int size) {
+    NNTK_API_GUARD();
     if (!complex || !split || size < 0) return;
     if (nntk_cuda_is_device_ptr(complex)) {
         (void)nntk_cuda_copy_strided(&complex->real, 2, split->real_p, 1, size);

@@ -10,6 +10,11 @@
 #include "nntk_b200_shim.h"
 #include "nntoolkitcore/b200_ext.h"
 
+/* Scoped hold of the process-wide recursive API lock (nntk_b200_shim.h): first statement of every public entry that enqueues
+ * device work or touches the shared runtime state; released on every return path (gcc/clang cleanup attribute). */
+static inline void nntk_api_unlock_cleanup_(int *unused) { (void)unused; nntk_cuda_api_unlock(); }
+#define NNTK_API_GUARD() int nntk_api_guard_ __attribute__((cleanup(nntk_api_unlock_cleanup_), unused)) = (nntk_cuda_api_lock(), 0)
+
 #define NNTK_LAYER_MAGIC 0x4e544b4cu /* 'NTKL' */
 enum { NNTK_L_BATCHNORM = 1, NNTK_L_CONV1D, NNTK_L_DENSE, NNTK_L_TDD, NNTK_L_RNN, NNTK_L_GRU, NNTK_L_LSTM };
 
@@ -18,6 +23,9 @@ typedef struct nntk_layer_hdr {
     int kind;
     float *h_block;   /* host weight block the caller writes through XGetWeights (pinned when a device exists) */
     float *d_block;   /* device mirror, same layout */
+    float *h_snap;    /* private pinned snapshot the H2D reads from: the caller may rewrite h_block right after an asynchronous
+                         (device-pointer) Apply returns, so the copy engine must never read h_block itself */
+    void *snap_ev;    /* recorded after the H2D of h_snap: the next restage waits for it before overwriting the snapshot */
     size_t n_floats;
     int frozen;       /* NNTKWeightsFreeze: skip the per-Apply restage */
     int staged;       /* device mirror valid */

@@ -71,6 +71,7 @@ static int logmel_launch(void *ctx, const float *d_in, float *d_out, long long f
 }
 
 int LogMelSpectrogramApplyBatch(LogMelSpectrogram f, const float *input, float *output, int n_clips) {
+    NNTK_API_GUARD();
     if (!f || n_clips < 0) {
         nntk_cuda_set_error(NNTK_ERR_ARG, "LogMelSpectrogramApplyBatch: bad arguments");
         return NNTK_ERR_ARG;
@@ -87,5 +88,6 @@ int LogMelSpectrogramApplyBatch(LogMelSpectrogram f, const float *input, float *
 
 /* void like the reference (:33): failures land in NNTKLastError() and on stderr */
 void LogMelSpectrogramApply(LogMelSpectrogram f, const float *input, float *output) {
+    NNTK_API_GUARD();
     (void)LogMelSpectrogramApplyBatch(f, input, output, 1);
 }

@@ -229,6 +229,7 @@ static int mel_launch(void *ctx, const float *d_in, float *d_out, long long firs
 
 /* void like the reference: failures land in NNTKLastError() and on stderr */
 void MelFilterBankApply(MelFilterBank b, const float *spectrogram, float *mel_spectrogram, int timesteps) {
+    NNTK_API_GUARD();
     if (!b || timesteps < 0) { nntk_cuda_set_error(NNTK_ERR_ARG, "MelFilterBankApply: bad arguments"); return; }
     int kind = nntk_ptr_kind(spectrogram, mel_spectrogram, "MelFilterBankApply");
     if (kind < 0 || nntk_mel_stage(b)) return;

@@ -79,6 +79,7 @@ static int ensure_state(nntk_recurrent *f) {
 }
 
 int NNTKResetState(void *layer) {
+    NNTK_API_GUARD();
     nntk_recurrent *f = (nntk_recurrent *)layer;
     if (!f || f->hdr.magic != NNTK_LAYER_MAGIC || f->hdr.kind < NNTK_L_RNN || f->hdr.kind > NNTK_L_LSTM) {
         nntk_cuda_set_error(NNTK_ERR_ARG, "NNTKResetState: not a recurrent layer handle");
@@ -126,9 +127,14 @@ static int rec_launch(void *ctx, const float *d_in, float *d_out, long long firs
     const size_t state_slots = (rc_->mode == 0) ? 0 : (G == NNTK_CELL_LSTM ? 2 : 1);
     const size_t state_total = ((state_slots * state_bytes + 255) / 256) * 256;
     size_t want = nntk_cuda_recurrent_workspace(&r) + state_total;
-    const size_t per_seq = sizeof(float) * ((size_t)T * G * H + 4 * (size_t)H);
+    /* the smallest workspace nntk_cuda_recurrent accepts: one sequence in its own accounting (projection + 6 H of ping-pong,
+     * + 256), derived from the device side so the two can never disagree */
+    nntk_recurrent_args one = r;
+    one.batch = 1;
+    const size_t per_seq = sizeof(float) * ((size_t)T * G * H + 6 * (size_t)H) + 256;
+    const size_t min_ws = nntk_cuda_recurrent_workspace(&one) > per_seq ? nntk_cuda_recurrent_workspace(&one) : per_seq;
     void *ws = NULL; size_t got = 0;
-    int rc = nntk_cuda_workspace(want, state_total + per_seq + 256, &ws, &got);
+    int rc = nntk_cuda_workspace(want, state_total + min_ws, &ws, &got);
     if (rc) return rc;
     float *d_hs = (float *)ws, *d_cs = (float *)((char *)ws + state_bytes);
     r.d_work = (float *)((char *)ws + state_total);
@@ -167,6 +173,7 @@ static int rec_launch(void *ctx, const float *d_in, float *d_out, long long firs
 
 static int rec_apply(nntk_recurrent *f, int mode, const float *input, float *output, int batch, float *h_state,
                      float *c_state, const char *who) {
+    NNTK_API_GUARD();
     if (!f || batch < 0) { nntk_cuda_set_error(NNTK_ERR_ARG, "%s: bad arguments", who); return NNTK_ERR_ARG; }
     int kind = nntk_ptr_kind(input, output, who);
     if (kind < 0) return kind;

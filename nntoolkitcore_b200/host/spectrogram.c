@@ -152,6 +152,7 @@ static void spectrogram_args(Spectrogram s, nntk_spectrogram_args *out) {
 }
 
 int SpectrogramApplyBatch(Spectrogram filter, const float *input, float *output, int n_clips) {
+    NNTK_API_GUARD();
     if (!filter || n_clips < 0) {
         nntk_cuda_set_error(NNTK_ERR_ARG, "SpectrogramApplyBatch: bad arguments");
         return NNTK_ERR_ARG;
@@ -168,5 +169,6 @@ int SpectrogramApplyBatch(Spectrogram filter, const float *input, float *output,
 
 /* void like the reference (spectrogram.c:113): failures land in NNTKLastError() and on stderr */
 void SpectrogramApply(Spectrogram filter, const float *input, float *output) {
+    NNTK_API_GUARD();
     (void)SpectrogramApplyBatch(filter, input, output, 1);
 }

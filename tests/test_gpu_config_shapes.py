@@ -1,0 +1,150 @@
+"""GPU tier: the tensor-core-mode kernels pinned AT THE BASELINE CONFIG SHAPES ("What's weak" #1).
+
+  * C4: LSTM 512 -> 512, T = 500 at a batch large enough that the large-batch path really runs (asserted through
+    NNTKDebugLastRecurrentPath), three sequences against the unmodified reference (layers/lstm.c:185-268);
+  * C5: the full chain spectrogram -> BN -> Conv1d+ReLU -> GRU -> GRU -> TDD+softmax at T = 998 -> 994 in tensor-core mode,
+    end to end against the reference chain (signal/spectrogram.c:113, layers/batch_norm.c:166, conv_1d.c:149, gru.c:189,
+    time_distributed_dense.c:52) at the stated 1e-3 on the softmax output and on every intermediate;
+  * the whole fp32-contract GPU suite re-run with NNTK_MATH_MODE=2 (3xTF32 on tcgen05) as the process default: the claim that
+    this mode holds 1e-5 is checked by the driver, not just stated;
+  * XApplyInferenceBatchState against the reference's single-stream stateful calls (layers/gru.c:197-201, lstm.c:257-265).
+"""
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import helpers
+from helpers import assert_parity, TF32_TOL
+from nntoolkitcore_b200 import layers as L
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parent.parent
+
+
+@pytest.fixture()
+def tf32(cuda, product):
+    assert product.NNTKSetMathMode(1) == 0
+    yield product
+    product.NNTKSetMathMode(0)
+
+
+def _path(lib):
+    return lib.NNTKDebugLastRecurrentPath().decode()
+
+
+def test_c4_lstm_large_batch_path_at_config_shape(tf32, ref):
+    """C4 unit at a batch above every persistent-cluster threshold: 500 steps of the large-batch tensor-core path"""
+    import torch
+    H, T, B = 512, 500, 1600
+    rng = np.random.default_rng(8)
+    pool = rng.standard_normal((64, T, H)).astype(np.float32)
+    dev = torch.device("cuda:0")
+    x = torch.from_numpy(pool).to(dev).repeat(B // 64, 1, 1).contiguous()
+    r = L.Recurrent(tf32, "lstm", H, H, T)
+    helpers.fill_recurrent(r, 400)
+    got = r.apply_batch(x)
+    torch.cuda.synchronize()
+    path = _path(tf32)
+    assert path in ("fused_tc", "step_tc_f16"), f"C4 at B = {B} ran '{path}', not a large-batch tensor-core kernel"
+    pick = [0, 63 + 64 * 7, B - 1]
+    for b in pick:
+        rr = L.Recurrent(ref, "lstm", H, H, T); helpers.copy_weights(rr, r)
+        want = rr.apply(pool[b % 64]); rr.close()
+        err, l2 = assert_parity(got[b].cpu().numpy(), want, tol=TF32_TOL, what=f"C4 LSTM-512 T=500 B={B} [{path}] sequence {b}")
+        assert l2 > 1e-7, "suspiciously exact: the tensor-core path did not run"
+    # every copy of a pool sequence must give the same answer wherever it sits in the batch (tile / wave / tail positions)
+    g = got.view(B // 64, 64, T, H)
+    assert torch.equal(g[0], g[-1]) and torch.equal(g[0], g[(B // 64) // 2])
+    r.close()
+
+
+def _chain(lib, B, to_dev=None):
+    n = 160000
+    spec = L.Spectrogram(lib, 512, 400, 240, n, 1.0, "hann_window")
+    T0, F = spec.out_shape
+    bn = L.BatchNorm(lib, F, 1e-3, T0); helpers.fill_bn(bn, 500)
+    conv = L.Conv1d(lib, F, 256, 5, 1, T0); helpers.fill_conv(conv, 501)
+    T1 = conv.out_shape[0]
+    relu = L.Activation(lib, L.ACT_RELU, T1 * 256)
+    g1 = L.Recurrent(lib, "gru", 256, 256, T1); helpers.fill_recurrent(g1, 502)
+    g2 = L.Recurrent(lib, "gru", 256, 256, T1); helpers.fill_recurrent(g2, 503)
+    tdd = L.Dense(lib, 256, 12, L.ACT_SOFTMAX, ts=T1); helpers.fill_dense(tdd, 504)
+    return dict(spec=spec, bn=bn, conv=conv, relu=relu, g1=g1, g2=g2, tdd=tdd, T0=T0, T1=T1, F=F)
+
+
+def test_c5_chain_end_to_end_at_config_shape(tf32, ref):
+    """the headline chain at its real length (T = 998 -> 994 steps through two GRU layers), tensor-core mode, vs the reference"""
+    import torch
+    B, n = 136, 160000
+    dev = torch.device("cuda:0")
+    clips = np.stack([helpers.audio_clip(i, n) for i in range(8)])
+    x = torch.from_numpy(clips).to(dev).repeat(B // 8, 1).contiguous()
+    c = _chain(tf32, B)
+    s = c["spec"].apply_batch(x)
+    s = c["bn"].apply_batch(s)
+    cv = c["conv"].apply_batch(s, act=c["relu"])
+    h1 = c["g1"].apply_batch(cv)
+    p1 = _path(tf32)
+    h2 = c["g2"].apply_batch(h1)
+    y = c["tdd"].apply_batch(h2)
+    torch.cuda.synchronize()
+    assert p1 in ("fused_tc", "cluster_h16"), f"C5 GRU ran '{p1}'"
+    for b in (0, 5, B - 1):
+        rc = _chain(ref, 1)
+        for k in ("bn", "conv", "g1", "g2", "tdd"):
+            helpers.copy_weights(rc[k], c[k])
+        w_cv = rc["relu"].apply(rc["conv"].apply(rc["bn"].apply(rc["spec"].apply(clips[b % 8]))))
+        w_h1 = rc["g1"].apply(w_cv)
+        w_h2 = rc["g2"].apply(w_h1)
+        w_y = rc["tdd"].apply(w_h2)
+        assert_parity(cv[b].cpu().numpy(), w_cv, tol=TF32_TOL, what=f"C5 chain conv+ReLU, clip {b}")
+        assert_parity(h1[b].cpu().numpy(), w_h1, tol=TF32_TOL, what=f"C5 chain GRU1 (994 steps) [{p1}], clip {b}")
+        assert_parity(h2[b].cpu().numpy(), w_h2, tol=TF32_TOL, what=f"C5 chain GRU2 (994 steps), clip {b}")
+        err, l2 = assert_parity(y[b].cpu().numpy(), w_y, tol=TF32_TOL, what=f"C5 chain softmax output, clip {b}")
+        assert l2 > 1e-8
+        for v in rc.values():
+            if hasattr(v, "close"):
+                v.close()
+    yv = y.view(B // 8, 8, c["T1"], 12)
+    assert torch.equal(yv[0], yv[-1]), "copies of the same clip at different batch positions differ"
+    if hasattr(tf32, "SpectrogramBNConv1dApplyBatch"):
+        fused = torch.empty_like(cv)
+        L.front_end(tf32, c["spec"], c["bn"], c["conv"], None, c["relu"], x, fused)
+        torch.cuda.synchronize()
+        assert_parity(fused.cpu().numpy(), cv.cpu().numpy(), tol=2e-6, what="fused front end vs the three separate calls")
+
+
+def test_fp32_contract_suite_holds_under_3xtf32_default():
+    """NNTK_MATH_MODE=2 as the process default: every test written for the FFMA path at 1e-5 must pass on the split-operand
+    tensor-core path too -- except the one that demands bit-exact copies through a delta kernel (FFMA-only property)"""
+    env = dict(os.environ, NNTK_MATH_MODE="2")
+    cmd = [sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu", "-p", "no:cacheprovider",
+           str(ROOT / "tests" / "test_gpu_parity.py"), str(ROOT / "tests" / "test_gpu_layers.py"), str(ROOT / "tests" / "test_gpu_next.py"),
+           "-k", "not delta_kernel_is_shifted_copy"]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, cwd=str(ROOT), timeout=1500)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1500:]
+
+
+@pytest.mark.parametrize("cell", ["gru", "lstm"])
+def test_batched_streaming_state_matches_reference_single_stream_calls(cuda, product, ref, cell):
+    """f3 against the REFERENCE: B concurrent streams fed in two chunks through XApplyInferenceBatchState == B reference handles
+    each called twice (the reference carries h / c across calls, gru.c:197-201, lstm.c:257-265)"""
+    in_size, H, T, B = 24, 64, 12, 7
+    rng = np.random.default_rng(44)
+    x = rng.standard_normal((B, 2 * T, in_size)).astype(np.float32)
+    half = L.Recurrent(product, cell, in_size, H, T); helpers.fill_recurrent(half, 405)
+    h = np.zeros((B, H), np.float32); c = np.zeros((B, H), np.float32)
+    kw = dict(h_state=h, c_state=c) if cell == "lstm" else dict(h_state=h)
+    a = half.apply_batch(np.ascontiguousarray(x[:, :T]), **kw)
+    b = half.apply_batch(np.ascontiguousarray(x[:, T:]), **kw)
+    for i in range(B):
+        r = L.Recurrent(ref, cell, in_size, H, T); helpers.copy_weights(r, half)
+        w1 = r.apply(x[i, :T]); w2 = r.apply(x[i, T:])
+        assert_parity(np.concatenate([a[i], b[i]]), np.concatenate([w1, w2]), what=f"{cell} streaming state vs reference, stream {i}")
+        assert_parity(h[i], w2[-1], what=f"{cell} final carried h, stream {i}")
+        r.close()
+    half.close()
