@@ -350,8 +350,12 @@ __global__ void __launch_bounds__(CL_THREADS, 1) recurrent_cluster_kernel(Cluste
 
 }  // namespace
 
+extern "C" int nntk_cuda_recurrent_fused_plan(const nntk_recurrent_args *r, int nb);          // recurrent_fused.cu
 extern "C" size_t nntk_cuda_recurrent_workspace(const nntk_recurrent_args *r) {
     if (!r) return 0;
+    // tensor-core mode, fused persistent kernel with the projection computed in-kernel: only the minimum the fallback paths need
+    if (nntk_cuda_math_mode() == 1 && r->cell != 1 && nntk_cuda_recurrent_fused_plan(r, r->batch) == 1)
+        return (size_t)32 * r->T * r->cell * r->H * sizeof(float) + (size_t)6 * 32 * r->H * sizeof(float) + 256;
     const size_t G = (size_t)r->cell;
     size_t xw = (size_t)((r->batch + 31) / 32 * 32) * r->T * G * r->H * sizeof(float);   // 32-sequence blocks
     size_t pp = (size_t)6 * r->batch * r->H * sizeof(float);   // exact h ping-pong + operand ping-pong (3xTF32: hi and lo parts)
@@ -433,6 +437,9 @@ extern "C" int nntk_cuda_recurrent_cluster_h16(const nntk_recurrent_args *r, int
                                                float *c, float *out, int *used);  // recurrent_cluster_h16.cu
 extern "C" int nntk_cuda_recurrent_cluster_h16_plan(const nntk_recurrent_args *r, int nb);
 extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_blocked);   // gemm_tc.cu
+extern "C" int nntk_cuda_recurrent_fused_plan(const nntk_recurrent_args *r, int nb);          // recurrent_fused.cu
+extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, const float *x, const float *xw, float *h, float *c,
+                                         float *out, int *used);
 
 // which kernel family ran the most recent recurrent chunk (tests pin the config-shape dispatch with it)
 static const char *g_last_path = "none";
@@ -459,6 +466,16 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     // single-pass TF32 rounding of x and W in the PROJECTION alone costs 1.2e-3 (each operand ~7e-4), the recurrent TF32
     // rounding only 3.5e-4 -- and the projection is the cheap part.  The tensor-core STEP kernels stay single-pass TF32.
     const int proj_mode = (G == 1) ? 0 : (mode == 1 ? 2 : mode);
+    // 0. tensor-core mode, default activations, H % 64 == 0: ONE persistent kernel per layer (recurrent_fused.cu).  Plan 1 also
+    //    computes the input projection inside that kernel -- no projection buffer, no GEMM launch; plan 2 reads the blocked
+    //    hoisted projection below.
+    const int fplan = (mode == 1 && G != 1) ? nntk_cuda_recurrent_fused_plan(r, nb) : 0;
+    if (fplan == 1) {
+        int used = 0;
+        int frc = nntk_cuda_recurrent_fused(r, nb, x, nullptr, h, c, out, &used);
+        if (frc) return frc;
+        if (used) { g_last_path = "fused_tc"; return 0; }
+    }
     static int min_batch = -1, use_h16 = -1;
     // never below 32: the blocked projection layout rounds the chunk up to 32 sequences and the chunker only reserves that
     // rounding for chunks of at least 32 (nntk_cuda_recurrent below)
@@ -477,7 +494,7 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     const bool step_x3 = mode == 2 && G != 1 && nb > 256 && (H & 3) == 0 && (GH & 31) == 0 && H <= 3072 && r->in <= 3072;
     // the blocked layout rounds the chunk up to 32 sequences: only when that (plus the ping-pong buffers) fits this workspace
     const bool blocked_fits = ((size_t)((nb + 31) / 32 * 32) * T * GH + (size_t)6 * nb * H) * sizeof(float) <= work_bytes;
-    if ((h16 || step_tc || step_x3) && blocked_fits && (((uintptr_t)xw) & 15) == 0) {
+    if ((h16 || step_tc || step_x3 || fplan == 2) && blocked_fits && (((uintptr_t)xw) & 15) == 0) {
         nntk_gemm_args gb = g;
         gb.batch = T; gb.rows = nb; gb.a_slab_stride = r->in; gb.lda = T * r->in;      // slab = timestep, row = sequence
         // 3xbf16 first (bf16 hi/lo split: ~2^-16 operand error, twice the tensor rate and half the operand bytes of 3xTF32);
@@ -495,6 +512,12 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
         rc = nntk_cuda_gemm(&g);
         if (proj_mode != mode) nntk_cuda_set_math_mode(mode);
         if (rc) return rc;
+    }
+    if (fplan == 2 && xw_blocked) {
+        int used = 0;
+        rc = nntk_cuda_recurrent_fused(r, nb, x, xw, h, c, out, &used);
+        if (rc) return rc;
+        if (used) { g_last_path = "fused_tc_xw"; return 0; }
     }
     // 2a'. TF32 mode, H <= 256, batch >= NNTK_CLUSTER_TC_MIN_BATCH (default 32): ONE persistent tensor-core cluster kernel
     //      for all T steps (recurrent_cluster_tc.cu: U resident in shared memory, DSMEM bulk-copy h exchange)
@@ -592,6 +615,13 @@ extern "C" int nntk_cuda_recurrent(const nntk_recurrent_args *r) {
             return NNTK_ERR_UNSUPPORTED_;
         }
     if (r->batch == 0 || r->T == 0) return 0;
+    // The fused persistent kernel (tensor-core mode) computes the projection itself: no workspace, so no batch chunking either
+    if (nntk_cuda_math_mode() == 1 && r->cell != 1 && nntk_cuda_recurrent_fused_plan(r, r->batch) == 1) {
+        int used = 0;
+        rc = nntk_cuda_recurrent_fused(r, r->batch, r->d_x, nullptr, r->d_h, r->d_c, r->d_out, &used);
+        if (rc) return rc;
+        if (used) { g_last_path = "fused_tc"; return 0; }
+    }
     // batch chunks that fit the workspace
     const size_t per_seq = ((size_t)r->T * r->cell * r->H + 6 * (size_t)r->H) * sizeof(float);
     size_t avail = r->work_bytes > 256 ? r->work_bytes - 256 : 0;

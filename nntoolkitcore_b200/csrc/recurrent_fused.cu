@@ -1,0 +1,838 @@
+// recurrent_fused.cu -- K3 + K4 in ONE persistent kernel per GRU / LSTM layer (tensor-core mode, default gate activations).
+// Replaces, for the shapes it covers, the hoisted-projection GEMM + persistent cluster kernel / per-step kernels of the
+// NNTK_MATH_TF32 mode (reference loops: layers/gru.c:129-204, layers/lstm.c:185-268).
+//
+// Work decomposition.  A CTA PAIR (2-CTA cluster, tcgen05.mma.cta_group::2, M = 128) owns 128 sequences -- 64 per CTA -- for
+// ALL T timesteps.  h never leaves the pair: there is no exchange between CTAs beyond the operand sharing of the 2-CTA MMA.
+//   * B operands (W for the input part, U for the recurrent part; fp16, repacked once per call so that a tile holds all gates
+//     of 64 hidden units) are STREAMED from L2 through a TMA ring, each CTA loading the rows of its 32 units of the tile; the
+//     pair's MMA reads both halves.  Nothing is resident: H = 512 works like H = 256.
+//   * A operands live in shared memory for the whole kernel: the fp16 image of h_{t-1} [64 rows x H] (rewritten by the
+//     epilogue once per step, after the step's last MMA) and -- FUSED mode -- the fp16 image of x_t [64 rows x in], produced by
+//     converter warps straight from the caller's fp32 rows: x_{t+1} waits in their REGISTERS while step t runs (the global
+//     loads are a whole step old when the tile frees up), so there is no staging buffer and no projection buffer at all:
+//     per layer HBM sees x once and h once -- the algorithmic traffic (r1: ~4.5x that).
+//     Input passes (RfParams::xp): 3 = x and W split into fp16 hi + lo, products hi*Wlo, lo*Whi, hi*Whi (x . W exact to ~2^-22,
+//     like the 3xbf16 projection it replaces; the default), 1 = hi*Whi only (fp16-rounded x and W: measured 1.2e-3 max error on
+//     N(0,1) inputs at in = 256, T = 300 -- too coarse for the mode's 1e-3 in general, fine for bounded activations).
+//     XW mode (H = 512 / in > 256, where the x tile does not fit) instead reads the hoisted projection in the blocked layout of
+//     gemm_tc.cu.
+//   * Accumulators in TMEM: one 128-column buffer per 64-unit tile (cta_group::2 layout: lanes 0-63 hold the columns computed
+//     from CTA 0's B rows = units 0-31 of the tile, lanes 64-127 units 32-63; scripts/probe_cg2.cu pins this).  GRU columns
+//     [x.Wh | z | r | h.Uh]: the input part writes the first three groups (N = 192), the recurrent part accumulates onto the last
+//     three (N = 192; the h.Uh group is re-zeroed by the epilogue), so r * (h.Uh + b_hh) + x.Wh keeps its two terms apart
+//     (gru.c:169-171).  LSTM columns [i | f | g | o], both parts N = 256.  N >= 192 matters: a pair MMA costs max(57, N/4)
+//     cycles (probe), so 32-unit tiles would run at 42 %.
+//   * The fp32 recurrent state (h for GRU, c for LSTM) also lives in TMEM (H/2 columns, lane = row x unit half): it is read
+//     and written only by the thread that owns (row, units); 64 x H floats would not fit the register file.
+//   * Input-part MMAs of the NEXT tile are issued one tile ahead of the recurrent part, and x_{t+1} . W does not depend on h:
+//     across the step boundary the tensor pipe works on it while the last tile's cell math finishes.
+// Warp roles: 0-7 epilogue (TMEM lane quarter = warp % 4; thread = one row x 16 units of the tile), 8-15 x converters (FUSED
+// only), then the four control warps: ring producer (TMA), MMA issuer (leader CTA, one thread), idle, TMEM allocation.  The
+// control warps sit LAST on purpose: the warp scheduler favours the highest warp id on a sub-partition, and with the issuer as
+// warp 1 (first version) it shared its scheduler with four polling / computing warps and needed 130-170 cycles per MMA
+// (the instruction itself: <= 57).  setmaxnreg moves registers from the control and converter warps to the epilogue warps.
+// Precision: fp16 operands (round to nearest), fp32 accumulate, fp32 state, MUFU.TANH gates: the 1e-3 class of the tensor-core
+// mode; tests/test_gpu_tf32.py and tests/test_gpu_config_shapes.py pin it against the reference at the config shapes.
+#include <cuda_fp16.h>
+#include <stdlib.h>
+#include <vector>
+#include "tc_common.cuh"
+
+namespace {
+
+constexpr int RF_ROWS = 64;                  // sequences per CTA (pair: 128)
+constexpr int RF_UT = 64;                    // hidden units per tile (pair), 32 per CTA
+constexpr int RF_THREADS_FUSED = 640, RF_THREADS_XW = 384;
+constexpr int RF_MAX_RING = 8;
+
+struct RfParams {
+    int B, H, in, T;
+    int return_sequences;
+    int ring_stages;
+    int xp;                          // FUSED: input passes, 1 or 3
+    int cs;                          // cluster size: 2, 4 or 8 CTAs = 1, 2 or 4 pairs sharing every B stage by TMA multicast
+    int xw_blocked_rows;             // XW mode: row_blocks of the blocked projection
+    const float *x;                  // FUSED: [B][T][in]
+    const float *bias_i, *bias_h;    // [G*H] each; bias_h may be null (not added)
+    const float *xw;                 // XW mode: blocked projection [T][row_blocks][G*H/4][32][4] (b_i already added)
+    float *h_state, *c_state;        // [B][H] in/out
+    float *out;                      // [B][T][H] or [B][H]
+    long long *dbg;                  // development: per-CTA wait-cycle counters [grid][16] (NNTK_RF_DBG=1), else null
+    int skip;                        // development (RF_DEBUG builds, NNTK_RF_SKIP): 1 no cell math / TMEM traffic, 2 no h_t stores,
+                                     // 4 no x conversion, 8 no MMAs (results are garbage: timing experiments only)
+};
+// cycles spent in a wait, accumulated per role (only when p.dbg): 0 mma:ring_full 1 mma:acc_empty 2 mma:h_full 3 mma:x_full
+// 4 epi:acc_full 5 epi:total 6 conv:convert 7 conv:x_empty 8 prod:ring_empty 10 mma:total 11 epi:store_wait
+// Compiled in only with -DRF_DEBUG=1 (NNTK_NVCC_EXTRA): the counters cost registers the control warps do not have.
+#ifndef RF_DEBUG
+#define RF_DEBUG 0
+#endif
+#if RF_DEBUG
+#define RF_T0() const long long t0__ = p.dbg ? clock64() : 0
+#define RF_T1(i) do { if (p.dbg) dbgc[i] += clock64() - t0__; } while (0)
+#define RF_DBG(stmt) do { if (p.dbg) { stmt; } } while (0)
+#define RF_SKIP(bit) (p.skip & (bit))
+#else
+#define RF_SKIP(bit) false
+#define RF_T0() do { } while (0)
+#define RF_T1(i) do { } while (0)
+#define RF_DBG(stmt) do { } while (0)
+#endif
+
+__device__ __forceinline__ uint32_t rf_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void rf_cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t rf_mapa(uint32_t a, uint32_t rank) {
+    uint32_t d; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(rank)); return d;
+}
+// Arrive on the barrier at cluster address `a` (the leader CTA's copy).  Default (CTA-scope) semantics on both sides, like
+// CUTLASS's ClusterBarrier: what crosses the pair is either TMEM traffic (ordered by tcgen05.fence + tcgen05.wait) or shared
+// memory read by the async proxy (ordered by fence.proxy.async before the arrive).  Cluster-scope release / acquire cost an
+// ERRBAR resp. a CCTL.IVALL per signal (ncu, first version: membar 3.1 of 16 stall cycles per issue).
+__device__ __forceinline__ void rf_arrive_cl(uint32_t a) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(a) : "memory");
+}
+__device__ __forceinline__ bool rf_elect() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+__device__ __forceinline__ void rf_fence_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+// TMA 2-D load, multicast to the CTAs of `mask` (same shared-memory offset in each); with .cta_group::2 the bytes are counted on
+// the barrier at offset `bar` (peer bit cleared) in the PAIR LEADER of every destination CTA -- CUTLASS's SM100_TMA_2SM_LOAD_MULTICAST
+__device__ __forceinline__ void rf_tma_2d_cg2_mc(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1, uint16_t mask) {
+    asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
+                 ::"r"(dst), "l"(map), "r"(bar & 0xFEFFFFFFu), "r"(c0), "r"(c1), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void rf_tma_store_3d(const CUtensorMap *map, const void *src, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                 ::"l"(map), "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void rf_mma(uint32_t d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+}
+// commit arriving on the barrier at this offset in every CTA of `mask` once all MMAs issued so far have completed
+__device__ __forceinline__ void rf_commit(uint64_t *bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void rf_ld8(uint32_t taddr, float (&r)[8]) {
+    uint32_t u[8];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]) : "r"(taddr));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r[i] = __uint_as_float(u[i]);
+}
+__device__ __forceinline__ void rf_st8(uint32_t taddr, const float (&r)[8]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 ::"r"(taddr), "r"(__float_as_uint(r[0])), "r"(__float_as_uint(r[1])), "r"(__float_as_uint(r[2])), "r"(__float_as_uint(r[3])),
+                   "r"(__float_as_uint(r[4])), "r"(__float_as_uint(r[5])), "r"(__float_as_uint(r[6])), "r"(__float_as_uint(r[7])) : "memory");
+}
+__device__ __forceinline__ void rf_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void rf_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ uint32_t rf_pack_sat(float a, float b) {      // two floats -> packed fp16, round to nearest, finite
+    uint32_t r;
+    asm("{\n\t.reg .f16 lo, hi;\n\tcvt.rn.satfinite.f16.f32 lo, %1;\n\tcvt.rn.satfinite.f16.f32 hi, %2;\n\tmov.b32 %0, {lo, hi};\n\t}"
+        : "=r"(r) : "f"(a), "f"(b));
+    return r;
+}
+// hi = fp16(v) pairs; lo = fp16(v - hi) pairs (v - hi is exact in fp32)
+__device__ __forceinline__ void rf_split2(float a, float b, uint32_t &hi, uint32_t &lo) {
+    hi = rf_pack_sat(a, b);
+    const __half2 h = *reinterpret_cast<const __half2 *>(&hi);
+    const float2 f = __half22float2(h);
+    lo = rf_pack_sat(a - f.x, b - f.y);
+}
+
+// shared-memory plan (host and device agree through this one struct)
+template <int G, bool FUSED>
+struct RfPlan {
+    int a_h, x_hi, x_lo, out_stg, bias, ring, bars, total;
+    int sub_bytes, stage_bytes;
+    __host__ __device__ RfPlan(int H, int in, int xp, int ring_stages) {
+        sub_bytes = 32 * G * 128;                            // one k-block of B: [32 G rows of this CTA][64 halves]
+        stage_bytes = 2 * sub_bytes;                         // a ring stage holds two k-blocks
+        int o = 0;
+        a_h = o; o += RF_ROWS * H * 2;                       // [H/64 k-blocks][64 rows][128 B]
+        x_hi = o; o += FUSED ? RF_ROWS * in * 2 : 0;         // [in/64][64 rows][128 B]
+        x_lo = o; o += (FUSED && xp == 3) ? RF_ROWS * in * 2 : 0;
+        out_stg = o; o += 8 * 2048;                          // per epilogue warp: [32 rows][16 floats], SWIZZLE_64B
+        ring = o; o += ring_stages * stage_bytes;
+        bias = o; o += 4 * H * 4;
+        bars = o; o += 1024;
+        total = o + 1024;                                    // + alignment slack
+    }
+};
+
+// barrier block layout (uint64 slots)
+constexpr int RFB_RING_FULL = 0, RFB_RING_EMPTY = RF_MAX_RING, RFB_ACC_FULL = 2 * RF_MAX_RING, RFB_ACC_EMPTY = RFB_ACC_FULL + 4,
+              RFB_H_FULL = RFB_ACC_EMPTY + 4, RFB_X_FULL = RFB_H_FULL + 1, RFB_X_EMPTY = RFB_X_FULL + 4, RFB_END = RFB_X_EMPTY + 1;
+
+// NCMAX: compile-time bound of the tiles per step (H / 64 <= NCMAX): sizes the register-resident pending-h array.
+template <int G, bool FUSED, int NCMAX>
+__global__ void __launch_bounds__(FUSED ? RF_THREADS_FUSED : RF_THREADS_XW, 1)
+recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_wl,
+                       const __grid_constant__ CUtensorMap map_u, const __grid_constant__ CUtensorMap map_out, RfParams p) {
+    constexpr int NW = 64 * G;                              // N of one MMA (LSTM 256, GRU 192)
+    constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(NW >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);   // f32 <- f16 x f16, K-major
+    constexpr int ROWS_B = 32 * G;                          // B rows per CTA per k-block
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const int H = p.H, IN = p.in, T = p.T, XP = p.xp;
+    const int NC = H / RF_UT;                               // tiles per step
+    const int KBH = H / 64, KBX = FUSED ? IN / 64 : 0;      // k-blocks of the recurrent / input part
+    const int NB = (512 - H / 2) / 128;                     // accumulator buffers (3 for H <= 256, 2 for H = 512)
+    const uint32_t STATE_COL = (uint32_t)(NB * 128);
+    const RfPlan<G, FUSED> pl(H, IN, XP, p.ring_stages);
+    uint8_t *sAh = smem + pl.a_h, *sXh = smem + pl.x_hi, *sXl = smem + pl.x_lo, *sOut = smem + pl.out_stg, *sRing = smem + pl.ring;
+    float *sBias = reinterpret_cast<float *>(smem + pl.bias);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + pl.bars);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + RFB_END);
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);          // warp-uniform for the compiler (role dispatch, uniform registers)
+    constexpr int CONV_W0 = 8, CTRL_W0 = FUSED ? 16 : 8;     // first converter / control warp
+    const uint32_t crank = rf_rank();                       // rank in the cluster; pairs are (0,1), (2,3), ...
+    const uint32_t rank = crank & 1u, leader = crank & ~1u; // rank inside the pair, cluster rank of the pair's leader
+    const int npairs = p.cs >> 1, pair_i = (int)(crank >> 1);
+    const uint16_t pair_mask = (uint16_t)(3u << leader), all_mask = (uint16_t)((1u << p.cs) - 1u);
+    const int row0 = (blockIdx.x >> 1) * 128 + (int)rank * RF_ROWS;      // first sequence of this CTA
+    // tile counters are 32-bit and advanced incrementally everywhere: 64-bit divisions in the issuer's loop cost ~13 000 cycles per
+    // step in the first version (more than all of the step's MMAs)
+
+    if (tid == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_wl) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_u) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_out) : "memory");
+        for (int s = 0; s < p.ring_stages; ++s) { mbar_init(bars + RFB_RING_FULL + s, 1); mbar_init(bars + RFB_RING_EMPTY + s, (uint32_t)npairs); }
+        for (int b = 0; b < 4; ++b) { mbar_init(bars + RFB_ACC_FULL + b, 1); mbar_init(bars + RFB_ACC_EMPTY + b, 16); }
+        mbar_init(bars + RFB_H_FULL, 16);
+        for (int b = 0; b < 4; ++b) mbar_init(bars + RFB_X_FULL + b, 16);
+        mbar_init(bars + RFB_X_EMPTY, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == CTRL_W0 + 3) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    // bias table [4][H]: GRU {b_i z + b_h z, b_i r + b_h r, b_i h, b_h h}; LSTM {b_i g + b_h g} per gate.  XW mode: b_i is in xw.
+    for (int i = tid; i < 4 * H; i += (int)blockDim.x) {
+        const int a = i / H, u = i - a * H;
+        const float *bi = FUSED ? p.bias_i : nullptr;
+        float v;
+        if (G == 3) {
+            if (a < 2) v = (bi ? __ldg(bi + a * H + u) : 0.f) + (p.bias_h ? __ldg(p.bias_h + a * H + u) : 0.f);
+            else if (a == 2) v = bi ? __ldg(bi + 2 * H + u) : 0.f;
+            else v = p.bias_h ? __ldg(p.bias_h + 2 * H + u) : 0.f;
+        } else {
+            v = (bi ? __ldg(bi + a * H + u) : 0.f) + (p.bias_h ? __ldg(p.bias_h + a * H + u) : 0.f);
+        }
+        sBias[i] = v;
+    }
+    tc_fence_before();
+    __syncthreads();
+    rf_cluster_sync();               // both CTAs' barriers exist before anybody arrives remotely
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+#if RF_DEBUG
+    long long dbgc[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const long long t_start = p.dbg ? clock64() : 0;
+#endif
+
+    if (warp >= CTRL_W0) {
+        if (FUSED) asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
+        if (warp == CTRL_W0 && lane == 0) {
+            // ===== ring producer: this CTA's half of every B stage (two k-blocks), in the order the MMA issuer consumes them =====
+            int stage = 0; uint32_t phase = 0;
+            // Every B stage is identical for all pairs of the cluster: this CTA fetches 1 / npairs of the rows of its half and
+            // multicasts them to the CTAs of the same half in every pair (L2 -> SM traffic / npairs: with 128 CTAs each pulling its own
+            // copy the stream ran at the per-SM share of the L2 bandwidth, ~43 B/cycle, and bounded the step).  A slot is free once ALL
+            // pairs' MMAs have read it (ring_empty counts one multicast commit per pair).
+            const uint32_t full_l = smem_u32(bars + RFB_RING_FULL), ring_a = smem_u32(sRing);
+            const int slice_rows = ROWS_B / npairs;
+            uint16_t half_mask = 0;
+            for (int i = 0; i < npairs; ++i) half_mask |= (uint16_t)(1u << (2 * i + (int)rank));
+            auto put = [&](const CUtensorMap *map, int kb0, int nkb, int tile) {
+                { RF_T0(); mbar_wait(bars + RFB_RING_EMPTY + stage, phase ^ 1); RF_T1(8); }
+                RF_T0();
+                if (rank == 0) mbar_expect_tx(bars + RFB_RING_FULL + stage, 2u * (uint32_t)(nkb * pl.sub_bytes));
+                for (int i = 0; i < nkb; ++i)
+                    rf_tma_2d_cg2_mc(ring_a + (uint32_t)(stage * pl.stage_bytes + i * pl.sub_bytes + pair_i * slice_rows * 128), map,
+                                     full_l + 8u * (uint32_t)stage, (kb0 + i) * 64, (tile * 2 + (int)rank) * ROWS_B + pair_i * slice_rows, half_mask);
+                RF_T1(9);
+                if (++stage == p.ring_stages) { stage = 0; phase ^= 1; }
+            };
+            auto put_x = [&](int tile) {
+                if (XP == 3) for (int kb = 0; kb < KBX; kb += 2) put(&map_wl, kb, min(2, KBX - kb), tile);
+                for (int kb = 0; kb < KBX; kb += 2) put(&map_w, kb, min(2, KBX - kb), tile);
+            };
+            if (FUSED) put_x(0);
+            for (int t = 0; t < T; ++t)
+                for (int c = 0; c < NC; ++c) {
+                    for (int kb = 0; kb < KBH; kb += 2) put(&map_u, kb, min(2, KBH - kb), c);
+                    if (FUSED && !(t == T - 1 && c == NC - 1)) put_x(c + 1 == NC ? 0 : c + 1);
+                }
+            RF_DBG(p.dbg[blockIdx.x * 16 + 8] = dbgc[8]; p.dbg[blockIdx.x * 16 + 9] = dbgc[9]);
+        } else if (warp == CTRL_W0 + 1 && rank == 0) {
+            // ===== MMA issuer (leader CTA): static order  X(0), then per tile g: H(g), X(g + 1) =====
+            // The WHOLE warp runs this code converged on warp-uniform values, and only the tcgen05 instructions are predicated on
+            // elect.sync (the CUTLASS way): descriptors then live in uniform registers.  Issued from one divergent thread the compiler
+            // wrapped every MMA in an ELECT / 5 x R2UR.BROADCAST / BRA loop -- ncu: ~80 cycles of issue overhead per 57-cycle MMA.
+            int stage = 0; uint32_t phase = 0;
+            const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+            const uint32_t ring_a = smem_u32(sRing), ah_a = smem_u32(sAh), xh_a = smem_u32(sXh), xl_a = smem_u32(sXl);
+            // one ring stage = up to two k-blocks of B; a0 (and a1 when given: the lo image first, then the hi image) are the A tiles
+            auto stage_mmas = [&](uint32_t d, uint32_t a0, uint32_t a1, int kb0, int nkb, bool first_acc) {
+                { RF_T0(); mbar_wait(bars + RFB_RING_FULL + stage, phase); RF_T1(0); }
+                tc_fence_after();
+                { RF_T0();
+                if (rf_elect()) {
+                for (int i = 0; i < nkb; ++i) {
+                    const uint64_t db = make_desc(ring_a + (uint32_t)(stage * pl.stage_bytes + i * pl.sub_bytes));
+                    if (RF_SKIP(8)) continue;
+                    if (a1) {
+                        const uint64_t dl = make_desc(a1 + (uint32_t)((kb0 + i) * RF_ROWS * 128));
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) rf_mma(d, dl + 2 * k, db + 2 * k, IDESC, 1u);
+                    }
+                    const uint64_t da = make_desc(a0 + (uint32_t)((kb0 + i) * RF_ROWS * 128));
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) rf_mma(d, da + 2 * k, db + 2 * k, IDESC, (first_acc && kb0 + i == 0 && k == 0) ? 0u : 1u);
+                }
+                rf_commit(bars + RFB_RING_EMPTY + stage, all_mask);
+                }
+                __syncwarp();
+                RF_T1(13); }
+                if (++stage == p.ring_stages) { stage = 0; phase ^= 1; }
+            };
+            // (t, c) = step and tile; buf = accumulator buffer of the tile, use = how often that buffer has been used before
+            auto x_part = [&](int t, int c, int buf, int use) {
+                if (use > 0) { RF_T0(); mbar_wait(bars + RFB_ACC_EMPTY + buf, (uint32_t)((use - 1) & 1)); RF_T1(1); }
+                tc_fence_after();
+                const uint32_t d = tmem + (uint32_t)(buf * 128);
+                if (XP == 3) {           // small terms first: x_hi . W_lo, then x_lo . W_hi + x_hi . W_hi off the same W_hi stage
+                    for (int kb = 0; kb < KBX; kb += 2) {
+                        if (c == 0) for (int i = kb; i < min(kb + 2, KBX); ++i) { RF_T0(); mbar_wait(bars + RFB_X_FULL + i, (uint32_t)(t & 1)); RF_T1(3); }
+                        stage_mmas(d, xh_a, 0u, kb, min(2, KBX - kb), true);
+                    }
+                    for (int kb = 0; kb < KBX; kb += 2) stage_mmas(d, xh_a, xl_a, kb, min(2, KBX - kb), false);
+                } else {
+                    for (int kb = 0; kb < KBX; kb += 2) {
+                        if (c == 0) for (int i = kb; i < min(kb + 2, KBX); ++i) { RF_T0(); mbar_wait(bars + RFB_X_FULL + i, (uint32_t)(t & 1)); RF_T1(3); }
+                        stage_mmas(d, xh_a, 0u, kb, min(2, KBX - kb), true);
+                    }
+                }
+                if (c == NC - 1) { if (rf_elect()) rf_commit(bars + RFB_X_EMPTY, pair_mask); __syncwarp(); }     // the x tile may be rewritten once these MMAs are done
+            };
+            auto h_part = [&](int t, int c, int buf, int use) {
+                if (c == 0) { RF_T0(); mbar_wait(bars + RFB_H_FULL, (uint32_t)(t & 1)); RF_T1(2); }
+                if (!FUSED && use > 0) { RF_T0(); mbar_wait(bars + RFB_ACC_EMPTY + buf, (uint32_t)((use - 1) & 1)); RF_T1(1); }
+                tc_fence_after();
+                // GRU fused: the recurrent part lands one 32-column group to the right ([z | r | h.Uh]) and always accumulates
+                const uint32_t d = tmem + (uint32_t)(buf * 128) + ((FUSED && G == 3) ? 32u : 0u);
+                for (int kb = 0; kb < KBH; kb += 2) stage_mmas(d, ah_a, 0u, kb, min(2, KBH - kb), !FUSED);
+                if (rf_elect()) rf_commit(bars + RFB_ACC_FULL + buf, pair_mask);
+                __syncwarp();
+            };
+            // the tile after (t, c) in issue order and its buffer bookkeeping
+            int buf = 0, use = 0;                 // of the tile whose recurrent part is issued next
+            if (FUSED) x_part(0, 0, 0, 0);
+            for (int t = 0; t < T; ++t)
+                for (int c = 0; c < NC; ++c) {
+                    h_part(t, c, buf, use);
+                    int nbuf = buf + 1, nuse = use;
+                    if (nbuf == NB) { nbuf = 0; ++nuse; }
+                    if (FUSED && !(t == T - 1 && c == NC - 1)) x_part(c + 1 == NC ? t + 1 : t, c + 1 == NC ? 0 : c + 1, nbuf, nuse);
+                    buf = nbuf; use = nuse;
+                }
+            RF_DBG(if (lane == 0) { for (int i = 0; i < 4; ++i) p.dbg[blockIdx.x * 16 + i] = dbgc[i]; p.dbg[blockIdx.x * 16 + 10] = clock64() - t_start;
+                   p.dbg[blockIdx.x * 16 + 12] = dbgc[12]; p.dbg[blockIdx.x * 16 + 13] = dbgc[13]; });
+        }
+    } else if (warp >= CONV_W0) {
+        // ===== x converters (FUSED only): fp32 rows of x_t from global -> fp16 hi (and lo) k-block tiles =====
+        // item (row, 16-byte chunk of the fp16 row = 8 floats): a warp covers 4 rows x 256 contiguous bytes per load instruction and
+        // 512 contiguous (swizzled) bytes per store.  x_{t+1} is loaded right after x_t has been converted and waits in registers.
+        if (FUSED) {
+            asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
+            const int ct = tid - CONV_W0 * 32;
+            const uint32_t xfull0 = rf_mapa(smem_u32(bars + RFB_X_FULL), leader);
+            // Registers hold k-blocks 0 and 1 of x_{t+1} (a whole step old when needed); k-blocks 2 and 3 are only pulled into L2
+            // then and loaded while the first two are being consumed -- holding all four (64 registers) spilled.
+            float4 v[2][2][2];
+            auto src_of = [&](int t, int kb, int it) -> const float4 * {
+                const int idx = it * 256 + ct, r = idx >> 3, ch = idx & 7, row = row0 + r;
+                return row < p.B ? reinterpret_cast<const float4 *>(p.x + ((size_t)row * T + t) * IN + kb * 64 + ch * 8) : nullptr;
+            };
+            auto preload = [&](int t) {
+#pragma unroll
+                for (int kb = 0; kb < 2; ++kb) {
+                    if (kb >= KBX) break;
+#pragma unroll
+                    for (int it = 0; it < 2; ++it) {
+                        const float4 *src = src_of(t, kb, it);
+                        if (src) { v[kb][it][0] = __ldg(src); v[kb][it][1] = __ldg(src + 1); }
+                        else v[kb][it][0] = v[kb][it][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                }
+                for (int kb = 2; kb < KBX; ++kb)
+#pragma unroll
+                    for (int it = 0; it < 2; ++it) {
+                        const float4 *src = src_of(t, kb, it);
+                        if (src) asm volatile("prefetch.global.L2 [%0];" ::"l"(src));
+                    }
+            };
+            auto emit = [&](int kb, int it, const float4 &a, const float4 &b) {
+                if (RF_SKIP(4)) return;
+                const int idx = it * 256 + ct, r = idx >> 3, ch = idx & 7;
+                uint4 hi, lo;
+                if (XP == 3) {
+                    rf_split2(a.x, a.y, hi.x, lo.x); rf_split2(a.z, a.w, hi.y, lo.y); rf_split2(b.x, b.y, hi.z, lo.z); rf_split2(b.z, b.w, hi.w, lo.w);
+                    *reinterpret_cast<uint4 *>(sXl + (size_t)kb * (RF_ROWS * 128) + r * 128 + ((ch ^ (r & 7)) << 4)) = lo;
+                } else {
+                    hi.x = rf_pack_sat(a.x, a.y); hi.y = rf_pack_sat(a.z, a.w); hi.z = rf_pack_sat(b.x, b.y); hi.w = rf_pack_sat(b.z, b.w);
+                }
+                *reinterpret_cast<uint4 *>(sXh + (size_t)kb * (RF_ROWS * 128) + r * 128 + ((ch ^ (r & 7)) << 4)) = hi;
+            };
+            auto publish = [&](int kb) {
+                rf_fence_async();
+                __syncwarp();
+                if (lane == 0) rf_arrive_cl(xfull0 + 8u * (uint32_t)kb);
+            };
+            preload(0);
+            for (int t = 0; t < T; ++t) {
+                if (t >= 1) { RF_T0(); mbar_wait(bars + RFB_X_EMPTY, (uint32_t)((t - 1) & 1)); RF_T1(7); }
+                RF_T0();
+                float4 w[2][2];
+                if (KBX > 2) {           // late k-block 2: in flight while 0 and 1 are converted
+#pragma unroll
+                    for (int it = 0; it < 2; ++it) {
+                        const float4 *src = src_of(t, 2, it);
+                        if (src) { w[it][0] = __ldg(src); w[it][1] = __ldg(src + 1); } else w[it][0] = w[it][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                }
+#pragma unroll
+                for (int kb = 0; kb < 2; ++kb) {
+                    if (kb >= KBX) break;
+#pragma unroll
+                    for (int it = 0; it < 2; ++it) emit(kb, it, v[kb][it][0], v[kb][it][1]);
+                    publish(kb);
+                }
+                for (int kb = 2; kb < KBX; ++kb) {
+                    float4 u[2][2];
+#pragma unroll
+                    for (int it = 0; it < 2; ++it) { u[it][0] = w[it][0]; u[it][1] = w[it][1]; }
+                    if (kb + 1 < KBX) {
+#pragma unroll
+                        for (int it = 0; it < 2; ++it) {
+                            const float4 *src = src_of(t, kb + 1, it);
+                            if (src) { w[it][0] = __ldg(src); w[it][1] = __ldg(src + 1); } else w[it][0] = w[it][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
+                    }
+#pragma unroll
+                    for (int it = 0; it < 2; ++it) emit(kb, it, u[it][0], u[it][1]);
+                    publish(kb);
+                }
+                RF_T1(6);
+                if (t + 1 < T) preload(t + 1);
+            }
+            RF_DBG(if (ct == 0) { p.dbg[blockIdx.x * 16 + 6] = dbgc[6]; p.dbg[blockIdx.x * 16 + 7] = dbgc[7]; });
+        }
+    } else {
+        // ===== epilogue (warps 0..7): thread = row m of this CTA x 16 hidden units of every tile =====
+        if (FUSED) asm volatile("setmaxnreg.inc.sync.aligned.u32 128;");
+        const int ew = warp, q = warp & 3, j = ew >> 2;
+        const int m = (q & 1) * 32 + lane, hf = q >> 1;
+        const int row = row0 + m;
+        const bool row_ok = row < p.B;
+        const uint32_t tl = tmem + ((uint32_t)(q * 32) << 16);           // this warp's TMEM lanes
+        const uint32_t acc_empty0 = rf_mapa(smem_u32(bars + RFB_ACC_EMPTY), leader), hfull0 = rf_mapa(smem_u32(bars + RFB_H_FULL), leader);
+        const int sw = m & 7;
+        // ---- prologue: state into TMEM, fp16 h_0 into the A tile, zero the h.Uh groups
+        for (int c = 0; c < NC; ++c) {
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int u0 = c * 64 + hf * 32 + j * 16 + e * 8;
+                float hv[8], sv[8];
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const float4 a = row_ok ? *reinterpret_cast<const float4 *>(p.h_state + (size_t)row * H + u0 + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    hv[4 * i] = a.x; hv[4 * i + 1] = a.y; hv[4 * i + 2] = a.z; hv[4 * i + 3] = a.w;
+                    if (G == 4) {
+                        const float4 b = row_ok ? *reinterpret_cast<const float4 *>(p.c_state + (size_t)row * H + u0 + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        sv[4 * i] = b.x; sv[4 * i + 1] = b.y; sv[4 * i + 2] = b.z; sv[4 * i + 3] = b.w;
+                    }
+                }
+                if (G == 4) rf_st8(tl + STATE_COL + (uint32_t)(c * 32 + j * 16 + e * 8), sv);
+                else rf_st8(tl + STATE_COL + (uint32_t)(c * 32 + j * 16 + e * 8), hv);
+                uint4 v;
+                v.x = rf_pack_sat(hv[0], hv[1]); v.y = rf_pack_sat(hv[2], hv[3]); v.z = rf_pack_sat(hv[4], hv[5]); v.w = rf_pack_sat(hv[6], hv[7]);
+                const int ch = hf * 4 + j * 2 + e;
+                *reinterpret_cast<uint4 *>(sAh + (size_t)c * (RF_ROWS * 128) + m * 128 + ((ch ^ sw) << 4)) = v;
+            }
+        }
+        if (FUSED && G == 3) {
+            const float z8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            for (int b = 0; b < NB; ++b) { rf_st8(tl + (uint32_t)(b * 128 + 96 + j * 16), z8); rf_st8(tl + (uint32_t)(b * 128 + 96 + j * 16 + 8), z8); }
+        }
+        rf_st_wait();
+        rf_fence_async();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) rf_arrive_cl(hfull0);
+        uint32_t hpend[NCMAX][8];       // fp16 h_t of the step's tiles x 16 units, written to the A tile once the step's MMAs are done
+        int buf = -1, use = 0;          // accumulator buffer of the current tile and how often it has been used before
+        for (int t = 0; t < T; ++t) {
+#pragma unroll
+            for (int c = 0; c < NCMAX; ++c) {
+                if (c >= NC) break;
+                if (++buf == NB) { buf = 0; ++use; }
+                const uint32_t acc = tl + (uint32_t)(buf * 128 + j * 16);
+                float4 xr[G][4];         // XW mode: the hoisted projection of this thread's 16 units
+                if (!FUSED) {
+                    const float4 *src = reinterpret_cast<const float4 *>(p.xw) +
+                                        (((long long)t * p.xw_blocked_rows + (row >> 5)) * (G * H >> 2) + ((c * 64 + hf * 32 + j * 16) >> 2)) * 32 + (row & 31);
+#pragma unroll
+                    for (int gg = 0; gg < G; ++gg)
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            xr[gg][i] = row_ok ? __ldg(src + ((long long)gg * (H >> 2) + i) * 32) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+                { RF_T0(); mbar_wait(bars + RFB_ACC_FULL + buf, (uint32_t)(use & 1)); RF_T1(4); }
+                tc_fence_after();
+                float hn[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) hn[i] = 0.f;
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    if (RF_SKIP(1)) break;
+                    const int ub = c * 64 + hf * 32 + j * 16 + e * 8;            // first of these 8 hidden units
+                    float a0[8], a1[8], a2[8], a3[8], st[8];
+                    rf_ld8(acc + (uint32_t)(e * 8), a0);
+                    rf_ld8(acc + (uint32_t)(32 + e * 8), a1);
+                    rf_ld8(acc + (uint32_t)(64 + e * 8), a2);
+                    if (G == 4 || FUSED) rf_ld8(acc + (uint32_t)(96 + e * 8), a3);
+                    rf_ld8(tl + STATE_COL + (uint32_t)(c * 32 + j * 16 + e * 8), st);
+                    rf_ld_wait();
+                    float b0[8], b1[8], b2[8], b3[8];
+#pragma unroll
+                    for (int i = 0; i < 2; ++i) {
+                        const float4 v0 = *reinterpret_cast<const float4 *>(sBias + 0 * H + ub + 4 * i), v1 = *reinterpret_cast<const float4 *>(sBias + 1 * H + ub + 4 * i),
+                                     v2 = *reinterpret_cast<const float4 *>(sBias + 2 * H + ub + 4 * i), v3 = *reinterpret_cast<const float4 *>(sBias + 3 * H + ub + 4 * i);
+                        b0[4 * i] = v0.x; b0[4 * i + 1] = v0.y; b0[4 * i + 2] = v0.z; b0[4 * i + 3] = v0.w;
+                        b1[4 * i] = v1.x; b1[4 * i + 1] = v1.y; b1[4 * i + 2] = v1.z; b1[4 * i + 3] = v1.w;
+                        b2[4 * i] = v2.x; b2[4 * i + 1] = v2.y; b2[4 * i + 2] = v2.z; b2[4 * i + 3] = v2.w;
+                        b3[4 * i] = v3.x; b3[4 * i + 1] = v3.y; b3[4 * i + 2] = v3.z; b3[4 * i + 3] = v3.w;
+                    }
+                    float sn[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        if (G == 3) {          // gru.c:156-186; columns FUSED: [x.Wh | z | r | h.Uh], XW: [z | r | h.Uh]
+                            float pz, pr, xh, hu;
+                            if (FUSED) { xh = a0[u] + b2[u]; pz = a1[u] + b0[u]; pr = a2[u] + b1[u]; hu = a3[u] + b3[u]; }
+                            else {
+                                const int k = e * 8 + u;
+                                pz = a0[u] + b0[u] + (&xr[0][k >> 2].x)[k & 3]; pr = a1[u] + b1[u] + (&xr[1][k >> 2].x)[k & 3];
+                                hu = a2[u] + b3[u]; xh = (&xr[2][k >> 2].x)[k & 3];
+                            }
+                            const float z = act_mufu(NNTK_ACT_SIGMOID, pz), r = act_mufu(NNTK_ACT_SIGMOID, pr);
+                            const float hh = act_mufu(NNTK_ACT_TANH, fmaf(r, hu, xh));
+                            sn[u] = fmaf(z, st[u] - hh, hh);               // (1 - z) hh + z h_{t-1}
+                            hn[e * 8 + u] = sn[u];
+                        } else {               // lstm.c:199-238; columns [i | f | g | o]
+                            float pi = a0[u] + b0[u], pf = a1[u] + b1[u], pg = a2[u] + b2[u], po = a3[u] + b3[u];
+                            if (!FUSED) {
+                                const int k = e * 8 + u;
+                                pi += (&xr[0][k >> 2].x)[k & 3]; pf += (&xr[1][k >> 2].x)[k & 3];
+                                pg += (&xr[2][k >> 2].x)[k & 3]; po += (&xr[G - 1][k >> 2].x)[k & 3];
+                            }
+                            const float ig = act_mufu(NNTK_ACT_SIGMOID, pi), fg = act_mufu(NNTK_ACT_SIGMOID, pf);
+                            const float gg = act_mufu(NNTK_ACT_TANH, pg), og = act_mufu(NNTK_ACT_SIGMOID, po);
+                            sn[u] = fmaf(fg, st[u], ig * gg);
+                            hn[e * 8 + u] = og * act_mufu(NNTK_ACT_TANH, sn[u]);
+                        }
+                    }
+                    rf_st8(tl + STATE_COL + (uint32_t)(c * 32 + j * 16 + e * 8), sn);
+                    if (FUSED && G == 3) { const float z8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}; rf_st8(acc + (uint32_t)(96 + e * 8), z8); }
+                }
+                rf_st_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) rf_arrive_cl(acc_empty0 + 8u * (uint32_t)buf);       // the accumulator buffer may be overwritten
+#pragma unroll
+                for (int i = 0; i < 8; ++i) hpend[c][i] = rf_pack_sat(hn[2 * i], hn[2 * i + 1]);
+                if (p.return_sequences && !RF_SKIP(2)) {
+                    // this warp's [32 rows][16 units] piece of h_t -> its own 2 KB staging tile (SWIZZLE_64B rows) -> one TMA store
+                    // per warp: no CTA-wide barrier in the epilogue (first version: two bar.sync + a store wait per tile)
+                    uint8_t *o = sOut + ew * 2048;
+                    { RF_T0(); if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); RF_T1(11); }    // the previous store has read it
+                    __syncwarp();
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        *reinterpret_cast<float4 *>(o + lane * 64 + ((i ^ ((lane >> 1) & 3)) << 4)) = make_float4(hn[4 * i], hn[4 * i + 1], hn[4 * i + 2], hn[4 * i + 3]);
+                    rf_fence_async();
+                    __syncwarp();
+                    if (lane == 0) {
+                        rf_tma_store_3d(&map_out, o, c * 64 + hf * 32 + j * 16, t, row0 + (q & 1) * 32);
+                        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    }
+                }
+                if (c == NC - 1) {
+                    // every recurrent-part MMA of this step has completed (they precede this tile's commit): h_t may now
+                    // replace h_{t-1} in the A tile.  The last step's h goes to the caller's state instead.
+                    if (t + 1 < T) {
+#pragma unroll
+                        for (int cc = 0; cc < NCMAX; ++cc) {
+                            if (cc >= NC) break;
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                const int ch = hf * 4 + j * 2 + e;
+                                *reinterpret_cast<uint4 *>(sAh + (size_t)cc * (RF_ROWS * 128) + m * 128 + ((ch ^ sw) << 4)) =
+                                    make_uint4(hpend[cc][4 * e], hpend[cc][4 * e + 1], hpend[cc][4 * e + 2], hpend[cc][4 * e + 3]);
+                            }
+                        }
+                        rf_fence_async();
+                        __syncwarp();
+                        if (lane == 0) rf_arrive_cl(hfull0);
+                    }
+                }
+                if (t == T - 1 && row_ok) {
+                    // final state (gru.c:201, lstm.c:264-265): exact fp32 h_T (and c_T from TMEM below)
+                    float *hs = p.h_state + (size_t)row * H + c * 64 + hf * 32 + j * 16;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const float4 v = make_float4(hn[4 * i], hn[4 * i + 1], hn[4 * i + 2], hn[4 * i + 3]);
+                        *reinterpret_cast<float4 *>(hs + 4 * i) = v;
+                        if (!p.return_sequences) *reinterpret_cast<float4 *>(p.out + (size_t)row * H + c * 64 + hf * 32 + j * 16 + 4 * i) = v;
+                    }
+                }
+            }
+        }
+        if (G == 4) {
+            tc_fence_after();
+            for (int c = 0; c < NC; ++c)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    float sv[8];
+                    rf_ld8(tl + STATE_COL + (uint32_t)(c * 32 + j * 16 + e * 8), sv);
+                    rf_ld_wait();
+                    if (row_ok) {
+                        float *cs = p.c_state + (size_t)row * H + c * 64 + hf * 32 + j * 16 + e * 8;
+                        *reinterpret_cast<float4 *>(cs) = make_float4(sv[0], sv[1], sv[2], sv[3]);
+                        *reinterpret_cast<float4 *>(cs + 4) = make_float4(sv[4], sv[5], sv[6], sv[7]);
+                    }
+                }
+        }
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");      // this warp's last stores have landed
+        RF_DBG(if (ew == 0 && lane == 0) { p.dbg[blockIdx.x * 16 + 4] = dbgc[4]; p.dbg[blockIdx.x * 16 + 5] = clock64() - t_start; p.dbg[blockIdx.x * 16 + 11] = dbgc[11]; });
+    }
+    tc_fence_before();
+    __syncthreads();
+    rf_cluster_sync();               // nobody leaves while the peer's MMA / TMA could still touch this CTA
+    if (warp == CTRL_W0 + 3) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+    }
+}
+
+// B operand repack: Wp[(tile * 2 + half) * 32 G + gi * 32 + ul][k] = half(W[k][gate(gi) * H + tile * 64 + half * 32 + ul]);
+// gate order `perm`: recurrent part GRU {z, r, h}, input part GRU {h, z, r} (column groups [x.Wh | z | r]), LSTM {i, f, g, o}.
+// Wl (optional): the fp16 image of the rounding residual W - half(W), for the 3-pass input part.
+__global__ void rf_pack_kernel(const float *__restrict__ W, __half *__restrict__ Wp, __half *__restrict__ Wl, int K, int H, int G, int p0, int p1,
+                               int p2, int p3) {
+    const long long total = (long long)G * H * K;
+    const int perm[4] = {p0, p1, p2, p3};
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int n = (int)(i / K), k = (int)(i - (long long)n * K);
+        const int th = n / (32 * G), rem = n - th * 32 * G, gi = rem >> 5, ul = rem & 31;
+        const int tile = th >> 1, half = th & 1;
+        const float w = __ldg(W + (long long)k * G * H + perm[gi] * H + tile * 64 + half * 32 + ul);
+        const __half hi = __float2half_rn(w);
+        Wp[i] = hi;
+        if (Wl) Wl[i] = __float2half_rn(w - __half2float(hi));
+    }
+}
+
+__half *g_rf_scratch = nullptr;
+size_t g_rf_halves = 0;
+
+template <int G, bool FUSED>
+int rf_ring_stages(int H, int in, int xp) {
+    int stages = RF_MAX_RING;
+    for (; stages >= 2; --stages) { RfPlan<G, FUSED> pl(H, in, xp, stages); if (pl.total <= 227 * 1024) break; }
+    return stages;
+}
+
+// dry: only report whether a cluster of p.cs CTAs of this kernel can be scheduled (1 = no)
+template <int G, bool FUSED, int NCMAX>
+int rf_launch(const CUtensorMap &mw, const CUtensorMap &mwl, const CUtensorMap &mu, const CUtensorMap &mo, RfParams &p, int pairs, cudaStream_t st, bool dry) {
+    auto kern = recurrent_fused_kernel<G, FUSED, NCMAX>;
+    const int stages = rf_ring_stages<G, FUSED>(p.H, p.in, p.xp);
+    if (stages < 3) return 1;
+    p.ring_stages = stages;
+    const RfPlan<G, FUSED> pl(p.H, p.in, p.xp, stages);
+    static size_t attr_smem = 0;
+    if ((size_t)pl.total > attr_smem) {
+        NNTK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
+        attr_smem = pl.total;
+    }
+    const int npairs = p.cs / 2, clusters = (pairs + npairs - 1) / npairs;       // surplus pairs run on out-of-range rows
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(clusters * p.cs));
+    cfg.blockDim = dim3(FUSED ? RF_THREADS_FUSED : RF_THREADS_XW);
+    cfg.dynamicSmemBytes = pl.total;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)p.cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    if (dry) {
+        int maxc = 0;
+        if (cudaOccupancyMaxActiveClusters(&maxc, kern, &cfg) != cudaSuccess || maxc < 1) { (void)cudaGetLastError(); return 1; }
+        return 0;
+    }
+    NNTK_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mw, mwl, mu, mo, p));
+    nntk_cuda_count_launch(1);
+    return 0;
+}
+
+int rf_xpasses() {
+    static int xp = 0;
+    if (!xp) { const char *e = getenv("NNTK_RECURRENT_X_PASSES"); xp = (e && atoi(e) == 1) ? 1 : 3; }
+    return xp;
+}
+
+}  // namespace
+
+// 0: not eligible; 1: FUSED (no projection needed); 2: XW mode (needs the blocked hoisted projection)
+extern "C" int nntk_cuda_recurrent_fused_plan(const nntk_recurrent_args *r, int nb) {
+    static int enabled = -1, min_batch = 0;
+    if (enabled < 0) {
+        const char *e = getenv("NNTK_RECURRENT_FUSED"); enabled = e ? atoi(e) : 1;
+        e = getenv("NNTK_RECURRENT_FUSED_MIN_BATCH"); min_batch = e ? atoi(e) : 65;
+    }
+    const int G = r->cell, H = r->H, T = r->T;
+    if (!enabled || (G != 3 && G != 4) || (H & 63) || H < 64 || H > 512 || T < 1 || nb < min_batch) return 0;
+    const int SG = NNTK_ACT_SIGMOID, TH = NNTK_ACT_TANH;
+    const bool def = (G == 3) ? (r->act[0] == SG && r->act[1] == SG && r->act[2] == TH)
+                              : (r->act[0] == SG && r->act[1] == SG && r->act[2] == TH && r->act[3] == SG && r->act[4] == TH);
+    if (!def || !get_encode()) return 0;
+    if ((r->in & 63) == 0 && r->in <= 256 && (((uintptr_t)r->d_x) & 15) == 0) {
+        const int stages = G == 3 ? rf_ring_stages<3, true>(H, r->in, rf_xpasses()) : rf_ring_stages<4, true>(H, r->in, rf_xpasses());
+        if (stages >= 3) return 1;
+    }
+    return 2;
+}
+
+// Runs all T steps of one batch chunk in ONE launch.  xw: the blocked hoisted projection (XW mode) or null (FUSED mode).
+extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, const float *x, const float *xw, float *h, float *c,
+                                         float *out, int *used) {
+    *used = 0;
+    const int G = r->cell, H = r->H, T = r->T, IN = r->in;
+    const int plan = nntk_cuda_recurrent_fused_plan(r, nb);
+    if (!plan || (plan == 2 && !xw)) return 0;
+    const bool fused = plan == 1 && !xw;
+    if ((((uintptr_t)h) | ((uintptr_t)out) | ((uintptr_t)x) | ((uintptr_t)c) | ((uintptr_t)xw)) & 15) return 0;
+    EncodeTiledFn encode = get_encode();
+    cudaStream_t st = nntk_stream();
+    const int xp = fused ? rf_xpasses() : 1;
+    const size_t un = (size_t)G * H * H, wn = fused ? (size_t)G * H * IN : 0, wln = (fused && xp == 3) ? wn : 0;
+    if (un + wn + wln > g_rf_halves) {
+        NNTK_CUDA_TRY(cudaStreamSynchronize(st));
+        if (g_rf_scratch) cudaFree(g_rf_scratch);
+        g_rf_scratch = nullptr; g_rf_halves = 0;
+        NNTK_CUDA_TRY(cudaMalloc(&g_rf_scratch, (un + wn + wln) * sizeof(__half)));
+        g_rf_halves = un + wn + wln;
+    }
+    __half *Up = g_rf_scratch, *Wp = g_rf_scratch + un, *Wl = wln ? g_rf_scratch + un + wn : nullptr;
+    {
+        const int blocks = (int)((un + 255) / 256 < 2048 ? (un + 255) / 256 : 2048);
+        rf_pack_kernel<<<blocks, 256, 0, st>>>(r->d_U, Up, nullptr, H, H, G, 0, 1, 2, 3);
+        NNTK_LAUNCH_CHECK("rf_pack_kernel");
+        if (fused) {
+            const int bw = (int)((wn + 255) / 256 < 2048 ? (wn + 255) / 256 : 2048);
+            if (G == 3) rf_pack_kernel<<<bw, 256, 0, st>>>(r->d_W, Wp, Wl, IN, H, G, 2, 0, 1, 0);
+            else rf_pack_kernel<<<bw, 256, 0, st>>>(r->d_W, Wp, Wl, IN, H, G, 0, 1, 2, 3);
+            NNTK_LAUNCH_CHECK("rf_pack_kernel");
+        }
+    }
+    // cluster size: as many pairs as share a B stream (at most 4), shrunk while the device cannot schedule such a cluster
+    const int pairs = (nb + 127) / 128;
+    static int max_cs = -1;
+    if (max_cs < 0) { const char *e = getenv("NNTK_RECURRENT_FUSED_CLUSTER"); max_cs = e ? atoi(e) : 8; if (max_cs != 2 && max_cs != 4 && max_cs != 8) max_cs = 8; }
+    int cs = pairs >= 4 ? 8 : pairs >= 2 ? 4 : 2;
+    if (cs > max_cs) cs = max_cs;
+    CUtensorMap mw, mwl, mu, mo;
+    auto enc2 = [&](CUtensorMap *m, void *base, int K) -> int {
+        cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)G * H};
+        cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+        cuuint32_t box[2] = {64, (cuuint32_t)(32 * G / (cs / 2))};       // one pair's slice of a CTA's rows
+        cuuint32_t es[2] = {1, 1};
+        CUresult cr = encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (cr != CUDA_SUCCESS) { nntk_cuda_set_error(NNTK_ERR_CUDA_, "recurrent_fused: weight tensor map rejected (CUresult %d)", (int)cr); return NNTK_ERR_CUDA_; }
+        return 0;
+    };
+    int rc;
+    RfParams p = {};
+    p.H = H; p.in = IN; p.xp = xp;
+    const bool small = H <= 256;
+#define RF_DISPATCH(DRY) \
+    (G == 3 ? (fused ? (small ? rf_launch<3, true, 4>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<3, true, 8>(mw, mwl, mu, mo, p, pairs, st, DRY)) \
+                     : (small ? rf_launch<3, false, 4>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<3, false, 8>(mw, mwl, mu, mo, p, pairs, st, DRY))) \
+            : (fused ? (small ? rf_launch<4, true, 4>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<4, true, 8>(mw, mwl, mu, mo, p, pairs, st, DRY)) \
+                     : (small ? rf_launch<4, false, 4>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<4, false, 8>(mw, mwl, mu, mo, p, pairs, st, DRY))))
+    for (;; cs /= 2) {
+        p.cs = cs;
+        rc = RF_DISPATCH(true);
+        if (rc < 0) return rc;
+        if (rc == 0 || cs == 2) break;
+    }
+    if (rc == 1) return 0;           // not even a pair fits: not eligible
+    if ((rc = enc2(&mu, Up, H))) return rc;
+    if (fused) { if ((rc = enc2(&mw, Wp, IN))) return rc; } else mw = mu;
+    if (Wl) { if ((rc = enc2(&mwl, Wl, IN))) return rc; } else mwl = mu;
+    if (r->return_sequences) {
+        // per-warp [32 rows][16 floats] pieces of h_t, SWIZZLE_64B
+        cuuint64_t dims[3] = {(cuuint64_t)H, (cuuint64_t)T, (cuuint64_t)nb};
+        cuuint64_t strides[2] = {(cuuint64_t)H * 4, (cuuint64_t)T * H * 4};
+        cuuint32_t box[3] = {16, 1, 32};
+        cuuint32_t es[3] = {1, 1, 1};
+        CUresult cr = encode(&mo, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, out, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                             CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (cr != CUDA_SUCCESS) { nntk_cuda_set_error(NNTK_ERR_CUDA_, "recurrent_fused: output tensor map rejected (CUresult %d)", (int)cr); return NNTK_ERR_CUDA_; }
+    } else mo = mu;
+    p.B = nb; p.T = T; p.return_sequences = r->return_sequences;
+    p.x = x; p.bias_i = r->d_bi;
+    p.bias_h = ((G == 3) || r->v2) ? r->d_bh : nullptr;
+    p.xw = xw; p.xw_blocked_rows = (nb + 31) / 32;
+    p.h_state = h; p.c_state = c; p.out = out;
+    static int want_dbg = -1;
+    if (want_dbg < 0) { const char *e = getenv("NNTK_RF_DBG"); want_dbg = e ? atoi(e) : 0; }
+    long long *d_dbg = nullptr;
+    if (want_dbg) { NNTK_CUDA_TRY(cudaMalloc(&d_dbg, (size_t)(pairs + 4) * 2 * 16 * 8)); NNTK_CUDA_TRY(cudaMemsetAsync(d_dbg, 0, (size_t)(pairs + 4) * 2 * 16 * 8, st)); }
+    p.dbg = d_dbg;
+    { const char *e = getenv("NNTK_RF_SKIP"); p.skip = e ? atoi(e) : 0; }
+    rc = RF_DISPATCH(false);
+#undef RF_DISPATCH
+    if (d_dbg) {
+        static const char *names[14] = {"mma:ring_full", "mma:acc_empty", "mma:h_full", "mma:x_full", "epi:acc_full", "epi:total", "conv:convert", "conv:x_empty",
+                                        "prod:ring_empty", "prod:tma_issue", "mma:total", "epi:store_wait", "mma:commit", "mma:issue"};
+        std::vector<long long> hst((size_t)pairs * 2 * 16);
+        cudaStreamSynchronize(st);
+        cudaMemcpy(hst.data(), d_dbg, hst.size() * 8, cudaMemcpyDeviceToHost);
+        cudaFree(d_dbg);
+        for (int i = 0; i < 14; ++i) {
+            double a0 = 0, a1 = 0;
+            for (int b = 0; b < pairs; ++b) { a0 += (double)hst[(size_t)(2 * b) * 16 + i]; a1 += (double)hst[(size_t)(2 * b + 1) * 16 + i]; }
+            fprintf(stderr, "[rf dbg] %-16s leader %10.0f  peer %10.0f cycles per step (avg over %d pairs; xp %d, ring %d, cluster %d)\n", names[i], a0 / pairs / T, a1 / pairs / T, pairs, p.xp, p.ring_stages, p.cs);
+        }
+    }
+    if (rc == 1) return 0;
+    if (rc) return rc;
+    *used = 1;
+    return 0;
+}

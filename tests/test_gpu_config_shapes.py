@@ -49,7 +49,7 @@ def test_c4_lstm_large_batch_path_at_config_shape(tf32, ref):
     got = r.apply_batch(x)
     torch.cuda.synchronize()
     path = _path(tf32)
-    assert path in ("fused_tc", "step_tc_f16"), f"C4 at B = {B} ran '{path}', not a large-batch tensor-core kernel"
+    assert path in ("fused_tc", "fused_tc_xw", "step_tc_f16"), f"C4 at B = {B} ran '{path}', not a large-batch tensor-core kernel"
     pick = [0, 63 + 64 * 7, B - 1]
     for b in pick:
         rr = L.Recurrent(ref, "lstm", H, H, T); helpers.copy_weights(rr, r)
