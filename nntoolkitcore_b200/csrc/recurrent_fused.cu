@@ -169,7 +169,8 @@ struct RfPlan {
 
 // barrier block layout (uint64 slots)
 constexpr int RFB_RING_FULL = 0, RFB_RING_EMPTY = RF_MAX_RING, RFB_ACC_FULL = 2 * RF_MAX_RING, RFB_ACC_EMPTY = RFB_ACC_FULL + 4,
-              RFB_H_FULL = RFB_ACC_EMPTY + 4, RFB_X_FULL = RFB_H_FULL + 1, RFB_X_EMPTY = RFB_X_FULL + 4, RFB_END = RFB_X_EMPTY + 1;
+              RFB_H_FULL = RFB_ACC_EMPTY + 4, RFB_X_FULL = RFB_H_FULL + 1 /* hi image */, RFB_XL_FULL = RFB_X_FULL + 1 /* lo image, per k-block */,
+              RFB_X_EMPTY = RFB_XL_FULL + 4, RFB_END = RFB_X_EMPTY + 1;
 
 // NCMAX: compile-time bound of the tiles per step (H / 64 <= NCMAX): sizes the register-resident pending-h array.
 template <int G, bool FUSED, int NCMAX>
@@ -211,7 +212,8 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         for (int s = 0; s < p.ring_stages; ++s) { mbar_init(bars + RFB_RING_FULL + s, 1); mbar_init(bars + RFB_RING_EMPTY + s, (uint32_t)npairs); }
         for (int b = 0; b < 4; ++b) { mbar_init(bars + RFB_ACC_FULL + b, 1); mbar_init(bars + RFB_ACC_EMPTY + b, 16); }
         mbar_init(bars + RFB_H_FULL, 16);
-        for (int b = 0; b < 4; ++b) mbar_init(bars + RFB_X_FULL + b, 16);
+        mbar_init(bars + RFB_X_FULL, 16);
+        for (int b = 0; b < 4; ++b) mbar_init(bars + RFB_XL_FULL + b, 16);
         mbar_init(bars + RFB_X_EMPTY, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -314,17 +316,15 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 if (use > 0) { RF_T0(); mbar_wait(bars + RFB_ACC_EMPTY + buf, (uint32_t)((use - 1) & 1)); RF_T1(1); }
                 tc_fence_after();
                 const uint32_t d = tmem + (uint32_t)(buf * 128);
+                if (c == 0) { RF_T0(); mbar_wait(bars + RFB_X_FULL, (uint32_t)(t & 1)); RF_T1(3); }       // the hi image of x_t
                 if (XP == 3) {           // small terms first: x_hi . W_lo, then x_lo . W_hi + x_hi . W_hi off the same W_hi stage
+                    for (int kb = 0; kb < KBX; kb += 2) stage_mmas(d, xh_a, 0u, kb, min(2, KBX - kb), true);
                     for (int kb = 0; kb < KBX; kb += 2) {
-                        if (c == 0) for (int i = kb; i < min(kb + 2, KBX); ++i) { RF_T0(); mbar_wait(bars + RFB_X_FULL + i, (uint32_t)(t & 1)); RF_T1(3); }
-                        stage_mmas(d, xh_a, 0u, kb, min(2, KBX - kb), true);
+                        if (c == 0) for (int i = kb; i < min(kb + 2, KBX); ++i) { RF_T0(); mbar_wait(bars + RFB_XL_FULL + i, (uint32_t)(t & 1)); RF_T1(3); }
+                        stage_mmas(d, xh_a, xl_a, kb, min(2, KBX - kb), false);
                     }
-                    for (int kb = 0; kb < KBX; kb += 2) stage_mmas(d, xh_a, xl_a, kb, min(2, KBX - kb), false);
                 } else {
-                    for (int kb = 0; kb < KBX; kb += 2) {
-                        if (c == 0) for (int i = kb; i < min(kb + 2, KBX); ++i) { RF_T0(); mbar_wait(bars + RFB_X_FULL + i, (uint32_t)(t & 1)); RF_T1(3); }
-                        stage_mmas(d, xh_a, 0u, kb, min(2, KBX - kb), true);
-                    }
+                    for (int kb = 0; kb < KBX; kb += 2) stage_mmas(d, xh_a, 0u, kb, min(2, KBX - kb), true);
                 }
                 if (c == NC - 1) { if (rf_elect()) rf_commit(bars + RFB_X_EMPTY, pair_mask); __syncwarp(); }     // the x tile may be rewritten once these MMAs are done
             };
@@ -359,82 +359,82 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         if (FUSED) {
             asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
             const int ct = tid - CONV_W0 * 32;
-            const uint32_t xfull0 = rf_mapa(smem_u32(bars + RFB_X_FULL), leader);
-            // Registers hold k-blocks 0 and 1 of x_{t+1} (a whole step old when needed); k-blocks 2 and 3 are only pulled into L2
-            // then and loaded while the first two are being consumed -- holding all four (64 registers) spilled.
-            float4 v[2][2][2];
+            const uint32_t xfull0 = rf_mapa(smem_u32(bars + RFB_X_FULL), leader), xlfull0 = rf_mapa(smem_u32(bars + RFB_XL_FULL), leader);
+            // item (row, 16-byte chunk of the fp16 row = 8 floats): a warp covers 4 rows x 256 contiguous bytes per load instruction and
+            // 512 contiguous (swizzled) bytes per store.  The fp16 HI image of x_{t+1} is built right after x_t has been handed over and
+            // waits in registers (32 for in = 256): when the tile frees up it is stored at once and the input part can start.  The LO
+            // image (3-pass mode) is recomputed then from a second read of the same rows -- L2 hits, one step old -- while the
+            // x_hi . W_lo pass runs.  (Holding raw fp32 rows, 64 registers, spilled; loading k-blocks late stalled the issuer 2 900
+            // cycles per step.)
+            uint4 hreg[4][2];
             auto src_of = [&](int t, int kb, int it) -> const float4 * {
                 const int idx = it * 256 + ct, r = idx >> 3, ch = idx & 7, row = row0 + r;
                 return row < p.B ? reinterpret_cast<const float4 *>(p.x + ((size_t)row * T + t) * IN + kb * 64 + ch * 8) : nullptr;
             };
+            auto tile_off = [&](int kb, int it) -> size_t {
+                const int idx = it * 256 + ct, r = idx >> 3, ch = idx & 7;
+                return (size_t)kb * (RF_ROWS * 128) + r * 128 + ((ch ^ (r & 7)) << 4);
+            };
             auto preload = [&](int t) {
 #pragma unroll
-                for (int kb = 0; kb < 2; ++kb) {
-                    if (kb >= KBX) break;
+                for (int k2 = 0; k2 < 4; k2 += 2) {          // two k-blocks of loads in flight at a time
+                    float4 a[2][2][2];
 #pragma unroll
-                    for (int it = 0; it < 2; ++it) {
-                        const float4 *src = src_of(t, kb, it);
-                        if (src) { v[kb][it][0] = __ldg(src); v[kb][it][1] = __ldg(src + 1); }
-                        else v[kb][it][0] = v[kb][it][1] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    }
-                }
-                for (int kb = 2; kb < KBX; ++kb)
+                    for (int kk = 0; kk < 2; ++kk)
 #pragma unroll
-                    for (int it = 0; it < 2; ++it) {
-                        const float4 *src = src_of(t, kb, it);
-                        if (src) asm volatile("prefetch.global.L2 [%0];" ::"l"(src));
-                    }
-            };
-            auto emit = [&](int kb, int it, const float4 &a, const float4 &b) {
-                if (RF_SKIP(4)) return;
-                const int idx = it * 256 + ct, r = idx >> 3, ch = idx & 7;
-                uint4 hi, lo;
-                if (XP == 3) {
-                    rf_split2(a.x, a.y, hi.x, lo.x); rf_split2(a.z, a.w, hi.y, lo.y); rf_split2(b.x, b.y, hi.z, lo.z); rf_split2(b.z, b.w, hi.w, lo.w);
-                    *reinterpret_cast<uint4 *>(sXl + (size_t)kb * (RF_ROWS * 128) + r * 128 + ((ch ^ (r & 7)) << 4)) = lo;
-                } else {
-                    hi.x = rf_pack_sat(a.x, a.y); hi.y = rf_pack_sat(a.z, a.w); hi.z = rf_pack_sat(b.x, b.y); hi.w = rf_pack_sat(b.z, b.w);
+                        for (int it = 0; it < 2; ++it) {
+                            const float4 *src = (k2 + kk < KBX) ? src_of(t, k2 + kk, it) : nullptr;
+                            if (src) { a[kk][it][0] = __ldg(src); a[kk][it][1] = __ldg(src + 1); }
+                            else a[kk][it][0] = a[kk][it][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
+#pragma unroll
+                    for (int kk = 0; kk < 2; ++kk)
+#pragma unroll
+                        for (int it = 0; it < 2; ++it) {
+                            const float4 u = a[kk][it][0], w = a[kk][it][1];
+                            hreg[k2 + kk][it] = make_uint4(rf_pack_sat(u.x, u.y), rf_pack_sat(u.z, u.w), rf_pack_sat(w.x, w.y), rf_pack_sat(w.z, w.w));
+                        }
                 }
-                *reinterpret_cast<uint4 *>(sXh + (size_t)kb * (RF_ROWS * 128) + r * 128 + ((ch ^ (r & 7)) << 4)) = hi;
-            };
-            auto publish = [&](int kb) {
-                rf_fence_async();
-                __syncwarp();
-                if (lane == 0) rf_arrive_cl(xfull0 + 8u * (uint32_t)kb);
             };
             preload(0);
             for (int t = 0; t < T; ++t) {
                 if (t >= 1) { RF_T0(); mbar_wait(bars + RFB_X_EMPTY, (uint32_t)((t - 1) & 1)); RF_T1(7); }
                 RF_T0();
-                float4 w[2][2];
-                if (KBX > 2) {           // late k-block 2: in flight while 0 and 1 are converted
+                if (!RF_SKIP(4)) {
 #pragma unroll
-                    for (int it = 0; it < 2; ++it) {
-                        const float4 *src = src_of(t, 2, it);
-                        if (src) { w[it][0] = __ldg(src); w[it][1] = __ldg(src + 1); } else w[it][0] = w[it][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int kb = 0; kb < 4; ++kb) {
+                        if (kb >= KBX) break;
+#pragma unroll
+                        for (int it = 0; it < 2; ++it) *reinterpret_cast<uint4 *>(sXh + tile_off(kb, it)) = hreg[kb][it];
                     }
                 }
+                rf_fence_async();
+                __syncwarp();
+                if (lane == 0) rf_arrive_cl(xfull0);
+                if (XP == 3) {
 #pragma unroll
-                for (int kb = 0; kb < 2; ++kb) {
-                    if (kb >= KBX) break;
-#pragma unroll
-                    for (int it = 0; it < 2; ++it) emit(kb, it, v[kb][it][0], v[kb][it][1]);
-                    publish(kb);
-                }
-                for (int kb = 2; kb < KBX; ++kb) {
-                    float4 u[2][2];
-#pragma unroll
-                    for (int it = 0; it < 2; ++it) { u[it][0] = w[it][0]; u[it][1] = w[it][1]; }
-                    if (kb + 1 < KBX) {
+                    for (int kb = 0; kb < 4; ++kb) {
+                        if (kb >= KBX) break;
+                        float4 a[2][2];
 #pragma unroll
                         for (int it = 0; it < 2; ++it) {
-                            const float4 *src = src_of(t, kb + 1, it);
-                            if (src) { w[it][0] = __ldg(src); w[it][1] = __ldg(src + 1); } else w[it][0] = w[it][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                            const float4 *src = src_of(t, kb, it);
+                            if (src) { a[it][0] = __ldg(src); a[it][1] = __ldg(src + 1); } else a[it][0] = a[it][1] = make_float4(0.f, 0.f, 0.f, 0.f);
                         }
-                    }
 #pragma unroll
-                    for (int it = 0; it < 2; ++it) emit(kb, it, u[it][0], u[it][1]);
-                    publish(kb);
+                        for (int it = 0; it < 2; ++it) {
+                            const uint4 h = hreg[kb][it];
+                            const float2 h0 = __half22float2(*reinterpret_cast<const __half2 *>(&h.x)), h1 = __half22float2(*reinterpret_cast<const __half2 *>(&h.y)),
+                                         h2 = __half22float2(*reinterpret_cast<const __half2 *>(&h.z)), h3 = __half22float2(*reinterpret_cast<const __half2 *>(&h.w));
+                            const float4 u = a[it][0], w = a[it][1];
+                            const uint4 lo = make_uint4(rf_pack_sat(u.x - h0.x, u.y - h0.y), rf_pack_sat(u.z - h1.x, u.w - h1.y),
+                                                        rf_pack_sat(w.x - h2.x, w.y - h2.y), rf_pack_sat(w.z - h3.x, w.w - h3.y));
+                            if (!RF_SKIP(4)) *reinterpret_cast<uint4 *>(sXl + tile_off(kb, it)) = lo;
+                        }
+                        rf_fence_async();
+                        __syncwarp();
+                        if (lane == 0) rf_arrive_cl(xlfull0 + 8u * (uint32_t)kb);
+                    }
                 }
                 RF_T1(6);
                 if (t + 1 < T) preload(t + 1);
@@ -495,6 +495,18 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 if (!FUSED) {
                     const float4 *src = reinterpret_cast<const float4 *>(p.xw) +
                                         (((long long)t * p.xw_blocked_rows + (row >> 5)) * (G * H >> 2) + ((c * 64 + hf * 32 + j * 16) >> 2)) * 32 + (row & 31);
+                    {   // the projection of the tile after next -> L2 (the loads below are waited for right away: from HBM they bounded the tile)
+                        int c2 = c + 2, t2 = t;
+                        if (c2 >= NC) { c2 -= NC; ++t2; }
+                        if (t2 < T && row_ok) {
+                            const float4 *nx = reinterpret_cast<const float4 *>(p.xw) +
+                                               (((long long)t2 * p.xw_blocked_rows + (row >> 5)) * (G * H >> 2) + ((c2 * 64 + hf * 32 + j * 16) >> 2)) * 32 + (row & 31);
+#pragma unroll
+                            for (int gg = 0; gg < G; ++gg)
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + ((long long)gg * (H >> 2) + i) * 32));
+                        }
+                    }
 #pragma unroll
                     for (int gg = 0; gg < G; ++gg)
 #pragma unroll
@@ -668,7 +680,7 @@ int rf_ring_stages(int H, int in, int xp) {
 
 // dry: only report whether a cluster of p.cs CTAs of this kernel can be scheduled (1 = no)
 template <int G, bool FUSED, int NCMAX>
-int rf_launch(const CUtensorMap &mw, const CUtensorMap &mwl, const CUtensorMap &mu, const CUtensorMap &mo, RfParams &p, int pairs, cudaStream_t st, bool dry) {
+int rf_launch(const CUtensorMap &mw, const CUtensorMap &mwl, const CUtensorMap &mu, const CUtensorMap &mo, RfParams &p, int pairs, cudaStream_t st, int *dry) {
     auto kern = recurrent_fused_kernel<G, FUSED, NCMAX>;
     const int stages = rf_ring_stages<G, FUSED>(p.H, p.in, p.xp);
     if (stages < 3) return 1;
@@ -689,9 +701,10 @@ int rf_launch(const CUtensorMap &mw, const CUtensorMap &mwl, const CUtensorMap &
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = (unsigned)p.cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    if (dry) {
+    if (dry) {           // *dry = pairs this cluster size keeps resident at once (0: cannot be scheduled)
         int maxc = 0;
-        if (cudaOccupancyMaxActiveClusters(&maxc, kern, &cfg) != cudaSuccess || maxc < 1) { (void)cudaGetLastError(); return 1; }
+        if (cudaOccupancyMaxActiveClusters(&maxc, kern, &cfg) != cudaSuccess || maxc < 1) { (void)cudaGetLastError(); *dry = 0; return 1; }
+        *dry = (clusters < maxc ? clusters : maxc) * npairs;
         return 0;
     }
     NNTK_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mw, mwl, mu, mo, p));
@@ -785,13 +798,20 @@ extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, c
                      : (small ? rf_launch<3, false, 4>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<3, false, 8>(mw, mwl, mu, mo, p, pairs, st, DRY))) \
             : (fused ? (small ? rf_launch<4, true, 4>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<4, true, 8>(mw, mwl, mu, mo, p, pairs, st, DRY)) \
                      : (small ? rf_launch<4, false, 4>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<4, false, 8>(mw, mwl, mu, mo, p, pairs, st, DRY))))
-    for (;; cs /= 2) {
-        p.cs = cs;
-        rc = RF_DISPATCH(true);
+    // The step is a latency chain, so a second wave doubles the time: take the cluster size that keeps the most pairs resident at
+    // once (ties: the larger cluster, it shares the B stream more widely).  Measured at 64 pairs: clusters of 8 run in two waves
+    // (43.7 ms per C5 GRU layer), clusters of 4 in one (12.2 ms).
+    int best_cs = 0, best_resident = 0;
+    for (int c = cs; c >= 2; c /= 2) {
+        int resident = 0;
+        p.cs = c;
+        rc = RF_DISPATCH(&resident);
         if (rc < 0) return rc;
-        if (rc == 0 || cs == 2) break;
+        if (resident > best_resident) { best_resident = resident; best_cs = c; }
     }
-    if (rc == 1) return 0;           // not even a pair fits: not eligible
+    if (!best_cs) return 0;          // not even a pair fits: not eligible
+    cs = best_cs;
+    p.cs = cs;
     if ((rc = enc2(&mu, Up, H))) return rc;
     if (fused) { if ((rc = enc2(&mw, Wp, IN))) return rc; } else mw = mu;
     if (Wl) { if ((rc = enc2(&mwl, Wl, IN))) return rc; } else mwl = mu;
@@ -816,7 +836,7 @@ extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, c
     if (want_dbg) { NNTK_CUDA_TRY(cudaMalloc(&d_dbg, (size_t)(pairs + 4) * 2 * 16 * 8)); NNTK_CUDA_TRY(cudaMemsetAsync(d_dbg, 0, (size_t)(pairs + 4) * 2 * 16 * 8, st)); }
     p.dbg = d_dbg;
     { const char *e = getenv("NNTK_RF_SKIP"); p.skip = e ? atoi(e) : 0; }
-    rc = RF_DISPATCH(false);
+    rc = RF_DISPATCH(nullptr);
 #undef RF_DISPATCH
     if (d_dbg) {
         static const char *names[14] = {"mma:ring_full", "mma:acc_empty", "mma:h_full", "mma:x_full", "epi:acc_full", "epi:total", "conv:convert", "conv:x_empty",
