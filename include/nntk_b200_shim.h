@@ -95,6 +95,10 @@ typedef struct {
 /* d_in [n_clips, input_size] -> d_out [n_clips, ntime, nfreq] */
 int nntk_cuda_spectrogram(const nntk_spectrogram_args *a, const float *d_in, float *d_out, int n_clips);
 
+/* The same with rows of out_pitch >= nfreq floats (pad columns zero): what the fused front end (SpectrogramBNConv1dApplyBatch)
+ * feeds the Conv1d's TMA im2col view without a re-layout pass.  Returns 1 (nothing enqueued) when the shape has no pitched kernel. */
+int nntk_cuda_spectrogram_pitched(const nntk_spectrogram_args *a, const float *d_in, float *d_out, int n_clips, int out_pitch);
+
 /* K1 with the log-mel epilogue (signal/log_mel_spectrogram.c:33-38 in one kernel).
  * The mel table is passed as a per-lane work list: entry (iter, lane) = {packed, weight}; packed = 8 * slot(bin) |
  * band << 15 | last << 31 with slot(k) = k + k / 16 (the kernel's conflict-free parking order of the spectrum).  A lane
@@ -153,6 +157,12 @@ int nntk_cuda_pack_conv_weights(const float *d_W, float *d_B, int cout, int cin,
  * activation repack [rows][C] -> [rows][Cpad]: give unaligned channel counts (Cin = 257) a 16-byte pitch for TMA */
 int nntk_cuda_pack_conv_weights_padded(const float *d_W, float *d_B, int cout, int cin, int cin_pad, int k);
 int nntk_cuda_pad_channels(const float *d_in, float *d_out, long long rows, int C, int Cpad);
+/* Conv weights with an input BatchNorm folded in (fused front end): conv(BN(x)) = conv'(x) with
+ *   B'[(k*cin_pad + ci)][co] = W[co][ci][k] * a[ci],  bias'[co] = b[co] + sum_{ci,k} W[co][ci][k] * (beta[ci] - mean[ci] * a[ci]),
+ *   a[ci] = gamma[ci] / sqrt(var[ci] + eps)   (layers/batch_norm.c:151-162 composed with layers/conv_1d.c:128-144).
+ * d_bn = gamma|beta|mean|var (4*cin); d_bias_out [cout]. */
+int nntk_cuda_pack_conv_weights_bn(const float *d_W, const float *d_b, const float *d_bn, float eps, float *d_B, float *d_bias_out,
+                                   int cout, int cin, int cin_pad, int k);
 
 /* bidirectional helpers (layers/bidirectional.c:10-85) */
 /* d_out[b][t][:] = d_in[b][T-1-t][:], rows of `vec` floats; not in-place */

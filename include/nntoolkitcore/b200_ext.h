@@ -105,6 +105,12 @@ int Conv1dApplyInferenceBatch(Conv1d filter, const float *input, float *output, 
  * NULL.  Equals the three reference calls conv_1d.c:149 -> batch_norm.c:166 -> activation.c:23 in that order. */
 int Conv1dBNActApplyInferenceBatch(Conv1d filter, BatchNorm bn, ActivationFunction act, const float *input,
                                    float *output, int batch);
+/* Fused front end: [n_clips, input_size] audio -> [n_clips, T_out, Cout].  Equals the reference calls signal/spectrogram.c:113 ->
+ * layers/batch_norm.c:166 (input_bn over the nfreq bins; may be NULL) -> layers/conv_1d.c:149 -> output_bn / act (may be NULL) per
+ * clip; the spectrogram never takes a separate BatchNorm or re-layout pass (the BatchNorm is folded into the conv weights: results
+ * agree with the separate calls to ~2e-7 relative, not bit for bit). */
+int SpectrogramBNConv1dApplyBatch(Spectrogram spectrogram, BatchNorm input_bn, Conv1d filter, BatchNorm output_bn,
+                                  ActivationFunction act, const float *input, float *output, int n_clips);
 /* [batch, in] -> [batch, out] */
 int DenseApplyInferenceBatch(Dense filter, const float *input, float *output, int batch);
 /* [batch, ts, in] -> [batch, ts, out] */

@@ -182,6 +182,7 @@ EXT_API = {
     "ActivationFunctionApplyBatch": (c_int, [H, c_void_p, c_void_p, c_int]),
     "Conv1dApplyInferenceBatch": (c_int, [H, c_void_p, c_void_p, c_int]),
     "Conv1dBNActApplyInferenceBatch": (c_int, [H, H, H, c_void_p, c_void_p, c_int]),
+    "SpectrogramBNConv1dApplyBatch": (c_int, [H, H, H, H, H, c_void_p, c_void_p, c_int]),
     "DenseApplyInferenceBatch": (c_int, [H, c_void_p, c_void_p, c_int]),
     "TimeDistributedDenseApplyInferenceBatch": (c_int, [H, c_void_p, c_void_p, c_int]),
     "RNNApplyInferenceBatch": (c_int, [H, c_void_p, c_void_p, c_int]),
@@ -204,7 +205,8 @@ SHIM_SYMBOLS = [
     "nntk_cuda_log_mel_spectrogram", "nntk_cuda_log_offset", "nntk_cuda_dft", "nntk_cuda_copy_strided",
     "nntk_cuda_bd_reverse", "nntk_cuda_bd_concat", "nntk_cuda_bd_sum",
     "nntk_cuda_batch_norm", "nntk_cuda_activation", "nntk_cuda_gemm", "nntk_cuda_pack_conv_weights",
-    "nntk_cuda_pack_conv_weights_padded", "nntk_cuda_pad_channels",
+    "nntk_cuda_pack_conv_weights_padded", "nntk_cuda_pad_channels", "nntk_cuda_pack_conv_weights_bn",
+    "nntk_cuda_spectrogram_pitched",
     "nntk_cuda_recurrent_workspace", "nntk_cuda_recurrent", "nntk_cuda_last_recurrent_path",
 ]
 

@@ -222,7 +222,52 @@ __global__ void pack_conv_weights_kernel(const float *__restrict__ W, float *__r
     }
 }
 
+// conv weights with an input BatchNorm folded in: B[(k*cin + ci)][co] = W[co][ci][k] * gamma[ci] / sqrt(var[ci] + eps)
+__global__ void pack_conv_weights_bn_kernel(const float *__restrict__ W, const float *__restrict__ bn, float eps, float *__restrict__ B, int cout,
+                                            int cin, int ks, int cin_src) {
+    const long long total = (long long)cout * cin * ks;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int co = (int)(i % cout);
+        const long long rest = i / cout;
+        const int ci = (int)(rest % cin);
+        const int k = (int)(rest / cin);
+        float v = 0.0f;
+        if (ci < cin_src) v = __ldg(W + ((long long)co * cin_src + ci) * ks + k) * (__ldg(bn + ci) / sqrtf(__ldg(bn + 3 * cin_src + ci) + eps));
+        B[i] = v;
+    }
+}
+// bias'[co] = b[co] + sum_{ci,k} W[co][ci][k] * (beta[ci] - mean[ci] * a[ci]); one warp per output channel, double accumulation
+__global__ void fold_bn_bias_kernel(const float *__restrict__ W, const float *__restrict__ b, const float *__restrict__ bn, float eps,
+                                    float *__restrict__ bias_out, int cout, int cin, int ks) {
+    const int co = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (co >= cout) return;
+    double acc = 0.0;
+    for (int ci = lane; ci < cin; ci += 32) {
+        const float a = __ldg(bn + ci) / sqrtf(__ldg(bn + 3 * cin + ci) + eps);
+        const double shift = (double)__ldg(bn + cin + ci) - (double)__ldg(bn + 2 * cin + ci) * (double)a;
+        double w = 0.0;
+        for (int k = 0; k < ks; ++k) w += (double)__ldg(W + ((long long)co * cin + ci) * ks + k);
+        acc += w * shift;
+    }
+    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) bias_out[co] = (float)((double)__ldg(b + co) + acc);
+}
+
 }  // namespace
+
+extern "C" int nntk_cuda_pack_conv_weights_bn(const float *d_W, const float *d_b, const float *d_bn, float eps, float *d_B, float *d_bias_out,
+                                              int cout, int cin, int cin_pad, int k) {
+    int rc = nntk_cuda_ensure_init();
+    if (rc) return rc;
+    const long long total = (long long)cout * cin_pad * k;
+    if (total <= 0) return 0;
+    long long blocks = (total + 255) / 256;
+    if (blocks > 4096) blocks = 4096;
+    pack_conv_weights_bn_kernel<<<(unsigned)blocks, 256, 0, nntk_stream()>>>(d_W, d_bn, eps, d_B, cout, cin_pad, k, cin);
+    fold_bn_bias_kernel<<<(unsigned)((cout + 7) / 8), 256, 0, nntk_stream()>>>(d_W, d_b, d_bn, eps, d_bias_out, cout, cin, k);
+    NNTK_LAUNCH_CHECK_N("pack_conv_weights_bn", 2);
+    return 0;
+}
 
 extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *g, int split);   // gemm_tc.cu
 #define NNTK_X3_MAX_K 3072

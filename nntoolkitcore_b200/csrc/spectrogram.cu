@@ -36,6 +36,7 @@ struct SpecParams {
     float psd_edge;     // PSD bins 0, nfreq-1: norm^2 * 0.25 / scale
     int mode;           // 0 magnitude, 1 PSD (generic kernel only; the 512 kernel is templated on it)
     int in_vec_ok;      // input base pointer 16-byte aligned
+    int out_pitch;      // floats between output rows (nfreq, or more: the pad columns are written as zeros -- fused front end)
     int n_mels, mel_iter;   // log-mel epilogue (MEL kernels only): bands, work-list entries per lane
     float log_offset;
 };
@@ -188,7 +189,8 @@ spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const floa
         const long long gi0 = (long long)g.clip * p.input_size + (long long)f0 * p.step;
         const int ia = p.in_vec_ok ? (int)(gi0 & 3) : 0;
         const float *buf = s_in + (it & 1) * p.in_cap + ia + lane;
-        float *orow = out + ((long long)g.clip * p.ntime + f0) * 257LL;
+        const int pitch = p.out_pitch;
+        float *orow = out + ((long long)g.clip * p.ntime + f0) * (long long)pitch;
 #pragma unroll 1
         for (int fa = 0; fa < nf; fa += 2) {
             const bool has_b = fa + 1 < nf;
@@ -235,7 +237,7 @@ spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const floa
             // split the packed pair in registers and store: slot j -> bin 64 j + c1, slot 4 + j -> bin 64 j + c2
             float pa[9], pb[9];
             spec_split_regs(lane, v, pa, pb);
-            float *ra = orow + (long long)fa * 257;
+            float *ra = orow + (long long)fa * pitch;
             float *ra1 = ra + c1, *ra2 = ra + c2;
             if (MODE == 0) {
 #pragma unroll
@@ -295,11 +297,16 @@ spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const floa
             for (int slot = 0; slot < 8; ++slot) {
                 float *dst = (slot < 4 ? ra1 : ra2) + 64 * (slot & 3);
                 dst[0] = pa[slot];
-                if (has_b) dst[257] = pb[slot];
+                if (has_b) dst[pitch] = pb[slot];
             }
-            if (l0) {   // bin 256
-                ra[256] = pa[8];
-                if (has_b) ra[256 + 257] = pb[8];
+            if (pitch == 257) {
+                if (l0) {   // bin 256
+                    ra[256] = pa[8];
+                    if (has_b) ra[256 + 257] = pb[8];
+                }
+            } else if (256 + lane < pitch) {   // bin 256 and the zero pad columns up to the pitch (<= 288) in one warp store
+                ra[256 + lane] = l0 ? pa[8] : 0.0f;
+                if (has_b) ra[256 + lane + pitch] = l0 ? pb[8] : 0.0f;
             }
         }
         if (!more) break;
@@ -377,10 +384,18 @@ spectrogram_generic_kernel(SpecParams p, int nfft, int log2n, const float *__res
 
 }  // namespace
 
-static int spectrogram_run(const nntk_spectrogram_args *a, const nntk_mel_args *m, const float *d_in, float *d_out, int n_clips);
+static int spectrogram_run(const nntk_spectrogram_args *a, const nntk_mel_args *m, const float *d_in, float *d_out, int n_clips, int out_pitch = 0);
 
 extern "C" int nntk_cuda_spectrogram(const nntk_spectrogram_args *a, const float *d_in, float *d_out, int n_clips) {
     return spectrogram_run(a, nullptr, d_in, d_out, n_clips);
+}
+
+// Rows of `out_pitch` >= nfreq floats, the pad columns written as zeros (fused front end: a 16- or 128-byte aligned row pitch
+// is what the TMA im2col view of the following Conv1d needs).  Returns 1 (nothing enqueued) when only the dense layout exists
+// for this shape (nfft != 512 or a pitch beyond 288).
+extern "C" int nntk_cuda_spectrogram_pitched(const nntk_spectrogram_args *a, const float *d_in, float *d_out, int n_clips, int out_pitch) {
+    if (!a || a->nfft != NNTK_SPEC_N || out_pitch < a->nfreq || out_pitch > 288) return 1;
+    return spectrogram_run(a, nullptr, d_in, d_out, n_clips, out_pitch);
 }
 
 extern "C" int nntk_cuda_log_mel_spectrogram(const nntk_spectrogram_args *a, const nntk_mel_args *m, const float *d_in,
@@ -394,7 +409,7 @@ extern "C" int nntk_cuda_log_mel_spectrogram(const nntk_spectrogram_args *a, con
     return spectrogram_run(a, m, d_in, d_out, n_clips);
 }
 
-static int spectrogram_run(const nntk_spectrogram_args *a, const nntk_mel_args *m, const float *d_in, float *d_out, int n_clips) {
+static int spectrogram_run(const nntk_spectrogram_args *a, const nntk_mel_args *m, const float *d_in, float *d_out, int n_clips, int out_pitch) {
     int rc = nntk_cuda_ensure_init();
     if (rc) return rc;
     if (!a || !d_in || !d_out || n_clips < 0 || a->nfft < 1 || a->window_size < 1 || a->window_size > a->nfft ||
@@ -420,6 +435,7 @@ static int spectrogram_run(const nntk_spectrogram_args *a, const nntk_mel_args *
     p.psd_mid = an * an * 0.25f * (2.0f / a->scale);
     p.psd_edge = an * an * 0.25f / a->scale;
     p.in_vec_ok = (((uintptr_t)d_in) & 15) == 0;
+    p.out_pitch = out_pitch > 0 ? out_pitch : a->nfreq;
     p.n_mels = m ? m->n_mels : 0;
     p.mel_iter = m ? m->n_iter : 0;
     p.log_offset = m ? m->log_offset : 0.0f;

@@ -13,6 +13,8 @@ struct Conv1dStruct {
     ConvWeights weights;
     float *d_packed; /* [K*Cin][Cout] */
     float *d_packed_pad; /* [K*Cin_pad][Cout], only when Cin % 4 != 0 (tensor-core modes need 16-byte row pitch) */
+    float *d_packed_bn;  /* fused front end: [K*pitch][Cout] with the input BatchNorm folded in | bias' [Cout] */
+    int packed_bn_pitch;
 };
 
 /* Channel count the tensor-core path lays the input out with.  Cin % 4 == 0 needs no repack.  Otherwise the repack is paid
@@ -82,6 +84,7 @@ void Conv1dDestroy(Conv1d filter) {
     if (!filter) return;
     nntk_cuda_free(filter->d_packed);
     nntk_cuda_free(filter->d_packed_pad);
+    nntk_cuda_free(filter->d_packed_bn);
     nntk_layer_release(&filter->hdr);
     free(filter);
 }
@@ -171,6 +174,135 @@ int Conv1dBNActApplyInferenceBatch(Conv1d filter, BatchNorm bn, ActivationFuncti
     const Conv1dConfig *c = &filter->config;
     return nntk_cuda_staged_run(input, output, sizeof(float) * (size_t)c->input_size * c->input_feature_channels,
                                 sizeof(float) * (size_t)c->output_size * c->output_feature_channels, batch, conv_launch, &cc);
+}
+
+/* ---- fused front end: SpectrogramApply -> BatchNormApplyInference -> Conv1dApplyInference (-> BatchNorm -> activation) ------------
+ * One K1 launch writes the magnitude rows at the pitch the Conv1d's implicit GEMM wants (pad columns zero), the input BatchNorm
+ * is folded into the conv weights (it is affine per input channel), and the conv epilogue carries the optional output BatchNorm
+ * and activation: the [clips, ntime, nfreq] spectrogram is written once and read once, where the three separate calls move it
+ * five times (K1 write, BN read + write, channel pad read + write, GEMM read).  Reference chain: signal/spectrogram.c:113-135,
+ * layers/batch_norm.c:140-189, layers/conv_1d.c:122-155. */
+typedef struct {
+    Spectrogram s; Conv1d f; const float *d_in_bn; float in_eps; const float *d_bn; float eps; int act; float act_a; int pitch;
+} front_ctx;
+
+static int front_launch(void *ctx, const float *d_in, float *d_out, long long first, int n) {
+    (void)first;
+    front_ctx *fc = (front_ctx *)ctx;
+    const Conv1dConfig *c = &fc->f->config;
+    nntk_spectrogram_args sa;
+    int rc = nntk_spectrogram_prepare(fc->s, &sa);
+    if (rc) return rc;
+    const int cp = fc->pitch;
+    const size_t per_clip = sizeof(float) * (size_t)c->input_size * cp;
+    void *ws = NULL; size_t got = 0;
+    if ((rc = nntk_cuda_workspace(per_clip * (size_t)n, per_clip, &ws, &got))) return rc;
+    const int chunk = (int)(got / per_clip < (size_t)n ? got / per_clip : (size_t)n);
+    nntk_gemm_args g;
+    g.a_slab_stride = (long long)c->input_size * cp;
+    g.lda = c->stride * cp;
+    g.rows = c->output_size;
+    g.N = c->output_feature_channels;
+    g.K = c->kernel_size * cp;
+    g.d_B = fc->f->d_packed_bn;
+    g.d_bias = fc->f->d_packed_bn + (size_t)c->kernel_size * cp * c->output_feature_channels;
+    g.d_bn = fc->d_bn;
+    g.bn_eps = fc->eps;
+    g.act = fc->act;
+    g.act_a = fc->act_a;
+    g.c_slab_stride = (long long)c->output_size * c->output_feature_channels;
+    g.ldc = c->output_feature_channels;
+    for (int b0 = 0; b0 < n; b0 += chunk) {
+        const int nb = b0 + chunk <= n ? chunk : n - b0;
+        rc = nntk_cuda_spectrogram_pitched(&sa, d_in + (size_t)b0 * sa.input_size, (float *)ws, nb, cp);
+        if (rc) return rc < 0 ? rc : NNTK_ERR_UNSUPPORTED;
+        g.d_A = (const float *)ws;
+        g.batch = nb;
+        g.d_C = d_out + (size_t)b0 * c->output_size * c->output_feature_channels;
+        if ((rc = nntk_cuda_gemm(&g))) return rc;
+    }
+    return 0;
+}
+
+int SpectrogramBNConv1dApplyBatch(Spectrogram spectrogram, BatchNorm input_bn, Conv1d filter, BatchNorm output_bn,
+                                  ActivationFunction act, const float *input, float *output, int n_clips) {
+    NNTK_API_GUARD();
+    if (!spectrogram || !filter || n_clips < 0) {
+        nntk_cuda_set_error(NNTK_ERR_ARG, "SpectrogramBNConv1dApplyBatch: bad arguments");
+        return NNTK_ERR_ARG;
+    }
+    int kind = nntk_ptr_kind(input, output, "SpectrogramBNConv1dApplyBatch");
+    if (kind < 0) return kind;
+    const Conv1dConfig *c = &filter->config;
+    const SpectrogramConfig sc = SpectrogramGetConfig(spectrogram);
+    if (sc.nfreq != c->input_feature_channels || sc.ntime_series != c->input_size) {
+        nntk_cuda_set_error(NNTK_ERR_ARG, "SpectrogramBNConv1dApplyBatch: the spectrogram emits [%d, %d], the Conv1d expects [%d, %d]",
+                            sc.ntime_series, sc.nfreq, c->input_size, c->input_feature_channels);
+        return NNTK_ERR_ARG;
+    }
+    front_ctx fc = {spectrogram, filter, NULL, 0.0f, NULL, 0.0f, NNTK_ACT_NONE, 1.0f, 0};
+    if (act) {
+        if (act->kind == NNTK_ACT_SOFTMAX || act->kind == NNTK_ACT_CUSTOM) {
+            nntk_cuda_set_error(NNTK_ERR_UNSUPPORTED, "SpectrogramBNConv1dApplyBatch: only identity/sigmoid/tanh/ReLU can be fused");
+            return NNTK_ERR_UNSUPPORTED;
+        }
+        fc.act = act->kind;
+        fc.act_a = act->a;
+    }
+    int rc = nntk_layer_stage(&filter->hdr), ch = 0;
+    if (rc) return rc;
+    if (input_bn) {
+        fc.d_in_bn = nntk_batch_norm_device_params(input_bn, &ch, &fc.in_eps);
+        if (!fc.d_in_bn) return NNTK_ERR_CUDA;
+        if (ch != c->input_feature_channels) {
+            nntk_cuda_set_error(NNTK_ERR_ARG, "SpectrogramBNConv1dApplyBatch: input BatchNorm has %d channels, the spectrogram %d bins", ch, sc.nfreq);
+            return NNTK_ERR_ARG;
+        }
+    }
+    if (output_bn) {
+        fc.d_bn = nntk_batch_norm_device_params(output_bn, &ch, &fc.eps);
+        if (!fc.d_bn) return NNTK_ERR_CUDA;
+        if (ch != c->output_feature_channels) {
+            nntk_cuda_set_error(NNTK_ERR_ARG, "SpectrogramBNConv1dApplyBatch: output BatchNorm has %d channels, Conv1d emits %d", ch, c->output_feature_channels);
+            return NNTK_ERR_ARG;
+        }
+    }
+    /* row pitch: 128-byte aligned rows on the tensor-core paths when that costs <= 15 % more K (cin_pad), 16-byte aligned for FFMA */
+    const int cin = c->input_feature_channels;
+    fc.pitch = nntk_cuda_math_mode() == NNTK_MATH_FP32 ? ((cin + 3) & ~3) : cin_pad(c);
+    if (sc.nfft != 512 || fc.pitch > 288 || !input_bn) {
+        /* shapes without a pitched K1 (or nothing to fold): the three reference-shaped calls through a scratch spectrogram */
+        const size_t spec_bytes = sizeof(float) * (size_t)n_clips * sc.ntime_series * sc.nfreq;
+        if (kind != 1) {
+            nntk_cuda_set_error(NNTK_ERR_UNSUPPORTED, "SpectrogramBNConv1dApplyBatch: host buffers need nfft = 512 and an input BatchNorm");
+            return NNTK_ERR_UNSUPPORTED;
+        }
+        void *tmp = NULL;
+        if ((rc = nntk_cuda_malloc(&tmp, spec_bytes))) return rc;
+        rc = SpectrogramApplyBatch(spectrogram, input, (float *)tmp, n_clips);
+        if (!rc && input_bn) rc = BatchNormApplyInferenceBatch(input_bn, (float *)tmp, (float *)tmp, n_clips);
+        if (!rc) rc = Conv1dBNActApplyInferenceBatch(filter, output_bn, act, (float *)tmp, output, n_clips);
+        if (!rc) rc = nntk_cuda_sync();
+        nntk_cuda_free(tmp);
+        return rc;
+    }
+    /* conv weights with the input BatchNorm folded in: rebuilt at every call (both weight blocks may have been rewritten) */
+    const size_t wn = (size_t)c->kernel_size * fc.pitch * c->output_feature_channels;
+    if (!filter->d_packed_bn || filter->packed_bn_pitch != fc.pitch) {
+        nntk_cuda_free(filter->d_packed_bn);
+        void *d = NULL;
+        filter->d_packed_bn = NULL;
+        if ((rc = nntk_cuda_malloc(&d, sizeof(float) * (wn + (size_t)c->output_feature_channels)))) return rc;
+        filter->d_packed_bn = (float *)d;
+        filter->packed_bn_pitch = fc.pitch;
+    }
+    const size_t w = (size_t)c->output_feature_channels * cin * c->kernel_size;
+    if ((rc = nntk_cuda_pack_conv_weights_bn(filter->hdr.d_block, filter->hdr.d_block + w, fc.d_in_bn, fc.in_eps, filter->d_packed_bn,
+                                             filter->d_packed_bn + wn, c->output_feature_channels, cin, fc.pitch, c->kernel_size)))
+        return rc;
+    if (kind == 1) return front_launch(&fc, input, output, 0, n_clips);
+    return nntk_cuda_staged_run(input, output, sizeof(float) * (size_t)sc.input_size,
+                                sizeof(float) * (size_t)c->output_size * c->output_feature_channels, n_clips, front_launch, &fc);
 }
 
 int Conv1dApplyInferenceBatch(Conv1d filter, const float *input, float *output, int batch) {

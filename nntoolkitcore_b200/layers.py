@@ -364,6 +364,16 @@ class Recurrent:
         self._acts = []
 
 
+def front_end(lib, spec, bn, conv, conv_bn, act, x, out=None):
+    """SpectrogramBNConv1dApplyBatch: audio [n, input_size] -> [n, T_out, Cout]; bn / conv_bn / act may be None"""
+    n = x.shape[0]
+    out = _new_out(x, (n,) + conv.out_shape) if out is None else out
+    rc = lib.SpectrogramBNConv1dApplyBatch(spec.handle, bn.handle if bn else None, conv.handle, conv_bn.handle if conv_bn else None,
+                                           act.handle if act else None, _ptr(x), _ptr(out), n)
+    _check(lib, rc, "SpectrogramBNConv1dApplyBatch")
+    return out
+
+
 def freeze(lib, *layers):
     for l in layers:
         _check(lib, lib.NNTKWeightsFreeze(l.handle), "NNTKWeightsFreeze")

@@ -111,11 +111,53 @@ def test_c5_chain_end_to_end_at_config_shape(tf32, ref):
                 v.close()
     yv = y.view(B // 8, 8, c["T1"], 12)
     assert torch.equal(yv[0], yv[-1]), "copies of the same clip at different batch positions differ"
-    if hasattr(tf32, "SpectrogramBNConv1dApplyBatch"):
-        fused = torch.empty_like(cv)
-        L.front_end(tf32, c["spec"], c["bn"], c["conv"], None, c["relu"], x, fused)
+    # the fused front end (one K1 launch at the conv's row pitch, BatchNorm folded into the conv weights) at the same shape
+    fused = torch.empty_like(cv)
+    L.front_end(tf32, c["spec"], c["bn"], c["conv"], None, c["relu"], x, fused)
+    torch.cuda.synchronize()
+    rc = _chain(ref, 1)
+    for k in ("bn", "conv"):
+        helpers.copy_weights(rc[k], c[k])
+    for b in (0, 5, B - 1):
+        w_cv = rc["relu"].apply(rc["conv"].apply(rc["bn"].apply(rc["spec"].apply(clips[b % 8]))))
+        assert_parity(fused[b].cpu().numpy(), w_cv, tol=TF32_TOL, what=f"fused front end (tensor-core mode) vs the reference chain, clip {b}")
+
+
+@pytest.mark.parametrize("mode,tol", [(0, helpers.FP32_TOL), (2, helpers.FP32_TOL), (1, TF32_TOL)])
+@pytest.mark.parametrize("win,nov,cout,k,stride,out_bn", [(400, 240, 64, 5, 1, False), (512, 352, 40, 3, 2, True)])
+def test_fused_front_end_matches_reference_chain(cuda, product, ref, mode, tol, win, nov, cout, k, stride, out_bn):
+    """SpectrogramBNConv1dApplyBatch == SpectrogramApply -> BatchNormApplyInference -> Conv1dApplyInference (-> BN -> ReLU) of the
+    reference, in every math mode, from device and from host buffers (signal/spectrogram.c:113, batch_norm.c:166, conv_1d.c:149)"""
+    import torch
+    n, B = 16000, 5
+    x = np.stack([helpers.audio_clip(40 + i, n) for i in range(B)])
+    assert product.NNTKSetMathMode(mode) == 0
+    try:
+        def chain(lib):
+            spec = L.Spectrogram(lib, 512, win, nov, n, 1.0, "hann_window")
+            T0, F = spec.out_shape
+            bn = L.BatchNorm(lib, F, 1e-3, T0); helpers.fill_bn(bn, 510)
+            conv = L.Conv1d(lib, F, cout, k, stride, T0); helpers.fill_conv(conv, 511)
+            T1 = conv.out_shape[0]
+            obn = L.BatchNorm(lib, cout, 1e-3, T1); helpers.fill_bn(obn, 512)
+            relu = L.Activation(lib, L.ACT_RELU, T1 * cout, a=1.5)
+            return spec, bn, conv, obn, relu
+        rs, rb, rcv, robn, rrelu = chain(ref)
+        want = []
+        for v in x:
+            w = rcv.apply(rb.apply(rs.apply(v)))
+            if out_bn:
+                w = robn.apply(w)
+            want.append(rrelu.apply(w))
+        want = np.stack(want)
+        ps, pb, pcv, pobn, prelu = chain(product)
+        got_dev = L.front_end(product, ps, pb, pcv, pobn if out_bn else None, prelu, torch.from_numpy(x).to(cuda))
         torch.cuda.synchronize()
-        assert_parity(fused.cpu().numpy(), cv.cpu().numpy(), tol=2e-6, what="fused front end vs the three separate calls")
+        assert_parity(got_dev.cpu().numpy(), want, tol=tol, what=f"fused front end, mode {mode}, device buffers")
+        got_host = L.front_end(product, ps, pb, pcv, pobn if out_bn else None, prelu, x)
+        assert np.array_equal(got_host, got_dev.cpu().numpy()), "host-buffer path differs from the device-buffer path"
+    finally:
+        product.NNTKSetMathMode(0)
 
 
 def test_fp32_contract_suite_holds_under_3xtf32_default():
