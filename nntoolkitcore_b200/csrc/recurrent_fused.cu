@@ -43,7 +43,7 @@ namespace {
 
 constexpr int RF_ROWS = 64;                  // sequences per CTA (pair: 128)
 constexpr int RF_UT = 64;                    // hidden units per tile (pair), 32 per CTA
-constexpr int RF_THREADS_FUSED = 640, RF_THREADS_XW = 384;
+constexpr int RF_THREADS_FUSED = 640, RF_THREADS_XW = 640;
 constexpr int RF_MAX_RING = 8;
 
 struct RfParams {
@@ -159,7 +159,7 @@ struct RfPlan {
         a_h = o; o += RF_ROWS * H * 2;                       // [H/64 k-blocks][64 rows][128 B]
         x_hi = o; o += FUSED ? RF_ROWS * in * 2 : 0;         // [in/64][64 rows][128 B]
         x_lo = o; o += (FUSED && xp == 3) ? RF_ROWS * in * 2 : 0;
-        out_stg = o; o += 8 * 2048;                          // per epilogue warp: [32 rows][16 floats], SWIZZLE_64B
+        out_stg = o; o += 8 * 2048;                          // per epilogue warp: [32 rows][16 floats] (SWIZZLE_64B) or 16 x [32 rows][8 floats]
         ring = o; o += ring_stages * stage_bytes;
         bias = o; o += 4 * H * 4;
         bars = o; o += 1024;
@@ -195,7 +195,10 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
 
     const int tid = threadIdx.x, lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);          // warp-uniform for the compiler (role dispatch, uniform registers)
-    constexpr int CONV_W0 = 8, CTRL_W0 = FUSED ? 16 : 8;     // first converter / control warp
+    // FUSED: 8 epilogue warps (16 units of a tile per thread) + 8 converter warps.  XW: 16 epilogue warps (8 units per thread) -- its
+    // epilogue also adds the hoisted projection and, with 8 warps, took 4 700 cycles per LSTM-512 tile against 2 064 of MMA.
+    constexpr int EPW = FUSED ? 8 : 16, UPT = 128 / EPW, NE = UPT / 8;
+    constexpr int CONV_W0 = 8, CTRL_W0 = 16;                 // first converter / control warp
     const uint32_t crank = rf_rank();                       // rank in the cluster; pairs are (0,1), (2,3), ...
     const uint32_t rank = crank & 1u, leader = crank & ~1u; // rank inside the pair, cluster rank of the pair's leader
     const int npairs = p.cs >> 1, pair_i = (int)(crank >> 1);
@@ -210,8 +213,8 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_u) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_out) : "memory");
         for (int s = 0; s < p.ring_stages; ++s) { mbar_init(bars + RFB_RING_FULL + s, 1); mbar_init(bars + RFB_RING_EMPTY + s, (uint32_t)npairs); }
-        for (int b = 0; b < 4; ++b) { mbar_init(bars + RFB_ACC_FULL + b, 1); mbar_init(bars + RFB_ACC_EMPTY + b, 16); }
-        mbar_init(bars + RFB_H_FULL, 16);
+        for (int b = 0; b < 4; ++b) { mbar_init(bars + RFB_ACC_FULL + b, 1); mbar_init(bars + RFB_ACC_EMPTY + b, 2 * EPW); }
+        mbar_init(bars + RFB_H_FULL, 2 * EPW);
         mbar_init(bars + RFB_X_FULL, 16);
         for (int b = 0; b < 4; ++b) mbar_init(bars + RFB_XL_FULL + b, 16);
         mbar_init(bars + RFB_X_EMPTY, 1);
@@ -247,6 +250,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
 
     if (warp >= CTRL_W0) {
         if (FUSED) asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
+        else asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
         if (warp == CTRL_W0 && lane == 0) {
             // ===== ring producer: this CTA's half of every B stage (two k-blocks), in the order the MMA issuer consumes them =====
             int stage = 0; uint32_t phase = 0;
@@ -332,9 +336,10 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 if (c == 0) { RF_T0(); mbar_wait(bars + RFB_H_FULL, (uint32_t)(t & 1)); RF_T1(2); }
                 if (!FUSED && use > 0) { RF_T0(); mbar_wait(bars + RFB_ACC_EMPTY + buf, (uint32_t)((use - 1) & 1)); RF_T1(1); }
                 tc_fence_after();
-                // GRU fused: the recurrent part lands one 32-column group to the right ([z | r | h.Uh]) and always accumulates
-                const uint32_t d = tmem + (uint32_t)(buf * 128) + ((FUSED && G == 3) ? 32u : 0u);
-                for (int kb = 0; kb < KBH; kb += 2) stage_mmas(d, ah_a, 0u, kb, min(2, KBH - kb), !FUSED);
+                // The recurrent part ALWAYS accumulates: onto the input part (FUSED) or onto the hoisted projection the epilogue stored
+                // into the buffer (XW).  GRU: it lands one 32-column group to the right ([z | r | h.Uh]); x.Wh stays in group 0.
+                const uint32_t d = tmem + (uint32_t)(buf * 128) + (G == 3 ? 32u : 0u);
+                for (int kb = 0; kb < KBH; kb += 2) stage_mmas(d, ah_a, 0u, kb, min(2, KBH - kb), false);
                 if (rf_elect()) rf_commit(bars + RFB_ACC_FULL + buf, pair_mask);
                 __syncwarp();
             };
@@ -352,7 +357,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
             RF_DBG(if (lane == 0) { for (int i = 0; i < 4; ++i) p.dbg[blockIdx.x * 16 + i] = dbgc[i]; p.dbg[blockIdx.x * 16 + 10] = clock64() - t_start;
                    p.dbg[blockIdx.x * 16 + 12] = dbgc[12]; p.dbg[blockIdx.x * 16 + 13] = dbgc[13]; });
         }
-    } else if (warp >= CONV_W0) {
+    } else if (FUSED && warp >= CONV_W0) {
         // ===== x converters (FUSED only): fp32 rows of x_t from global -> fp16 hi (and lo) k-block tiles =====
         // item (row, 16-byte chunk of the fp16 row = 8 floats): a warp covers 4 rows x 256 contiguous bytes per load instruction and
         // 512 contiguous (swizzled) bytes per store.  x_{t+1} is loaded right after x_t has been converted and waits in registers.
@@ -444,6 +449,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     } else {
         // ===== epilogue (warps 0..7): thread = row m of this CTA x 16 hidden units of every tile =====
         if (FUSED) asm volatile("setmaxnreg.inc.sync.aligned.u32 128;");
+        else asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");
         const int ew = warp, q = warp & 3, j = ew >> 2;
         const int m = (q & 1) * 32 + lane, hf = q >> 1;
         const int row = row0 + m;
@@ -454,8 +460,8 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         // ---- prologue: state into TMEM, fp16 h_0 into the A tile, zero the h.Uh groups
         for (int c = 0; c < NC; ++c) {
 #pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const int u0 = c * 64 + hf * 32 + j * 16 + e * 8;
+            for (int e = 0; e < NE; ++e) {
+                const int u0 = c * 64 + hf * 32 + j * UPT + e * 8;
                 float hv[8], sv[8];
 #pragma unroll
                 for (int i = 0; i < 2; ++i) {
@@ -466,68 +472,90 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                         sv[4 * i] = b.x; sv[4 * i + 1] = b.y; sv[4 * i + 2] = b.z; sv[4 * i + 3] = b.w;
                     }
                 }
-                if (G == 4) rf_st8(tl + STATE_COL + (uint32_t)(c * 32 + j * 16 + e * 8), sv);
-                else rf_st8(tl + STATE_COL + (uint32_t)(c * 32 + j * 16 + e * 8), hv);
+                if (G == 4) rf_st8(tl + STATE_COL + (uint32_t)(c * 32 + j * UPT + e * 8), sv);
+                else rf_st8(tl + STATE_COL + (uint32_t)(c * 32 + j * UPT + e * 8), hv);
                 uint4 v;
                 v.x = rf_pack_sat(hv[0], hv[1]); v.y = rf_pack_sat(hv[2], hv[3]); v.z = rf_pack_sat(hv[4], hv[5]); v.w = rf_pack_sat(hv[6], hv[7]);
-                const int ch = hf * 4 + j * 2 + e;
+                const int ch = (hf * 32 + j * UPT) / 8 + e;
                 *reinterpret_cast<uint4 *>(sAh + (size_t)c * (RF_ROWS * 128) + m * 128 + ((ch ^ sw) << 4)) = v;
             }
         }
-        if (FUSED && G == 3) {
+        // XW mode: the hoisted projection of a tile is STORED INTO ITS ACCUMULATOR BUFFER before the tile's MMAs run (which then
+        // accumulate onto it): the loads are issued a whole tile earlier, while the previous occupant of the buffer is being
+        // processed, so their latency never sits between the MMA and the cell math (loaded and waited for per tile they made the
+        // LSTM-512 epilogue 4 700 cycles against 2 064 of MMA).  Column groups as in FUSED mode: GRU [x.Wh | z | r | h.Uh = 0],
+        // LSTM [i | f | g | o].
+        auto xw_src = [&](int t2, int c2) -> const float4 * {
+            return reinterpret_cast<const float4 *>(p.xw) +
+                   (((long long)t2 * p.xw_blocked_rows + (row >> 5)) * (G * H >> 2) + ((c2 * 64 + hf * 32 + j * UPT) >> 2)) * 32 + (row & 31);
+        };
+        auto xw_load = [&](float4 (&xn)[G][UPT / 4], int t2, int c2) {
+            const float4 *src = xw_src(t2, c2);
+#pragma unroll
+            for (int gg = 0; gg < G; ++gg)
+#pragma unroll
+                for (int i = 0; i < UPT / 4; ++i)
+                    xn[gg][i] = (row_ok && t2 < T) ? __ldg(src + ((long long)gg * (H >> 2) + i) * 32) : make_float4(0.f, 0.f, 0.f, 0.f);
+        };
+        auto xw_store = [&](const float4 (&xn)[G][UPT / 4], int b) {       // projection gate gg -> column group: GRU z, r, h -> 1, 2, 0
+#pragma unroll
+            for (int gg = 0; gg < G; ++gg) {
+                const int grp = G == 3 ? (gg == 2 ? 0 : gg + 1) : gg;
+#pragma unroll
+                for (int e = 0; e < NE; ++e) {
+                    const float v8[8] = {xn[gg][2 * e].x, xn[gg][2 * e].y, xn[gg][2 * e].z, xn[gg][2 * e].w,
+                                         xn[gg][2 * e + 1].x, xn[gg][2 * e + 1].y, xn[gg][2 * e + 1].z, xn[gg][2 * e + 1].w};
+                    rf_st8(tl + (uint32_t)(b * 128 + grp * 32 + j * UPT + e * 8), v8);
+                }
+            }
+        };
+        if (G == 3) {
             const float z8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-            for (int b = 0; b < NB; ++b) { rf_st8(tl + (uint32_t)(b * 128 + 96 + j * 16), z8); rf_st8(tl + (uint32_t)(b * 128 + 96 + j * 16 + 8), z8); }
+            for (int b = 0; b < NB; ++b)
+#pragma unroll
+                for (int e = 0; e < NE; ++e) rf_st8(tl + (uint32_t)(b * 128 + 96 + j * UPT + e * 8), z8);
+        }
+        if (!FUSED) {
+            for (int b = 0; b < NB; ++b) {          // tiles 0 .. NB-1 in issue order
+                float4 xn[G][UPT / 4];
+                xw_load(xn, b / NC, b % NC);
+                xw_store(xn, b);
+            }
         }
         rf_st_wait();
         rf_fence_async();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) rf_arrive_cl(hfull0);
-        uint32_t hpend[NCMAX][8];       // fp16 h_t of the step's tiles x 16 units, written to the A tile once the step's MMAs are done
+        uint32_t hpend[NCMAX][UPT / 2]; // fp16 h_t of the step's tiles x UPT units, written to the A tile once the step's MMAs are done
         int buf = -1, use = 0;          // accumulator buffer of the current tile and how often it has been used before
         for (int t = 0; t < T; ++t) {
 #pragma unroll
             for (int c = 0; c < NCMAX; ++c) {
                 if (c >= NC) break;
                 if (++buf == NB) { buf = 0; ++use; }
-                const uint32_t acc = tl + (uint32_t)(buf * 128 + j * 16);
-                float4 xr[G][4];         // XW mode: the hoisted projection of this thread's 16 units
+                const uint32_t acc = tl + (uint32_t)(buf * 128 + j * UPT);
+                float4 xn[G][UPT / 4];   // XW mode: the hoisted projection of the NEXT occupant of this buffer (tile g + NB)
                 if (!FUSED) {
-                    const float4 *src = reinterpret_cast<const float4 *>(p.xw) +
-                                        (((long long)t * p.xw_blocked_rows + (row >> 5)) * (G * H >> 2) + ((c * 64 + hf * 32 + j * 16) >> 2)) * 32 + (row & 31);
-                    {   // the projection of the tile after next -> L2 (the loads below are waited for right away: from HBM they bounded the tile)
-                        int c2 = c + 2, t2 = t;
-                        if (c2 >= NC) { c2 -= NC; ++t2; }
-                        if (t2 < T && row_ok) {
-                            const float4 *nx = reinterpret_cast<const float4 *>(p.xw) +
-                                               (((long long)t2 * p.xw_blocked_rows + (row >> 5)) * (G * H >> 2) + ((c2 * 64 + hf * 32 + j * 16) >> 2)) * 32 + (row & 31);
-#pragma unroll
-                            for (int gg = 0; gg < G; ++gg)
-#pragma unroll
-                                for (int i = 0; i < 4; ++i) asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + ((long long)gg * (H >> 2) + i) * 32));
-                        }
-                    }
-#pragma unroll
-                    for (int gg = 0; gg < G; ++gg)
-#pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            xr[gg][i] = row_ok ? __ldg(src + ((long long)gg * (H >> 2) + i) * 32) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    int c2 = c + NB, t2 = t;
+                    while (c2 >= NC) { c2 -= NC; ++t2; }
+                    xw_load(xn, t2, c2);
                 }
                 { RF_T0(); mbar_wait(bars + RFB_ACC_FULL + buf, (uint32_t)(use & 1)); RF_T1(4); }
                 tc_fence_after();
-                float hn[16];
+                float hn[UPT];
 #pragma unroll
-                for (int i = 0; i < 16; ++i) hn[i] = 0.f;
+                for (int i = 0; i < UPT; ++i) hn[i] = 0.f;
 #pragma unroll
-                for (int e = 0; e < 2; ++e) {
+                for (int e = 0; e < NE; ++e) {
                     if (RF_SKIP(1)) break;
-                    const int ub = c * 64 + hf * 32 + j * 16 + e * 8;            // first of these 8 hidden units
+                    const int ub = c * 64 + hf * 32 + j * UPT + e * 8;            // first of these 8 hidden units
                     float a0[8], a1[8], a2[8], a3[8], st[8];
                     rf_ld8(acc + (uint32_t)(e * 8), a0);
                     rf_ld8(acc + (uint32_t)(32 + e * 8), a1);
                     rf_ld8(acc + (uint32_t)(64 + e * 8), a2);
-                    if (G == 4 || FUSED) rf_ld8(acc + (uint32_t)(96 + e * 8), a3);
-                    rf_ld8(tl + STATE_COL + (uint32_t)(c * 32 + j * 16 + e * 8), st);
+                    rf_ld8(acc + (uint32_t)(96 + e * 8), a3);
+                    rf_ld8(tl + STATE_COL + (uint32_t)(c * 32 + j * UPT + e * 8), st);
                     rf_ld_wait();
                     float b0[8], b1[8], b2[8], b3[8];
 #pragma unroll
@@ -542,53 +570,45 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                     float sn[8];
 #pragma unroll
                     for (int u = 0; u < 8; ++u) {
-                        if (G == 3) {          // gru.c:156-186; columns FUSED: [x.Wh | z | r | h.Uh], XW: [z | r | h.Uh]
-                            float pz, pr, xh, hu;
-                            if (FUSED) { xh = a0[u] + b2[u]; pz = a1[u] + b0[u]; pr = a2[u] + b1[u]; hu = a3[u] + b3[u]; }
-                            else {
-                                const int k = e * 8 + u;
-                                pz = a0[u] + b0[u] + (&xr[0][k >> 2].x)[k & 3]; pr = a1[u] + b1[u] + (&xr[1][k >> 2].x)[k & 3];
-                                hu = a2[u] + b3[u]; xh = (&xr[2][k >> 2].x)[k & 3];
-                            }
+                        if (G == 3) {          // gru.c:156-186; columns [x.Wh | z | r | h.Uh]
+                            const float xh = a0[u] + b2[u], pz = a1[u] + b0[u], pr = a2[u] + b1[u], hu = a3[u] + b3[u];
                             const float z = act_mufu(NNTK_ACT_SIGMOID, pz), r = act_mufu(NNTK_ACT_SIGMOID, pr);
                             const float hh = act_mufu(NNTK_ACT_TANH, fmaf(r, hu, xh));
                             sn[u] = fmaf(z, st[u] - hh, hh);               // (1 - z) hh + z h_{t-1}
                             hn[e * 8 + u] = sn[u];
                         } else {               // lstm.c:199-238; columns [i | f | g | o]
-                            float pi = a0[u] + b0[u], pf = a1[u] + b1[u], pg = a2[u] + b2[u], po = a3[u] + b3[u];
-                            if (!FUSED) {
-                                const int k = e * 8 + u;
-                                pi += (&xr[0][k >> 2].x)[k & 3]; pf += (&xr[1][k >> 2].x)[k & 3];
-                                pg += (&xr[2][k >> 2].x)[k & 3]; po += (&xr[G - 1][k >> 2].x)[k & 3];
-                            }
+                            const float pi = a0[u] + b0[u], pf = a1[u] + b1[u], pg = a2[u] + b2[u], po = a3[u] + b3[u];
                             const float ig = act_mufu(NNTK_ACT_SIGMOID, pi), fg = act_mufu(NNTK_ACT_SIGMOID, pf);
                             const float gg = act_mufu(NNTK_ACT_TANH, pg), og = act_mufu(NNTK_ACT_SIGMOID, po);
                             sn[u] = fmaf(fg, st[u], ig * gg);
                             hn[e * 8 + u] = og * act_mufu(NNTK_ACT_TANH, sn[u]);
                         }
                     }
-                    rf_st8(tl + STATE_COL + (uint32_t)(c * 32 + j * 16 + e * 8), sn);
-                    if (FUSED && G == 3) { const float z8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}; rf_st8(acc + (uint32_t)(96 + e * 8), z8); }
+                    rf_st8(tl + STATE_COL + (uint32_t)(c * 32 + j * UPT + e * 8), sn);
+                    if (G == 3) { const float z8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}; rf_st8(acc + (uint32_t)(96 + e * 8), z8); }
                 }
+                if (!FUSED) xw_store(xn, buf);
                 rf_st_wait();
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) rf_arrive_cl(acc_empty0 + 8u * (uint32_t)buf);       // the accumulator buffer may be overwritten
 #pragma unroll
-                for (int i = 0; i < 8; ++i) hpend[c][i] = rf_pack_sat(hn[2 * i], hn[2 * i + 1]);
+                for (int i = 0; i < UPT / 2; ++i) hpend[c][i] = rf_pack_sat(hn[2 * i], hn[2 * i + 1]);
                 if (p.return_sequences && !RF_SKIP(2)) {
-                    // this warp's [32 rows][16 units] piece of h_t -> its own 2 KB staging tile (SWIZZLE_64B rows) -> one TMA store
-                    // per warp: no CTA-wide barrier in the epilogue (first version: two bar.sync + a store wait per tile)
-                    uint8_t *o = sOut + ew * 2048;
+                    // this warp's [32 rows][UPT units] piece of h_t -> its own staging tile (UPT = 16: 64-byte rows, SWIZZLE_64B; UPT = 8:
+                    // 32-byte rows, unswizzled) -> one TMA store per warp: no CTA-wide barrier in the epilogue (first version: two
+                    // bar.sync + a store wait per tile)
+                    uint8_t *o = sOut + ew * (32 * UPT * 4);
                     { RF_T0(); if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); RF_T1(11); }    // the previous store has read it
                     __syncwarp();
 #pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        *reinterpret_cast<float4 *>(o + lane * 64 + ((i ^ ((lane >> 1) & 3)) << 4)) = make_float4(hn[4 * i], hn[4 * i + 1], hn[4 * i + 2], hn[4 * i + 3]);
+                    for (int i = 0; i < UPT / 4; ++i)
+                        *reinterpret_cast<float4 *>(o + lane * (UPT * 4) + ((UPT == 16 ? (i ^ ((lane >> 1) & 3)) : i) << 4)) =
+                            make_float4(hn[4 * i], hn[4 * i + 1], hn[4 * i + 2], hn[4 * i + 3]);
                     rf_fence_async();
                     __syncwarp();
                     if (lane == 0) {
-                        rf_tma_store_3d(&map_out, o, c * 64 + hf * 32 + j * 16, t, row0 + (q & 1) * 32);
+                        rf_tma_store_3d(&map_out, o, c * 64 + hf * 32 + j * UPT, t, row0 + (q & 1) * 32);
                         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                     }
                 }
@@ -600,8 +620,8 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                         for (int cc = 0; cc < NCMAX; ++cc) {
                             if (cc >= NC) break;
 #pragma unroll
-                            for (int e = 0; e < 2; ++e) {
-                                const int ch = hf * 4 + j * 2 + e;
+                            for (int e = 0; e < NE; ++e) {
+                                const int ch = (hf * 32 + j * UPT) / 8 + e;
                                 *reinterpret_cast<uint4 *>(sAh + (size_t)cc * (RF_ROWS * 128) + m * 128 + ((ch ^ sw) << 4)) =
                                     make_uint4(hpend[cc][4 * e], hpend[cc][4 * e + 1], hpend[cc][4 * e + 2], hpend[cc][4 * e + 3]);
                             }
@@ -613,12 +633,12 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 }
                 if (t == T - 1 && row_ok) {
                     // final state (gru.c:201, lstm.c:264-265): exact fp32 h_T (and c_T from TMEM below)
-                    float *hs = p.h_state + (size_t)row * H + c * 64 + hf * 32 + j * 16;
+                    float *hs = p.h_state + (size_t)row * H + c * 64 + hf * 32 + j * UPT;
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
+                    for (int i = 0; i < UPT / 4; ++i) {
                         const float4 v = make_float4(hn[4 * i], hn[4 * i + 1], hn[4 * i + 2], hn[4 * i + 3]);
                         *reinterpret_cast<float4 *>(hs + 4 * i) = v;
-                        if (!p.return_sequences) *reinterpret_cast<float4 *>(p.out + (size_t)row * H + c * 64 + hf * 32 + j * 16 + 4 * i) = v;
+                        if (!p.return_sequences) *reinterpret_cast<float4 *>(p.out + (size_t)row * H + c * 64 + hf * 32 + j * UPT + 4 * i) = v;
                     }
                 }
             }
@@ -627,12 +647,12 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
             tc_fence_after();
             for (int c = 0; c < NC; ++c)
 #pragma unroll
-                for (int e = 0; e < 2; ++e) {
+                for (int e = 0; e < NE; ++e) {
                     float sv[8];
-                    rf_ld8(tl + STATE_COL + (uint32_t)(c * 32 + j * 16 + e * 8), sv);
+                    rf_ld8(tl + STATE_COL + (uint32_t)(c * 32 + j * UPT + e * 8), sv);
                     rf_ld_wait();
                     if (row_ok) {
-                        float *cs = p.c_state + (size_t)row * H + c * 64 + hf * 32 + j * 16 + e * 8;
+                        float *cs = p.c_state + (size_t)row * H + c * 64 + hf * 32 + j * UPT + e * 8;
                         *reinterpret_cast<float4 *>(cs) = make_float4(sv[0], sv[1], sv[2], sv[3]);
                         *reinterpret_cast<float4 *>(cs + 4) = make_float4(sv[4], sv[5], sv[6], sv[7]);
                     }
@@ -816,13 +836,13 @@ extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, c
     if (fused) { if ((rc = enc2(&mw, Wp, IN))) return rc; } else mw = mu;
     if (Wl) { if ((rc = enc2(&mwl, Wl, IN))) return rc; } else mwl = mu;
     if (r->return_sequences) {
-        // per-warp [32 rows][16 floats] pieces of h_t, SWIZZLE_64B
+        // per-warp pieces of h_t: FUSED [32 rows][16 floats] (SWIZZLE_64B), XW [32 rows][8 floats] (unswizzled)
         cuuint64_t dims[3] = {(cuuint64_t)H, (cuuint64_t)T, (cuuint64_t)nb};
         cuuint64_t strides[2] = {(cuuint64_t)H * 4, (cuuint64_t)T * H * 4};
-        cuuint32_t box[3] = {16, 1, 32};
+        cuuint32_t box[3] = {(cuuint32_t)(fused ? 16 : 8), 1, 32};
         cuuint32_t es[3] = {1, 1, 1};
         CUresult cr = encode(&mo, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, out, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                             CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                             fused ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (cr != CUDA_SUCCESS) { nntk_cuda_set_error(NNTK_ERR_CUDA_, "recurrent_fused: output tensor map rejected (CUresult %d)", (int)cr); return NNTK_ERR_CUDA_; }
     } else mo = mu;
     p.B = nb; p.T = T; p.return_sequences = r->return_sequences;
