@@ -254,7 +254,10 @@ def build_c5(env, units, with_input=True):
     tdd_bytes = 4.0 * units * T1 * (256 + 12)
     tmode = env.args.mode != "fp32"
     if fused_front:
-        stages = [("spectrogram+BN+conv+ReLU (fused front end)", front, dict(bound="tensor" if tmode else "ffma", flop=conv_flop, kind="tf32"))]
+        stages = [("spectrogram+BN+conv+ReLU (fused front end)", front,
+                   dict(bound="tensor" if tmode else "ffma", flop=conv_flop, kind="tf32", bytes=4.0 * units * (CLIP_N + T1 * 256), kernels=2,
+                        note="two kernels: K1 at the conv's row pitch (HBM-bound) + the implicit GEMM (tensor-bound); "
+                             "profiles/r2_launches_c5.csv: 3.8 ms + 8.9 ms at 8 192 clips"))]
     else:
         stages = [("spectrogram", lambda: spec.apply_batch(x, s), dict(bound="hbm", bytes=spec_bytes)),
                   ("batchnorm", lambda: bn.apply_batch(s, s), dict(bound="hbm", bytes=8.0 * units * T0 * F)),
@@ -417,6 +420,8 @@ def stage_report(env, stages, ms):
         else:
             r.update(algorithmic_flop=w["flop"], achieved=w["flop"] / (t * 1e-3) / 1e12, unit="TFLOP/s", peak=None)
         r["frac"] = (r["achieved"] / r["peak"]) if r.get("peak") else None
+        if "kernels" in w:
+            r["kernels"] = w["kernels"]; r["note"] = w["note"]
         out.append(r)
     return out
 
@@ -581,8 +586,9 @@ def run_workload(env, name, steps, warmup, clk=None, with_e2e=False, with_stages
 
 
 def pick_roofline(env, res):
-    """the dominant kernel stage by CUDA-event share of the step"""
-    st = max(res["stages"], key=lambda s: s["ms"])
+    """the dominant KERNEL by CUDA-event share of the step: stages that are one kernel launch compete with their full time, a stage
+    made of several kernels with its time per kernel (its split is in the committed ncu launch list)"""
+    st = max(res["stages"], key=lambda s: s["ms"] / s.get("kernels", 1))
     share = st["ms"] / sum(s["ms"] for s in res["stages"])
     traffic, kernel = traffic_for(res["workload"], st["stage"], res["units_per_gpu"])
     if st["bound"] == "hbm":

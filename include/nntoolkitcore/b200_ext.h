@@ -64,7 +64,8 @@ const char *NNTKDebugLastRecurrentPath(void);
 #define NNTK_MATH_TF32 1    /* tcgen05 kind::tf32, operands rounded to 10-bit mantissa; 1e-3 */
 #define NNTK_MATH_TF32X3 2  /* tcgen05, hi/lo operand split, 3 MMAs per product, accumulate truncation compensated: holds the
                                fp32 contract (1e-5) at ~1/3 of the TF32 rate (recurrent steps too, for batches above
-                               256); reduction lengths above 3 072 stay on FFMA */
+                               256); reduction lengths above 1 536 stay on FFMA (the truncating
+                               accumulate of the tensor core: csrc/gemm.cu) */
 int NNTKSetMathMode(int mode);
 int NNTKGetMathMode(void);
 

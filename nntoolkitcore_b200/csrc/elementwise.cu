@@ -23,8 +23,11 @@ __device__ __forceinline__ void st_stream(float4 *p, float4 v) {
 // element only in the sense of the reference's op order: x_mu / sd with an IEEE divide (batch_norm.c:151-162).
 // VEC: C % 4 == 0 and 16-byte aligned pointers.
 template <bool VEC>
+// The data pointers of every kernel in this file are NOT __restrict__ and are never read through the non-coherent path: the
+// reference allows input == output for BatchNorm and the activations, and the library itself calls them in place (Dense softmax,
+// the unfused log-mel tail).
 __global__ void __launch_bounds__(256) batch_norm_kernel(const float *__restrict__ prm, int C, float eps,
-                                                         const float *__restrict__ in, float *__restrict__ out,
+                                                         const float *in, float *out,
                                                          long long total) {
     const float *gamma = prm, *beta = prm + C, *mean = prm + 2 * C, *var = prm + 3 * C;
     const long long stride = (long long)gridDim.x * blockDim.x;
@@ -48,14 +51,13 @@ __global__ void __launch_bounds__(256) batch_norm_kernel(const float *__restrict
     } else {
         for (; i < total; i += stride) {
             const int c = (int)(i % C);
-            out[i] = nntk_bn(__ldg(in + i), __ldg(gamma + c), __ldg(beta + c), __ldg(mean + c), __ldg(var + c), eps);
+            out[i] = nntk_bn(in[i], __ldg(gamma + c), __ldg(beta + c), __ldg(mean + c), __ldg(var + c), eps);
         }
     }
 }
 
 template <bool VEC>
-__global__ void __launch_bounds__(256) activation_kernel(int kind, float a, const float *__restrict__ in,
-                                                         float *__restrict__ out, long long total) {
+__global__ void __launch_bounds__(256) activation_kernel(int kind, float a, const float *in, float *out, long long total) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (VEC) {
@@ -77,8 +79,7 @@ __global__ void __launch_bounds__(256) activation_kernel(int kind, float a, cons
 // softmax without max-subtraction, exactly the reference's definition (activation_default.c:149-167):
 // e_j = expf(x_j); y_j = e_j / sum(e).  One warp per vector; the sum is a lane-strided partial + shuffle tree
 // (the reference sums sequentially: results agree to rounding, not bit-for-bit).
-__global__ void __launch_bounds__(256) softmax_kernel(int V, const float *__restrict__ in, float *__restrict__ out,
-                                                      long long n_vec) {
+__global__ void __launch_bounds__(256) softmax_kernel(int V, const float *in, float *out, long long n_vec) {
     const int lane = threadIdx.x & 31;
     const long long warps = ((long long)gridDim.x * blockDim.x) >> 5;
     for (long long r = (((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5); r < n_vec; r += warps) {
@@ -92,10 +93,12 @@ __global__ void __launch_bounds__(256) softmax_kernel(int V, const float *__rest
             for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
             if (lane < V) y[lane] = e / s;
         } else {
+            // in-place safe: a lane only ever rereads elements it alone writes (j = lane + 32 i), and the sum is complete
+            // before the first write
             for (int j = lane; j < V; j += 32) s += expf(x[j]);
 #pragma unroll
             for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            for (int j = lane; j < V; j += 32) y[j] = expf(x[j]) / s;
+            for (int j = lane; j < V; j += 32) { const float e = expf(x[j]); y[j] = e / s; }
         }
     }
 }
@@ -208,8 +211,7 @@ extern "C" int nntk_cuda_activation(int kind, float relu_a, int vector_size, con
 
 // out = logf(in + offset): the tail of the unfused log-mel chain (signal/log_mel_spectrogram.c:36-37)
 namespace {
-__global__ void __launch_bounds__(256) log_offset_kernel(const float *__restrict__ in, float *__restrict__ out, long long n,
-                                                         float offset) {
+__global__ void __launch_bounds__(256) log_offset_kernel(const float *in, float *out, long long n, float offset) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = logf(in[i] + offset);
 }
@@ -252,7 +254,7 @@ __global__ void __launch_bounds__(256) bd_concat_kernel(const V *__restrict__ fw
         out[i] = c < cols ? fwd[row * cols + c] : bwd[row * cols + (c - cols)];
     }
 }
-__global__ void __launch_bounds__(256) bd_sum_kernel(const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ out, long long n) {
+__global__ void __launch_bounds__(256) bd_sum_kernel(const float *a, const float *b, float *out, long long n) {      // out may alias a or b
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = a[i] + b[i];
 }

@@ -491,7 +491,7 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     // It is the planned path when neither cluster kernel can hold the shape (H > 256 or H % 32 != 0) and the batch is large.
     const bool step_tc = mode == 1 && G != 1 && !h16 && nb > 256 && (H > 256 || (H & 31)) && (H & 3) == 0 && (GH & 31) == 0;
     // TF32X3 mode (fp32 contract on the tensor cores): large batches run the same per-step kernel with hi/lo split operands
-    const bool step_x3 = mode == 2 && G != 1 && nb > 256 && (H & 3) == 0 && (GH & 31) == 0 && H <= 3072 && r->in <= 3072;
+    const bool step_x3 = mode == 2 && G != 1 && nb > 256 && (H & 3) == 0 && (GH & 31) == 0 && H <= 1536 && r->in <= 1536;
     // the blocked layout rounds the chunk up to 32 sequences: only when that (plus the ping-pong buffers) fits this workspace
     const bool blocked_fits = ((size_t)((nb + 31) / 32 * 32) * T * GH + (size_t)6 * nb * H) * sizeof(float) <= work_bytes;
     if ((h16 || step_tc || step_x3 || fplan == 2) && blocked_fits && (((uintptr_t)xw) & 15) == 0) {

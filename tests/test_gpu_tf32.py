@@ -160,7 +160,7 @@ def x3(cuda, product):
 
 @pytest.mark.parametrize("cin,cout,k,s,T,B", [(128, 256, 5, 1, 300, 3), (64, 96, 3, 2, 257, 2), (256, 256, 5, 1, 130, 2),
                                               (16, 8, 1, 1, 40, 1), (20, 40, 3, 1, 50, 2), (257, 64, 5, 1, 60, 2),
-                                              (512, 256, 5, 1, 40, 2), (1024, 128, 7, 1, 30, 1)])   # K = 2 560; 7 168 (> 3 072: FFMA)
+                                              (512, 256, 5, 1, 40, 2), (1024, 128, 7, 1, 30, 1)])   # K = 2 560 and 7 168: above the 3xTF32 cap (1 536), FFMA
 def test_conv1d_3xtf32(x3, ref, cin, cout, k, s, T, B):
     rng = np.random.default_rng(3)
     x = rng.standard_normal((B, T, cin)).astype(np.float32)
