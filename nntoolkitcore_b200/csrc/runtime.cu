@@ -13,7 +13,7 @@ std::atomic<long long> g_launches{0};
 int g_device = -1;            // -1: not initialised
 int g_sm_count = 0;
 cudaStream_t g_stream = 0;    // legacy default stream unless the caller sets one
-int g_math_mode = 0;
+int g_math_mode = 2;            // NNTK_MATH_TF32X3: the fp32 contract (1e-5) on the tensor cores, FFMA above its K cap (b200_ext.h)
 bool g_math_mode_set = false;
 thread_local char t_err[512] = {0};
 thread_local int t_err_code = 0;

@@ -35,7 +35,7 @@ def rec(cell, in_size, H, T, B, mode, tol, env=None, seq=True):
     want = np.stack([port_cases.recurrent(port, cell, in_size, H, T, seq, True, w, x[i]) for i in pick])
     err, l2 = helpers.assert_parity(got[pick].cpu().numpy(), want, tol=tol, what=f"{cell} {in_size}->{H} T{T} B{B} mode {mode}")
     print(f"ok {cell} in={in_size} H={H} T={T} B={B} mode={mode} path={path} err={err:.2e}", flush=True)
-    r.close(); lib.NNTKSetMathMode(0)
+    r.close(); lib.NNTKSetMathMode(2)
 
 
 rec("gru", 24, 64, 6, 5, 0, 1e-5)                       # fp32 DSMEM cluster kernel (2 CTAs)
@@ -62,7 +62,7 @@ want = port_cases.batch_norm(port, F, 1e-3, bn.gamma, bn.beta, bn.mean, bn.var, 
 want = np.maximum(port_cases.conv(port, F, 64, 5, 1, T0, conv.W, conv.b, want), 0)
 helpers.assert_parity(f.cpu().numpy(), want, tol=1e-3, what="fused front end")
 print("ok fused front end", flush=True)
-lib.NNTKSetMathMode(0)
+lib.NNTKSetMathMode(2)
 big = np.stack([helpers.audio_clip(i % 4, 160000) for i in range(40)])          # 40 x (0.64 + 1.02) MB: several staging chunks
 s2 = L.Spectrogram(lib, 512, 512, 352, 160000, 1.0, "hann_window")
 out = s2.apply_batch(big)

@@ -14,6 +14,7 @@ REF_SO = ORACLE / "_ref" / "libnntk_ref.so"
 PORT_SO = ORACLE / "liboracle_port.so"
 FP32_TOL = 1e-5   # north_star: fp32 path within 1e-5 relative
 TF32_TOL = 1e-3   # north_star: TF32/bf16 tensor-core path within 1e-3
+DEFAULT_MATH_MODE = int(__import__("os").environ.get("NNTK_MATH_MODE", "2"))   # the library's process default (b200_ext.h)
 
 _ref = _port = None
 

@@ -29,7 +29,7 @@ ROOT = Path(__file__).resolve().parent.parent
 def tf32(cuda, product):
     assert product.NNTKSetMathMode(1) == 0
     yield product
-    product.NNTKSetMathMode(0)
+    product.NNTKSetMathMode(helpers.DEFAULT_MATH_MODE)
 
 
 def _path(lib):
@@ -157,16 +157,17 @@ def test_fused_front_end_matches_reference_chain(cuda, product, ref, mode, tol, 
         got_host = L.front_end(product, ps, pb, pcv, pobn if out_bn else None, prelu, x)
         assert np.array_equal(got_host, got_dev.cpu().numpy()), "host-buffer path differs from the device-buffer path"
     finally:
-        product.NNTKSetMathMode(0)
+        product.NNTKSetMathMode(helpers.DEFAULT_MATH_MODE)
 
 
-def test_fp32_contract_suite_holds_under_3xtf32_default():
-    """NNTK_MATH_MODE=2 as the process default: every test written for the FFMA path at 1e-5 must pass on the split-operand
-    tensor-core path too -- except the one that demands bit-exact copies through a delta kernel (FFMA-only property)"""
-    env = dict(os.environ, NNTK_MATH_MODE="2")
+@pytest.mark.parametrize("mode", ["0", "2"])
+def test_fp32_contract_suite_in_both_fp32_contract_modes(mode):
+    """The 1e-5 suite (parity / layers / next rows) must hold in BOTH modes that promise the fp32 contract: NNTK_MATH_MODE=2 (3xTF32
+    on tcgen05, the library default) and NNTK_MATH_MODE=0 (FFMA).  The in-process run of those files covers whatever the default is;
+    this re-runs them with the mode forced through the environment so that neither path can rot."""
+    env = dict(os.environ, NNTK_MATH_MODE=mode)
     cmd = [sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu", "-p", "no:cacheprovider",
-           str(ROOT / "tests" / "test_gpu_parity.py"), str(ROOT / "tests" / "test_gpu_layers.py"), str(ROOT / "tests" / "test_gpu_next.py"),
-           "-k", "not delta_kernel_is_shifted_copy"]
+           str(ROOT / "tests" / "test_gpu_parity.py"), str(ROOT / "tests" / "test_gpu_layers.py"), str(ROOT / "tests" / "test_gpu_next.py")]
     r = subprocess.run(cmd, env=env, capture_output=True, text=True, cwd=str(ROOT), timeout=1500)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1500:]
 

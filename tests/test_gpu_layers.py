@@ -69,7 +69,12 @@ def test_conv1d_delta_kernel_is_shifted_copy(cuda, product):
         c.W[ch, ch, 1] = 1.0
     c.b[:] = np.arange(cout, dtype=np.float32)
     x = np.random.default_rng(1).standard_normal((1, 20, cin)).astype(np.float32)
-    out = c.apply_batch(x)
+    # bit-exact copies are a property of the FFMA kernel (NNTK_MATH_FP32); the tensor-core modes round through their operand split
+    assert product.NNTKSetMathMode(0) == 0
+    try:
+        out = c.apply_batch(x)
+    finally:
+        product.NNTKSetMathMode(helpers.DEFAULT_MATH_MODE)
     assert np.array_equal(out[0], x[0, 1:19] + c.b)
     c.close()
 

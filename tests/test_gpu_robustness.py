@@ -112,7 +112,7 @@ def test_tensor_core_compensation_outside_the_zero_mean_regime(cuda, product, re
     try:
         got = c_new.apply_batch(x)
     finally:
-        product.NNTKSetMathMode(0)
+        product.NNTKSetMathMode(helpers.DEFAULT_MATH_MODE)
     assert_parity(got, want, tol=tol, what=f"conv, non-negative operands, K = {cin * k}, mode {mode}")
 
 

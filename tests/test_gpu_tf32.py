@@ -14,7 +14,7 @@ pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300)]
 def tf32(cuda, product):
     assert product.NNTKSetMathMode(1) == 0
     yield product
-    product.NNTKSetMathMode(0)
+    product.NNTKSetMathMode(helpers.DEFAULT_MATH_MODE)
 
 
 @pytest.mark.parametrize("cin,cout,k,s,T,B", [(128, 256, 5, 1, 300, 3), (64, 96, 3, 2, 257, 2), (256, 256, 5, 1, 130, 2),
@@ -155,7 +155,7 @@ X3_TOL = helpers.FP32_TOL
 def x3(cuda, product):
     assert product.NNTKSetMathMode(2) == 0
     yield product
-    product.NNTKSetMathMode(0)
+    product.NNTKSetMathMode(helpers.DEFAULT_MATH_MODE)
 
 
 @pytest.mark.parametrize("cin,cout,k,s,T,B", [(128, 256, 5, 1, 300, 3), (64, 96, 3, 2, 257, 2), (256, 256, 5, 1, 130, 2),
