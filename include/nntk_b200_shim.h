@@ -194,6 +194,8 @@ size_t nntk_cuda_recurrent_workspace(const nntk_recurrent_args *r);
 /* name of the kernel family that ran the most recent recurrent chunk: "fused_tc", "cluster_h16", "cluster_tf32", "cluster_fp32",
  * "step_tc_f16", "step_tc_x3", "step_fp32" (diagnostics; tests pin the dispatch at the BASELINE shapes with it) */
 const char *nntk_cuda_last_recurrent_path(void);
+/* input passes (1 or 3) the most recent fused recurrent launch took after its adaptive pre-scan; synchronises (tests only) */
+int nntk_cuda_last_recurrent_xpasses(void);
 int nntk_cuda_recurrent(const nntk_recurrent_args *r);
 
 #ifdef __cplusplus

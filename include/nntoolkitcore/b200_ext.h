@@ -58,6 +58,7 @@ void NNTKClearError(void);
 long long NNTKDebugLaunchCount(void);
 /* Which recurrent kernel family served the most recent RNN/GRU/LSTM Apply (see nntk_b200_shim.h). */
 const char *NNTKDebugLastRecurrentPath(void);
+int NNTKDebugLastRecurrentInputPasses(void);   /* 1 or 3: fp16 passes the fused recurrent kernel took for x.W (synchronises) */
 
 /* GEMM-shaped stages (Conv1d, Dense/TDD, recurrent projections and steps) can run in three math modes. */
 #define NNTK_MATH_FP32 0    /* FFMA on CUDA cores; matches the reference within 1e-5 */

@@ -167,7 +167,7 @@ REFERENCE_API = {
 EXT_API = {
     "NNTKInit": (c_int, [c_int]), "NNTKSetStream": (c_int, [c_void_p]), "NNTKGetStream": (c_void_p, []),
     "NNTKSynchronize": (c_int, []), "NNTKLastError": (c_char_p, []), "NNTKClearError": (None, []),
-    "NNTKDebugLaunchCount": (C.c_longlong, []), "NNTKDebugLastRecurrentPath": (c_char_p, []),
+    "NNTKDebugLaunchCount": (C.c_longlong, []), "NNTKDebugLastRecurrentPath": (c_char_p, []), "NNTKDebugLastRecurrentInputPasses": (c_int, []),
     "NNTKSetMathMode": (c_int, [c_int]), "NNTKGetMathMode": (c_int, []),
     "NNTKDeviceAlloc": (c_void_p, [c_size_t]), "NNTKDeviceFree": (None, [c_void_p]),
     "NNTKHostAlloc": (c_void_p, [c_size_t]), "NNTKHostFree": (None, [c_void_p]),
@@ -207,7 +207,7 @@ SHIM_SYMBOLS = [
     "nntk_cuda_batch_norm", "nntk_cuda_activation", "nntk_cuda_gemm", "nntk_cuda_pack_conv_weights",
     "nntk_cuda_pack_conv_weights_padded", "nntk_cuda_pad_channels", "nntk_cuda_pack_conv_weights_bn",
     "nntk_cuda_spectrogram_pitched",
-    "nntk_cuda_recurrent_workspace", "nntk_cuda_recurrent", "nntk_cuda_last_recurrent_path",
+    "nntk_cuda_recurrent_workspace", "nntk_cuda_recurrent", "nntk_cuda_last_recurrent_path", "nntk_cuda_last_recurrent_xpasses",
 ]
 
 

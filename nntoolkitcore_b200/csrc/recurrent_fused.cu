@@ -50,7 +50,9 @@ struct RfParams {
     int B, H, in, T;
     int return_sequences;
     int ring_stages;
-    int xp;                          // FUSED: input passes, 1 or 3
+    int xp;                          // FUSED: input passes the launch is PLANNED for (shared memory, packed operands), 1 or 3
+    const float *stats;              // adaptive input passes: {max_rows |x_t|^2, max_cols |W_n|^2, passes taken (written by the kernel)}
+    float adapt_thr;                 //   3 planned passes drop to 1 when sqrt(stats[0] * stats[1]) <= adapt_thr (see rf_xpasses_note)
     int cs;                          // cluster size: 2, 4 or 8 CTAs = 1, 2 or 4 pairs sharing every B stage by TMA multicast
     int xw_blocked_rows;             // XW mode: row_blocks of the blocked projection
     const float *x;                  // FUSED: [B][T][in]
@@ -182,12 +184,17 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     constexpr int ROWS_B = 32 * G;                          // B rows per CTA per k-block
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    const int H = p.H, IN = p.in, T = p.T, XP = p.xp;
+    // Input passes actually taken.  The two correction passes (x_hi . W_lo, x_lo . W_hi) exist because fp16-rounded x and W put
+    // ~2^-12 * sqrt(2/3) * |x_t| * |W_n| / ... of noise into every pre-activation of every step; when a pre-scan of this call's x
+    // and W bounds |x_t| |W_n| by adapt_thr that noise stays ~4x under the mode's 1e-3 and the passes are skipped (rf_xpasses_note).
+    // Every role of every CTA evaluates the same two numbers, so the whole grid takes the same branch.
+    const int XP = (p.xp == 3 && p.stats && sqrtf(__ldg(p.stats) * __ldg(p.stats + 1)) <= p.adapt_thr) ? 1 : p.xp;
+    const int H = p.H, IN = p.in, T = p.T;
     const int NC = H / RF_UT;                               // tiles per step
     const int KBH = H / 64, KBX = FUSED ? IN / 64 : 0;      // k-blocks of the recurrent / input part
     const int NB = (512 - H / 2) / 128;                     // accumulator buffers (3 for H <= 256, 2 for H = 512)
     const uint32_t STATE_COL = (uint32_t)(NB * 128);
-    const RfPlan<G, FUSED> pl(H, IN, XP, p.ring_stages);
+    const RfPlan<G, FUSED> pl(H, IN, p.xp, p.ring_stages);
     uint8_t *sAh = smem + pl.a_h, *sXh = smem + pl.x_hi, *sXl = smem + pl.x_lo, *sOut = smem + pl.out_stg, *sRing = smem + pl.ring;
     float *sBias = reinterpret_cast<float *>(smem + pl.bias);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + pl.bars);
@@ -207,6 +214,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     // tile counters are 32-bit and advanced incrementally everywhere: 64-bit divisions in the issuer's loop cost ~13 000 cycles per
     // step in the first version (more than all of the step's MMAs)
 
+    if (tid == 0 && blockIdx.x == 0 && p.stats) const_cast<float *>(p.stats)[2] = (float)XP;
     if (tid == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_wl) : "memory");
@@ -688,6 +696,35 @@ __global__ void rf_pack_kernel(const float *__restrict__ W, __half *__restrict__
     }
 }
 
+// rf_xpasses_note -- adaptive input passes.  Measured (tests, emulation): with ONE fp16 pass a GRU 256 -> 256 on N(0,1) inputs
+// (|x_t| |W_n| ~ 18) drifts to 1.2e-3 max error after 300 steps; the C5 layers (|x_t| |W_n| = 1.7 and 2.3: post-ReLU features, h in
+// [-1, 1]) stay at 1.3e-4 / 2.1e-4 after 994.  The error is linear in that product, so a bound of 5 keeps the single-pass noise
+// near 3e-4, below the recurrent part's own fp16 rounding.  The scan below reads x once (HBM-bound, ~1.3 ms for 8.3 GB) and saves
+// two of the four tensor-core passes (4 ms per C5 layer).
+__global__ void rf_xnorm_kernel(const float *__restrict__ x, long long rows, int in, float *stats) {
+    const int lane = threadIdx.x & 31;
+    const long long warps = ((long long)gridDim.x * blockDim.x) >> 5;
+    float best = 0.0f;
+    for (long long r = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < rows; r += warps) {
+        const float4 *p = reinterpret_cast<const float4 *>(x + r * in);
+        float s = 0.0f;
+        for (int i = lane; i < (in >> 2); i += 32) { const float4 v = __ldg(p + i); s = fmaf(v.x, v.x, fmaf(v.y, v.y, fmaf(v.z, v.z, fmaf(v.w, v.w, s)))); }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        best = fmaxf(best, s);          // NaN / Inf inputs: fmaxf drops NaN, Inf stays -> 3 passes
+    }
+    if (lane == 0) atomicMax(reinterpret_cast<int *>(stats), __float_as_int(best));      // non-negative floats order like ints
+}
+__global__ void rf_wnorm_kernel(const float *__restrict__ W, int in, int cols, float *stats) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    float s = 0.0f;
+    if (n < cols) for (int k = 0; k < in; ++k) { const float w = __ldg(W + (long long)k * cols + n); s = fmaf(w, w, s); }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) s = fmaxf(s, __shfl_xor_sync(0xffffffffu, s, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(reinterpret_cast<int *>(stats + 1), __float_as_int(s));
+}
+float *g_rf_stats = nullptr;
+
 __half *g_rf_scratch = nullptr;
 size_t g_rf_halves = 0;
 
@@ -758,6 +795,14 @@ extern "C" int nntk_cuda_recurrent_fused_plan(const nntk_recurrent_args *r, int 
         if (stages >= 3) return 1;
     }
     return 2;
+}
+
+// input passes the most recent FUSED launch actually took (1 or 3; 0: none ran).  Synchronises the stream: diagnostics / tests only.
+extern "C" int nntk_cuda_last_recurrent_xpasses(void) {
+    if (!g_rf_stats) return 0;
+    float v[4] = {0, 0, 0, 0};
+    if (cudaStreamSynchronize(nntk_stream()) != cudaSuccess || cudaMemcpy(v, g_rf_stats, sizeof(v), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    return (int)v[2];
 }
 
 // Runs all T steps of one batch chunk in ONE launch.  xw: the blocked hoisted projection (XW mode) or null (FUSED mode).
@@ -849,6 +894,23 @@ extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, c
     p.x = x; p.bias_i = r->d_bi;
     p.bias_h = ((G == 3) || r->v2) ? r->d_bh : nullptr;
     p.xw = xw; p.xw_blocked_rows = (nb + 31) / 32;
+    static int adaptive = -1;
+    static float adapt_thr = 5.0f;
+    if (adaptive < 0) {
+        const char *e = getenv("NNTK_RECURRENT_X_ADAPTIVE"); adaptive = e ? atoi(e) : 1;
+        if ((e = getenv("NNTK_RECURRENT_X_ADAPT_THR"))) adapt_thr = (float)atof(e);
+    }
+    if (!g_rf_stats) NNTK_CUDA_TRY(cudaMalloc(&g_rf_stats, 4 * sizeof(float)));
+    NNTK_CUDA_TRY(cudaMemsetAsync(g_rf_stats, 0, 4 * sizeof(float), st));
+    p.stats = g_rf_stats; p.adapt_thr = adapt_thr;
+    if (fused && xp == 3 && adaptive && (IN & 3) == 0) {
+        const long long rows = (long long)nb * T;
+        rf_xnorm_kernel<<<148 * 8, 256, 0, st>>>(x, rows, IN, g_rf_stats);
+        rf_wnorm_kernel<<<(G * H + 255) / 256, 256, 0, st>>>(r->d_W, IN, G * H, g_rf_stats);
+        NNTK_LAUNCH_CHECK_N("rf_xnorm_kernel", 2);
+    } else if (fused && xp == 3) {
+        p.adapt_thr = -1.0f;          // never satisfied: all three passes
+    }
     p.h_state = h; p.c_state = c; p.out = out;
     static int want_dbg = -1;
     if (want_dbg < 0) { const char *e = getenv("NNTK_RF_DBG"); want_dbg = e ? atoi(e) : 0; }

@@ -82,6 +82,7 @@ const char *NNTKLastError(void) { return nntk_cuda_last_error(); }
 void NNTKClearError(void) { nntk_cuda_clear_error(); }
 long long NNTKDebugLaunchCount(void) { return nntk_cuda_launch_count(); }
 const char *NNTKDebugLastRecurrentPath(void) { return nntk_cuda_last_recurrent_path(); }
+int NNTKDebugLastRecurrentInputPasses(void) { return nntk_cuda_last_recurrent_xpasses(); }
 int NNTKSetMathMode(int mode) { NNTK_API_GUARD(); return nntk_cuda_set_math_mode(mode); }
 int NNTKGetMathMode(void) { return nntk_cuda_math_mode(); }
 void *NNTKDeviceAlloc(size_t bytes) { void *p = NULL; return nntk_cuda_malloc(&p, bytes) ? NULL : p; }
