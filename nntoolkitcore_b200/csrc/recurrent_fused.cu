@@ -48,6 +48,7 @@ constexpr int RF_MAX_RING = 8;
 
 struct RfParams {
     int B, H, in, T;
+    int rows;                        // real sequences per CTA: 64, or 32 (half-filled M tile, twice the pairs: for batches that would leave SMs idle)
     int return_sequences;
     int ring_stages;
     int xp;                          // FUSED: input passes the launch is PLANNED for (shared memory, packed operands), 1 or 3
@@ -206,11 +207,12 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     // epilogue also adds the hoisted projection and, with 8 warps, took 4 700 cycles per LSTM-512 tile against 2 064 of MMA.
     constexpr int EPW = FUSED ? 8 : 16, UPT = 128 / EPW, NE = UPT / 8;
     constexpr int CONV_W0 = 8, CTRL_W0 = 16;                 // first converter / control warp
-    const uint32_t crank = rf_rank();                       // rank in the cluster; pairs are (0,1), (2,3), ...
+    const uint32_t crank = __shfl_sync(0xffffffffu, rf_rank(), 0);   // rank in the cluster (warp-uniform for the compiler); pairs are (0,1), (2,3), ...
     const uint32_t rank = crank & 1u, leader = crank & ~1u; // rank inside the pair, cluster rank of the pair's leader
     const int npairs = p.cs >> 1, pair_i = (int)(crank >> 1);
     const uint16_t pair_mask = (uint16_t)(3u << leader), all_mask = (uint16_t)((1u << p.cs) - 1u);
-    const int row0 = (blockIdx.x >> 1) * 128 + (int)rank * RF_ROWS;      // first sequence of this CTA
+    const int row0 = ((blockIdx.x >> 1) * 2 + (int)rank) * p.rows;       // first sequence of this CTA
+    const int EPA = p.rows == RF_ROWS ? EPW : EPW / 2;      // epilogue warps with real rows (32-row mode: lane quarters 0 and 2 only)
     // tile counters are 32-bit and advanced incrementally everywhere: 64-bit divisions in the issuer's loop cost ~13 000 cycles per
     // step in the first version (more than all of the step's MMAs)
 
@@ -221,8 +223,8 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_u) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_out) : "memory");
         for (int s = 0; s < p.ring_stages; ++s) { mbar_init(bars + RFB_RING_FULL + s, 1); mbar_init(bars + RFB_RING_EMPTY + s, (uint32_t)npairs); }
-        for (int b = 0; b < 4; ++b) { mbar_init(bars + RFB_ACC_FULL + b, 1); mbar_init(bars + RFB_ACC_EMPTY + b, 2 * EPW); }
-        mbar_init(bars + RFB_H_FULL, 2 * EPW);
+        for (int b = 0; b < 4; ++b) { mbar_init(bars + RFB_ACC_FULL + b, 1); mbar_init(bars + RFB_ACC_EMPTY + b, 2 * EPA); }
+        mbar_init(bars + RFB_H_FULL, 2 * EPA);
         mbar_init(bars + RFB_X_FULL, 16);
         for (int b = 0; b < 4; ++b) mbar_init(bars + RFB_XL_FULL + b, 16);
         mbar_init(bars + RFB_X_EMPTY, 1);
@@ -246,6 +248,11 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         }
         sBias[i] = v;
     }
+    if (p.rows < RF_ROWS) {
+        // 32-row mode: rows 32..63 of every A tile never receive data; give the MMA zeros instead of stale shared memory
+        for (int i = tid; i < (pl.out_stg >> 4); i += (int)blockDim.x) reinterpret_cast<uint4 *>(smem)[i] = make_uint4(0u, 0u, 0u, 0u);
+        rf_fence_async();
+    }
     tc_fence_before();
     __syncthreads();
     rf_cluster_sync();               // both CTAs' barriers exist before anybody arrives remotely
@@ -259,8 +266,12 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     if (warp >= CTRL_W0) {
         if (FUSED) asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
         else asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-        if (warp == CTRL_W0 && lane == 0) {
+        if (warp == CTRL_W0) {
             // ===== ring producer: this CTA's half of every B stage (two k-blocks), in the order the MMA issuer consumes them =====
+            // Like the MMA issuer the WHOLE warp runs the loop converged on warp-uniform values and only the TMA / expect_tx
+            // instructions are predicated on elect.sync: issued from one divergent lane every UTMALDG sat in an ELECT / 4 x
+            // R2UR.BROADCAST / BRA loop (measured with the kernel's counters: ~180 cycles per TMA, 5 700 of a step's 16 200 cycles,
+            // and the step time did not move when MMAs, cell math or stores were switched off: the ring was the floor).
             int stage = 0; uint32_t phase = 0;
             // Every B stage is identical for all pairs of the cluster: this CTA fetches 1 / npairs of the rows of its half and
             // multicasts them to the CTAs of the same half in every pair (L2 -> SM traffic / npairs: with 128 CTAs each pulling its own
@@ -273,10 +284,13 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
             auto put = [&](const CUtensorMap *map, int kb0, int nkb, int tile) {
                 { RF_T0(); mbar_wait(bars + RFB_RING_EMPTY + stage, phase ^ 1); RF_T1(8); }
                 RF_T0();
-                if (rank == 0) mbar_expect_tx(bars + RFB_RING_FULL + stage, 2u * (uint32_t)(nkb * pl.sub_bytes));
-                for (int i = 0; i < nkb; ++i)
-                    rf_tma_2d_cg2_mc(ring_a + (uint32_t)(stage * pl.stage_bytes + i * pl.sub_bytes + pair_i * slice_rows * 128), map,
-                                     full_l + 8u * (uint32_t)stage, (kb0 + i) * 64, (tile * 2 + (int)rank) * ROWS_B + pair_i * slice_rows, half_mask);
+                if (rf_elect()) {
+                    if (rank == 0) mbar_expect_tx(bars + RFB_RING_FULL + stage, 2u * (uint32_t)(nkb * pl.sub_bytes));
+                    for (int i = 0; i < nkb; ++i)
+                        rf_tma_2d_cg2_mc(ring_a + (uint32_t)(stage * pl.stage_bytes + i * pl.sub_bytes + pair_i * slice_rows * 128), map,
+                                         full_l + 8u * (uint32_t)stage, (kb0 + i) * 64, (tile * 2 + (int)rank) * ROWS_B + pair_i * slice_rows, half_mask);
+                }
+                __syncwarp();
                 RF_T1(9);
                 if (++stage == p.ring_stages) { stage = 0; phase ^= 1; }
             };
@@ -290,7 +304,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                     for (int kb = 0; kb < KBH; kb += 2) put(&map_u, kb, min(2, KBH - kb), c);
                     if (FUSED && !(t == T - 1 && c == NC - 1)) put_x(c + 1 == NC ? 0 : c + 1);
                 }
-            RF_DBG(p.dbg[blockIdx.x * 16 + 8] = dbgc[8]; p.dbg[blockIdx.x * 16 + 9] = dbgc[9]);
+            RF_DBG(if (lane == 0) { p.dbg[blockIdx.x * 16 + 8] = dbgc[8]; p.dbg[blockIdx.x * 16 + 9] = dbgc[9]; });
         } else if (warp == CTRL_W0 + 1 && rank == 0) {
             // ===== MMA issuer (leader CTA): static order  X(0), then per tile g: H(g), X(g + 1) =====
             // The WHOLE warp runs this code converged on warp-uniform values, and only the tcgen05 instructions are predicated on
@@ -380,9 +394,10 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
             // x_hi . W_lo pass runs.  (Holding raw fp32 rows, 64 registers, spilled; loading k-blocks late stalled the issuer 2 900
             // cycles per step.)
             uint4 hreg[4][2];
+            const int nit = p.rows == RF_ROWS ? 2 : 1;           // 32-row mode: items 256.. are rows 32..63 (stay zero)
             auto src_of = [&](int t, int kb, int it) -> const float4 * {
                 const int idx = it * 256 + ct, r = idx >> 3, ch = idx & 7, row = row0 + r;
-                return row < p.B ? reinterpret_cast<const float4 *>(p.x + ((size_t)row * T + t) * IN + kb * 64 + ch * 8) : nullptr;
+                return (row < p.B && r < p.rows) ? reinterpret_cast<const float4 *>(p.x + ((size_t)row * T + t) * IN + kb * 64 + ch * 8) : nullptr;
             };
             auto tile_off = [&](int kb, int it) -> size_t {
                 const int idx = it * 256 + ct, r = idx >> 3, ch = idx & 7;
@@ -396,7 +411,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                     for (int kk = 0; kk < 2; ++kk)
 #pragma unroll
                         for (int it = 0; it < 2; ++it) {
-                            const float4 *src = (k2 + kk < KBX) ? src_of(t, k2 + kk, it) : nullptr;
+                            const float4 *src = (k2 + kk < KBX && it < nit) ? src_of(t, k2 + kk, it) : nullptr;
                             if (src) { a[kk][it][0] = __ldg(src); a[kk][it][1] = __ldg(src + 1); }
                             else a[kk][it][0] = a[kk][it][1] = make_float4(0.f, 0.f, 0.f, 0.f);
                         }
@@ -418,7 +433,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                     for (int kb = 0; kb < 4; ++kb) {
                         if (kb >= KBX) break;
 #pragma unroll
-                        for (int it = 0; it < 2; ++it) *reinterpret_cast<uint4 *>(sXh + tile_off(kb, it)) = hreg[kb][it];
+                        for (int it = 0; it < 2; ++it) if (it < nit) *reinterpret_cast<uint4 *>(sXh + tile_off(kb, it)) = hreg[kb][it];
                     }
                 }
                 rf_fence_async();
@@ -431,7 +446,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                         float4 a[2][2];
 #pragma unroll
                         for (int it = 0; it < 2; ++it) {
-                            const float4 *src = src_of(t, kb, it);
+                            const float4 *src = it < nit ? src_of(t, kb, it) : nullptr;
                             if (src) { a[it][0] = __ldg(src); a[it][1] = __ldg(src + 1); } else a[it][0] = a[it][1] = make_float4(0.f, 0.f, 0.f, 0.f);
                         }
 #pragma unroll
@@ -442,7 +457,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                             const float4 u = a[it][0], w = a[it][1];
                             const uint4 lo = make_uint4(rf_pack_sat(u.x - h0.x, u.y - h0.y), rf_pack_sat(u.z - h1.x, u.w - h1.y),
                                                         rf_pack_sat(w.x - h2.x, w.y - h2.y), rf_pack_sat(w.z - h3.x, w.w - h3.y));
-                            if (!RF_SKIP(4)) *reinterpret_cast<uint4 *>(sXl + tile_off(kb, it)) = lo;
+                            if (!RF_SKIP(4) && it < nit) *reinterpret_cast<uint4 *>(sXl + tile_off(kb, it)) = lo;
                         }
                         rf_fence_async();
                         __syncwarp();
@@ -465,6 +480,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         const uint32_t tl = tmem + ((uint32_t)(q * 32) << 16);           // this warp's TMEM lanes
         const uint32_t acc_empty0 = rf_mapa(smem_u32(bars + RFB_ACC_EMPTY), leader), hfull0 = rf_mapa(smem_u32(bars + RFB_H_FULL), leader);
         const int sw = m & 7;
+        if (p.rows == RF_ROWS || !(q & 1)) {       // 32-row mode: lane quarters 1 and 3 hold no sequences
         // ---- prologue: state into TMEM, fp16 h_0 into the A tile, zero the h.Uh groups
         for (int c = 0; c < NC; ++c) {
 #pragma unroll
@@ -667,6 +683,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 }
         }
         if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");      // this warp's last stores have landed
+        }
         RF_DBG(if (ew == 0 && lane == 0) { p.dbg[blockIdx.x * 16 + 4] = dbgc[4]; p.dbg[blockIdx.x * 16 + 5] = clock64() - t_start; p.dbg[blockIdx.x * 16 + 11] = dbgc[11]; });
     }
     tc_fence_before();
@@ -838,11 +855,10 @@ extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, c
         }
     }
     // cluster size: as many pairs as share a B stream (at most 4), shrunk while the device cannot schedule such a cluster
-    const int pairs = (nb + 127) / 128;
+    int pairs = (nb + 127) / 128;
     static int max_cs = -1;
     if (max_cs < 0) { const char *e = getenv("NNTK_RECURRENT_FUSED_CLUSTER"); max_cs = e ? atoi(e) : 8; if (max_cs != 2 && max_cs != 4 && max_cs != 8) max_cs = 8; }
-    int cs = pairs >= 4 ? 8 : pairs >= 2 ? 4 : 2;
-    if (cs > max_cs) cs = max_cs;
+    int cs = 2;
     CUtensorMap mw, mwl, mu, mo;
     auto enc2 = [&](CUtensorMap *m, void *base, int K) -> int {
         cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)G * H};
@@ -856,7 +872,7 @@ extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, c
     };
     int rc;
     RfParams p = {};
-    p.H = H; p.in = IN; p.xp = xp;
+    p.H = H; p.in = IN; p.xp = xp; p.rows = RF_ROWS;
     const bool small = H <= 256;
 #define RF_DISPATCH(DRY) \
     (G == 3 ? (fused ? (small ? rf_launch<3, true, 4>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<3, true, 8>(mw, mwl, mu, mo, p, pairs, st, DRY)) \
@@ -867,13 +883,31 @@ extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, c
     // once (ties: the larger cluster, it shares the B stream more widely).  Measured at 64 pairs: clusters of 8 run in two waves
     // (43.7 ms per C5 GRU layer), clusters of 4 in one (12.2 ms).
     int best_cs = 0, best_resident = 0;
-    for (int c = cs; c >= 2; c /= 2) {
-        int resident = 0;
-        p.cs = c;
-        rc = RF_DISPATCH(&resident);
-        if (rc < 0) return rc;
-        if (resident > best_resident) { best_resident = resident; best_cs = c; }
+    auto pick = [&](int np) -> int {
+        best_cs = 0; best_resident = 0;
+        int c0 = np >= 4 ? 8 : np >= 2 ? 4 : 2;
+        if (c0 > max_cs) c0 = max_cs;
+        for (int c = c0; c >= 2; c /= 2) {
+            int resident = 0;
+            p.cs = c;
+            const int pairs = np;        // RF_DISPATCH reads `pairs`
+            const int rc2 = RF_DISPATCH(&resident);
+            if (rc2 < 0) return rc2;
+            if (resident > best_resident) { best_resident = resident; best_cs = c; }
+        }
+        return 0;
+    };
+    // 32-row mode: a batch whose 128-sequence pairs would leave more than half of the SMs idle runs on pairs of 64 sequences
+    // (M tile half filled: the tensor pipe has the slack, the epilogue -- the bound -- and the weight stream get twice the SMs),
+    // provided all of those pairs are still resident in one wave.  NNTK_RECURRENT_FUSED_ROWS=64 / 32 forces a mode.
+    static int force_rows = -1;
+    if (force_rows < 0) { const char *e = getenv("NNTK_RECURRENT_FUSED_ROWS"); force_rows = e ? atoi(e) : 0; }
+    if (force_rows != 64) {
+        const int pairs32 = (nb + 63) / 64;
+        if ((rc = pick(pairs32)) < 0) return rc;
+        if (best_cs && (best_resident >= pairs32 || force_rows == 32)) { p.rows = 32; pairs = pairs32; }
     }
+    if (p.rows == RF_ROWS) { if ((rc = pick(pairs)) < 0) return rc; }
     if (!best_cs) return 0;          // not even a pair fits: not eligible
     cs = best_cs;
     p.cs = cs;
