@@ -49,6 +49,9 @@ constexpr int RF_MAX_RING = 8;
 struct RfParams {
     int B, H, in, T;
     int rows;                        // real sequences per CTA: 64, or 32 (half-filled M tile, twice the pairs: for batches that would leave SMs idle)
+    int split;                       // pairs per slice of sequences: 1, or 2 = the hidden units of a slice are split across the two pairs of a
+                                     // 4-CTA cluster (each streams half of the weights, owns half of the tiles; h_t halves are exchanged through
+                                     // distributed shared memory once per step)
     int return_sequences;
     int ring_stages;
     int xp;                          // FUSED: input passes the launch is PLANNED for (shared memory, packed operands), 1 or 3
@@ -173,7 +176,8 @@ struct RfPlan {
 // barrier block layout (uint64 slots)
 constexpr int RFB_RING_FULL = 0, RFB_RING_EMPTY = RF_MAX_RING, RFB_ACC_FULL = 2 * RF_MAX_RING, RFB_ACC_EMPTY = RFB_ACC_FULL + 4,
               RFB_H_FULL = RFB_ACC_EMPTY + 4, RFB_X_FULL = RFB_H_FULL + 1 /* hi image */, RFB_XL_FULL = RFB_X_FULL + 1 /* lo image, per k-block */,
-              RFB_X_EMPTY = RFB_XL_FULL + 4, RFB_END = RFB_X_EMPTY + 1;
+              RFB_X_EMPTY = RFB_XL_FULL + 4, RFB_A_FREE = RFB_X_EMPTY + 1 /* split mode: both pairs' MMAs of the step have read A_h */,
+              RFB_END = RFB_A_FREE + 1;
 
 // NCMAX: compile-time bound of the tiles per step (H / 64 <= NCMAX): sizes the register-resident pending-h array.
 template <int G, bool FUSED, int NCMAX>
@@ -191,9 +195,10 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     // Every role of every CTA evaluates the same two numbers, so the whole grid takes the same branch.
     const int XP = (p.xp == 3 && p.stats && sqrtf(__ldg(p.stats) * __ldg(p.stats + 1)) <= p.adapt_thr) ? 1 : p.xp;
     const int H = p.H, IN = p.in, T = p.T;
-    const int NC = H / RF_UT;                               // tiles per step
+    const int S = p.split;                                  // pairs per slice (1 or 2)
+    const int NCT = H / RF_UT, NC = NCT / S;                // tiles per step: of the layer / of this pair
     const int KBH = H / 64, KBX = FUSED ? IN / 64 : 0;      // k-blocks of the recurrent / input part
-    const int NB = (512 - H / 2) / 128;                     // accumulator buffers (3 for H <= 256, 2 for H = 512)
+    const int NB = (512 - H / S / 2) / 128;                 // accumulator buffers (3 when the pair owns <= 256 units, 2 for 512)
     const uint32_t STATE_COL = (uint32_t)(NB * 128);
     const RfPlan<G, FUSED> pl(H, IN, p.xp, p.ring_stages);
     uint8_t *sAh = smem + pl.a_h, *sXh = smem + pl.x_hi, *sXl = smem + pl.x_lo, *sOut = smem + pl.out_stg, *sRing = smem + pl.ring;
@@ -209,9 +214,13 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     constexpr int CONV_W0 = 8, CTRL_W0 = 16;                 // first converter / control warp
     const uint32_t crank = __shfl_sync(0xffffffffu, rf_rank(), 0);   // rank in the cluster (warp-uniform for the compiler); pairs are (0,1), (2,3), ...
     const uint32_t rank = crank & 1u, leader = crank & ~1u; // rank inside the pair, cluster rank of the pair's leader
-    const int npairs = p.cs >> 1, pair_i = (int)(crank >> 1);
-    const uint16_t pair_mask = (uint16_t)(3u << leader), all_mask = (uint16_t)((1u << p.cs) - 1u);
-    const int row0 = ((blockIdx.x >> 1) * 2 + (int)rank) * p.rows;       // first sequence of this CTA
+    // unsplit: the cs / 2 pairs of a cluster work on different slices and share every B stage by multicast (npairs, pair_i).
+    // split: the cluster is ONE slice, pair s = crank / 2 owns tiles [s NC, (s + 1) NC) and streams only their weights.
+    const int npairs = S == 2 ? 1 : p.cs >> 1, pair_i = S == 2 ? 0 : (int)(crank >> 1);
+    const int tile0 = S == 2 ? (int)(crank >> 1) * NC : 0;
+    const uint16_t pair_mask = (uint16_t)(3u << leader), all_mask = S == 2 ? pair_mask : (uint16_t)((1u << p.cs) - 1u);
+    const int slice = S == 2 ? (int)(blockIdx.x >> 2) : (int)(blockIdx.x >> 1);
+    const int row0 = (slice * 2 + (int)rank) * p.rows;      // first sequence of this CTA
     const int EPA = p.rows == RF_ROWS ? EPW : EPW / 2;      // epilogue warps with real rows (32-row mode: lane quarters 0 and 2 only)
     // tile counters are 32-bit and advanced incrementally everywhere: 64-bit divisions in the issuer's loop cost ~13 000 cycles per
     // step in the first version (more than all of the step's MMAs)
@@ -224,7 +233,8 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_out) : "memory");
         for (int s = 0; s < p.ring_stages; ++s) { mbar_init(bars + RFB_RING_FULL + s, 1); mbar_init(bars + RFB_RING_EMPTY + s, (uint32_t)npairs); }
         for (int b = 0; b < 4; ++b) { mbar_init(bars + RFB_ACC_FULL + b, 1); mbar_init(bars + RFB_ACC_EMPTY + b, 2 * EPA); }
-        mbar_init(bars + RFB_H_FULL, 2 * EPA);
+        mbar_init(bars + RFB_H_FULL, 2 * EPA * S);
+        mbar_init(bars + RFB_A_FREE, (uint32_t)S);
         mbar_init(bars + RFB_X_FULL, 16);
         for (int b = 0; b < 4; ++b) mbar_init(bars + RFB_XL_FULL + b, 16);
         mbar_init(bars + RFB_X_EMPTY, 1);
@@ -281,6 +291,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
             const int slice_rows = ROWS_B / npairs;
             uint16_t half_mask = 0;
             for (int i = 0; i < npairs; ++i) half_mask |= (uint16_t)(1u << (2 * i + (int)rank));
+            if (S == 2) half_mask = (uint16_t)(1u << crank);
             auto put = [&](const CUtensorMap *map, int kb0, int nkb, int tile) {
                 { RF_T0(); mbar_wait(bars + RFB_RING_EMPTY + stage, phase ^ 1); RF_T1(8); }
                 RF_T0();
@@ -298,11 +309,11 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 if (XP == 3) for (int kb = 0; kb < KBX; kb += 2) put(&map_wl, kb, min(2, KBX - kb), tile);
                 for (int kb = 0; kb < KBX; kb += 2) put(&map_w, kb, min(2, KBX - kb), tile);
             };
-            if (FUSED) put_x(0);
+            if (FUSED) put_x(tile0);
             for (int t = 0; t < T; ++t)
                 for (int c = 0; c < NC; ++c) {
-                    for (int kb = 0; kb < KBH; kb += 2) put(&map_u, kb, min(2, KBH - kb), c);
-                    if (FUSED && !(t == T - 1 && c == NC - 1)) put_x(c + 1 == NC ? 0 : c + 1);
+                    for (int kb = 0; kb < KBH; kb += 2) put(&map_u, kb, min(2, KBH - kb), tile0 + c);
+                    if (FUSED && !(t == T - 1 && c == NC - 1)) put_x(tile0 + (c + 1 == NC ? 0 : c + 1));
                 }
             RF_DBG(if (lane == 0) { p.dbg[blockIdx.x * 16 + 8] = dbgc[8]; p.dbg[blockIdx.x * 16 + 9] = dbgc[9]; });
         } else if (warp == CTRL_W0 + 1 && rank == 0) {
@@ -362,7 +373,10 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 // into the buffer (XW).  GRU: it lands one 32-column group to the right ([z | r | h.Uh]); x.Wh stays in group 0.
                 const uint32_t d = tmem + (uint32_t)(buf * 128) + (G == 3 ? 32u : 0u);
                 for (int kb = 0; kb < KBH; kb += 2) stage_mmas(d, ah_a, 0u, kb, min(2, KBH - kb), false);
-                if (rf_elect()) rf_commit(bars + RFB_ACC_FULL + buf, pair_mask);
+                if (rf_elect()) {
+                    rf_commit(bars + RFB_ACC_FULL + buf, pair_mask);
+                    if (S == 2 && c == NC - 1) rf_commit(bars + RFB_A_FREE, (uint16_t)0xF);    // this pair is done reading h_{t-1}
+                }
                 __syncwarp();
             };
             // the tile after (t, c) in issue order and its buffer bookkeeping
@@ -479,10 +493,13 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         const bool row_ok = row < p.B;
         const uint32_t tl = tmem + ((uint32_t)(q * 32) << 16);           // this warp's TMEM lanes
         const uint32_t acc_empty0 = rf_mapa(smem_u32(bars + RFB_ACC_EMPTY), leader), hfull0 = rf_mapa(smem_u32(bars + RFB_H_FULL), leader);
+        const uint32_t hfull1 = rf_mapa(smem_u32(bars + RFB_H_FULL), leader ^ 2u);       // split mode: the other pair's leader
+        const uint32_t sAh_peer = rf_mapa(smem_u32(sAh), crank ^ 2u);                    // split mode: the same rows' A tile in the other pair
         const int sw = m & 7;
         if (p.rows == RF_ROWS || !(q & 1)) {       // 32-row mode: lane quarters 1 and 3 hold no sequences
         // ---- prologue: state into TMEM, fp16 h_0 into the A tile, zero the h.Uh groups
-        for (int c = 0; c < NC; ++c) {
+        for (int c = 0; c < NCT; ++c) {                  // the A tile holds ALL of h; TMEM only the state of this pair's tiles
+            const bool own = c >= tile0 && c < tile0 + NC;
 #pragma unroll
             for (int e = 0; e < NE; ++e) {
                 const int u0 = c * 64 + hf * 32 + j * UPT + e * 8;
@@ -491,13 +508,15 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 for (int i = 0; i < 2; ++i) {
                     const float4 a = row_ok ? *reinterpret_cast<const float4 *>(p.h_state + (size_t)row * H + u0 + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
                     hv[4 * i] = a.x; hv[4 * i + 1] = a.y; hv[4 * i + 2] = a.z; hv[4 * i + 3] = a.w;
-                    if (G == 4) {
+                    if (G == 4 && own) {
                         const float4 b = row_ok ? *reinterpret_cast<const float4 *>(p.c_state + (size_t)row * H + u0 + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
                         sv[4 * i] = b.x; sv[4 * i + 1] = b.y; sv[4 * i + 2] = b.z; sv[4 * i + 3] = b.w;
                     }
                 }
-                if (G == 4) rf_st8(tl + STATE_COL + (uint32_t)(c * 32 + j * UPT + e * 8), sv);
-                else rf_st8(tl + STATE_COL + (uint32_t)(c * 32 + j * UPT + e * 8), hv);
+                if (own) {
+                    if (G == 4) rf_st8(tl + STATE_COL + (uint32_t)((c - tile0) * 32 + j * UPT + e * 8), sv);
+                    else rf_st8(tl + STATE_COL + (uint32_t)((c - tile0) * 32 + j * UPT + e * 8), hv);
+                }
                 uint4 v;
                 v.x = rf_pack_sat(hv[0], hv[1]); v.y = rf_pack_sat(hv[2], hv[3]); v.z = rf_pack_sat(hv[4], hv[5]); v.w = rf_pack_sat(hv[6], hv[7]);
                 const int ch = (hf * 32 + j * UPT) / 8 + e;
@@ -511,7 +530,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         // LSTM [i | f | g | o].
         auto xw_src = [&](int t2, int c2) -> const float4 * {
             return reinterpret_cast<const float4 *>(p.xw) +
-                   (((long long)t2 * p.xw_blocked_rows + (row >> 5)) * (G * H >> 2) + ((c2 * 64 + hf * 32 + j * UPT) >> 2)) * 32 + (row & 31);
+                   (((long long)t2 * p.xw_blocked_rows + (row >> 5)) * (G * H >> 2) + (((tile0 + c2) * 64 + hf * 32 + j * UPT) >> 2)) * 32 + (row & 31);
         };
         auto xw_load = [&](float4 (&xn)[G][UPT / 4], int t2, int c2) {
             const float4 *src = xw_src(t2, c2);
@@ -550,7 +569,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         rf_fence_async();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) rf_arrive_cl(hfull0);
+        if (lane == 0) { rf_arrive_cl(hfull0); if (S == 2) rf_arrive_cl(hfull1); }
         uint32_t hpend[NCMAX][UPT / 2]; // fp16 h_t of the step's tiles x UPT units, written to the A tile once the step's MMAs are done
         int buf = -1, use = 0;          // accumulator buffer of the current tile and how often it has been used before
         for (int t = 0; t < T; ++t) {
@@ -573,7 +592,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
 #pragma unroll
                 for (int e = 0; e < NE; ++e) {
                     if (RF_SKIP(1)) break;
-                    const int ub = c * 64 + hf * 32 + j * UPT + e * 8;            // first of these 8 hidden units
+                    const int ub = (tile0 + c) * 64 + hf * 32 + j * UPT + e * 8;  // first of these 8 hidden units
                     float a0[8], a1[8], a2[8], a3[8], st[8];
                     rf_ld8(acc + (uint32_t)(e * 8), a0);
                     rf_ld8(acc + (uint32_t)(32 + e * 8), a1);
@@ -632,7 +651,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                     rf_fence_async();
                     __syncwarp();
                     if (lane == 0) {
-                        rf_tma_store_3d(&map_out, o, c * 64 + hf * 32 + j * UPT, t, row0 + (q & 1) * 32);
+                        rf_tma_store_3d(&map_out, o, (tile0 + c) * 64 + hf * 32 + j * UPT, t, row0 + (q & 1) * 32);
                         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                     }
                 }
@@ -640,29 +659,36 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                     // every recurrent-part MMA of this step has completed (they precede this tile's commit): h_t may now
                     // replace h_{t-1} in the A tile.  The last step's h goes to the caller's state instead.
                     if (t + 1 < T) {
+                        // split mode: the other pair's MMAs of this step read ITS copy of h_{t-1}, which this warp is about to overwrite too
+                        if (S == 2) mbar_wait(bars + RFB_A_FREE, (uint32_t)(t & 1));
 #pragma unroll
                         for (int cc = 0; cc < NCMAX; ++cc) {
                             if (cc >= NC) break;
 #pragma unroll
                             for (int e = 0; e < NE; ++e) {
                                 const int ch = (hf * 32 + j * UPT) / 8 + e;
-                                *reinterpret_cast<uint4 *>(sAh + (size_t)cc * (RF_ROWS * 128) + m * 128 + ((ch ^ sw) << 4)) =
-                                    make_uint4(hpend[cc][4 * e], hpend[cc][4 * e + 1], hpend[cc][4 * e + 2], hpend[cc][4 * e + 3]);
+                                const uint32_t off = (uint32_t)((tile0 + cc) * (RF_ROWS * 128) + m * 128 + ((ch ^ sw) << 4));
+                                *reinterpret_cast<uint4 *>(sAh + off) = make_uint4(hpend[cc][4 * e], hpend[cc][4 * e + 1], hpend[cc][4 * e + 2], hpend[cc][4 * e + 3]);
+                                if (S == 2)
+                                    asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sAh_peer + off), "r"(hpend[cc][4 * e]), "r"(hpend[cc][4 * e + 1]),
+                                                 "r"(hpend[cc][4 * e + 2]), "r"(hpend[cc][4 * e + 3]) : "memory");
                             }
                         }
-                        rf_fence_async();
+                        if (S == 2) asm volatile("fence.proxy.async;" ::: "memory"); else rf_fence_async();
+                        // the remote stores must have landed in the other pair's shared memory before its leader's barrier can complete
+                        if (S == 2) asm volatile("fence.acq_rel.cluster;" ::: "memory");
                         __syncwarp();
-                        if (lane == 0) rf_arrive_cl(hfull0);
+                        if (lane == 0) { rf_arrive_cl(hfull0); if (S == 2) rf_arrive_cl(hfull1); }
                     }
                 }
                 if (t == T - 1 && row_ok) {
                     // final state (gru.c:201, lstm.c:264-265): exact fp32 h_T (and c_T from TMEM below)
-                    float *hs = p.h_state + (size_t)row * H + c * 64 + hf * 32 + j * UPT;
+                    float *hs = p.h_state + (size_t)row * H + (tile0 + c) * 64 + hf * 32 + j * UPT;
 #pragma unroll
                     for (int i = 0; i < UPT / 4; ++i) {
                         const float4 v = make_float4(hn[4 * i], hn[4 * i + 1], hn[4 * i + 2], hn[4 * i + 3]);
                         *reinterpret_cast<float4 *>(hs + 4 * i) = v;
-                        if (!p.return_sequences) *reinterpret_cast<float4 *>(p.out + (size_t)row * H + c * 64 + hf * 32 + j * UPT + 4 * i) = v;
+                        if (!p.return_sequences) *reinterpret_cast<float4 *>(p.out + (size_t)row * H + (tile0 + c) * 64 + hf * 32 + j * UPT + 4 * i) = v;
                     }
                 }
             }
@@ -676,7 +702,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                     rf_ld8(tl + STATE_COL + (uint32_t)(c * 32 + j * UPT + e * 8), sv);
                     rf_ld_wait();
                     if (row_ok) {
-                        float *cs = p.c_state + (size_t)row * H + c * 64 + hf * 32 + j * UPT + e * 8;
+                        float *cs = p.c_state + (size_t)row * H + (tile0 + c) * 64 + hf * 32 + j * UPT + e * 8;
                         *reinterpret_cast<float4 *>(cs) = make_float4(sv[0], sv[1], sv[2], sv[3]);
                         *reinterpret_cast<float4 *>(cs + 4) = make_float4(sv[4], sv[5], sv[6], sv[7]);
                     }
@@ -860,10 +886,11 @@ extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, c
     if (max_cs < 0) { const char *e = getenv("NNTK_RECURRENT_FUSED_CLUSTER"); max_cs = e ? atoi(e) : 8; if (max_cs != 2 && max_cs != 4 && max_cs != 8) max_cs = 8; }
     int cs = 2;
     CUtensorMap mw, mwl, mu, mo;
+    RfParams p = {};
     auto enc2 = [&](CUtensorMap *m, void *base, int K) -> int {
         cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)G * H};
         cuuint64_t strides[1] = {(cuuint64_t)K * 2};
-        cuuint32_t box[2] = {64, (cuuint32_t)(32 * G / (cs / 2))};       // one pair's slice of a CTA's rows
+        cuuint32_t box[2] = {64, (cuuint32_t)(32 * G / (p.split == 2 ? 1 : cs / 2))};       // one pair's slice of a CTA's rows
         cuuint32_t es[2] = {1, 1};
         CUresult cr = encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -871,9 +898,8 @@ extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, c
         return 0;
     };
     int rc;
-    RfParams p = {};
-    p.H = H; p.in = IN; p.xp = xp; p.rows = RF_ROWS;
-    const bool small = H <= 256;
+    p.H = H; p.in = IN; p.xp = xp; p.rows = RF_ROWS; p.split = 1;
+    bool small = H <= 256;
 #define RF_DISPATCH(DRY) \
     (G == 3 ? (fused ? (small ? rf_launch<3, true, 4>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<3, true, 8>(mw, mwl, mu, mo, p, pairs, st, DRY)) \
                      : (small ? rf_launch<3, false, 4>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<3, false, 8>(mw, mwl, mu, mo, p, pairs, st, DRY))) \
@@ -887,7 +913,8 @@ extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, c
         best_cs = 0; best_resident = 0;
         int c0 = np >= 4 ? 8 : np >= 2 ? 4 : 2;
         if (c0 > max_cs) c0 = max_cs;
-        for (int c = c0; c >= 2; c /= 2) {
+        if (p.split == 2) c0 = 4;        // a split slice IS a 4-CTA cluster
+        for (int c = c0; c >= (p.split == 2 ? 4 : 2); c /= 2) {
             int resident = 0;
             p.cs = c;
             const int pairs = np;        // RF_DISPATCH reads `pairs`
@@ -897,17 +924,29 @@ extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, c
         }
         return 0;
     };
-    // 32-row mode: a batch whose 128-sequence pairs would leave more than half of the SMs idle runs on pairs of 64 sequences
-    // (M tile half filled: the tensor pipe has the slack, the epilogue -- the bound -- and the weight stream get twice the SMs),
-    // provided all of those pairs are still resident in one wave.  NNTK_RECURRENT_FUSED_ROWS=64 / 32 forces a mode.
-    static int force_rows = -1;
+    // A batch whose 128-sequence pairs would leave most SMs idle is spread wider, as long as everything stays resident in ONE wave
+    // (the step is a latency chain: a second wave doubles the time).  In order of preference:
+    //   split 2 + 32 rows : 4 x the pairs        split 2 : hidden units of a slice across two pairs (each streams half of the
+    //   weights and owns half of the tiles; h_t halves exchanged through DSMEM)        32 rows : half-filled M tile
+    // NNTK_RECURRENT_FUSED_ROWS = 64 / 32 and NNTK_RECURRENT_FUSED_SPLIT = 1 / 2 force a shape.
+    static int force_rows = -1, force_split = -1;
     if (force_rows < 0) { const char *e = getenv("NNTK_RECURRENT_FUSED_ROWS"); force_rows = e ? atoi(e) : 0; }
-    if (force_rows != 64) {
-        const int pairs32 = (nb + 63) / 64;
-        if ((rc = pick(pairs32)) < 0) return rc;
-        if (best_cs && (best_resident >= pairs32 || force_rows == 32)) { p.rows = 32; pairs = pairs32; }
+    if (force_split < 0) { const char *e = getenv("NNTK_RECURRENT_FUSED_SPLIT"); force_split = e ? atoi(e) : 0; }
+    const bool can_split = (H % 128) == 0;
+    bool chosen = false;
+    for (int opt = 0; opt < 4 && !chosen; ++opt) {
+        const int o_split = opt < 2 ? 2 : 1, o_rows = (opt & 1) ? 64 : 32;      // (2,32) (2,64) (1,32) (1,64)
+        if (o_split == 2 && !can_split) continue;
+        if ((force_rows == 32 || force_rows == 64) && o_rows != force_rows) continue;
+        if ((force_split == 1 || force_split == 2) && o_split != force_split) continue;
+        const int np = ((nb + 2 * o_rows - 1) / (2 * o_rows)) * o_split;
+        p.split = o_split; p.rows = o_rows; small = H / o_split <= 256;
+        if ((rc = pick(np)) < 0) return rc;
+        const bool last = (o_split == 1 && o_rows == 64) || (force_rows && force_split) || (force_split == o_split && force_rows == 0 && o_rows == 64) ||
+                          (force_rows == o_rows && force_split == 0 && o_split == 1);
+        if (best_cs && (best_resident >= np || last)) { pairs = np; chosen = true; }
     }
-    if (p.rows == RF_ROWS) { if ((rc = pick(pairs)) < 0) return rc; }
+    if (!chosen) { p.split = 1; p.rows = RF_ROWS; small = H <= 256; if ((rc = pick(pairs)) < 0) return rc; }
     if (!best_cs) return 0;          // not even a pair fits: not eligible
     cs = best_cs;
     p.cs = cs;
