@@ -197,6 +197,16 @@ const char *nntk_cuda_last_recurrent_path(void);
 /* input passes (1 or 3) the most recent fused recurrent launch took after its adaptive pre-scan; synchronises (tests only) */
 int nntk_cuda_last_recurrent_xpasses(void);
 int nntk_cuda_recurrent(const nntk_recurrent_args *r);
+/* Allocation-free variant of nntk_cuda_recurrent.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  The caller
+ * passes weights, inputs, state and outputs as device pointers exactly as for nntk_cuda_recurrent; d_work / work_bytes are
+ * ignored: the scratch (hoisted projection + ping-pong buffers, 4 (batch T G H + 6 batch H) bytes) lives in a file-scope device
+ * array of NNTK_RECURRENT_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit.  Always the fp32 (FFMA) path,
+ * whatever the math mode.  Larger problems are rejected with NNTK_ERR_ARG and a message in nntk_cuda_last_error().  Calls no
+ * cudaMalloc / cudaFree / allocating library routine.  All calls share the one array: calls whose kernels overlap on the GPU
+ * (different streams) race; calls on one stream are safe, nothing in the array has to be cleared between them. */
+#define NNTK_RECURRENT_STATIC_SCRATCH_BYTES (32u << 20)
+int nntk_cuda_recurrent_static_scratch(const nntk_recurrent_args *r);
 
 #ifdef __cplusplus
 }

@@ -208,6 +208,7 @@ SHIM_SYMBOLS = [
     "nntk_cuda_pack_conv_weights_padded", "nntk_cuda_pad_channels", "nntk_cuda_pack_conv_weights_bn",
     "nntk_cuda_spectrogram_pitched",
     "nntk_cuda_recurrent_workspace", "nntk_cuda_recurrent", "nntk_cuda_last_recurrent_path", "nntk_cuda_last_recurrent_xpasses",
+    "nntk_cuda_recurrent_static_scratch",
 ]
 
 

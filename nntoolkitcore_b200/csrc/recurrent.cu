@@ -646,3 +646,67 @@ extern "C" int nntk_cuda_recurrent(const nntk_recurrent_args *r) {
     }
     return 0;
 }
+
+// ---- allocation-free variant -----------------------------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same layer forward as nntk_cuda_recurrent on its
+// fp32 path -- hoisted projection GEMM (FFMA), then the persistent fp32 cluster kernel or the per-step FFMA kernels -- with the
+// scratch (projection xw[batch, T, G*H] + 6 [batch, H] ping-pong buffers) taken from ONE file-scope device array instead of the
+// caller's workspace.  Every GPU that loads the library holds the array (NNTK_RECURRENT_STATIC_SCRATCH_BYTES) until exit.
+// Nothing in it has to start at zero: the projection is fully written before it is read and every ping-pong buffer is written
+// by step t before step t + 1 reads it, so the previous call's contents are simply overwritten.  All calls share the array:
+// two calls whose kernels overlap on the GPU (different streams, or two host threads each with its own stream) race.
+static __device__ __align__(256) float g_recurrent_static_scratch[NNTK_RECURRENT_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+extern "C" int nntk_cuda_recurrent_static_scratch(const nntk_recurrent_args *r) {
+    int rc = nntk_cuda_ensure_init();
+    if (rc) return rc;
+    if (!r || (r->cell != 1 && r->cell != 3 && r->cell != 4) || r->in < 1 || r->H < 1 || r->T < 0 || r->batch < 0 ||
+        !r->d_W || !r->d_U || !r->d_bi || !r->d_bh || !r->d_x || !r->d_h || !r->d_out || (r->cell == 4 && !r->d_c)) {
+        nntk_cuda_set_error(NNTK_ERR_ARG_, "recurrent_static_scratch: bad arguments");
+        return NNTK_ERR_ARG_;
+    }
+    for (int i = 0; i < 5; ++i)
+        if (r->act[i] == NNTK_ACT_SOFTMAX || r->act[i] == NNTK_ACT_CUSTOM) {
+            nntk_cuda_set_error(NNTK_ERR_UNSUPPORTED_, "recurrent_static_scratch: gate activation kind %d cannot run fused on the device", r->act[i]);
+            return NNTK_ERR_UNSUPPORTED_;
+        }
+    if (r->batch == 0 || r->T == 0) return 0;
+    // the whole batch in one chunk (nothing here may grow a buffer): projection + ping-pong must fit the array
+    const double need_d = ((double)r->batch * r->T * r->cell * r->H + 6.0 * r->batch * r->H) * sizeof(float);
+    if (need_d > (double)NNTK_RECURRENT_STATIC_SCRATCH_BYTES) {
+        nntk_cuda_set_error(NNTK_ERR_ARG_,
+                            "recurrent_static_scratch: batch %d x T %d x %d gates x H %d needs %.0f bytes of scratch, the static array holds %llu "
+                            "(NNTK_RECURRENT_STATIC_SCRATCH_BYTES); use nntk_cuda_recurrent with a caller-owned workspace",
+                            r->batch, r->T, r->cell, r->H, need_d, (unsigned long long)NNTK_RECURRENT_STATIC_SCRATCH_BYTES);
+        return NNTK_ERR_ARG_;
+    }
+    nntk_cuda_api_lock();
+    // In host code the array's name is only a stand-in: its device address is looked up once per device, with that device current
+    // (nntk_cuda_ensure_init above made it so), and that pointer is what the kernels get.
+    static float *scratch_of_device[64] = {nullptr};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64) {
+        nntk_cuda_api_unlock();
+        nntk_cuda_set_error(NNTK_ERR_CUDA_, "recurrent_static_scratch: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+        return NNTK_ERR_CUDA_;
+    }
+    if (!scratch_of_device[dev]) {
+        float *ptr = nullptr;
+        e = cudaGetSymbolAddress((void **)&ptr, g_recurrent_static_scratch);
+        if (e != cudaSuccess || !ptr) {
+            nntk_cuda_api_unlock();
+            nntk_cuda_set_error(NNTK_ERR_CUDA_, "recurrent_static_scratch: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            return NNTK_ERR_CUDA_;
+        }
+        scratch_of_device[dev] = ptr;
+    }
+    // the fp32 path of the dispatcher is the one that neither allocates nor repacks operands into library-owned buffers
+    const int mode = nntk_cuda_math_mode();
+    if (mode != 0) nntk_cuda_set_math_mode(0);
+    rc = recurrent_chunk(r, 0, r->batch, scratch_of_device[dev], (size_t)NNTK_RECURRENT_STATIC_SCRATCH_BYTES);
+    if (mode != 0) nntk_cuda_set_math_mode(mode);
+    nntk_cuda_api_unlock();
+    return rc;
+}
