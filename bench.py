@@ -683,7 +683,7 @@ def run_ours(args):
     if rank == 0 and world == 1 and not args.no_cpu:
         import bench_cpu
         procs = bench_cpu.host_cores()
-        units = max({"c5": 2, "c2": 16, "c3": 2, "c4": 1}[name] * procs, 16)
+        units = max({"c5": 6, "c2": 16, "c3": 2, "c4": 1}[name] * procs, 16)      # c5: ~20 core-seconds of reference work
         pool = bench_cpu.Pool(name, dict(nfft=512, window_size=512, noverlap=352, input_size=CLIP_N), procs)
         try:
             pool.run(procs)
