@@ -98,6 +98,14 @@ int nntk_cuda_spectrogram(const nntk_spectrogram_args *a, const float *d_in, flo
 /* The same with rows of out_pitch >= nfreq floats (pad columns zero): what the fused front end (SpectrogramBNConv1dApplyBatch)
  * feeds the Conv1d's TMA im2col view without a re-layout pass.  Returns 1 (nothing enqueued) when the shape has no pitched kernel. */
 int nntk_cuda_spectrogram_pitched(const nntk_spectrogram_args *a, const float *d_in, float *d_out, int n_clips, int out_pitch);
+/* The tensor-core front end's variant: rows of out_pitch fp16 values (even, nfreq < out_pitch <= 288; same 10 explicit mantissa
+ * bits as a TF32 operand, half the bytes).  *d_ovf is set to 1 when a value does not fit fp16's range: the caller's fp32 path,
+ * enqueued behind it and gated on that flag, then produces the result (signal/spectrogram.c:113-135 either way). */
+int nntk_cuda_spectrogram_half(const nntk_spectrogram_args *a, const float *d_in, void *d_out_half, int n_clips, int out_pitch, int *d_ovf);
+/* gate for the NEXT 512-point spectrogram launches, until cleared with NULL: they return at once unless *d_flag == run_if */
+void nntk_cuda_spectrogram_gate(const int *d_flag, int run_if);
+/* device address of the front end's overflow flag (one int per device, in the library image); NULL without a device */
+int *nntk_cuda_front_flag(void);
 
 /* K1 with the log-mel epilogue (signal/log_mel_spectrogram.c:33-38 in one kernel).
  * The mel table is passed as a per-lane work list: entry (iter, lane) = {packed, weight}; packed = 8 * slot(bin) |
@@ -151,6 +159,14 @@ typedef struct {
     int ldc;
 } nntk_gemm_args;
 int nntk_cuda_gemm(const nntk_gemm_args *g);
+/* the tcgen05 kernel directly (split 0: single-pass TF32, 1: 3xTF32): 0 done, 1 shape not eligible (nothing enqueued), < 0 error */
+int nntk_cuda_gemm_tf32(const nntk_gemm_args *g, int split);
+/* Single-pass fp16-operand tcgen05 GEMM for the tensor-core front end: g->d_A points to fp16 rows (lda / a_slab_stride count
+ * halves, multiples of 8), d_B is fp32 and repacked to fp16 here; *d_ovf is set when a weight does not fit fp16 and the GEMM
+ * kernel only runs while *d_ovf == 0.  Returns 0 done, 1 not eligible (nothing enqueued), < 0 error.  (layers/conv_1d.c:122-155) */
+int nntk_cuda_gemm_f16(const nntk_gemm_args *g, int *d_ovf);
+/* gate for the NEXT tensor-core GEMM launches, until cleared with NULL: they return at once unless *d_flag == run_if */
+void nntk_cuda_gemm_tc_gate(const int *d_flag, int run_if);
 /* conv weights W[Cout][Cin][K] -> B[(k*Cin + ci)][co]   (layers/conv_1d.c:128-140 order -> implicit-GEMM order) */
 int nntk_cuda_pack_conv_weights(const float *d_W, float *d_B, int cout, int cin, int k);
 /* the same with the channel dimension zero-padded to cin_pad (rows k*cin_pad + ci, ci >= cin are zero), and the matching

@@ -17,6 +17,7 @@
 // so A is a 3-D TMA tensor {K*Cin, T_out, batch} with OVERLAPPING rows (row stride = stride*Cin floats).
 // Weights are re-laid K-major (Bt[N][K]) per call -- they may legally change between Applies.
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include "tc_common.cuh"
 
 namespace {
@@ -39,6 +40,9 @@ struct TcParams {
     const float *scale, *shift;   // folded epilogue: y = act(acc * scale[n] + shift[n])
     int act;
     float act_a;
+    int half_fmt;                 // BF16 kernels: operand format of kind::f16 -- 1 bf16 (3xbf16 split), 0 fp16 (single pass, fp16 front end)
+    const int *gate;              // when set the kernel runs only if *gate == gate_run_if (fp16 front end and its fp32 fallback)
+    int gate_run_if;
 };
 
 template <int BN, int STAGES>
@@ -66,6 +70,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_empty + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (p.gate && __ldg(p.gate) != p.gate_run_if) return;      // the whole grid takes the same branch, before any barrier / TMEM state exists
     constexpr uint32_t TMEM_COLS = 2 * BN;        // two accumulator buffers (256 or 512 columns: powers of two)
     constexpr int BKE = BF16 ? 2 * BK : BK;       // elements per 128-byte k-block
 
@@ -113,8 +118,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         if (lane == 0) {
             // instruction descriptor: D=f32, A=B=tf32, both K-major, N>>3 at bit 17, M>>4 at bit 24
             // (bf16: a/b format 1, kind::f16)
-            constexpr uint32_t fmt = BF16 ? 1u : 2u;
-            constexpr uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+            const uint32_t fmt = BF16 ? (uint32_t)p.half_fmt : 2u;
+            const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
             int stage = 0; uint32_t phase = 0;
             uint32_t it = 0;
             for (long long tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
@@ -346,6 +351,25 @@ __global__ void transpose_weights_bf16_kernel(const float *__restrict__ B, __nv_
     }
 }
 
+// Bt[n][k] = fp16(B[k][n]), zero tail up to kpad; *ovf = 1 when a weight does not fit fp16 (single-pass fp16 front end)
+__global__ void transpose_weights_f16_kernel(const float *__restrict__ B, __half *__restrict__ Bt, int K, int N, int kpad, int *ovf) {
+    __shared__ float tile[32][33];
+    const int k0 = blockIdx.x * 32, n0 = blockIdx.y * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int k = k0 + i, n = n0 + threadIdx.x;
+        tile[i][threadIdx.x] = (k < K && n < N) ? B[(long long)k * N + n] : 0.0f;
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int n = n0 + i, k = k0 + threadIdx.x;
+        if (n < N && k < kpad) {
+            const float v = tile[threadIdx.x][i];
+            if (!(fabsf(v) <= 65504.0f)) *ovf = 1;
+            Bt[(long long)n * kpad + k] = __float2half_rn(v);
+        }
+    }
+}
+
 // scale[n], shift[n] such that act(acc*scale + shift) == act(BN(acc + bias)) up to rounding; the scale also carries the
 // compensation of the A-operand truncation bias (see TF32_TRUNC_BIAS).
 __global__ void fold_epilogue_kernel(const float *bias, const float *bn, float eps, int N, float *scale, float *shift, float comp) {
@@ -368,6 +392,8 @@ float *g_scratch = nullptr;      // Bt | scale | shift
 size_t g_scratch_floats = 0;
 float *g_split = nullptr;        // split mode: hi | lo copies of A
 size_t g_split_floats = 0;
+const int *g_tc_gate = nullptr;  // applied to every tensor-core GEMM launch while set (nntk_cuda_gemm_tc_gate)
+int g_tc_gate_run_if = 0;
 
 }  // namespace
 
@@ -380,6 +406,7 @@ static int launch_tc(const CUtensorMap &ma, const CUtensorMap &mb, TcParams &p, 
         attr_done = true;
     }
     long long grid = p.total_tiles < nntk_cuda_sm_count() ? p.total_tiles : nntk_cuda_sm_count();
+    p.gate = g_tc_gate; p.gate_run_if = g_tc_gate_run_if;
     gemm_tf32_kernel<BN, STAGES, FAST, BF16><<<(unsigned)grid, NUM_THREADS, SL::TOTAL, st>>>(ma, mb, p);
     NNTK_LAUNCH_CHECK("gemm_tf32_kernel");
     return 0;
@@ -509,9 +536,95 @@ extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_
     p.rows = a->rows;
     p.C = a->d_C; p.c_slab = a->c_slab_stride; p.ldc = a->ldc;
     p.scale = scale; p.shift = shift; p.act = a->act; p.act_a = a->act_a;
+    p.half_fmt = 1;
     // FAST epilogue: whole 32-column chunks and 16-byte aligned output rows (every BASELINE shape except the 12-wide TDD)
     if (bf) return BN == 256 ? launch_tc<256, 4, true, true>(ma, mb, p, st) : launch_tc<128, 6, true, true>(ma, mb, p, st);
     if (BN == 32) return fast ? launch_tc<32, 8, true>(ma, mb, p, st) : launch_tc<32, 8, false>(ma, mb, p, st);
     if (BN == 256) return fast ? launch_tc<256, 4, true>(ma, mb, p, st) : launch_tc<256, 4, false>(ma, mb, p, st);
     return fast ? launch_tc<128, 6, true>(ma, mb, p, st) : launch_tc<128, 6, false>(ma, mb, p, st);
+}
+
+// Gate for the NEXT tensor-core GEMM launches (until cleared with a null flag): the kernels return at once unless *flag == run_if.
+// Set and cleared under the API lock by the fp16 front end (host/conv_1d.c) around its fp32 fallback.
+extern "C" void nntk_cuda_gemm_tc_gate(const int *d_flag, int run_if) { g_tc_gate = d_flag; g_tc_gate_run_if = run_if; }
+
+// Single-pass fp16 GEMM of the tensor-core front end: A = fp16 rows produced by nntk_cuda_spectrogram_half (a->d_A points to
+// halves; lda and a_slab_stride count halves), B = fp32 [K][N] repacked to fp16 here, fp32 accumulate, the usual folded epilogue.
+// fp16 and TF32 operands carry the same 10 explicit mantissa bits, at twice the tensor rate and half the operand bytes; what
+// fp16 lacks is range, so *d_ovf is set when a weight does not fit and the kernel itself only runs while *d_ovf == 0 (the
+// spectrogram kernel sets the same flag) -- the caller enqueues its TF32 path behind it, gated the other way.
+// returns 0 done, 1 not eligible, < 0 error.
+extern "C" int nntk_cuda_gemm_f16(const nntk_gemm_args *a, int *d_ovf) {
+    if (!a || !d_ovf || (a->lda & 7) || (a->a_slab_stride & 7) || (((uintptr_t)a->d_A) & 15) || a->rows < 1 || a->batch < 1) return 1;
+    const int K = a->K, N = a->N;
+    if ((N % 32) || (a->ldc % 4) || (a->c_slab_stride % 4) || (((uintptr_t)a->d_C) & 15) || N <= 32) return 1;
+    EncodeTiledFn encode = get_encode();
+    if (!encode) return 1;
+    cudaStream_t st = nntk_stream();
+    const int BKE = 2 * BK;
+    const int kpad = ((K + BKE - 1) / BKE) * BKE;
+    const size_t need = ((size_t)N * kpad + 1) / 2 + 2 * (size_t)N + 64;
+    if (need > g_scratch_floats) {
+        NNTK_CUDA_TRY(cudaStreamSynchronize(st));
+        if (g_scratch) cudaFree(g_scratch);
+        g_scratch = nullptr; g_scratch_floats = 0;
+        NNTK_CUDA_TRY(cudaMalloc(&g_scratch, need * sizeof(float)));
+        g_scratch_floats = need;
+    }
+    __half *Bt = reinterpret_cast<__half *>(g_scratch);
+    float *scale = g_scratch + ((((size_t)N * kpad + 1) / 2 + 3) & ~(size_t)3);
+    float *shift = scale + N;
+    dim3 tb(32, 8), tg((kpad + 31) / 32, (N + 31) / 32);
+    transpose_weights_f16_kernel<<<tg, tb, 0, st>>>(a->d_B, Bt, K, N, kpad, d_ovf);
+    fold_epilogue_kernel<<<(N + 127) / 128, 128, 0, st>>>(a->d_bias, a->d_bn, a->bn_eps, N, scale, shift, 1.0f);
+    NNTK_LAUNCH_CHECK_N("gemm_f16 prologue", 2);
+    const int BN = N > 128 ? 256 : 128;
+    const long long slab = a->batch > 1 ? a->a_slab_stride : (long long)a->rows * a->lda;
+    CUtensorMap ma, mb;
+    {
+        cuuint64_t dims[4] = {(cuuint64_t)K, (cuuint64_t)a->rows, (cuuint64_t)a->batch, 1};
+        cuuint64_t slab_bytes = (cuuint64_t)slab * 2;
+        if (slab_bytes == 0) slab_bytes = 16;
+        cuuint64_t strides[3] = {(cuuint64_t)a->lda * 2, slab_bytes, 16};
+        cuuint32_t box[4] = {(cuuint32_t)BKE, BM, 1, 1};
+        cuuint32_t estr[4] = {1, 1, 1, 1};
+        CUresult r = encode(&ma, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<float *>(a->d_A), dims, strides, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) {
+            nntk_cuda_set_error(NNTK_ERR_CUDA_, "gemm_f16: tensor map for A rejected (CUresult %d): K %d rows %d batch %d lda %d", (int)r, K, a->rows, a->batch, a->lda);
+            return NNTK_ERR_CUDA_;
+        }
+    }
+    {
+        cuuint64_t dims[2] = {(cuuint64_t)kpad, (cuuint64_t)N};
+        cuuint64_t strides[1] = {(cuuint64_t)kpad * 2};
+        cuuint32_t box[2] = {(cuuint32_t)BKE, (cuuint32_t)BN};
+        cuuint32_t estr[2] = {1, 1};
+        CUresult r = encode(&mb, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (void *)Bt, dims, strides, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) {
+            nntk_cuda_set_error(NNTK_ERR_CUDA_, "gemm_f16: tensor map for B rejected (CUresult %d)", (int)r);
+            return NNTK_ERR_CUDA_;
+        }
+    }
+    TcParams p;
+    p.N = N;
+    p.n_tiles = (N + BN - 1) / BN;
+    p.m_tiles_per_slab = (a->rows + BM - 1) / BM;
+    p.kb_pass = (K + BKE - 1) / BKE;
+    p.k_blocks = p.kb_pass;
+    p.c_blocked = 0; p.row_blocks = (a->rows + 31) / 32;
+    p.total_tiles = (long long)p.n_tiles * p.m_tiles_per_slab * a->batch;
+    p.rows = a->rows;
+    p.C = a->d_C; p.c_slab = a->c_slab_stride; p.ldc = a->ldc;
+    p.scale = scale; p.shift = shift; p.act = a->act; p.act_a = a->act_a;
+    p.half_fmt = 0;
+    // runs only while nothing overflowed; an outer gate (there is none in the front end at this point) would be overridden
+    const int *saved = g_tc_gate; const int saved_if = g_tc_gate_run_if;
+    g_tc_gate = d_ovf; g_tc_gate_run_if = 0;
+    const int rc = BN == 256 ? launch_tc<256, 4, true, true>(ma, mb, p, st) : launch_tc<128, 6, true, true>(ma, mb, p, st);
+    g_tc_gate = saved; g_tc_gate_run_if = saved_if;
+    return rc;
 }

@@ -17,6 +17,7 @@
 // O(nfft^2) DFT from the twiddle table otherwise.  Correct for every nfft the reference accepts, not tuned.
 //
 // HBM roofline: algorithmic bytes per clip = 4*input_size + 4*ntime*nfreq.
+#include <cuda_fp16.h>
 #include "common.cuh"
 #define NNTK_SPEC_PACKED 1   // complex adds / subtracts of the butterflies as sm_100 FADD2 / FFMA2 (spectrogram_core.h)
 #include "spectrogram_core.h"
@@ -39,6 +40,10 @@ struct SpecParams {
     int out_pitch;      // floats between output rows (nfreq, or more: the pad columns are written as zeros -- fused front end)
     int n_mels, mel_iter;   // log-mel epilogue (MEL kernels only): bands, work-list entries per lane
     float log_offset;
+    int half_out;       // 1: rows of out_pitch fp16 values (the tensor-core front end's conv operand) instead of floats
+    int *ovf;           // half_out: set to 1 when a value does not fit fp16 (|v| > 65504 or Inf) -- the caller's fp32 fallback then runs
+    const int *gate;    // when set the kernel runs only if *gate == gate_run_if (the fp32 fallback of the fp16 front end)
+    int gate_run_if;
 };
 
 __device__ __forceinline__ float sqrt_approx(float x) {
@@ -137,6 +142,7 @@ spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const floa
     g.clip = gw / p.tiles_per_clip;
     g.t = gw - g.clip * p.tiles_per_clip;
     if (g.clip >= p.n_clips) return;
+    if (p.gate && __ldg(p.gate) != p.gate_run_if) return;
     if (lane == 0) {
         mbar_init(&full[0], 1);
         mbar_init(&full[1], 1);
@@ -167,6 +173,13 @@ spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const floa
     const float2 *x2_ld1 = sx + spec_x2_ld_base(lane, 1);
     const int c1 = spec_lane_c(lane, 0), c2 = spec_lane_c(lane, 1);
     const bool l0 = lane == 0;
+    // fp16 rows: a lane holds bins 64 j + c1 and 64 j + c2 -- never two neighbours.  For every pair of slots (A, B) = (j, j + 1) of
+    // the same half s one shuffle with the lane that holds the neighbouring bin leaves (A[i], A[i+1]) in the lane of an even local
+    // index i and (B[i-1], B[i]) in the lane of an odd one: one 4-byte store per lane, the warp writes 64 + 64 contiguous bytes.
+    const int hi0 = c1, hi1 = l0 ? 0 : 32 - c1;                     // local index of this lane's bin inside the 32-bin group, s = 0 / 1
+    const int hp0 = spec_lane_c1(hi0 ^ 1);                          // lane holding local index i ^ 1 (spec_lane_c1 is an involution)
+    const int hp1 = (hi1 ^ 1) == 0 ? 0 : spec_lane_c1(32 - (hi1 ^ 1));
+    float hmax = 0.0f;                                              // largest |value| this lane stored as fp16
     // PSD: bins 0 and nfreq-1 are not doubled (spectrogram.c:41-47): psd_edge / psd_mid = 0.5
     const float edge = 0.5f;
 
@@ -293,6 +306,32 @@ spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const floa
                 __syncwarp();   // before the next pair's exchange-1 stores overwrite mg / so
                 continue;
             }
+            if (p.half_out) {
+                __half *ha = reinterpret_cast<__half *>(out) + ((long long)g.clip * p.ntime + f0 + fa) * (long long)pitch;
+#pragma unroll
+                for (int s2 = 0; s2 < 2; ++s2) {
+                    const int li = s2 ? hi1 : hi0, lp = s2 ? hp1 : hp0;
+                    const bool ev = !(li & 1);
+#pragma unroll
+                    for (int j = 0; j < 4; j += 2) {
+                        const int A = 4 * s2 + j, B = A + 1;
+                        const float ga = __shfl_sync(0xffffffffu, ev ? pa[B] : pa[A], lp);
+                        const float gb = __shfl_sync(0xffffffffu, ev ? pb[B] : pb[A], lp);
+                        const float a0 = ev ? pa[A] : ga, a1 = ev ? ga : pa[B];       // two neighbouring bins of frame a
+                        const float b0 = ev ? pb[A] : gb, b1 = ev ? gb : pb[B];       // ... of frame b
+                        hmax = fmaxf(hmax, fmaxf(fmaxf(fabsf(a0), fabsf(a1)), fmaxf(fabsf(b0), fabsf(b1))));
+                        __half *dst = ha + 64 * (ev ? j : j + 1) + 32 * s2 + (li & ~1);
+                        *reinterpret_cast<__half2 *>(dst) = __floats2half2_rn(a0, a1);
+                        if (has_b) *reinterpret_cast<__half2 *>(dst + pitch) = __floats2half2_rn(b0, b1);
+                    }
+                }
+                if (256 + 2 * lane < pitch) {        // bin 256 and the zero pad
+                    if (l0) hmax = fmaxf(hmax, fmaxf(fabsf(pa[8]), fabsf(pb[8])));
+                    *reinterpret_cast<__half2 *>(ha + 256 + 2 * lane) = __floats2half2_rn(l0 ? pa[8] : 0.0f, 0.0f);
+                    if (has_b) *reinterpret_cast<__half2 *>(ha + pitch + 256 + 2 * lane) = __floats2half2_rn(l0 ? pb[8] : 0.0f, 0.0f);
+                }
+                continue;
+            }
 #pragma unroll
             for (int slot = 0; slot < 8; ++slot) {
                 float *dst = (slot < 4 ? ra1 : ra2) + 64 * (slot & 3);
@@ -312,6 +351,7 @@ spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const floa
         if (!more) break;
         g = gn;
     }
+    if (p.half_out && p.ovf && !(hmax <= 65504.0f)) *p.ovf = 1;
 }
 
 // ---- generic nfft -------------------------------------------------------------------------------------------------
@@ -384,7 +424,38 @@ spectrogram_generic_kernel(SpecParams p, int nfft, int log2n, const float *__res
 
 }  // namespace
 
-static int spectrogram_run(const nntk_spectrogram_args *a, const nntk_mel_args *m, const float *d_in, float *d_out, int n_clips, int out_pitch = 0);
+static int spectrogram_run(const nntk_spectrogram_args *a, const nntk_mel_args *m, const float *d_in, float *d_out, int n_clips, int out_pitch = 0,
+                           int half_out = 0, int *d_ovf = nullptr);
+
+// Gate for the NEXT 512-point launches (until cleared with a null flag): the kernel returns at once unless *flag == run_if.  Used
+// by the fp16 front end (host/conv_1d.c): its fp32 fallback is enqueued behind the fp16 kernels and only does work when they
+// reported a value outside fp16's range.  Set and cleared under the API lock by the one caller.
+static const int *g_spec_gate = nullptr;
+static int g_spec_gate_run_if = 0;
+extern "C" void nntk_cuda_spectrogram_gate(const int *d_flag, int run_if) { g_spec_gate = d_flag; g_spec_gate_run_if = run_if; }
+
+// The front end's overflow flag: one int per device, in the library's own image (no allocation to manage); host code needs its
+// device address, looked up once per device.
+static __device__ int g_front_flag;
+extern "C" int *nntk_cuda_front_flag(void) {
+    static int *addr[64] = {nullptr};
+    int dev = -1;
+    if (nntk_cuda_ensure_init() || cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    if (!addr[dev]) {
+        int *ptr = nullptr;
+        if (cudaGetSymbolAddress((void **)&ptr, g_front_flag) != cudaSuccess) { (void)cudaGetLastError(); return nullptr; }
+        addr[dev] = ptr;
+    }
+    return addr[dev];
+}
+
+// fp16 rows of `out_pitch` halves (even, nfreq <= out_pitch <= 288): bins as cvt.rn fp16, pad columns zero.  *d_ovf is set to 1
+// when some value does not fit fp16 (the caller then runs its fp32 path; the fp16 rows are garbage in that case).  Returns 1
+// (nothing enqueued) for shapes without the 512-point kernel.
+extern "C" int nntk_cuda_spectrogram_half(const nntk_spectrogram_args *a, const float *d_in, void *d_out_half, int n_clips, int out_pitch, int *d_ovf) {
+    if (!a || a->nfft != NNTK_SPEC_N || out_pitch < a->nfreq + 1 || out_pitch > 288 || (out_pitch & 1) || !d_ovf) return 1;
+    return spectrogram_run(a, nullptr, d_in, reinterpret_cast<float *>(d_out_half), n_clips, out_pitch, 1, d_ovf);
+}
 
 extern "C" int nntk_cuda_spectrogram(const nntk_spectrogram_args *a, const float *d_in, float *d_out, int n_clips) {
     return spectrogram_run(a, nullptr, d_in, d_out, n_clips);
@@ -409,7 +480,8 @@ extern "C" int nntk_cuda_log_mel_spectrogram(const nntk_spectrogram_args *a, con
     return spectrogram_run(a, m, d_in, d_out, n_clips);
 }
 
-static int spectrogram_run(const nntk_spectrogram_args *a, const nntk_mel_args *m, const float *d_in, float *d_out, int n_clips, int out_pitch) {
+static int spectrogram_run(const nntk_spectrogram_args *a, const nntk_mel_args *m, const float *d_in, float *d_out, int n_clips, int out_pitch,
+                           int half_out, int *d_ovf) {
     int rc = nntk_cuda_ensure_init();
     if (rc) return rc;
     if (!a || !d_in || !d_out || n_clips < 0 || a->nfft < 1 || a->window_size < 1 || a->window_size > a->nfft ||
@@ -439,6 +511,8 @@ static int spectrogram_run(const nntk_spectrogram_args *a, const nntk_mel_args *
     p.n_mels = m ? m->n_mels : 0;
     p.mel_iter = m ? m->n_iter : 0;
     p.log_offset = m ? m->log_offset : 0.0f;
+    p.half_out = half_out; p.ovf = d_ovf;
+    p.gate = (a->nfft == NNTK_SPEC_N) ? g_spec_gate : nullptr; p.gate_run_if = g_spec_gate_run_if;
     cudaStream_t st = nntk_stream();
 
     if (a->nfft == NNTK_SPEC_N) {

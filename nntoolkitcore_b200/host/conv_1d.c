@@ -194,10 +194,22 @@ static int front_launch(void *ctx, const float *d_in, float *d_out, long long fi
     int rc = nntk_spectrogram_prepare(fc->s, &sa);
     if (rc) return rc;
     const int cp = fc->pitch;
-    const size_t per_clip = sizeof(float) * (size_t)c->input_size * cp;
+    /* Tensor-core mode: the spectrogram rows are written and read as fp16 -- the same 10 explicit mantissa bits as the TF32 operand
+     * they replace, half the bytes on both sides and twice the tensor rate (C5 front end 13.0 ms -> see DESIGN.md).  fp16 lacks
+     * range, so both fp16 kernels raise a device flag when a value does not fit, and the fp32 / TF32 pair is enqueued right behind
+     * them, gated on that flag: it costs two empty launches when nothing overflowed and produces the result when something did
+     * (audio in int16 scale, huge BatchNorm gains).  NNTK_FRONT_F16=0 disables the fp16 rows. */
+    static int want_f16 = -1;
+    if (want_f16 < 0) { const char *e = getenv("NNTK_FRONT_F16"); want_f16 = e ? atoi(e) : 1; }
+    int *flag = NULL;
+    const int f16 = want_f16 && nntk_cuda_math_mode() == NNTK_MATH_TF32 && cp == 288 && (c->output_feature_channels % 32) == 0 &&
+                    c->output_feature_channels > 32 && (flag = nntk_cuda_front_flag()) != NULL;
+    const size_t rows_f32 = sizeof(float) * (size_t)c->input_size * cp, rows_f16 = rows_f32 / 2;
+    const size_t per_clip = rows_f32 + (f16 ? rows_f16 : 0);
     void *ws = NULL; size_t got = 0;
     if ((rc = nntk_cuda_workspace(per_clip * (size_t)n, per_clip, &ws, &got))) return rc;
     const int chunk = (int)(got / per_clip < (size_t)n ? got / per_clip : (size_t)n);
+    void *ws16 = (char *)ws + rows_f32 * (size_t)chunk;       /* [chunk] fp16 rows behind the [chunk] fp32 rows */
     nntk_gemm_args g;
     g.a_slab_stride = (long long)c->input_size * cp;
     g.lda = c->stride * cp;
@@ -214,12 +226,33 @@ static int front_launch(void *ctx, const float *d_in, float *d_out, long long fi
     g.ldc = c->output_feature_channels;
     for (int b0 = 0; b0 < n; b0 += chunk) {
         const int nb = b0 + chunk <= n ? chunk : n - b0;
-        rc = nntk_cuda_spectrogram_pitched(&sa, d_in + (size_t)b0 * sa.input_size, (float *)ws, nb, cp);
-        if (rc) return rc < 0 ? rc : NNTK_ERR_UNSUPPORTED;
-        g.d_A = (const float *)ws;
         g.batch = nb;
         g.d_C = d_out + (size_t)b0 * c->output_size * c->output_feature_channels;
-        if ((rc = nntk_cuda_gemm(&g))) return rc;
+        int gated = 0;
+        if (f16) {
+            if ((rc = nntk_cuda_memset(flag, 0, sizeof(int)))) return rc;
+            rc = nntk_cuda_spectrogram_half(&sa, d_in + (size_t)b0 * sa.input_size, ws16, nb, cp, flag);
+            if (rc < 0) return rc;
+            if (rc == 0) {
+                g.d_A = (const float *)ws16;
+                rc = nntk_cuda_gemm_f16(&g, flag);
+                if (rc < 0) return rc;
+                gated = 1;      /* rc == 1: the fp16 rows were written but the GEMM is not eligible -- the ungated path below */
+                if (rc == 1) gated = 0;
+            }
+        }
+        if (gated) { nntk_cuda_spectrogram_gate(flag, 1); nntk_cuda_gemm_tc_gate(flag, 1); }
+        rc = nntk_cuda_spectrogram_pitched(&sa, d_in + (size_t)b0 * sa.input_size, (float *)ws, nb, cp);
+        if (rc == 0) {
+            g.d_A = (const float *)ws;
+            if (gated) {
+                /* only the (gated) tensor-core kernel may run here: the FFMA kernel nntk_cuda_gemm falls back to knows no gate */
+                rc = nntk_cuda_gemm_tf32(&g, 0);
+                if (rc == 1) { nntk_cuda_set_error(NNTK_ERR_CUDA, "front end: the TF32 fallback GEMM is not eligible for a shape the fp16 GEMM took"); rc = NNTK_ERR_CUDA; }
+            } else rc = nntk_cuda_gemm(&g);
+        } else if (rc > 0) rc = NNTK_ERR_UNSUPPORTED;
+        if (gated) { nntk_cuda_spectrogram_gate(NULL, 0); nntk_cuda_gemm_tc_gate(NULL, 0); }
+        if (rc) return rc;
     }
     return 0;
 }

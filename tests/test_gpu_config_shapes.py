@@ -217,3 +217,36 @@ def test_fused_recurrent_adaptive_input_passes(tf32, port, scale, passes):
     assert _path(tf32) == "fused_tc"
     assert tf32.NNTKDebugLastRecurrentInputPasses() == passes
     assert_parity(got[pick].cpu().numpy(), want, tol=TF32_TOL, what=f"GRU-256 T=300, inputs x {scale}: {passes} input pass(es)")
+
+
+@pytest.mark.parametrize("gain", [1.0, 3.0e4, 1.0e7])
+def test_front_end_fp16_rows_and_their_fp32_fallback(tf32, ref, gain):
+    """tensor-core mode writes the spectrogram rows as fp16; when a magnitude does not fit fp16 (here: a huge input gain) the kernels
+    raise the device flag and the gated fp32 / TF32 pair behind them produces the result -- every case against the reference chain,
+    the expected flag derived from the reference's own spectrogram"""
+    import ctypes as C
+    import torch
+    n, B = 16000, 6
+    x = np.stack([helpers.audio_clip(70 + i, n) for i in range(B)]) * np.float32(gain)
+
+    def chain(lib):
+        spec = L.Spectrogram(lib, 512, 400, 240, n, 1.0, "hann_window")
+        T0, F = spec.out_shape
+        bn = L.BatchNorm(lib, F, 1e-3, T0); helpers.fill_bn(bn, 520)
+        conv = L.Conv1d(lib, F, 64, 5, 1, T0); helpers.fill_conv(conv, 521)
+        relu = L.Activation(lib, L.ACT_RELU, conv.out_shape[0] * 64)
+        return spec, bn, conv, relu
+    rs, rb, rcv, rrelu = chain(ref)
+    want = np.stack([rrelu.apply(rcv.apply(rb.apply(rs.apply(v)))) for v in x])
+    peak = max(float(np.abs(rs.apply(v)).max()) for v in x)
+    overflowed = int(peak > 65504.0)
+    assert overflowed == (gain >= 1.0e7), f"test set-up: gain {gain} gives a peak magnitude of {peak}"
+    ps, pb, pcv, prelu = chain(tf32)
+    got = L.front_end(tf32, ps, pb, pcv, None, prelu, torch.from_numpy(x).to(torch.device("cuda:0")))
+    torch.cuda.synchronize()
+    tf32.nntk_cuda_front_flag.restype = C.c_void_p
+    flag = torch.zeros(1, dtype=torch.int32, device="cuda:0")
+    assert tf32.nntk_cuda_d2d(C.c_void_p(flag.data_ptr()), C.c_void_p(tf32.nntk_cuda_front_flag()), C.c_size_t(4)) == 0
+    torch.cuda.synchronize()
+    assert int(flag.item()) == overflowed, f"gain {gain}: overflow flag {int(flag.item())}"
+    assert_parity(got.cpu().numpy(), want, tol=TF32_TOL, what=f"front end with fp16 rows, audio gain {gain} (fallback ran: {overflowed})")
