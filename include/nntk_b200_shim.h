@@ -159,6 +159,9 @@ typedef struct {
     int ldc;
 } nntk_gemm_args;
 int nntk_cuda_gemm(const nntk_gemm_args *g);
+/* C = softmax over each whole row of (A B + bias), N <= 32, in the tensor-core GEMM's epilogue (layers/dense.c:122-142 followed by
+ * activation_default.c:149-167 in one kernel).  0 done, 1 not eligible (nothing enqueued), < 0 error */
+int nntk_cuda_gemm_row_softmax(const nntk_gemm_args *g);
 /* the tcgen05 kernel directly (split 0: single-pass TF32, 1: 3xTF32): 0 done, 1 shape not eligible (nothing enqueued), < 0 error */
 int nntk_cuda_gemm_tf32(const nntk_gemm_args *g, int split);
 /* Single-pass fp16-operand tcgen05 GEMM for the tensor-core front end: g->d_A points to fp16 rows (lda / a_slab_stride count

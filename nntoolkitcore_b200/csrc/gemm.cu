@@ -277,6 +277,23 @@ extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *g, int split);   // gem
 // reductions run the FFMA kernel.
 #define NNTK_X3_MAX_K 1536
 
+extern "C" void nntk_cuda_gemm_tc_row_softmax(int on);      // gemm_tc.cu
+// C = softmax_rows(A B + bias) for N <= 32 on the tensor-core kernel, the softmax over each whole output row taken in the GEMM
+// epilogue (TimeDistributedDense + softmax of the KWS chain: saves the second pass over the result).  Same expf / divide as the
+// stand-alone softmax kernel.  Returns 0 done, 1 not eligible (FFMA mode, N > 32, K beyond the X3 cap, shape rules), < 0 error.
+extern "C" int nntk_cuda_gemm_row_softmax(const nntk_gemm_args *a) {
+    int rc = nntk_cuda_ensure_init();
+    if (rc) return rc;
+    if (!a || !a->d_A || !a->d_B || !a->d_C || a->batch < 1 || a->rows < 1 || a->N < 1 || a->N > 32 || a->K < 1 || a->d_bn ||
+        (a->act != NNTK_ACT_NONE && a->act != NNTK_ACT_IDENTITY)) return 1;
+    const int mode = nntk_cuda_math_mode();
+    if (mode == 0 || (mode == 2 && a->K > NNTK_X3_MAX_K)) return 1;
+    nntk_cuda_gemm_tc_row_softmax(1);
+    rc = nntk_cuda_gemm_tf32(a, mode == 2);
+    nntk_cuda_gemm_tc_row_softmax(0);
+    return rc;
+}
+
 extern "C" int nntk_cuda_gemm(const nntk_gemm_args *a) {
     int rc = nntk_cuda_ensure_init();
     if (rc) return rc;

@@ -244,7 +244,27 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                     }
                 } else {
                     tc_ld_32x32(taddr + c0, r);
-                    if (row_ok) {
+                    if (BN == 32 && p.act == NNTK_ACT_SOFTMAX) {
+                        // the whole output row (N <= 32) sits in this thread: softmax over it here instead of a second pass over
+                        // the result (activation_default.c:149-167: e_j = exp(x_j), y_j = e_j / sum, summed in index order, no max shift)
+                        if (row_ok) {
+                            float e[32], sum = 0.0f;
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) {
+                                const int n = n0 + j;
+                                e[j] = 0.0f;
+                                if (n < p.N) { e[j] = expf(fmaf(__uint_as_float(r[j]), __ldg(p.scale + n), __ldg(p.shift + n))); sum += e[j]; }
+                            }
+#pragma unroll
+                            for (int j = 0; j < 32; j += 4) {
+                                const int n = n0 + j;
+                                const float v[4] = {e[j] / sum, e[j + 1] / sum, e[j + 2] / sum, e[j + 3] / sum};
+                                if (vec_ok && n + 3 < p.N) *reinterpret_cast<float4 *>(crow + n) = make_float4(v[0], v[1], v[2], v[3]);
+                                else
+                                    for (int q2 = 0; q2 < 4; ++q2) if (n + q2 < p.N) crow[n + q2] = v[q2];
+                            }
+                        }
+                    } else if (row_ok) {
 #pragma unroll
                         for (int j = 0; j < 32; j += 4) {
                             float v[4];
@@ -392,6 +412,7 @@ float *g_scratch = nullptr;      // Bt | scale | shift
 size_t g_scratch_floats = 0;
 float *g_split = nullptr;        // split mode: hi | lo copies of A
 size_t g_split_floats = 0;
+int g_tc_row_softmax = 0;        // the next launch fuses a softmax over the whole output row (N <= 32) into its epilogue
 const int *g_tc_gate = nullptr;  // applied to every tensor-core GEMM launch while set (nntk_cuda_gemm_tc_gate)
 int g_tc_gate_run_if = 0;
 
@@ -435,7 +456,9 @@ extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_
     // split: 0 single TF32 pass, 1 3xTF32 (fp32 operands split into tf32 hi/lo), 2 3xbf16 (bf16 hi/lo at twice the tensor
     // rate and half the operand bytes; ~2^-16 relative operand error, used by the recurrent projection of the TF32 mode)
     const bool bf = split == 2;
-    const bool fast = c_blocked || ((N % 32 == 0) && (a->ldc % 4 == 0) && (a->c_slab_stride % 4 == 0) && ((((uintptr_t)a->d_C) & 15) == 0));
+    const bool row_softmax = g_tc_row_softmax && N <= 32 && !c_blocked && split != 2;
+    const bool fast = !row_softmax && (c_blocked || ((N % 32 == 0) && (a->ldc % 4 == 0) && (a->c_slab_stride % 4 == 0) && ((((uintptr_t)a->d_C) & 15) == 0)));
+    if (g_tc_row_softmax && !row_softmax) return 1;
     if (bf && (!fast || (a->lda & 7) || (a->a_slab_stride & 7))) return 1;
     const int BKE = bf ? 2 * BK : BK;           // elements per k-block
     const size_t esz = bf ? 2 : 4;
@@ -537,6 +560,7 @@ extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_
     p.C = a->d_C; p.c_slab = a->c_slab_stride; p.ldc = a->ldc;
     p.scale = scale; p.shift = shift; p.act = a->act; p.act_a = a->act_a;
     p.half_fmt = 1;
+    if (row_softmax) p.act = NNTK_ACT_SOFTMAX;
     // FAST epilogue: whole 32-column chunks and 16-byte aligned output rows (every BASELINE shape except the 12-wide TDD)
     if (bf) return BN == 256 ? launch_tc<256, 4, true, true>(ma, mb, p, st) : launch_tc<128, 6, true, true>(ma, mb, p, st);
     if (BN == 32) return fast ? launch_tc<32, 8, true>(ma, mb, p, st) : launch_tc<32, 8, false>(ma, mb, p, st);
@@ -546,6 +570,7 @@ extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_
 
 // Gate for the NEXT tensor-core GEMM launches (until cleared with a null flag): the kernels return at once unless *flag == run_if.
 // Set and cleared under the API lock by the fp16 front end (host/conv_1d.c) around its fp32 fallback.
+extern "C" void nntk_cuda_gemm_tc_row_softmax(int on) { g_tc_row_softmax = on; }
 extern "C" void nntk_cuda_gemm_tc_gate(const int *d_flag, int run_if) { g_tc_gate = d_flag; g_tc_gate_run_if = run_if; }
 
 // Single-pass fp16 GEMM of the tensor-core front end: A = fp16 rows produced by nntk_cuda_spectrogram_half (a->d_A points to

@@ -68,7 +68,13 @@ static int dense_launch(void *ctx, const float *d_in, float *d_out, long long fi
     g.act = (kind == NNTK_ACT_SOFTMAX) ? NNTK_ACT_NONE : kind;
     g.act_a = nntk_act_a(act);
     g.d_C = d_out; g.c_slab_stride = 0; g.ldc = c->output_size;
-    int rc = nntk_cuda_gemm(&g);
+    int rc;
+    if (kind == NNTK_ACT_SOFTMAX && act->vector_size == c->output_size && c->output_size <= 32) {
+        /* the whole row is one softmax vector and fits one epilogue thread: fused into the tensor-core GEMM when that is eligible */
+        rc = nntk_cuda_gemm_row_softmax(&g);
+        if (rc <= 0) return rc;
+    }
+    rc = nntk_cuda_gemm(&g);
     if (rc || kind != NNTK_ACT_SOFTMAX) return rc;
     if (act->vector_size < 1 || c->output_size % act->vector_size) {
         nntk_cuda_set_error(NNTK_ERR_ARG, "Dense: softmax vector_size %d does not divide output_size %d", act->vector_size, c->output_size);
