@@ -166,8 +166,11 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             mbar_wait(&tmem_full[buf], use & 1);
             tc_fence_after();
 #pragma unroll 1
-            constexpr int HALF_COLS = BN >= 64 ? BN / 2 : BN;      // BN = 32: one 32-column chunk, drained by column-half 0 alone
-            for (int c0 = half * HALF_COLS; c0 < (half + 1) * HALF_COLS && c0 < BN; c0 += 32) {
+            // BN = 32: one 32-column chunk per tile -- the two warps of a lane quarter take alternate tiles (= alternate accumulator
+            // buffers), so all eight epilogue warps work (drained by column-half 0 alone, the epilogue bounded the 12-wide TDD)
+            constexpr int HALF_COLS = BN >= 64 ? BN / 2 : BN;
+            const int c_begin = BN >= 64 ? half * HALF_COLS : (((int)(it & 1) == half) ? 0 : BN);
+            for (int c0 = c_begin; c0 < (BN >= 64 ? (half + 1) * HALF_COLS : BN); c0 += 32) {
                 const int n0 = n_t * BN + c0;
                 if (n0 >= p.N) break;                       // warp-uniform
                 uint32_t r[32];
@@ -258,7 +261,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 #pragma unroll
                             for (int j = 0; j < 32; j += 4) {
                                 const int n = n0 + j;
-                                const float v[4] = {e[j] / sum, e[j + 1] / sum, e[j + 2] / sum, e[j + 3] / sum};
+                                const float v[4] = {__fdividef(e[j], sum), __fdividef(e[j + 1], sum), __fdividef(e[j + 2], sum), __fdividef(e[j + 3], sum)};
                                 if (vec_ok && n + 3 < p.N) *reinterpret_cast<float4 *>(crow + n) = make_float4(v[0], v[1], v[2], v[3]);
                                 else
                                     for (int q2 = 0; q2 < 4; ++q2) if (n + q2 < p.N) crow[n + q2] = v[q2];
