@@ -43,7 +43,14 @@ namespace {
 
 constexpr int RF_ROWS = 64;                  // sequences per CTA (pair: 128)
 constexpr int RF_UT = 64;                    // hidden units per tile (pair), 32 per CTA
-constexpr int RF_THREADS_FUSED = 640, RF_THREADS_XW = 640;
+// FUSED mode epilogue warps: 8 (16 hidden units of a tile per thread; 20 warps per CTA) or 16 (8 units per thread; 28 warps, 80
+// registers per epilogue thread).  Measured on the C5 GRU layer (8 192 x 994 steps): 8 warps 7.5 ms, 16 warps 8.25 ms (the
+// register diet spills ~360 bytes per thread and the converters load one k-block at a time) -- so 8 it is; -DRF_FUSED_EPW=16 keeps
+// the experiment buildable.
+#ifndef RF_FUSED_EPW
+#define RF_FUSED_EPW 8
+#endif
+constexpr int RF_THREADS_FUSED = RF_FUSED_EPW == 16 ? 896 : 640, RF_THREADS_XW = 640;
 constexpr int RF_MAX_RING = 8;
 
 struct RfParams {
@@ -210,8 +217,8 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);          // warp-uniform for the compiler (role dispatch, uniform registers)
     // FUSED: 8 epilogue warps (16 units of a tile per thread) + 8 converter warps.  XW: 16 epilogue warps (8 units per thread) -- its
     // epilogue also adds the hoisted projection and, with 8 warps, took 4 700 cycles per LSTM-512 tile against 2 064 of MMA.
-    constexpr int EPW = FUSED ? 8 : 16, UPT = 128 / EPW, NE = UPT / 8;
-    constexpr int CONV_W0 = 8, CTRL_W0 = 16;                 // first converter / control warp
+    constexpr int EPW = FUSED ? RF_FUSED_EPW : 16, UPT = 128 / EPW, NE = UPT / 8;
+    constexpr int CONV_W0 = FUSED ? EPW : 8, CTRL_W0 = FUSED ? EPW + 8 : 16;     // first converter / control warp
     const uint32_t crank = __shfl_sync(0xffffffffu, rf_rank(), 0);   // rank in the cluster (warp-uniform for the compiler); pairs are (0,1), (2,3), ...
     const uint32_t rank = crank & 1u, leader = crank & ~1u; // rank inside the pair, cluster rank of the pair's leader
     // unsplit: the cs / 2 pairs of a cluster work on different slices and share every B stage by multicast (npairs, pair_i).
@@ -274,7 +281,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
 #endif
 
     if (warp >= CTRL_W0) {
-        if (FUSED) asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
+        if (FUSED && RF_FUSED_EPW == 8) asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
         else asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
         if (warp == CTRL_W0) {
             // ===== ring producer: this CTA's half of every B stage (two k-blocks), in the order the MMA issuer consumes them =====
@@ -398,7 +405,8 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         // item (row, 16-byte chunk of the fp16 row = 8 floats): a warp covers 4 rows x 256 contiguous bytes per load instruction and
         // 512 contiguous (swizzled) bytes per store.  x_{t+1} is loaded right after x_t has been converted and waits in registers.
         if (FUSED) {
-            asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
+            if (RF_FUSED_EPW == 8) asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
+            else asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
             const int ct = tid - CONV_W0 * 32;
             const uint32_t xfull0 = rf_mapa(smem_u32(bars + RFB_X_FULL), leader), xlfull0 = rf_mapa(smem_u32(bars + RFB_XL_FULL), leader);
             // item (row, 16-byte chunk of the fp16 row = 8 floats): a warp covers 4 rows x 256 contiguous bytes per load instruction and
@@ -418,11 +426,12 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 return (size_t)kb * (RF_ROWS * 128) + r * 128 + ((ch ^ (r & 7)) << 4);
             };
             auto preload = [&](int t) {
+                constexpr int KK = RF_FUSED_EPW == 8 ? 2 : 1;   // k-blocks of loads in flight at a time (64 registers per converter thread: one)
 #pragma unroll
-                for (int k2 = 0; k2 < 4; k2 += 2) {          // two k-blocks of loads in flight at a time
-                    float4 a[2][2][2];
+                for (int k2 = 0; k2 < 4; k2 += KK) {
+                    float4 a[KK][2][2];
 #pragma unroll
-                    for (int kk = 0; kk < 2; ++kk)
+                    for (int kk = 0; kk < KK; ++kk)
 #pragma unroll
                         for (int it = 0; it < 2; ++it) {
                             const float4 *src = (k2 + kk < KBX && it < nit) ? src_of(t, k2 + kk, it) : nullptr;
@@ -430,7 +439,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                             else a[kk][it][0] = a[kk][it][1] = make_float4(0.f, 0.f, 0.f, 0.f);
                         }
 #pragma unroll
-                    for (int kk = 0; kk < 2; ++kk)
+                    for (int kk = 0; kk < KK; ++kk)
 #pragma unroll
                         for (int it = 0; it < 2; ++it) {
                             const float4 u = a[kk][it][0], w = a[kk][it][1];
@@ -485,7 +494,8 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         }
     } else {
         // ===== epilogue (warps 0..7): thread = row m of this CTA x 16 hidden units of every tile =====
-        if (FUSED) asm volatile("setmaxnreg.inc.sync.aligned.u32 128;");
+        if (FUSED && RF_FUSED_EPW == 8) asm volatile("setmaxnreg.inc.sync.aligned.u32 128;");
+        else if (FUSED) asm volatile("setmaxnreg.inc.sync.aligned.u32 80;");
         else asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");
         const int ew = warp, q = warp & 3, j = ew >> 2;
         const int m = (q & 1) * 32 + lane, hf = q >> 1;
@@ -970,10 +980,11 @@ extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, c
         // per-warp pieces of h_t: FUSED [32 rows][16 floats] (SWIZZLE_64B), XW [32 rows][8 floats] (unswizzled)
         cuuint64_t dims[3] = {(cuuint64_t)H, (cuuint64_t)T, (cuuint64_t)nb};
         cuuint64_t strides[2] = {(cuuint64_t)H * 4, (cuuint64_t)T * H * 4};
-        cuuint32_t box[3] = {(cuuint32_t)(fused ? 16 : 8), 1, 32};
+        const bool wide = fused && RF_FUSED_EPW == 8;
+        cuuint32_t box[3] = {(cuuint32_t)(wide ? 16 : 8), 1, 32};
         cuuint32_t es[3] = {1, 1, 1};
         CUresult cr = encode(&mo, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, out, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                             fused ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                             wide ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (cr != CUDA_SUCCESS) { nntk_cuda_set_error(NNTK_ERR_CUDA_, "recurrent_fused: output tensor map rejected (CUresult %d)", (int)cr); return NNTK_ERR_CUDA_; }
     } else mo = mu;
     p.B = nb; p.T = T; p.return_sequences = r->return_sequences;
