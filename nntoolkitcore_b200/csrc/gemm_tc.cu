@@ -41,6 +41,8 @@ struct TcParams {
     int act;
     float act_a;
     int half_fmt;                 // BF16 kernels: operand format of kind::f16 -- 1 bf16 (3xbf16 split), 0 fp16 (single pass, fp16 front end)
+    int cs;                       // cluster size (1, 2 or 4; needs n_tiles == 1): the CTAs of a cluster walk their tiles in lockstep and
+                                  // each fetches 1 / cs of every B stage, multicast to all -- the weight stream leaves L2 once per cluster
     const int *gate;              // when set the kernel runs only if *gate == gate_run_if (fp16 front end and its fp32 fallback)
     int gate_run_if;
 };
@@ -54,6 +56,21 @@ struct SmemLayout {
     static constexpr int STG_OFFSET = BAR_OFFSET + 256;                         // epilogue staging: 8 warps x 2 KB
     static constexpr int TOTAL = STG_OFFSET + 8 * 2048 + 1024;                  // + alignment slack
 };
+
+__device__ __forceinline__ uint32_t tc_cluster_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void tc_cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// 2-D tile load multicast to the CTAs of `mask`: same shared-memory offset and same mbarrier offset in each of them
+__device__ __forceinline__ void tma_load_2d_mc(void *dst, const CUtensorMap *map, uint64_t *bar, int c0, int c1, uint16_t mask) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
+                 ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(mask) : "memory");
+}
+// commit arriving on the barrier at this offset in every CTA of `mask`
+__device__ __forceinline__ void tc_commit_mc(uint64_t *bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"(mask) : "memory");
+}
 
 // BF16 = true: the operands are bf16 (kind::f16, K = 16 per MMA, 64 elements per 128-byte k-block) -- the 3xbf16 split mode
 // of the hoisted recurrent projection.  Byte-wise the stages, swizzle and descriptors are the same as for tf32.
@@ -77,7 +94,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
-        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], (uint32_t)p.cs); }
         for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -87,14 +104,22 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     }
     tc_fence_before();
     __syncthreads();
+    if (p.cs > 1) tc_cluster_sync();            // every CTA's barriers exist before a peer's multicast or commit can reach them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // Clusters walk in lockstep: every CTA runs the same number of tiles; surplus iterations redo the last tile without storing it.
+    const long long n_iter = (p.total_tiles + gridDim.x - 1) / gridDim.x;
+    const uint16_t mc_mask = (uint16_t)((1u << p.cs) - 1u);
 
     if (warp == 0) {
         // ===== TMA producer =====
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
-            for (long long tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+            const uint32_t crank = p.cs > 1 ? tc_cluster_rank() : 0u;
+            const int b_rows = BN / p.cs;               // this CTA's slice of every B stage
+            for (long long i = 0; i < n_iter; ++i) {
+                long long tile = blockIdx.x + i * gridDim.x;
+                if (tile >= p.total_tiles) tile = p.total_tiles - 1;
                 const int n_t = (int)(tile % p.n_tiles);
                 const long long rest = tile / p.n_tiles;
                 const int m_t = (int)(rest % p.m_tiles_per_slab);
@@ -108,7 +133,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                     // with the number of accumulation steps at full magnitude), so they run while the sum is still tiny.
                     const int pass = kb / p.kb_pass, akb = kb - pass * p.kb_pass;
                     tma_load_4d(sa, &map_a, &full_bar[stage], akb * BKE, m_t * BM, slab, pass == 1 ? 1 : 0);
-                    tma_load_2d(sa + SL::A_BYTES, &map_b, &full_bar[stage], kb * BKE, n_t * BN);
+                    if (p.cs == 1) tma_load_2d(sa + SL::A_BYTES, &map_b, &full_bar[stage], kb * BKE, n_t * BN);
+                    else tma_load_2d_mc(sa + SL::A_BYTES + crank * b_rows * 128, &map_b, &full_bar[stage], kb * BKE, n_t * BN + (int)crank * b_rows, mc_mask);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -122,7 +148,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
             int stage = 0; uint32_t phase = 0;
             uint32_t it = 0;
-            for (long long tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+            for (long long i = 0; i < n_iter; ++i, ++it) {
                 const uint32_t buf = it & 1, use = it >> 1;
                 mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);     // epilogue has drained this accumulator
                 tc_fence_after();
@@ -138,7 +164,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                         if (BF16) tc_mma_f16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
                         else tc_mma_tf32(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
                     }
-                    tc_commit(&empty_bar[stage]);               // smem stage free once these MMAs have read it
+                    if (p.cs == 1) tc_commit(&empty_bar[stage]);   // smem stage free once these MMAs have read it
+                    else tc_commit_mc(&empty_bar[stage], mc_mask); // ... in every CTA of the cluster: each of them writes part of it
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
                 tc_commit(&tmem_full[buf]);                      // accumulator complete
@@ -152,12 +179,21 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         uint8_t *stg = smem + SL::STG_OFFSET + (warp - 2) * 2048;      // [32 rows][64 bytes], xor-swizzled 16-byte slots
         uint32_t it = 0;
         const bool vec_ok = ((p.ldc & 3) == 0) && ((p.c_slab & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
-        for (long long tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+        for (long long i = 0; i < n_iter; ++i, ++it) {
+            const long long tile = blockIdx.x + i * gridDim.x;
+            const uint32_t buf = it & 1, use = it >> 1;
+            if (tile >= p.total_tiles) {             // lockstep filler: nothing to store
+                mbar_wait(&tmem_full[buf], use & 1);
+                tc_fence_after();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+                continue;
+            }
             const int n_t = (int)(tile % p.n_tiles);
             const long long rest = tile / p.n_tiles;
             const int m_t = (int)(rest % p.m_tiles_per_slab);
             const long long slab = rest / p.m_tiles_per_slab;
-            const uint32_t buf = it & 1, use = it >> 1;
             const int row = m_t * BM + row_in_tile;
             const bool row_ok = row < p.rows;
             float *crow = p.C + slab * p.c_slab + (long long)row * p.ldc;
@@ -165,11 +201,11 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             const uint32_t taddr = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16);
             mbar_wait(&tmem_full[buf], use & 1);
             tc_fence_after();
-#pragma unroll 1
             // BN = 32: one 32-column chunk per tile -- the two warps of a lane quarter take alternate tiles (= alternate accumulator
             // buffers), so all eight epilogue warps work (drained by column-half 0 alone, the epilogue bounded the 12-wide TDD)
             constexpr int HALF_COLS = BN >= 64 ? BN / 2 : BN;
             const int c_begin = BN >= 64 ? half * HALF_COLS : (((int)(it & 1) == half) ? 0 : BN);
+#pragma unroll 1
             for (int c0 = c_begin; c0 < (BN >= 64 ? (half + 1) * HALF_COLS : BN); c0 += 32) {
                 const int n0 = n_t * BN + c0;
                 if (n0 >= p.N) break;                       // warp-uniform
@@ -293,6 +329,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     }
     tc_fence_before();
     __syncthreads();
+    if (p.cs > 1) tc_cluster_sync();            // nobody leaves while a peer's multicast or commit could still touch this CTA
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
@@ -415,6 +452,7 @@ float *g_scratch = nullptr;      // Bt | scale | shift
 size_t g_scratch_floats = 0;
 float *g_split = nullptr;        // split mode: hi | lo copies of A
 size_t g_split_floats = 0;
+int g_tc_cluster = 1;            // cluster size requested for the NEXT launch (its B tensor map must have been encoded with BN / cs rows)
 int g_tc_row_softmax = 0;        // the next launch fuses a softmax over the whole output row (N <= 32) into its epilogue
 const int *g_tc_gate = nullptr;  // applied to every tensor-core GEMM launch while set (nntk_cuda_gemm_tc_gate)
 int g_tc_gate_run_if = 0;
@@ -431,6 +469,24 @@ static int launch_tc(const CUtensorMap &ma, const CUtensorMap &mb, TcParams &p, 
     }
     long long grid = p.total_tiles < nntk_cuda_sm_count() ? p.total_tiles : nntk_cuda_sm_count();
     p.gate = g_tc_gate; p.gate_run_if = g_tc_gate_run_if;
+    p.cs = g_tc_cluster;
+    g_tc_cluster = 1;
+    if (p.cs > 1 && (p.n_tiles != 1 || grid < p.cs || (BN / p.cs) % 8)) {        // the caller encoded B for slices: it must have checked
+        nntk_cuda_set_error(NNTK_ERR_CUDA_, "gemm_tc: cluster of %d requested for a launch that cannot take it", p.cs);
+        return NNTK_ERR_CUDA_;
+    }
+    if (p.cs > 1) {
+        grid -= grid % p.cs;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(NUM_THREADS); cfg.dynamicSmemBytes = SL::TOTAL; cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = (unsigned)p.cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        NNTK_CUDA_TRY(cudaLaunchKernelEx(&cfg, gemm_tf32_kernel<BN, STAGES, FAST, BF16>, ma, mb, p));
+        nntk_cuda_count_launch(1);
+        return 0;
+    }
     gemm_tf32_kernel<BN, STAGES, FAST, BF16><<<(unsigned)grid, NUM_THREADS, SL::TOTAL, st>>>(ma, mb, p);
     NNTK_LAUNCH_CHECK("gemm_tf32_kernel");
     return 0;
@@ -608,6 +664,15 @@ extern "C" int nntk_cuda_gemm_f16(const nntk_gemm_args *a, int *d_ovf) {
     NNTK_LAUNCH_CHECK_N("gemm_f16 prologue", 2);
     const int BN = N > 128 ? 256 : 128;
     const long long slab = a->batch > 1 ? a->a_slab_stride : (long long)a->rows * a->lda;
+    // Every tile streams the whole weight matrix (N <= BN: one n-tile).  Measured on the C5 conv (ncu, 8 192 clips): 148 CTAs each
+    // pulling their own copy: 5.65 ms, 87.6 GB through L2, tensor pipe 69.5 % active; clusters of 2 sharing each B stage by
+    // multicast: 5.31 ms, 65.7 GB, 73 %; clusters of 4: 8.7 ms (53 GB, 37 %: four CTAs in lockstep on a 4-stage ring stall each
+    // other).  What is left is shared-memory bandwidth: per 128-cycle MMA 12 KB of operand reads + 12 KB of TMA writes.
+    static int want_cs = -1;
+    if (want_cs < 0) { const char *e = getenv("NNTK_GEMM_CLUSTER"); want_cs = e ? atoi(e) : 2; if (want_cs != 1 && want_cs != 2 && want_cs != 4) want_cs = 2; }
+    const long long tiles_total = (long long)((a->rows + BM - 1) / BM) * a->batch;
+    int cs = (N <= BN && tiles_total >= 2LL * nntk_cuda_sm_count()) ? want_cs : 1;
+    while (cs > 1 && ((BN / cs) % 8 || nntk_cuda_sm_count() % cs)) cs >>= 1;
     CUtensorMap ma, mb;
     {
         cuuint64_t dims[4] = {(cuuint64_t)K, (cuuint64_t)a->rows, (cuuint64_t)a->batch, 1};
@@ -627,7 +692,7 @@ extern "C" int nntk_cuda_gemm_f16(const nntk_gemm_args *a, int *d_ovf) {
     {
         cuuint64_t dims[2] = {(cuuint64_t)kpad, (cuuint64_t)N};
         cuuint64_t strides[1] = {(cuuint64_t)kpad * 2};
-        cuuint32_t box[2] = {(cuuint32_t)BKE, (cuuint32_t)BN};
+        cuuint32_t box[2] = {(cuuint32_t)BKE, (cuuint32_t)(BN / cs)};
         cuuint32_t estr[2] = {1, 1};
         CUresult r = encode(&mb, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (void *)Bt, dims, strides, box, estr,
                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -652,6 +717,7 @@ extern "C" int nntk_cuda_gemm_f16(const nntk_gemm_args *a, int *d_ovf) {
     // runs only while nothing overflowed; an outer gate (there is none in the front end at this point) would be overridden
     const int *saved = g_tc_gate; const int saved_if = g_tc_gate_run_if;
     g_tc_gate = d_ovf; g_tc_gate_run_if = 0;
+    g_tc_cluster = cs;
     const int rc = BN == 256 ? launch_tc<256, 4, true, true>(ma, mb, p, st) : launch_tc<128, 6, true, true>(ma, mb, p, st);
     g_tc_gate = saved; g_tc_gate_run_if = saved_if;
     return rc;

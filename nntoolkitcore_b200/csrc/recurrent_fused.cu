@@ -112,6 +112,16 @@ __device__ __forceinline__ bool rf_elect() {
     asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
     return pred != 0;
 }
+// shared-memory accesses by 32-bit shared address: through generic pointers the compiler emitted LD.E / ST.E (address-space
+// resolution per access) in the epilogue's dependent chain
+__device__ __forceinline__ float4 rf_lds128(uint32_t a) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void rf_sts128(uint32_t a, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
+}
 __device__ __forceinline__ void rf_fence_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 // TMA 2-D load, multicast to the CTAs of `mask` (same shared-memory offset in each); with .cta_group::2 the bytes are counted on
 // the barrier at offset `bar` (peer bit cleared) in the PAIR LEADER of every destination CTA -- CUTLASS's SM100_TMA_2SM_LOAD_MULTICAST
@@ -506,6 +516,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         const uint32_t hfull1 = rf_mapa(smem_u32(bars + RFB_H_FULL), leader ^ 2u);       // split mode: the other pair's leader
         const uint32_t sAh_peer = rf_mapa(smem_u32(sAh), crank ^ 2u);                    // split mode: the same rows' A tile in the other pair
         const int sw = m & 7;
+        const uint32_t sBias_a = smem_u32(sBias), sAh_a = smem_u32(sAh), sOut_a = smem_u32(sOut);
         if (p.rows == RF_ROWS || !(q & 1)) {       // 32-row mode: lane quarters 1 and 3 hold no sequences
         // ---- prologue: state into TMEM, fp16 h_0 into the A tile, zero the h.Uh groups
         for (int c = 0; c < NCT; ++c) {                  // the A tile holds ALL of h; TMEM only the state of this pair's tiles
@@ -613,8 +624,8 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                     float b0[8], b1[8], b2[8], b3[8];
 #pragma unroll
                     for (int i = 0; i < 2; ++i) {
-                        const float4 v0 = *reinterpret_cast<const float4 *>(sBias + 0 * H + ub + 4 * i), v1 = *reinterpret_cast<const float4 *>(sBias + 1 * H + ub + 4 * i),
-                                     v2 = *reinterpret_cast<const float4 *>(sBias + 2 * H + ub + 4 * i), v3 = *reinterpret_cast<const float4 *>(sBias + 3 * H + ub + 4 * i);
+                        const float4 v0 = rf_lds128(sBias_a + 4u * (uint32_t)(0 * H + ub + 4 * i)), v1 = rf_lds128(sBias_a + 4u * (uint32_t)(1 * H + ub + 4 * i)),
+                                     v2 = rf_lds128(sBias_a + 4u * (uint32_t)(2 * H + ub + 4 * i)), v3 = rf_lds128(sBias_a + 4u * (uint32_t)(3 * H + ub + 4 * i));
                         b0[4 * i] = v0.x; b0[4 * i + 1] = v0.y; b0[4 * i + 2] = v0.z; b0[4 * i + 3] = v0.w;
                         b1[4 * i] = v1.x; b1[4 * i + 1] = v1.y; b1[4 * i + 2] = v1.z; b1[4 * i + 3] = v1.w;
                         b2[4 * i] = v2.x; b2[4 * i + 1] = v2.y; b2[4 * i + 2] = v2.z; b2[4 * i + 3] = v2.w;
@@ -652,12 +663,13 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                     // 32-byte rows, unswizzled) -> one TMA store per warp: no CTA-wide barrier in the epilogue (first version: two
                     // bar.sync + a store wait per tile)
                     uint8_t *o = sOut + ew * (32 * UPT * 4);
+                    const uint32_t o_a = sOut_a + (uint32_t)(ew * (32 * UPT * 4));
                     { RF_T0(); if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); RF_T1(11); }    // the previous store has read it
                     __syncwarp();
 #pragma unroll
                     for (int i = 0; i < UPT / 4; ++i)
-                        *reinterpret_cast<float4 *>(o + lane * (UPT * 4) + ((UPT == 16 ? (i ^ ((lane >> 1) & 3)) : i) << 4)) =
-                            make_float4(hn[4 * i], hn[4 * i + 1], hn[4 * i + 2], hn[4 * i + 3]);
+                        rf_sts128(o_a + (uint32_t)(lane * (UPT * 4) + ((UPT == 16 ? (i ^ ((lane >> 1) & 3)) : i) << 4)),
+                                  __float_as_uint(hn[4 * i]), __float_as_uint(hn[4 * i + 1]), __float_as_uint(hn[4 * i + 2]), __float_as_uint(hn[4 * i + 3]));
                     rf_fence_async();
                     __syncwarp();
                     if (lane == 0) {
@@ -678,7 +690,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                             for (int e = 0; e < NE; ++e) {
                                 const int ch = (hf * 32 + j * UPT) / 8 + e;
                                 const uint32_t off = (uint32_t)((tile0 + cc) * (RF_ROWS * 128) + m * 128 + ((ch ^ sw) << 4));
-                                *reinterpret_cast<uint4 *>(sAh + off) = make_uint4(hpend[cc][4 * e], hpend[cc][4 * e + 1], hpend[cc][4 * e + 2], hpend[cc][4 * e + 3]);
+                                rf_sts128(sAh_a + off, hpend[cc][4 * e], hpend[cc][4 * e + 1], hpend[cc][4 * e + 2], hpend[cc][4 * e + 3]);
                                 if (S == 2)
                                     asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sAh_peer + off), "r"(hpend[cc][4 * e]), "r"(hpend[cc][4 * e + 1]),
                                                  "r"(hpend[cc][4 * e + 2]), "r"(hpend[cc][4 * e + 3]) : "memory");
