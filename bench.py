@@ -40,7 +40,7 @@ sys.path.insert(0, str(ROOT / "tests"))
 METRIC = "audio-sec/sec"
 MODES = {"fp32": 0, "tf32": 1, "x3": 2}
 DTYPE = {"fp32": "f32 (FFMA, 1e-5 contract)",
-         "tf32": "tf32 conv/dense + f16-operand recurrent steps on tcgen05, f32 accumulate and state (stated tolerance 1e-3)",
+         "tf32": "tf32 conv/dense (f16 operands in the fused front end) + f16-operand recurrent steps on tcgen05, f32 accumulate and state (stated tolerance 1e-3)",
          "x3": "3xTF32 split operands on tcgen05, f32-equivalent (1e-5 contract)"}
 CLIP_N, CLIP_S = 160000, 10.0
 
@@ -255,9 +255,11 @@ def build_c5(env, units, with_input=True):
     tmode = env.args.mode != "fp32"
     if fused_front:
         stages = [("spectrogram+BN+conv+ReLU (fused front end)", front,
-                   dict(bound="tensor" if tmode else "ffma", flop=conv_flop, kind="tf32", bytes=4.0 * units * (CLIP_N + T1 * 256), kernels=2,
-                        note="two kernels: K1 at the conv's row pitch (HBM-bound) + the implicit GEMM (tensor-bound); "
-                             "profiles/r2_launches_c5.csv: 3.8 ms + 8.9 ms at 8 192 clips"))]
+                   dict(bound="tensor" if tmode else "ffma", flop=conv_flop, kind="f16" if env.args.mode == "tf32" else "tf32",
+                        bytes=4.0 * units * (CLIP_N + T1 * 256), kernels=2,
+                        note="two kernels: K1 writing fp16 rows at the conv's pitch (instruction-bound) + the single-pass fp16 implicit GEMM "
+                             "(2-CTA clusters share the weight stream); profiles/r2_launches_c5.csv: 4.0 ms + 5.3 ms at 8 192 clips; "
+                             "two empty gated launches of the fp32 fallback ride behind them"))]
     else:
         stages = [("spectrogram", lambda: spec.apply_batch(x, s), dict(bound="hbm", bytes=spec_bytes)),
                   ("batchnorm", lambda: bn.apply_batch(s, s), dict(bound="hbm", bytes=8.0 * units * T0 * F)),
