@@ -64,6 +64,8 @@ struct RfParams {
     int xp;                          // FUSED: input passes the launch is PLANNED for (shared memory, packed operands), 1 or 3
     const float *stats;              // adaptive input passes: {max_rows |x_t|^2, max_cols |W_n|^2, passes taken (written by the kernel)}
     float adapt_thr;                 //   3 planned passes drop to 1 when sqrt(stats[0] * stats[1]) <= adapt_thr (see rf_xpasses_note)
+    int per_step;                    // 1: the decision is taken per pair and per STEP inside the kernel (no pre-scan of x): the converter warps publish
+                                     //    max |x_t|^2 of their rows with the x tile, the issuer skips the two correction passes' MMAs for that step
     int cs;                          // cluster size: 2, 4 or 8 CTAs = 1, 2 or 4 pairs sharing every B stage by TMA multicast
     int xw_blocked_rows;             // XW mode: row_blocks of the blocked projection
     const float *x;                  // FUSED: [B][T][in]
@@ -106,6 +108,15 @@ __device__ __forceinline__ uint32_t rf_mapa(uint32_t a, uint32_t rank) {
 // ERRBAR resp. a CCTL.IVALL per signal (ncu, first version: membar 3.1 of 16 stall cycles per issue).
 __device__ __forceinline__ void rf_arrive_cl(uint32_t a) {
     asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(a) : "memory");
+}
+// cluster-scope acquire / release pair for GENERIC data that crosses the pair (the converters' row norms): only the converter warps
+// and one issuer wait per step pay for it
+__device__ __forceinline__ void rf_mbar_wait_cl(uint64_t *bar, uint32_t parity) {
+    asm volatile("{\n\t.reg .pred p;\n\tWLC:\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n\t@p bra WDC;\n\tbra WLC;\n\tWDC:\n\t}"
+                 ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void rf_arrive_cl_release(uint32_t a) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(a) : "memory");
 }
 __device__ __forceinline__ bool rf_elect() {
     uint32_t pred;
@@ -210,7 +221,8 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     // ~2^-12 * sqrt(2/3) * |x_t| * |W_n| / ... of noise into every pre-activation of every step; when a pre-scan of this call's x
     // and W bounds |x_t| |W_n| by adapt_thr that noise stays ~4x under the mode's 1e-3 and the passes are skipped (rf_xpasses_note).
     // Every role of every CTA evaluates the same two numbers, so the whole grid takes the same branch.
-    const int XP = (p.xp == 3 && p.stats && sqrtf(__ldg(p.stats) * __ldg(p.stats + 1)) <= p.adapt_thr) ? 1 : p.xp;
+    const bool PS = FUSED && p.per_step && p.xp == 3 && p.stats;      // per-step decision: everything is staged for three passes
+    const int XP = PS ? 3 : ((p.xp == 3 && p.stats && sqrtf(__ldg(p.stats) * __ldg(p.stats + 1)) <= p.adapt_thr) ? 1 : p.xp);
     const int H = p.H, IN = p.in, T = p.T;
     const int S = p.split;                                  // pairs per slice (1 or 2)
     const int NCT = H / RF_UT, NC = NCT / S;                // tiles per step: of the layer / of this pair
@@ -222,6 +234,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     float *sBias = reinterpret_cast<float *>(smem + pl.bias);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + pl.bars);
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + RFB_END);
+    float *xs = reinterpret_cast<float *>(smem + pl.bars + 512);     // [2][16] max |x_t|^2 per converter warp of the pair (leader CTA's copy is read)
 
     const int tid = threadIdx.x, lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);          // warp-uniform for the compiler (role dispatch, uniform registers)
@@ -242,7 +255,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     // tile counters are 32-bit and advanced incrementally everywhere: 64-bit divisions in the issuer's loop cost ~13 000 cycles per
     // step in the first version (more than all of the step's MMAs)
 
-    if (tid == 0 && blockIdx.x == 0 && p.stats) const_cast<float *>(p.stats)[2] = (float)XP;
+    if (tid == 0 && blockIdx.x == 0 && p.stats && !PS) const_cast<float *>(p.stats)[2] = (float)XP;
     if (tid == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_wl) : "memory");
@@ -365,12 +378,38 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 RF_T1(13); }
                 if (++stage == p.ring_stages) { stage = 0; phase ^= 1; }
             };
+            // a ring stage whose MMAs this pair does not need (per-step decision: one pass): consume it and hand it back
+            auto stage_skip = [&]() {
+                { RF_T0(); mbar_wait(bars + RFB_RING_FULL + stage, phase); RF_T1(0); }
+                if (rf_elect()) rf_commit(bars + RFB_RING_EMPTY + stage, all_mask);
+                __syncwarp();
+                if (++stage == p.ring_stages) { stage = 0; phase ^= 1; }
+            };
+            const float wstat = PS ? __ldg(p.stats + 1) : 0.0f;
+            int xp_t = XP, any3 = 0;     // passes of the step whose input parts are being issued
             // (t, c) = step and tile; buf = accumulator buffer of the tile, use = how often that buffer has been used before
             auto x_part = [&](int t, int c, int buf, int use) {
                 if (use > 0) { RF_T0(); mbar_wait(bars + RFB_ACC_EMPTY + buf, (uint32_t)((use - 1) & 1)); RF_T1(1); }
                 tc_fence_after();
                 const uint32_t d = tmem + (uint32_t)(buf * 128);
-                if (c == 0) { RF_T0(); mbar_wait(bars + RFB_X_FULL, (uint32_t)(t & 1)); RF_T1(3); }       // the hi image of x_t
+                if (c == 0) {            // the hi image of x_t (and, per-step mode, the row norms the converters published with it)
+                    RF_T0();
+                    if (PS) rf_mbar_wait_cl(bars + RFB_X_FULL, (uint32_t)(t & 1)); else mbar_wait(bars + RFB_X_FULL, (uint32_t)(t & 1));
+                    RF_T1(3);
+                    if (PS) {
+                        float mx = 0.0f;
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) mx = fmaxf(mx, xs[(t & 1) * 16 + i]);
+                        xp_t = (sqrtf(mx * wstat) <= p.adapt_thr) ? 1 : 3;       // Inf stays, NaN rows were dropped by fmaxf
+                        any3 |= xp_t == 3;
+                    }
+                }
+                if (PS && xp_t == 1) {   // everything was staged for three passes; this step takes one
+                    for (int kb = 0; kb < KBX; kb += 2) stage_skip();
+                    for (int kb = 0; kb < KBX; kb += 2) stage_mmas(d, xh_a, 0u, kb, min(2, KBX - kb), true);
+                    // the lo image still arrives every step: keep the barrier phases in step (late: it is long there)
+                    if (c == NC - 1) for (int i = 0; i < KBX; ++i) mbar_wait(bars + RFB_XL_FULL + i, (uint32_t)(t & 1));
+                } else
                 if (XP == 3) {           // small terms first: x_hi . W_lo, then x_lo . W_hi + x_hi . W_hi off the same W_hi stage
                     for (int kb = 0; kb < KBX; kb += 2) stage_mmas(d, xh_a, 0u, kb, min(2, KBX - kb), true);
                     for (int kb = 0; kb < KBX; kb += 2) {
@@ -407,6 +446,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                     if (FUSED && !(t == T - 1 && c == NC - 1)) x_part(c + 1 == NC ? t + 1 : t, c + 1 == NC ? 0 : c + 1, nbuf, nuse);
                     buf = nbuf; use = nuse;
                 }
+            if (PS && lane == 0) atomicMax(reinterpret_cast<int *>(const_cast<float *>(p.stats) + 2), __float_as_int(any3 ? 3.0f : 1.0f));
             RF_DBG(if (lane == 0) { for (int i = 0; i < 4; ++i) p.dbg[blockIdx.x * 16 + i] = dbgc[i]; p.dbg[blockIdx.x * 16 + 10] = clock64() - t_start;
                    p.dbg[blockIdx.x * 16 + 12] = dbgc[12]; p.dbg[blockIdx.x * 16 + 13] = dbgc[13]; });
         }
@@ -435,7 +475,10 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 const int idx = it * 256 + ct, r = idx >> 3, ch = idx & 7;
                 return (size_t)kb * (RF_ROWS * 128) + r * 128 + ((ch ^ (r & 7)) << 4);
             };
+            // per-step mode: this warp's max |x_t|^2 over its rows, published to the leader CTA with the x tile
+            const uint32_t xs_leader = rf_mapa(smem_u32(xs), leader) + 4u * (uint32_t)((int)rank * 8 + (ct >> 5));
             auto preload = [&](int t) {
+                float ss[2] = {0.0f, 0.0f};     // sum of squares of this thread's chunk of its two rows, over the k-blocks
                 constexpr int KK = RF_FUSED_EPW == 8 ? 2 : 1;   // k-blocks of loads in flight at a time (64 registers per converter thread: one)
 #pragma unroll
                 for (int k2 = 0; k2 < 4; k2 += KK) {
@@ -453,8 +496,19 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
 #pragma unroll
                         for (int it = 0; it < 2; ++it) {
                             const float4 u = a[kk][it][0], w = a[kk][it][1];
+                            if (PS) ss[it] = fmaf(u.x, u.x, fmaf(u.y, u.y, fmaf(u.z, u.z, fmaf(u.w, u.w, fmaf(w.x, w.x, fmaf(w.y, w.y, fmaf(w.z, w.z, fmaf(w.w, w.w, ss[it]))))))));
                             hreg[k2 + kk][it] = make_uint4(rf_pack_sat(u.x, u.y), rf_pack_sat(u.z, u.w), rf_pack_sat(w.x, w.y), rf_pack_sat(w.z, w.w));
                         }
+                }
+                if (PS) {
+                    // the 8 threads of a row are 8 consecutive lanes; then the max over the warp's 4 + 4 rows.  The slot of parity t was
+                    // last read by the issuer for step t - 2, before it released the x tile this warp waited for since (X_EMPTY)
+#pragma unroll
+                    for (int o = 1; o < 8; o <<= 1) { ss[0] += __shfl_xor_sync(0xffffffffu, ss[0], o); ss[1] += __shfl_xor_sync(0xffffffffu, ss[1], o); }
+                    float m2 = fmaxf(ss[0], ss[1]);
+                    m2 = fmaxf(m2, __shfl_xor_sync(0xffffffffu, m2, 8));
+                    m2 = fmaxf(m2, __shfl_xor_sync(0xffffffffu, m2, 16));
+                    if (lane == 0) asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(xs_leader + 64u * (uint32_t)(t & 1)), "f"(m2) : "memory");
                 }
             };
             preload(0);
@@ -471,7 +525,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 }
                 rf_fence_async();
                 __syncwarp();
-                if (lane == 0) rf_arrive_cl(xfull0);
+                if (lane == 0) { if (PS) rf_arrive_cl_release(xfull0); else rf_arrive_cl(xfull0); }
                 if (XP == 3) {
 #pragma unroll
                     for (int kb = 0; kb < 4; ++kb) {
@@ -1012,7 +1066,15 @@ extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, c
     if (!g_rf_stats) NNTK_CUDA_TRY(cudaMalloc(&g_rf_stats, 4 * sizeof(float)));
     NNTK_CUDA_TRY(cudaMemsetAsync(g_rf_stats, 0, 4 * sizeof(float), st));
     p.stats = g_rf_stats; p.adapt_thr = adapt_thr;
-    if (fused && xp == 3 && adaptive && (IN & 3) == 0) {
+    static int per_step = -1;
+    if (per_step < 0) { const char *e = getenv("NNTK_RECURRENT_X_PERSTEP"); per_step = e ? atoi(e) : 1; }
+    p.per_step = 0;
+    if (fused && xp == 3 && adaptive && per_step) {
+        // the decision moves into the kernel: per pair and per step, from the row norms its converter warps see anyway
+        rf_wnorm_kernel<<<(G * H + 255) / 256, 256, 0, st>>>(r->d_W, IN, G * H, g_rf_stats);
+        NNTK_LAUNCH_CHECK("rf_wnorm_kernel");
+        p.per_step = 1;
+    } else if (fused && xp == 3 && adaptive && (IN & 3) == 0) {
         const long long rows = (long long)nb * T;
         rf_xnorm_kernel<<<148 * 8, 256, 0, st>>>(x, rows, IN, g_rf_stats);
         rf_wnorm_kernel<<<(G * H + 255) / 256, 256, 0, st>>>(r->d_W, IN, G * H, g_rf_stats);
