@@ -47,10 +47,10 @@ struct TcParams {
     int gate_run_if;
 };
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, bool CG2 = false>
 struct SmemLayout {
     static constexpr int A_BYTES = BM * BK * 4;
-    static constexpr int B_BYTES = BN * BK * 4;
+    static constexpr int B_BYTES = (CG2 ? BN / 2 : BN) * BK * 4;     // CG2: this CTA's half of the pair's B tile
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
     static constexpr int STG_OFFSET = BAR_OFFSET + 256;                         // epilogue staging: 8 warps x 2 KB
@@ -72,12 +72,39 @@ __device__ __forceinline__ void tc_commit_mc(uint64_t *bar, uint16_t mask) {
                  ::"r"(smem_u32(bar)), "h"(mask) : "memory");
 }
 
+// ---- cta_group::2 (CG2 kernels): a CTA pair works on one 256-row tile; each CTA stages its own 128 rows of A and HALF of the B tile
+__device__ __forceinline__ uint32_t tc_mapa(uint32_t a, uint32_t rank) {
+    uint32_t d; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(rank)); return d;
+}
+// loads executed by BOTH CTAs; the bytes are counted on the barrier at cluster address bar_cl (the leader's)
+__device__ __forceinline__ void tma_load_4d_cg2(void *dst, const CUtensorMap *map, uint32_t bar_cl, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(map), "r"(bar_cl), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_cg2(void *dst, const CUtensorMap *map, uint32_t bar_cl, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(map), "r"(bar_cl), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_mma_cg2(bool f16, uint32_t d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+    if (f16) asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+    else asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void tc_commit_cg2(uint64_t *bar) {       // arrives on the barrier at this offset in both CTAs of the pair
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void tc_arrive_cl(uint32_t a) { asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(a) : "memory"); }
+
 // BF16 = true: the operands are bf16 (kind::f16, K = 16 per MMA, 64 elements per 128-byte k-block) -- the 3xbf16 split mode
 // of the hoisted recurrent projection.  Byte-wise the stages, swizzle and descriptors are the same as for tf32.
-template <int BN, int STAGES, bool FAST, bool BF16>
+// CG2 = true: tcgen05.mma.cta_group::2, M = 256 per CTA pair (launched as clusters of 2): each CTA stages its own 128 rows of A and
+// half of the B tile, so per MMA an SM reads 8 KB of operands instead of 12 and TMA writes 32 KB per k-block instead of 48 --
+// shared-memory bandwidth (reads + TMA writes ~ 190 B/cycle wanted, 128 there) was what held the one-CTA kernel at ~70 % tensor
+// activity.  The leader CTA issues; accumulator rows 128 r .. 128 r + 127 live in CTA r's TMEM; each CTA runs its own epilogue.
+template <int BN, int STAGES, bool FAST, bool BF16, bool CG2 = false>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, TcParams p) {
-    using SL = SmemLayout<BN, STAGES>;
+    using SL = SmemLayout<BN, STAGES, CG2>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + SL::BAR_OFFSET);
@@ -94,21 +121,29 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
-        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], (uint32_t)p.cs); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], EPI_WARPS); }
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], CG2 ? 1u : (uint32_t)p.cs); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], CG2 ? 2 * EPI_WARPS : EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(TMEM_COLS) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if (CG2) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(TMEM_COLS) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(TMEM_COLS) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tc_fence_before();
     __syncthreads();
-    if (p.cs > 1) tc_cluster_sync();            // every CTA's barriers exist before a peer's multicast or commit can reach them
+    if (CG2 || p.cs > 1) tc_cluster_sync();            // every CTA's barriers exist before a peer's multicast or commit can reach them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     // Clusters walk in lockstep: every CTA runs the same number of tiles; surplus iterations redo the last tile without storing it.
-    const long long n_iter = (p.total_tiles + gridDim.x - 1) / gridDim.x;
+    // CG2: the walkers are CTA pairs, total_tiles counts 256-row pair tiles and CTA r of the pair owns 128-row tile 2 m + r of the slab
+    const uint32_t pr = CG2 ? (tc_cluster_rank() & 1u) : 0u;
+    const long long walkers = CG2 ? (gridDim.x >> 1) : gridDim.x, me = CG2 ? (blockIdx.x >> 1) : blockIdx.x;
+    const long long n_iter = (p.total_tiles + walkers - 1) / walkers;
     const uint16_t mc_mask = (uint16_t)((1u << p.cs) - 1u);
 
     if (warp == 0) {
@@ -118,15 +153,24 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             const uint32_t crank = p.cs > 1 ? tc_cluster_rank() : 0u;
             const int b_rows = BN / p.cs;               // this CTA's slice of every B stage
             for (long long i = 0; i < n_iter; ++i) {
-                long long tile = blockIdx.x + i * gridDim.x;
+                long long tile = me + i * walkers;
                 if (tile >= p.total_tiles) tile = p.total_tiles - 1;
                 const int n_t = (int)(tile % p.n_tiles);
                 const long long rest = tile / p.n_tiles;
-                const int m_t = (int)(rest % p.m_tiles_per_slab);
+                const int m_t = (CG2 ? 2 : 1) * (int)(rest % p.m_tiles_per_slab) + (int)pr;
                 const int slab = (int)(rest / p.m_tiles_per_slab);
                 for (int kb = 0; kb < p.k_blocks; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t *sa = smem + stage * SL::STAGE_BYTES;
+                    if (CG2) {       // both CTAs' bytes are counted on the LEADER's barrier
+                        const uint32_t full_cl = tc_mapa(smem_u32(&full_bar[stage]), tc_cluster_rank() & ~1u);
+                        if (pr == 0) mbar_expect_tx(&full_bar[stage], 2 * SL::STAGE_BYTES);
+                        const int pass = kb / p.kb_pass, akb = kb - pass * p.kb_pass;
+                        tma_load_4d_cg2(sa, &map_a, full_cl, akb * BKE, m_t * BM, slab, pass == 1 ? 1 : 0);
+                        tma_load_2d_cg2(sa + SL::A_BYTES, &map_b, full_cl, kb * BKE, n_t * BN + (int)pr * (BN / 2));
+                        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                        continue;
+                    }
                     mbar_expect_tx(&full_bar[stage], SL::STAGE_BYTES);
                     // split (3xTF32) mode: passes hi*Wlo, lo*Whi, hi*Whi -- B' = [Wlo; Whi; Whi] along K, A = hi, lo, hi.  The
                     // two small passes come FIRST: the tensor core's fp32 accumulate truncates (measured: error grows
@@ -140,12 +184,12 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer =====
-        if (lane == 0) {
+        // ===== MMA issuer (CG2: the pair's leader only) =====
+        if (lane == 0 && pr == 0) {
             // instruction descriptor: D=f32, A=B=tf32, both K-major, N>>3 at bit 17, M>>4 at bit 24
             // (bf16: a/b format 1, kind::f16)
             const uint32_t fmt = BF16 ? (uint32_t)p.half_fmt : 2u;
-            const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+            const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((CG2 ? 2 * BM : BM) >> 4) << 24);
             int stage = 0; uint32_t phase = 0;
             uint32_t it = 0;
             for (long long i = 0; i < n_iter; ++i, ++it) {
@@ -161,14 +205,17 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k) {
                         // advance 32 bytes along K inside the 128-byte swizzle atom: +2 in the (addr >> 4) field
-                        if (BF16) tc_mma_f16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                        if (CG2) tc_mma_cg2(BF16, tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                        else if (BF16) tc_mma_f16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
                         else tc_mma_tf32(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) ? 1u : 0u);
                     }
-                    if (p.cs == 1) tc_commit(&empty_bar[stage]);   // smem stage free once these MMAs have read it
+                    if (CG2) tc_commit_cg2(&empty_bar[stage]);     // frees the stage in both CTAs of the pair
+                    else if (p.cs == 1) tc_commit(&empty_bar[stage]);   // smem stage free once these MMAs have read it
                     else tc_commit_mc(&empty_bar[stage], mc_mask); // ... in every CTA of the cluster: each of them writes part of it
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
-                tc_commit(&tmem_full[buf]);                      // accumulator complete
+                if (CG2) tc_commit_cg2(&tmem_full[buf]);         // accumulator complete: each CTA's epilogue drains its 128 rows
+                else tc_commit(&tmem_full[buf]);
             }
         }
     } else {
@@ -179,20 +226,21 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         uint8_t *stg = smem + SL::STG_OFFSET + (warp - 2) * 2048;      // [32 rows][64 bytes], xor-swizzled 16-byte slots
         uint32_t it = 0;
         const bool vec_ok = ((p.ldc & 3) == 0) && ((p.c_slab & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
+        const uint32_t tmem_empty_leader = CG2 ? tc_mapa(smem_u32(&tmem_empty[0]), tc_cluster_rank() & ~1u) : 0u;
         for (long long i = 0; i < n_iter; ++i, ++it) {
-            const long long tile = blockIdx.x + i * gridDim.x;
+            const long long tile = me + i * walkers;
             const uint32_t buf = it & 1, use = it >> 1;
             if (tile >= p.total_tiles) {             // lockstep filler: nothing to store
                 mbar_wait(&tmem_full[buf], use & 1);
                 tc_fence_after();
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+                if (lane == 0) { if (CG2) tc_arrive_cl(tmem_empty_leader + 8u * buf); else mbar_arrive(&tmem_empty[buf]); }
                 continue;
             }
             const int n_t = (int)(tile % p.n_tiles);
             const long long rest = tile / p.n_tiles;
-            const int m_t = (int)(rest % p.m_tiles_per_slab);
+            const int m_t = (CG2 ? 2 : 1) * (int)(rest % p.m_tiles_per_slab) + (int)pr;
             const long long slab = rest / p.m_tiles_per_slab;
             const int row = m_t * BM + row_in_tile;
             const bool row_ok = row < p.rows;
@@ -324,15 +372,16 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+            if (lane == 0) { if (CG2) tc_arrive_cl(tmem_empty_leader + 8u * buf); else mbar_arrive(&tmem_empty[buf]); }
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (p.cs > 1) tc_cluster_sync();            // nobody leaves while a peer's multicast or commit could still touch this CTA
+    if (CG2 || p.cs > 1) tc_cluster_sync();     // nobody leaves while a peer's multicast, commit or MMA could still touch this CTA
     if (warp == 1) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+        if (CG2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+        else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
     }
 }
 
@@ -492,6 +541,40 @@ static int launch_tc(const CUtensorMap &ma, const CUtensorMap &mb, TcParams &p, 
     return 0;
 }
 
+// cta_group::2 launch: clusters of 2, p.total_tiles / p.m_tiles_per_slab count 256-row PAIR tiles, the B map's box is BN / 2 rows
+template <bool BF16>
+static int launch_tc_cg2(const CUtensorMap &ma, const CUtensorMap &mb, TcParams &p, cudaStream_t st) {
+    constexpr int BN = 256, STAGES = 6;
+    using SL = SmemLayout<BN, STAGES, true>;
+    auto kern = gemm_tf32_kernel<BN, STAGES, true, BF16, true>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        NNTK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::TOTAL));
+        attr_done = true;
+    }
+    long long pairs = nntk_cuda_sm_count() / 2;
+    if (p.total_tiles < pairs) pairs = p.total_tiles;
+    p.gate = g_tc_gate; p.gate_run_if = g_tc_gate_run_if;
+    p.cs = 1;
+    g_tc_cluster = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(2 * pairs)); cfg.blockDim = dim3(NUM_THREADS); cfg.dynamicSmemBytes = SL::TOTAL; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    NNTK_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, ma, mb, p));
+    nntk_cuda_count_launch(1);
+    return 0;
+}
+// whether a launch takes the cta_group::2 kernel: 256-wide n tiles, the vectorised epilogue, and enough 256-row tiles to fill the pairs
+static bool want_cg2(int BN, bool fast, int rows, int batch, int n_tiles) {
+    static int on = -1;
+    if (on < 0) { const char *e = getenv("NNTK_GEMM_CG2"); on = e ? atoi(e) : 1; }
+    const long long pair_tiles = (long long)((rows + 2 * BM - 1) / (2 * BM)) * batch * n_tiles;
+    return on && BN == 256 && fast && pair_tiles >= nntk_cuda_sm_count();
+}
+
 // returns 0 done, 1 not eligible (caller runs the fp32 kernel), <0 error.  split != 0: 3xTF32 (hi/lo operand split, three
 // passes folded into ONE K loop of length 3K -- the kernel is unchanged), fp32-class accuracy at a third of the TF32 rate.
 extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_blocked);
@@ -576,6 +659,7 @@ extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_
     // narrow outputs (the 12-wide TDD of C5): a 32-column tile keeps the B stage at 4 KB instead of 16 KB -- with BN = 128 the
     // zero-padded weight tile was as many bytes per stage as the activations and halved the HBM-bound kernel's input rate
     const int BN = N > 128 ? 256 : (N > 32 || bf) ? 128 : 32;
+    const bool cg2 = want_cg2(BN, fast, a->rows, a->batch, (N + BN - 1) / BN);
     const CUtensorMapDataType dt = bf ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
     CUtensorMap ma, mb;
     {
@@ -597,7 +681,7 @@ extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_
     {
         cuuint64_t dims[2] = {(cuuint64_t)ldbt, (cuuint64_t)N};
         cuuint64_t strides[1] = {(cuuint64_t)ldbt * esz};
-        cuuint32_t box[2] = {(cuuint32_t)BKE, (cuuint32_t)BN};
+        cuuint32_t box[2] = {(cuuint32_t)BKE, (cuuint32_t)(cg2 ? BN / 2 : BN)};
         cuuint32_t estr[2] = {1, 1};
         CUresult r = encode(&mb, dt, 2, (void *)Bt, dims, strides, box, estr,
                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -620,6 +704,11 @@ extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_
     p.scale = scale; p.shift = shift; p.act = a->act; p.act_a = a->act_a;
     p.half_fmt = 1;
     if (row_softmax) p.act = NNTK_ACT_SOFTMAX;
+    if (cg2) {
+        p.m_tiles_per_slab = (a->rows + 2 * BM - 1) / (2 * BM);
+        p.total_tiles = (long long)p.n_tiles * p.m_tiles_per_slab * a->batch;
+        return bf ? launch_tc_cg2<true>(ma, mb, p, st) : launch_tc_cg2<false>(ma, mb, p, st);
+    }
     // FAST epilogue: whole 32-column chunks and 16-byte aligned output rows (every BASELINE shape except the 12-wide TDD)
     if (bf) return BN == 256 ? launch_tc<256, 4, true, true>(ma, mb, p, st) : launch_tc<128, 6, true, true>(ma, mb, p, st);
     if (BN == 32) return fast ? launch_tc<32, 8, true>(ma, mb, p, st) : launch_tc<32, 8, false>(ma, mb, p, st);
@@ -673,6 +762,8 @@ extern "C" int nntk_cuda_gemm_f16(const nntk_gemm_args *a, int *d_ovf) {
     const long long tiles_total = (long long)((a->rows + BM - 1) / BM) * a->batch;
     int cs = (N <= BN && tiles_total >= 2LL * nntk_cuda_sm_count()) ? want_cs : 1;
     while (cs > 1 && ((BN / cs) % 8 || nntk_cuda_sm_count() % cs)) cs >>= 1;
+    const bool cg2 = want_cg2(BN, true, a->rows, a->batch, (N + BN - 1) / BN);
+    if (cg2) cs = 2;          // the B map's box is half a tile either way
     CUtensorMap ma, mb;
     {
         cuuint64_t dims[4] = {(cuuint64_t)K, (cuuint64_t)a->rows, (cuuint64_t)a->batch, 1};
@@ -718,7 +809,11 @@ extern "C" int nntk_cuda_gemm_f16(const nntk_gemm_args *a, int *d_ovf) {
     const int *saved = g_tc_gate; const int saved_if = g_tc_gate_run_if;
     g_tc_gate = d_ovf; g_tc_gate_run_if = 0;
     g_tc_cluster = cs;
-    const int rc = BN == 256 ? launch_tc<256, 4, true, true>(ma, mb, p, st) : launch_tc<128, 6, true, true>(ma, mb, p, st);
+    if (cg2) {
+        p.m_tiles_per_slab = (a->rows + 2 * BM - 1) / (2 * BM);
+        p.total_tiles = (long long)p.n_tiles * p.m_tiles_per_slab * a->batch;
+    }
+    const int rc = cg2 ? launch_tc_cg2<true>(ma, mb, p, st) : BN == 256 ? launch_tc<256, 4, true, true>(ma, mb, p, st) : launch_tc<128, 6, true, true>(ma, mb, p, st);
     g_tc_gate = saved; g_tc_gate_run_if = saved_if;
     return rc;
 }

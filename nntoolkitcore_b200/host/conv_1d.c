@@ -202,7 +202,8 @@ static int front_launch(void *ctx, const float *d_in, float *d_out, long long fi
     static int want_f16 = -1;
     if (want_f16 < 0) { const char *e = getenv("NNTK_FRONT_F16"); want_f16 = e ? atoi(e) : 1; }
     int *flag = NULL;
-    const int f16 = want_f16 && nntk_cuda_math_mode() == NNTK_MATH_TF32 && cp == 288 && (c->output_feature_channels % 32) == 0 &&
+    const int f16 = want_f16 && nntk_cuda_math_mode() == NNTK_MATH_TF32 && (cp & 7) == 0 && cp > c->input_feature_channels && cp <= 288 &&
+                    (c->output_feature_channels % 32) == 0 &&
                     c->output_feature_channels > 32 && (flag = nntk_cuda_front_flag()) != NULL;
     const size_t rows_f32 = sizeof(float) * (size_t)c->input_size * cp, rows_f16 = rows_f32 / 2;
     const size_t per_clip = rows_f32 + (f16 ? rows_f16 : 0);
@@ -303,6 +304,8 @@ int SpectrogramBNConv1dApplyBatch(Spectrogram spectrogram, BatchNorm input_bn, C
     /* row pitch: 128-byte aligned rows on the tensor-core paths when that costs <= 15 % more K (cin_pad), 16-byte aligned for FFMA */
     const int cin = c->input_feature_channels;
     fc.pitch = nntk_cuda_math_mode() == NNTK_MATH_FP32 ? ((cin + 3) & ~3) : cin_pad(c);
+    /* (fp16 rows at the tighter 264-element pitch -- 21 instead of 23 k-blocks per tile -- measured SLOWER: 5.18 vs 4.82 ms for the
+     * C5 conv; rows that are not 128-byte aligned cost the TMA im2col loads more than the 9 % fewer MMAs save) */
     if (sc.nfft != 512 || fc.pitch > 288 || !input_bn) {
         /* shapes without a pitched K1 (or nothing to fold): the three reference-shaped calls through a scratch spectrogram */
         const size_t spec_bytes = sizeof(float) * (size_t)n_clips * sc.ntime_series * sc.nfreq;
