@@ -68,6 +68,10 @@ struct RfParams {
                                      //    max |x_t|^2 of their rows with the x tile, the issuer skips the two correction passes' MMAs for that step
     int cs;                          // cluster size: 2, 4 or 8 CTAs = 1, 2 or 4 pairs sharing every B stage by TMA multicast
     int xw_blocked_rows;             // XW mode: row_blocks of the blocked projection
+    int verify;                      // one-pass plan launched on the strength of a SAMPLED pre-scan: the converters still publish every step's row
+                                     //    norms and the issuer raises stats[3] when one breaks the bound (the three-pass launch behind then runs)
+    int sel;                         // 0 always run; 1 run iff the sampled bound holds; 2 run iff it does not, or launch 1 raised stats[3]
+    const float *h_init, *c_init;    // initial state read by the prologue (a copy when two launches share h_state / c_state), else = h_state / c_state
     const float *x;                  // FUSED: [B][T][in]
     const float *bias_i, *bias_h;    // [G*H] each; bias_h may be null (not added)
     const float *xw;                 // XW mode: blocked projection [T][row_blocks][G*H/4][32][4] (b_i already added)
@@ -221,7 +225,13 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     // ~2^-12 * sqrt(2/3) * |x_t| * |W_n| / ... of noise into every pre-activation of every step; when a pre-scan of this call's x
     // and W bounds |x_t| |W_n| by adapt_thr that noise stays ~4x under the mode's 1e-3 and the passes are skipped (rf_xpasses_note).
     // Every role of every CTA evaluates the same two numbers, so the whole grid takes the same branch.
+    if (p.sel) {         // speculative pair of launches (see nntk_cuda_recurrent_fused): the whole grid takes the same branch, before any state exists
+        const bool ok = sqrtf(__ldg(p.stats) * __ldg(p.stats + 1)) <= p.adapt_thr;
+        const int viol = *reinterpret_cast<const volatile int *>(p.stats + 3);
+        if (p.sel == 1 ? !ok : (ok && !viol)) return;
+    }
     const bool PS = FUSED && p.per_step && p.xp == 3 && p.stats;      // per-step decision: everything is staged for three passes
+    const bool PUB = FUSED && (PS || (p.verify && p.stats));          // the converters publish max |x_t|^2 per step
     const int XP = PS ? 3 : ((p.xp == 3 && p.stats && sqrtf(__ldg(p.stats) * __ldg(p.stats + 1)) <= p.adapt_thr) ? 1 : p.xp);
     const int H = p.H, IN = p.in, T = p.T;
     const int S = p.split;                                  // pairs per slice (1 or 2)
@@ -255,7 +265,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     // tile counters are 32-bit and advanced incrementally everywhere: 64-bit divisions in the issuer's loop cost ~13 000 cycles per
     // step in the first version (more than all of the step's MMAs)
 
-    if (tid == 0 && blockIdx.x == 0 && p.stats && !PS) const_cast<float *>(p.stats)[2] = (float)XP;
+    if (tid == 0 && blockIdx.x == 0 && p.stats && !PUB) const_cast<float *>(p.stats)[2] = (float)XP;
     if (tid == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_wl) : "memory");
@@ -385,7 +395,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 __syncwarp();
                 if (++stage == p.ring_stages) { stage = 0; phase ^= 1; }
             };
-            const float wstat = PS ? __ldg(p.stats + 1) : 0.0f;
+            const float wstat = PUB ? __ldg(p.stats + 1) : 0.0f;
             int xp_t = XP, any3 = 0;     // passes of the step whose input parts are being issued
             // (t, c) = step and tile; buf = accumulator buffer of the tile, use = how often that buffer has been used before
             auto x_part = [&](int t, int c, int buf, int use) {
@@ -394,14 +404,15 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 const uint32_t d = tmem + (uint32_t)(buf * 128);
                 if (c == 0) {            // the hi image of x_t (and, per-step mode, the row norms the converters published with it)
                     RF_T0();
-                    if (PS) rf_mbar_wait_cl(bars + RFB_X_FULL, (uint32_t)(t & 1)); else mbar_wait(bars + RFB_X_FULL, (uint32_t)(t & 1));
+                    if (PUB) rf_mbar_wait_cl(bars + RFB_X_FULL, (uint32_t)(t & 1)); else mbar_wait(bars + RFB_X_FULL, (uint32_t)(t & 1));
                     RF_T1(3);
-                    if (PS) {
+                    if (PUB) {
                         float mx = 0.0f;
 #pragma unroll
                         for (int i = 0; i < 16; ++i) mx = fmaxf(mx, xs[(t & 1) * 16 + i]);
-                        xp_t = (sqrtf(mx * wstat) <= p.adapt_thr) ? 1 : 3;       // Inf stays, NaN rows were dropped by fmaxf
-                        any3 |= xp_t == 3;
+                        const bool small = sqrtf(mx * wstat) <= p.adapt_thr;       // Inf stays, NaN rows were dropped by fmaxf
+                        if (PS) { xp_t = small ? 1 : 3; any3 |= xp_t == 3; }
+                        else if (!small && lane == 0) *reinterpret_cast<volatile int *>(const_cast<float *>(p.stats) + 3) = 1;   // one-pass plan broken
                     }
                 }
                 if (PS && xp_t == 1) {   // everything was staged for three passes; this step takes one
@@ -446,7 +457,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                     if (FUSED && !(t == T - 1 && c == NC - 1)) x_part(c + 1 == NC ? t + 1 : t, c + 1 == NC ? 0 : c + 1, nbuf, nuse);
                     buf = nbuf; use = nuse;
                 }
-            if (PS && lane == 0) atomicMax(reinterpret_cast<int *>(const_cast<float *>(p.stats) + 2), __float_as_int(any3 ? 3.0f : 1.0f));
+            if (PUB && lane == 0) atomicMax(reinterpret_cast<int *>(const_cast<float *>(p.stats) + 2), __float_as_int(any3 ? 3.0f : 1.0f));
             RF_DBG(if (lane == 0) { for (int i = 0; i < 4; ++i) p.dbg[blockIdx.x * 16 + i] = dbgc[i]; p.dbg[blockIdx.x * 16 + 10] = clock64() - t_start;
                    p.dbg[blockIdx.x * 16 + 12] = dbgc[12]; p.dbg[blockIdx.x * 16 + 13] = dbgc[13]; });
         }
@@ -496,11 +507,11 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
 #pragma unroll
                         for (int it = 0; it < 2; ++it) {
                             const float4 u = a[kk][it][0], w = a[kk][it][1];
-                            if (PS) ss[it] = fmaf(u.x, u.x, fmaf(u.y, u.y, fmaf(u.z, u.z, fmaf(u.w, u.w, fmaf(w.x, w.x, fmaf(w.y, w.y, fmaf(w.z, w.z, fmaf(w.w, w.w, ss[it]))))))));
+                            if (PUB) ss[it] = fmaf(u.x, u.x, fmaf(u.y, u.y, fmaf(u.z, u.z, fmaf(u.w, u.w, fmaf(w.x, w.x, fmaf(w.y, w.y, fmaf(w.z, w.z, fmaf(w.w, w.w, ss[it]))))))));
                             hreg[k2 + kk][it] = make_uint4(rf_pack_sat(u.x, u.y), rf_pack_sat(u.z, u.w), rf_pack_sat(w.x, w.y), rf_pack_sat(w.z, w.w));
                         }
                 }
-                if (PS) {
+                if (PUB) {
                     // the 8 threads of a row are 8 consecutive lanes; then the max over the warp's 4 + 4 rows.  The slot of parity t was
                     // last read by the issuer for step t - 2, before it released the x tile this warp waited for since (X_EMPTY)
 #pragma unroll
@@ -525,11 +536,12 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 }
                 rf_fence_async();
                 __syncwarp();
-                if (lane == 0) { if (PS) rf_arrive_cl_release(xfull0); else rf_arrive_cl(xfull0); }
+                if (lane == 0) { if (PUB) rf_arrive_cl_release(xfull0); else rf_arrive_cl(xfull0); }
                 if (XP == 3) {
 #pragma unroll
                     for (int kb = 0; kb < 4; ++kb) {
                         if (kb >= KBX) break;
+                        if (RF_SKIP(16)) { if (lane == 0) rf_arrive_cl(xlfull0 + 8u * (uint32_t)kb); continue; }   // timing experiment: no lo image
                         float4 a[2][2];
 #pragma unroll
                         for (int it = 0; it < 2; ++it) {
@@ -581,10 +593,10 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 float hv[8], sv[8];
 #pragma unroll
                 for (int i = 0; i < 2; ++i) {
-                    const float4 a = row_ok ? *reinterpret_cast<const float4 *>(p.h_state + (size_t)row * H + u0 + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    const float4 a = row_ok ? *reinterpret_cast<const float4 *>(p.h_init + (size_t)row * H + u0 + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
                     hv[4 * i] = a.x; hv[4 * i + 1] = a.y; hv[4 * i + 2] = a.z; hv[4 * i + 3] = a.w;
                     if (G == 4 && own) {
-                        const float4 b = row_ok ? *reinterpret_cast<const float4 *>(p.c_state + (size_t)row * H + u0 + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        const float4 b = row_ok ? *reinterpret_cast<const float4 *>(p.c_init + (size_t)row * H + u0 + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
                         sv[4 * i] = b.x; sv[4 * i + 1] = b.y; sv[4 * i + 2] = b.z; sv[4 * i + 3] = b.w;
                     }
                 }
@@ -820,20 +832,20 @@ __global__ void rf_pack_kernel(const float *__restrict__ W, __half *__restrict__
 // [-1, 1]) stay at 1.3e-4 / 2.1e-4 after 994.  The error is linear in that product, so a bound of 5 keeps the single-pass noise
 // near 3e-4, below the recurrent part's own fp16 rounding.  The scan below reads x once (HBM-bound, ~1.3 ms for 8.3 GB) and saves
 // two of the four tensor-core passes (4 ms per C5 layer).
-__global__ void __launch_bounds__(256) rf_xnorm_kernel(const float *__restrict__ x, long long rows, int in, float *stats) {
+__global__ void __launch_bounds__(256) rf_xnorm_kernel(const float *__restrict__ x, long long rows, int in, float *stats, int stride) {
     const int lane = threadIdx.x & 31;
     const long long warps = ((long long)gridDim.x * blockDim.x) >> 5;
     const int n4 = in >> 2;
     float best = 0.0f;
     // four rows per warp iteration: their loads are independent and all in flight before the first shuffle (one row at a time the
     // load -> 5 shuffles -> next load chain ran at 4.2 TB/s)
-    for (long long r = (((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 4; r < rows; r += warps * 4) {
+    for (long long r = (((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 4; r * stride < rows; r += warps * 4) {
         float s[4] = {0.0f, 0.0f, 0.0f, 0.0f};
         for (int i = lane; i < n4; i += 32) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                if (r + k < rows) {
-                    const float4 v = __ldcs(reinterpret_cast<const float4 *>(x + (r + k) * in) + i);
+                if ((r + k) * stride < rows) {          // stride > 1: a sample (every stride-th row); the launch that trusts it verifies every step
+                    const float4 v = __ldcs(reinterpret_cast<const float4 *>(x + (r + k) * stride * in) + i);
                     s[k] = fmaf(v.x, v.x, fmaf(v.y, v.y, fmaf(v.z, v.z, fmaf(v.w, v.w, s[k]))));
                 }
             }
@@ -937,9 +949,14 @@ extern "C" int nntk_cuda_last_recurrent_xpasses(void) {
     return (int)v[2];
 }
 
-// Runs all T steps of one batch chunk in ONE launch.  xw: the blocked hoisted projection (XW mode) or null (FUSED mode).
-extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, const float *x, const float *xw, float *h, float *c,
-                                         float *out, int *used) {
+float *g_rf_state = nullptr;     // copies of the initial state for the speculative pair of launches
+size_t g_rf_state_floats = 0;
+
+// One launch.  spec: 0 plain; 1 / 2 = first (one-pass plan, verified per step, runs iff the sampled bound holds) / second (three-pass
+// staging with the per-step decision, runs iff the bound failed or the first launch raised the flag) launch of the speculative pair;
+// the caller has prepared g_rf_stats for them.  h_init / c_init: where the prologue reads the initial state.
+static int rf_fused_run(const nntk_recurrent_args *r, int nb, const float *x, const float *xw, float *h, float *c, float *out, int *used,
+                        int spec, const float *h_init, const float *c_init) {
     *used = 0;
     const int G = r->cell, H = r->H, T = r->T, IN = r->in;
     const int plan = nntk_cuda_recurrent_fused_plan(r, nb);
@@ -948,7 +965,7 @@ extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, c
     if ((((uintptr_t)h) | ((uintptr_t)out) | ((uintptr_t)x) | ((uintptr_t)c) | ((uintptr_t)xw)) & 15) return 0;
     EncodeTiledFn encode = get_encode();
     cudaStream_t st = nntk_stream();
-    const int xp = fused ? rf_xpasses() : 1;
+    const int xp = fused ? (spec == 1 ? 1 : rf_xpasses()) : 1;
     const size_t un = (size_t)G * H * H, wn = fused ? (size_t)G * H * IN : 0, wln = (fused && xp == 3) ? wn : 0;
     if (un + wn + wln > g_rf_halves) {
         NNTK_CUDA_TRY(cudaStreamSynchronize(st));
@@ -1064,19 +1081,23 @@ extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, c
         if ((e = getenv("NNTK_RECURRENT_X_ADAPT_THR"))) adapt_thr = (float)atof(e);
     }
     if (!g_rf_stats) NNTK_CUDA_TRY(cudaMalloc(&g_rf_stats, 4 * sizeof(float)));
-    NNTK_CUDA_TRY(cudaMemsetAsync(g_rf_stats, 0, 4 * sizeof(float), st));
+    if (!spec) NNTK_CUDA_TRY(cudaMemsetAsync(g_rf_stats, 0, 4 * sizeof(float), st));
     p.stats = g_rf_stats; p.adapt_thr = adapt_thr;
     static int per_step = -1;
     if (per_step < 0) { const char *e = getenv("NNTK_RECURRENT_X_PERSTEP"); per_step = e ? atoi(e) : 1; }
     p.per_step = 0;
-    if (fused && xp == 3 && adaptive && per_step) {
+    p.sel = spec; p.verify = spec == 1;
+    p.h_init = h_init ? h_init : h; p.c_init = c_init ? c_init : c;
+    if (spec) {
+        p.per_step = spec == 2;           // stats prepared by the caller (sampled row norms, W norms, cleared flag)
+    } else if (fused && xp == 3 && adaptive && per_step) {
         // the decision moves into the kernel: per pair and per step, from the row norms its converter warps see anyway
         rf_wnorm_kernel<<<(G * H + 255) / 256, 256, 0, st>>>(r->d_W, IN, G * H, g_rf_stats);
         NNTK_LAUNCH_CHECK("rf_wnorm_kernel");
         p.per_step = 1;
     } else if (fused && xp == 3 && adaptive && (IN & 3) == 0) {
         const long long rows = (long long)nb * T;
-        rf_xnorm_kernel<<<148 * 8, 256, 0, st>>>(x, rows, IN, g_rf_stats);
+        rf_xnorm_kernel<<<148 * 8, 256, 0, st>>>(x, rows, IN, g_rf_stats, 1);
         rf_wnorm_kernel<<<(G * H + 255) / 256, 256, 0, st>>>(r->d_W, IN, G * H, g_rf_stats);
         NNTK_LAUNCH_CHECK_N("rf_xnorm_kernel", 2);
     } else if (fused && xp == 3) {
@@ -1108,4 +1129,48 @@ extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, c
     if (rc) return rc;
     *used = 1;
     return 0;
+}
+
+// Runs all T steps of one batch chunk.  xw: the blocked hoisted projection (XW mode) or null (FUSED mode).
+// FUSED mode, adaptive input passes: a SPECULATIVE PAIR of launches.  Staging everything for three passes and skipping the
+// correction passes' MMAs per step (the per-step kernel) still streams W_lo through the ring: measured 8.5 ms per C5 GRU layer
+// against 7.4 ms for a kernel planned for one pass.  So: (1) a sampled pre-scan (every 16th row of x: 0.1 ms instead of 1.2)
+// gives an optimistic bound; (2) the ONE-PASS kernel runs iff that bound holds, checks every step's true row norms (its
+// converters see them anyway) and raises a flag when one breaks the bound; (3) the three-pass / per-step kernel is enqueued
+// right behind and runs iff the sampled bound failed or the flag was raised, from a copy of the initial state -- an empty launch
+// in the normal case.  All decisions are taken on the device; nothing synchronises.
+extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, const float *x, const float *xw, float *h, float *c,
+                                         float *out, int *used) {
+    static int speculate = -1, adaptive = -1, per_step = -1;
+    if (speculate < 0) {
+        const char *e = getenv("NNTK_RECURRENT_X_SPECULATE"); speculate = e ? atoi(e) : 1;
+        e = getenv("NNTK_RECURRENT_X_ADAPTIVE"); adaptive = e ? atoi(e) : 1;
+        e = getenv("NNTK_RECURRENT_X_PERSTEP"); per_step = e ? atoi(e) : 1;
+    }
+    const int G = r->cell, H = r->H, T = r->T, IN = r->in;
+    const bool fused = !xw && nntk_cuda_recurrent_fused_plan(r, nb) == 1;
+    if (!(fused && speculate && adaptive && per_step && rf_xpasses() == 3 && (IN & 3) == 0 && (G != 4 || c)))
+        return rf_fused_run(r, nb, x, xw, h, c, out, used, 0, nullptr, nullptr);
+    cudaStream_t st = nntk_stream();
+    const size_t sn = (size_t)nb * H, need = sn * (G == 4 ? 2 : 1);
+    if (need > g_rf_state_floats) {
+        NNTK_CUDA_TRY(cudaStreamSynchronize(st));
+        if (g_rf_state) cudaFree(g_rf_state);
+        g_rf_state = nullptr; g_rf_state_floats = 0;
+        NNTK_CUDA_TRY(cudaMalloc(&g_rf_state, need * sizeof(float)));
+        g_rf_state_floats = need;
+    }
+    if (!g_rf_stats) NNTK_CUDA_TRY(cudaMalloc(&g_rf_stats, 4 * sizeof(float)));
+    NNTK_CUDA_TRY(cudaMemsetAsync(g_rf_stats, 0, 4 * sizeof(float), st));
+    NNTK_CUDA_TRY(cudaMemcpyAsync(g_rf_state, h, sn * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    if (G == 4) NNTK_CUDA_TRY(cudaMemcpyAsync(g_rf_state + sn, c, sn * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    const long long rows = (long long)nb * T;
+    rf_xnorm_kernel<<<148 * 4, 256, 0, st>>>(x, rows, IN, g_rf_stats, 16);
+    rf_wnorm_kernel<<<(G * H + 255) / 256, 256, 0, st>>>(r->d_W, IN, G * H, g_rf_stats);
+    NNTK_LAUNCH_CHECK_N("rf_xnorm_kernel", 2);
+    int used1 = 0;
+    int rc = rf_fused_run(r, nb, x, nullptr, h, c, out, &used1, 1, g_rf_state, G == 4 ? g_rf_state + sn : nullptr);
+    if (rc) return rc;
+    if (!used1) return rf_fused_run(r, nb, x, xw, h, c, out, used, 0, nullptr, nullptr);     // nothing was launched: the plain path
+    return rf_fused_run(r, nb, x, nullptr, h, c, out, used, 2, g_rf_state, G == 4 ? g_rf_state + sn : nullptr);
 }

@@ -250,3 +250,27 @@ def test_front_end_fp16_rows_and_their_fp32_fallback(tf32, ref, gain):
     torch.cuda.synchronize()
     assert int(flag.item()) == overflowed, f"gain {gain}: overflow flag {int(flag.item())}"
     assert_parity(got.cpu().numpy(), want, tol=TF32_TOL, what=f"front end with fp16 rows, audio gain {gain} (fallback ran: {overflowed})")
+
+
+def test_fused_recurrent_speculative_one_pass_launch_is_verified(tf32, port):
+    """the one-pass launch trusts a SAMPLED pre-scan (every 16th row of x); a loud frame on an unsampled row must be caught by the
+    launch's own per-step check and the three-pass launch behind it must redo the layer -- output and final state vs the oracle"""
+    import port_cases
+    import torch
+    rng = np.random.default_rng(17)
+    B, T, H = 130, 60, 256
+    x = (0.2 * rng.standard_normal((B, T, H))).astype(np.float32)
+    x[77, 33] *= 40.0                      # flat row 77 * 60 + 33 = 4653 = 16 * 290 + 13: not sampled; |x_t| |W_n| ~ 140
+    pick = [0, 77, 129]
+    w = port_cases.recurrent_weights("gru", H, H, 421)
+    h0 = (0.1 * rng.standard_normal((B, H))).astype(np.float32)
+    want = np.stack([port_cases.recurrent(port, "gru", H, H, T, True, True, w, x[i], h=h0[i].copy()) for i in pick])
+    r = L.Recurrent(tf32, "gru", H, H, T); helpers.fill_recurrent(r, 421)
+    dev = torch.device("cuda:0")
+    h = torch.from_numpy(h0).to(dev)
+    got = r.apply_batch(torch.from_numpy(x).to(dev), h_state=h)
+    torch.cuda.synchronize()
+    assert _path(tf32) == "fused_tc"
+    assert tf32.NNTKDebugLastRecurrentInputPasses() == 3, "the loud frame was not caught: the three-pass launch did not run"
+    assert_parity(got[pick].cpu().numpy(), want, tol=TF32_TOL, what="GRU-256 with one loud unsampled frame (speculative one-pass launch redone)")
+    assert_parity(h[pick].cpu().numpy(), want[:, -1], tol=TF32_TOL, what="... final state written by the second launch")
