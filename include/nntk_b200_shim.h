@@ -215,6 +215,9 @@ size_t nntk_cuda_recurrent_workspace(const nntk_recurrent_args *r);
 const char *nntk_cuda_last_recurrent_path(void);
 /* input passes (1 or 3) the most recent fused recurrent launch took after its adaptive pre-scan; synchronises (tests only) */
 int nntk_cuda_last_recurrent_xpasses(void);
+/* operand passes the hoisted projection of the most recent large-batch recurrent layer took in tensor-core mode: 1 (single fp16 pass:
+ * max |x_t| max |W_n| under the bound), 3 (3xbf16), 0 (no adaptive projection ran); synchronises (tests only) */
+int nntk_cuda_last_proj_passes(void);
 int nntk_cuda_recurrent(const nntk_recurrent_args *r);
 /* Allocation-free variant of nntk_cuda_recurrent.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  The caller

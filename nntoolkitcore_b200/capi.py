@@ -209,7 +209,7 @@ SHIM_SYMBOLS = [
     "nntk_cuda_spectrogram_pitched",
     "nntk_cuda_recurrent_workspace", "nntk_cuda_recurrent", "nntk_cuda_last_recurrent_path", "nntk_cuda_last_recurrent_xpasses",
     "nntk_cuda_recurrent_static_scratch", "nntk_cuda_spectrogram_half", "nntk_cuda_spectrogram_gate", "nntk_cuda_front_flag",
-    "nntk_cuda_gemm_f16", "nntk_cuda_gemm_tc_gate", "nntk_cuda_gemm_tf32", "nntk_cuda_gemm_row_softmax",
+    "nntk_cuda_gemm_f16", "nntk_cuda_gemm_tc_gate", "nntk_cuda_gemm_tf32", "nntk_cuda_gemm_row_softmax", "nntk_cuda_last_proj_passes",
 ]
 
 

@@ -437,6 +437,7 @@ extern "C" int nntk_cuda_recurrent_cluster_h16(const nntk_recurrent_args *r, int
                                                float *c, float *out, int *used);  // recurrent_cluster_h16.cu
 extern "C" int nntk_cuda_recurrent_cluster_h16_plan(const nntk_recurrent_args *r, int nb);
 extern "C" int nntk_cuda_gemm_tf32_ex(const nntk_gemm_args *a, int split, int c_blocked);   // gemm_tc.cu
+extern "C" int nntk_cuda_gemm_proj_adaptive(const nntk_gemm_args *a, float thr);             // gemm_tc.cu
 extern "C" int nntk_cuda_recurrent_fused_plan(const nntk_recurrent_args *r, int nb);          // recurrent_fused.cu
 extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, const float *x, const float *xw, float *h, float *c,
                                          float *out, int *used);
@@ -501,7 +502,11 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
         // shapes its 2-byte pitch rules exclude fall back to 3xTF32
         static int proj_bf16 = -1;
         if (proj_bf16 < 0) { const char *e = getenv("NNTK_PROJ_BF16X3"); proj_bf16 = e ? atoi(e) : 1; }
-        rc = (proj_bf16 && !step_x3) ? nntk_cuda_gemm_tf32_ex(&gb, 2, 1) : 1;
+        // ... and a single fp16 pass instead when the inputs are small enough for it (decided on the device: gemm_tc.cu)
+        static float adapt_thr = -1.0f;
+        if (adapt_thr < 0.0f) { const char *e = getenv("NNTK_RECURRENT_X_ADAPT_THR"); adapt_thr = e ? (float)atof(e) : 6.5f; }
+        rc = (proj_bf16 && !step_x3 && mode == 1) ? nntk_cuda_gemm_proj_adaptive(&gb, adapt_thr) : 1;
+        if (rc == 1) rc = (proj_bf16 && !step_x3) ? nntk_cuda_gemm_tf32_ex(&gb, 2, 1) : 1;
         if (rc == 1) rc = nntk_cuda_gemm_tf32_ex(&gb, 1, 1);
         if (rc < 0) return rc;
         xw_blocked = rc == 0;

@@ -827,11 +827,13 @@ __global__ void rf_pack_kernel(const float *__restrict__ W, __half *__restrict__
     }
 }
 
-// rf_xpasses_note -- adaptive input passes.  Measured (tests, emulation): with ONE fp16 pass a GRU 256 -> 256 on N(0,1) inputs
-// (|x_t| |W_n| ~ 18) drifts to 1.2e-3 max error after 300 steps; the C5 layers (|x_t| |W_n| = 1.7 and 2.3: post-ReLU features, h in
-// [-1, 1]) stay at 1.3e-4 / 2.1e-4 after 994.  The error is linear in that product, so a bound of 5 keeps the single-pass noise
-// near 3e-4, below the recurrent part's own fp16 rounding.  The scan below reads x once (HBM-bound, ~1.3 ms for 8.3 GB) and saves
-// two of the four tensor-core passes (4 ms per C5 layer).
+// rf_xpasses_note -- adaptive input passes.  Calibration (tests, emulation, scripts): with ONE fp16 pass for x . W
+//   GRU 256 -> 256, N(0,1) inputs (max |x_t| max |W_n| = 18), 300 steps: 1.2e-3 max error   -> three passes needed
+//   C5 GRU layers (1.7 and 2.3: post-ReLU features, h in [-1, 1]), 994 steps: 1.3e-4 / 2.1e-4
+//   C4 second LSTM-512 layer (5.6: its input is the first layer's h), 500 steps, whole stack vs the reference: 1.6e-4 scaled max
+//   error, 2.9e-4 rel-L2 (three passes: 0.7e-4 / 1.5e-4)
+// The error is linear in that product, so a bound of 6.5 keeps the single-pass noise at ~4e-4, inside the mode's 1e-3 together
+// with the recurrent part's own fp16 rounding (<= 3.6e-4).  NNTK_RECURRENT_X_ADAPT_THR overrides it.
 __global__ void __launch_bounds__(256) rf_xnorm_kernel(const float *__restrict__ x, long long rows, int in, float *stats, int stride) {
     const int lane = threadIdx.x & 31;
     const long long warps = ((long long)gridDim.x * blockDim.x) >> 5;
@@ -1075,7 +1077,7 @@ static int rf_fused_run(const nntk_recurrent_args *r, int nb, const float *x, co
     p.bias_h = ((G == 3) || r->v2) ? r->d_bh : nullptr;
     p.xw = xw; p.xw_blocked_rows = (nb + 31) / 32;
     static int adaptive = -1;
-    static float adapt_thr = 5.0f;
+    static float adapt_thr = 6.5f;
     if (adaptive < 0) {
         const char *e = getenv("NNTK_RECURRENT_X_ADAPTIVE"); adaptive = e ? atoi(e) : 1;
         if ((e = getenv("NNTK_RECURRENT_X_ADAPT_THR"))) adapt_thr = (float)atof(e);

@@ -274,3 +274,27 @@ def test_fused_recurrent_speculative_one_pass_launch_is_verified(tf32, port):
     assert tf32.NNTKDebugLastRecurrentInputPasses() == 3, "the loud frame was not caught: the three-pass launch did not run"
     assert_parity(got[pick].cpu().numpy(), want, tol=TF32_TOL, what="GRU-256 with one loud unsampled frame (speculative one-pass launch redone)")
     assert_parity(h[pick].cpu().numpy(), want[:, -1], tol=TF32_TOL, what="... final state written by the second launch")
+
+
+@pytest.mark.parametrize("scale,passes", [(1.0, 3), (0.12, 1)])
+def test_c4_projection_operand_passes(tf32, ref, scale, passes):
+    """LSTM 512 -> 512, T = 500 (C4): the hoisted projection takes 3xbf16 for N(0,1) inputs (|x_t| |W_n| ~ 17) and a single fp16 pass
+    when the inputs are small (0.12 N(0,1): ~ 2; the second layer of the stack sees ~ 3.5) -- both within 1e-3 of the reference"""
+    import torch
+    H, T, B = 512, 500, 1600
+    rng = np.random.default_rng(9)
+    pool = (scale * rng.standard_normal((64, T, H))).astype(np.float32)
+    dev = torch.device("cuda:0")
+    x = torch.from_numpy(pool).to(dev).repeat(B // 64, 1, 1).contiguous()
+    r = L.Recurrent(tf32, "lstm", H, H, T)
+    helpers.fill_recurrent(r, 430)
+    got = r.apply_batch(x)
+    torch.cuda.synchronize()
+    assert _path(tf32) == "fused_tc_xw"
+    tf32.nntk_cuda_last_proj_passes.restype = __import__("ctypes").c_int
+    assert tf32.nntk_cuda_last_proj_passes() == passes
+    for b in (3, B - 1):
+        rr = L.Recurrent(ref, "lstm", H, H, T); helpers.copy_weights(rr, r)
+        want = rr.apply(pool[b % 64]); rr.close()
+        assert_parity(got[b].cpu().numpy(), want, tol=TF32_TOL, what=f"C4 LSTM-512 T=500, inputs x {scale}: {passes} projection pass(es), sequence {b}")
+    r.close()
