@@ -5,8 +5,9 @@
     compute-sanitizer --tool racecheck python scripts/sanitize_cases.py
 
 Covers: the fp32 DSMEM cluster kernel, the TF32 and fp16 tcgen05 cluster kernels (incl. the one-slice remainder launch), the fused
-persistent pair kernel (FUSED 1- and 3-pass, XW mode, clusters of 2 / 4), the per-step tensor-core kernel, the tcgen05 GEMM, K1
-(dense and pitched) and the host-buffer staging pipeline with >= 3 chunks.  Results are checked against the oracle port so a
+persistent pair kernel (FUSED 1- and 3-pass, XW mode, clusters of 2 / 4, split and 32-row shapes, the speculative pair of launches and
+the per-step decision), the per-step tensor-core kernel, the tcgen05 GEMM (one-CTA, multicast clusters, cta_group::2, gated launches),
+K1 (dense, pitched, fp16 rows) and the host-buffer staging pipeline with >= 3 chunks.  Results are checked against the oracle port so a
 "clean" run also means a correct one."""
 import os, sys
 from pathlib import Path
@@ -47,6 +48,12 @@ rec("lstm", 64, 128, 4, 70, 1, 1e-3, seq=False)         # fused pair kernel, LST
 rec("gru", 40, 128, 4, 140, 1, 1e-3)                    # fused pair kernel, XW mode (in % 64 != 0)
 rec("lstm", 64, 264, 3, 290, 1, 1e-3)                   # per-step tensor-core kernel (H % 32 != 0)
 rec("gru", 32, 64, 4, 300, 2, 1e-5)                     # 3xTF32 per-step kernel
+rec("gru", 64, 128, 5, 700, 1, 1e-3)                    # fused pair kernel: split mode + 32-row mode candidates, speculative pair of launches
+rec("gru", 64, 128, 5, 700, 1, 1e-3, env={"NNTK_RECURRENT_X_SPECULATE": "0"})       # ... the per-step kernel alone
+os.environ["NNTK_RECURRENT_X_SPECULATE"] = "1"
+rec("lstm", 64, 128, 4, 600, 1, 1e-3, env={"NNTK_RECURRENT_FUSED_SPLIT": "2"})      # split mode forced: DSMEM exchange of h_t halves
+os.environ.pop("NNTK_RECURRENT_FUSED_SPLIT")
+rec("lstm", 72, 256, 4, 1500, 1, 1e-3)                  # XW mode behind the adaptive projection (cta_group::2 GEMM, gated fp16 / 3xbf16)
 
 # conv on tcgen05 + the fused front end (pitched K1) + the staging pipeline with host buffers (>= 3 chunks of ~32 MiB)
 assert lib.NNTKSetMathMode(1) == 0
