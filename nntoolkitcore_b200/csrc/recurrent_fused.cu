@@ -190,12 +190,12 @@ template <int G, bool FUSED>
 struct RfPlan {
     int a_h, x_hi, x_lo, out_stg, bias, ring, bars, total;
     int sub_bytes, stage_bytes;
-    __host__ __device__ RfPlan(int H, int in, int xp, int ring_stages) {
+    __host__ __device__ RfPlan(int H, int in, int xp, int ring_stages, bool dbx = false) {
         sub_bytes = 32 * G * 128;                            // one k-block of B: [32 G rows of this CTA][64 halves]
         stage_bytes = 2 * sub_bytes;                         // a ring stage holds two k-blocks
         int o = 0;
         a_h = o; o += RF_ROWS * H * 2;                       // [H/64 k-blocks][64 rows][128 B]
-        x_hi = o; o += FUSED ? RF_ROWS * in * 2 : 0;         // [in/64][64 rows][128 B]
+        x_hi = o; o += FUSED ? RF_ROWS * in * 2 * (dbx ? 2 : 1) : 0;   // [in/64][64 rows][128 B]; DBX kernels: two of them (steps t and t + 1)
         x_lo = o; o += (FUSED && xp == 3) ? RF_ROWS * in * 2 : 0;
         out_stg = o; o += 8 * 2048;                          // per epilogue warp: [32 rows][16 floats] (SWIZZLE_64B) or 16 x [32 rows][8 floats]
         ring = o; o += ring_stages * stage_bytes;
@@ -209,11 +209,14 @@ struct RfPlan {
 constexpr int RFB_RING_FULL = 0, RFB_RING_EMPTY = RF_MAX_RING, RFB_ACC_FULL = 2 * RF_MAX_RING, RFB_ACC_EMPTY = RFB_ACC_FULL + 4,
               RFB_H_FULL = RFB_ACC_EMPTY + 4, RFB_X_FULL = RFB_H_FULL + 1 /* hi image */, RFB_XL_FULL = RFB_X_FULL + 1 /* lo image, per k-block */,
               RFB_X_EMPTY = RFB_XL_FULL + 4, RFB_A_FREE = RFB_X_EMPTY + 1 /* split mode: both pairs' MMAs of the step have read A_h */,
-              RFB_END = RFB_A_FREE + 1;
+              RFB_XF2 = RFB_A_FREE + 1 /* DBX kernels: x tile of parity b full */, RFB_XE2 = RFB_XF2 + 2 /* ... free again */,
+              RFB_END = RFB_XE2 + 2;
 
 // NCMAX: compile-time bound of the tiles per step (H / 64 <= NCMAX): sizes the register-resident pending-h array.
-template <int G, bool FUSED, int NCMAX>
-__global__ void __launch_bounds__(FUSED ? RF_THREADS_FUSED : RF_THREADS_XW, 1)
+// DBX (FUSED, one-pass plan only): 16 epilogue warps (8 units of a tile per thread, 96 registers) + 8 slim converter warps that write
+// the fp16 image of x_t straight into one of TWO x tiles (no register-resident copy: 40 registers) + 4 control warps = 896 threads.
+template <int G, bool FUSED, int NCMAX, bool DBX = false>
+__global__ void __launch_bounds__(FUSED ? (DBX ? 896 : RF_THREADS_FUSED) : RF_THREADS_XW, 1)
 recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_wl,
                        const __grid_constant__ CUtensorMap map_u, const __grid_constant__ CUtensorMap map_out, RfParams p) {
     constexpr int NW = 64 * G;                              // N of one MMA (LSTM 256, GRU 192)
@@ -239,7 +242,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     const int KBH = H / 64, KBX = FUSED ? IN / 64 : 0;      // k-blocks of the recurrent / input part
     const int NB = (512 - H / S / 2) / 128;                 // accumulator buffers (3 when the pair owns <= 256 units, 2 for 512)
     const uint32_t STATE_COL = (uint32_t)(NB * 128);
-    const RfPlan<G, FUSED> pl(H, IN, p.xp, p.ring_stages);
+    const RfPlan<G, FUSED> pl(H, IN, p.xp, p.ring_stages, DBX);
     uint8_t *sAh = smem + pl.a_h, *sXh = smem + pl.x_hi, *sXl = smem + pl.x_lo, *sOut = smem + pl.out_stg, *sRing = smem + pl.ring;
     float *sBias = reinterpret_cast<float *>(smem + pl.bias);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + pl.bars);
@@ -250,7 +253,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);          // warp-uniform for the compiler (role dispatch, uniform registers)
     // FUSED: 8 epilogue warps (16 units of a tile per thread) + 8 converter warps.  XW: 16 epilogue warps (8 units per thread) -- its
     // epilogue also adds the hoisted projection and, with 8 warps, took 4 700 cycles per LSTM-512 tile against 2 064 of MMA.
-    constexpr int EPW = FUSED ? RF_FUSED_EPW : 16, UPT = 128 / EPW, NE = UPT / 8;
+    constexpr int EPW = FUSED ? (DBX ? 16 : RF_FUSED_EPW) : 16, UPT = 128 / EPW, NE = UPT / 8;
     constexpr int CONV_W0 = FUSED ? EPW : 8, CTRL_W0 = FUSED ? EPW + 8 : 16;     // first converter / control warp
     const uint32_t crank = __shfl_sync(0xffffffffu, rf_rank(), 0);   // rank in the cluster (warp-uniform for the compiler); pairs are (0,1), (2,3), ...
     const uint32_t rank = crank & 1u, leader = crank & ~1u; // rank inside the pair, cluster rank of the pair's leader
@@ -278,6 +281,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         mbar_init(bars + RFB_X_FULL, 16);
         for (int b = 0; b < 4; ++b) mbar_init(bars + RFB_XL_FULL + b, 16);
         mbar_init(bars + RFB_X_EMPTY, 1);
+        for (int b = 0; b < 2; ++b) { mbar_init(bars + RFB_XF2 + b, 16); mbar_init(bars + RFB_XE2 + b, 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == CTRL_W0 + 3) {
@@ -314,7 +318,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
 #endif
 
     if (warp >= CTRL_W0) {
-        if (FUSED && RF_FUSED_EPW == 8) asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
+        if (FUSED && !DBX && RF_FUSED_EPW == 8) asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
         else asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
         if (warp == CTRL_W0) {
             // ===== ring producer: this CTA's half of every B stage (two k-blocks), in the order the MMA issuer consumes them =====
@@ -397,6 +401,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
             };
             const float wstat = PUB ? __ldg(p.stats + 1) : 0.0f;
             int xp_t = XP, any3 = 0;     // passes of the step whose input parts are being issued
+            uint32_t xh_t = xh_a;        // its x tile (DBX: alternates)
             // (t, c) = step and tile; buf = accumulator buffer of the tile, use = how often that buffer has been used before
             auto x_part = [&](int t, int c, int buf, int use) {
                 if (use > 0) { RF_T0(); mbar_wait(bars + RFB_ACC_EMPTY + buf, (uint32_t)((use - 1) & 1)); RF_T1(1); }
@@ -404,6 +409,10 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 const uint32_t d = tmem + (uint32_t)(buf * 128);
                 if (c == 0) {            // the hi image of x_t (and, per-step mode, the row norms the converters published with it)
                     RF_T0();
+                    if (DBX) {           // x tile of parity t & 1, used for the (t >> 1)-th time
+                        if (PUB) rf_mbar_wait_cl(bars + RFB_XF2 + (t & 1), (uint32_t)((t >> 1) & 1)); else mbar_wait(bars + RFB_XF2 + (t & 1), (uint32_t)((t >> 1) & 1));
+                        xh_t = xh_a + (uint32_t)((t & 1) * RF_ROWS * IN * 2);
+                    } else
                     if (PUB) rf_mbar_wait_cl(bars + RFB_X_FULL, (uint32_t)(t & 1)); else mbar_wait(bars + RFB_X_FULL, (uint32_t)(t & 1));
                     RF_T1(3);
                     if (PUB) {
@@ -428,9 +437,9 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                         stage_mmas(d, xh_a, xl_a, kb, min(2, KBX - kb), false);
                     }
                 } else {
-                    for (int kb = 0; kb < KBX; kb += 2) stage_mmas(d, xh_a, 0u, kb, min(2, KBX - kb), true);
+                    for (int kb = 0; kb < KBX; kb += 2) stage_mmas(d, DBX ? xh_t : xh_a, 0u, kb, min(2, KBX - kb), true);
                 }
-                if (c == NC - 1) { if (rf_elect()) rf_commit(bars + RFB_X_EMPTY, pair_mask); __syncwarp(); }     // the x tile may be rewritten once these MMAs are done
+                if (c == NC - 1) { if (rf_elect()) rf_commit(bars + (DBX ? RFB_XE2 + (t & 1) : RFB_X_EMPTY), pair_mask); __syncwarp(); }     // the x tile may be rewritten once these MMAs are done
             };
             auto h_part = [&](int t, int c, int buf, int use) {
                 if (c == 0) { RF_T0(); mbar_wait(bars + RFB_H_FULL, (uint32_t)(t & 1)); RF_T1(2); }
@@ -465,6 +474,54 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         // ===== x converters (FUSED only): fp32 rows of x_t from global -> fp16 hi (and lo) k-block tiles =====
         // item (row, 16-byte chunk of the fp16 row = 8 floats): a warp covers 4 rows x 256 contiguous bytes per load instruction and
         // 512 contiguous (swizzled) bytes per store.  x_{t+1} is loaded right after x_t has been converted and waits in registers.
+        if (FUSED && DBX) {
+            // slim converters: x_t goes global -> registers (one k-block at a time) -> fp16 -> the x tile of parity t & 1, up to two
+            // steps ahead of the MMAs; nothing is kept in registers across steps
+            asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+            const int ct = tid - CONV_W0 * 32;
+            const uint32_t xf_leader = rf_mapa(smem_u32(bars + RFB_XF2), leader);
+            const uint32_t xs_leader = rf_mapa(smem_u32(xs), leader) + 4u * (uint32_t)((int)rank * 8 + (ct >> 5));
+            const int nit = p.rows == RF_ROWS ? 2 : 1;
+            const int r0 = ct >> 3, ch = ct & 7;                 // item (row r0 + 32 it, 16-byte chunk ch of the fp16 row)
+            for (int t = 0; t < T; ++t) {
+                const int b = t & 1;
+                if (t >= 2) mbar_wait(bars + RFB_XE2 + b, (uint32_t)(((t - 2) >> 1) & 1));
+                uint8_t *tile = sXh + (size_t)b * (RF_ROWS * IN * 2);
+                float ss0 = 0.0f, ss1 = 0.0f;
+                for (int kb = 0; kb < KBX; ++kb) {
+                    float4 a[2][2];
+#pragma unroll
+                    for (int it = 0; it < 2; ++it) {
+                        const int r = r0 + 32 * it, row = row0 + r;
+                        if (it < nit && row < p.B) {
+                            const float4 *src = reinterpret_cast<const float4 *>(p.x + ((size_t)row * T + t) * IN + kb * 64 + ch * 8);
+                            a[it][0] = __ldg(src); a[it][1] = __ldg(src + 1);
+                        } else a[it][0] = a[it][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+#pragma unroll
+                    for (int it = 0; it < 2; ++it) {
+                        const float4 u = a[it][0], w = a[it][1];
+                        const float q = fmaf(u.x, u.x, fmaf(u.y, u.y, fmaf(u.z, u.z, fmaf(u.w, u.w, fmaf(w.x, w.x, fmaf(w.y, w.y, fmaf(w.z, w.z, w.w * w.w)))))));
+                        if (it == 0) ss0 += q; else ss1 += q;
+                        const int r = r0 + 32 * it;
+                        if (it < nit)
+                            *reinterpret_cast<uint4 *>(tile + (size_t)kb * (RF_ROWS * 128) + r * 128 + ((ch ^ (r & 7)) << 4)) =
+                                make_uint4(rf_pack_sat(u.x, u.y), rf_pack_sat(u.z, u.w), rf_pack_sat(w.x, w.y), rf_pack_sat(w.z, w.w));
+                    }
+                }
+                if (PUB) {
+#pragma unroll
+                    for (int o = 1; o < 8; o <<= 1) { ss0 += __shfl_xor_sync(0xffffffffu, ss0, o); ss1 += __shfl_xor_sync(0xffffffffu, ss1, o); }
+                    float m2 = fmaxf(ss0, ss1);
+                    m2 = fmaxf(m2, __shfl_xor_sync(0xffffffffu, m2, 8));
+                    m2 = fmaxf(m2, __shfl_xor_sync(0xffffffffu, m2, 16));
+                    if (lane == 0) asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(xs_leader + 64u * (uint32_t)b), "f"(m2) : "memory");
+                }
+                rf_fence_async();
+                __syncwarp();
+                if (lane == 0) { if (PUB) rf_arrive_cl_release(xf_leader + 8u * (uint32_t)b); else rf_arrive_cl(xf_leader + 8u * (uint32_t)b); }
+            }
+        } else
         if (FUSED) {
             if (RF_FUSED_EPW == 8) asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
             else asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
@@ -570,7 +627,8 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         }
     } else {
         // ===== epilogue (warps 0..7): thread = row m of this CTA x 16 hidden units of every tile =====
-        if (FUSED && RF_FUSED_EPW == 8) asm volatile("setmaxnreg.inc.sync.aligned.u32 128;");
+        if (FUSED && DBX) asm volatile("setmaxnreg.inc.sync.aligned.u32 96;");
+        else if (FUSED && RF_FUSED_EPW == 8) asm volatile("setmaxnreg.inc.sync.aligned.u32 128;");
         else if (FUSED) asm volatile("setmaxnreg.inc.sync.aligned.u32 80;");
         else asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");
         const int ew = warp, q = warp & 3, j = ew >> 2;
@@ -875,20 +933,20 @@ __half *g_rf_scratch = nullptr;
 size_t g_rf_halves = 0;
 
 template <int G, bool FUSED>
-int rf_ring_stages(int H, int in, int xp) {
+int rf_ring_stages(int H, int in, int xp, bool dbx = false) {
     int stages = RF_MAX_RING;
-    for (; stages >= 2; --stages) { RfPlan<G, FUSED> pl(H, in, xp, stages); if (pl.total <= 227 * 1024) break; }
+    for (; stages >= 2; --stages) { RfPlan<G, FUSED> pl(H, in, xp, stages, dbx); if (pl.total <= 227 * 1024) break; }
     return stages;
 }
 
 // dry: only report whether a cluster of p.cs CTAs of this kernel can be scheduled (1 = no)
-template <int G, bool FUSED, int NCMAX>
+template <int G, bool FUSED, int NCMAX, bool DBX = false>
 int rf_launch(const CUtensorMap &mw, const CUtensorMap &mwl, const CUtensorMap &mu, const CUtensorMap &mo, RfParams &p, int pairs, cudaStream_t st, int *dry) {
-    auto kern = recurrent_fused_kernel<G, FUSED, NCMAX>;
-    const int stages = rf_ring_stages<G, FUSED>(p.H, p.in, p.xp);
+    auto kern = recurrent_fused_kernel<G, FUSED, NCMAX, DBX>;
+    const int stages = rf_ring_stages<G, FUSED>(p.H, p.in, p.xp, DBX);
     if (stages < 3) return 1;
     p.ring_stages = stages;
-    const RfPlan<G, FUSED> pl(p.H, p.in, p.xp, stages);
+    const RfPlan<G, FUSED> pl(p.H, p.in, p.xp, stages, DBX);
     static size_t attr_smem = 0;
     if ((size_t)pl.total > attr_smem) {
         NNTK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
@@ -897,7 +955,7 @@ int rf_launch(const CUtensorMap &mw, const CUtensorMap &mwl, const CUtensorMap &
     const int npairs = p.cs / 2, clusters = (pairs + npairs - 1) / npairs;       // surplus pairs run on out-of-range rows
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(clusters * p.cs));
-    cfg.blockDim = dim3(FUSED ? RF_THREADS_FUSED : RF_THREADS_XW);
+    cfg.blockDim = dim3(FUSED ? (DBX ? 896 : RF_THREADS_FUSED) : RF_THREADS_XW);
     cfg.dynamicSmemBytes = pl.total;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -1008,8 +1066,19 @@ static int rf_fused_run(const nntk_recurrent_args *r, int nb, const float *x, co
     int rc;
     p.H = H; p.in = IN; p.xp = xp; p.rows = RF_ROWS; p.split = 1;
     bool small = H <= 256;
+    // NNTK_RECURRENT_FUSED_DBX=1: one-pass FUSED launches take the DBX structure (16 epilogue warps at 96 registers, slim converters,
+    // double-buffered x tile).  Measured on the C5 GRU layer: 8.15 ms against 7.85 ms for the 8-warp epilogue -- twice the epilogue
+    // warps do not shorten the step, so the step is NOT bound by the epilogue's own speed: per step the tensor pipe is busy
+    // ~7.3 k cycles (128 MMAs of >= 57 cycles) and idles through the recurrence's chain (last recurrent MMA -> last tile's
+    // epilogue -> h_full -> first recurrent MMA of the next step).  Kept buildable, off by default.
+    static int want_dbx = -1;
+    if (want_dbx < 0) { const char *e = getenv("NNTK_RECURRENT_FUSED_DBX"); want_dbx = e ? atoi(e) : 0; }
+    const bool dbx = want_dbx && fused && xp == 1 &&
+                     (G == 3 ? rf_ring_stages<3, true>(H, IN, 1, true) : rf_ring_stages<4, true>(H, IN, 1, true)) >= 3;
 #define RF_DISPATCH(DRY) \
-    (G == 3 ? (fused ? (small ? rf_launch<3, true, 4>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<3, true, 8>(mw, mwl, mu, mo, p, pairs, st, DRY)) \
+    (dbx ? (G == 3 ? (small ? rf_launch<3, true, 4, true>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<3, true, 8, true>(mw, mwl, mu, mo, p, pairs, st, DRY)) \
+                   : (small ? rf_launch<4, true, 4, true>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<4, true, 8, true>(mw, mwl, mu, mo, p, pairs, st, DRY))) : \
+     G == 3 ? (fused ? (small ? rf_launch<3, true, 4>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<3, true, 8>(mw, mwl, mu, mo, p, pairs, st, DRY)) \
                      : (small ? rf_launch<3, false, 4>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<3, false, 8>(mw, mwl, mu, mo, p, pairs, st, DRY))) \
             : (fused ? (small ? rf_launch<4, true, 4>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<4, true, 8>(mw, mwl, mu, mo, p, pairs, st, DRY)) \
                      : (small ? rf_launch<4, false, 4>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<4, false, 8>(mw, mwl, mu, mo, p, pairs, st, DRY))))
@@ -1065,7 +1134,7 @@ static int rf_fused_run(const nntk_recurrent_args *r, int nb, const float *x, co
         // per-warp pieces of h_t: FUSED [32 rows][16 floats] (SWIZZLE_64B), XW [32 rows][8 floats] (unswizzled)
         cuuint64_t dims[3] = {(cuuint64_t)H, (cuuint64_t)T, (cuuint64_t)nb};
         cuuint64_t strides[2] = {(cuuint64_t)H * 4, (cuuint64_t)T * H * 4};
-        const bool wide = fused && RF_FUSED_EPW == 8;
+        const bool wide = fused && RF_FUSED_EPW == 8 && !dbx;
         cuuint32_t box[3] = {(cuuint32_t)(wide ? 16 : 8), 1, 32};
         cuuint32_t es[3] = {1, 1, 1};
         CUresult cr = encode(&mo, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, out, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
