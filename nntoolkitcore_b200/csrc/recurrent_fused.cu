@@ -68,6 +68,7 @@ struct RfParams {
                                      //    max |x_t|^2 of their rows with the x tile, the issuer skips the two correction passes' MMAs for that step
     int cs;                          // cluster size: 2, 4 or 8 CTAs = 1, 2 or 4 pairs sharing every B stage by TMA multicast
     int xw_blocked_rows;             // XW mode: row_blocks of the blocked projection
+    int lookahead;                   // FUSED: tiles the input parts run ahead of the recurrent parts (1 or 2; NNTK_RECURRENT_FUSED_LOOKAHEAD)
     int verify;                      // one-pass plan launched on the strength of a SAMPLED pre-scan: the converters still publish every step's row
                                      //    norms and the issuer raises stats[3] when one breaks the bound (the three-pass launch behind then runs)
     int sel;                         // 0 always run; 1 run iff the sampled bound holds; 2 run iff it does not, or launch 1 raised stats[3]
@@ -242,6 +243,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     const int KBH = H / 64, KBX = FUSED ? IN / 64 : 0;      // k-blocks of the recurrent / input part
     const int NB = (512 - H / S / 2) / 128;                 // accumulator buffers (3 when the pair owns <= 256 units, 2 for 512)
     const uint32_t STATE_COL = (uint32_t)(NB * 128);
+    const int LA = (p.lookahead >= 2 && NB >= 3) ? 2 : 1;   // input parts issued LA tiles ahead of the recurrent parts
     const RfPlan<G, FUSED> pl(H, IN, p.xp, p.ring_stages, DBX);
     uint8_t *sAh = smem + pl.a_h, *sXh = smem + pl.x_hi, *sXl = smem + pl.x_lo, *sOut = smem + pl.out_stg, *sRing = smem + pl.ring;
     float *sBias = reinterpret_cast<float *>(smem + pl.bias);
@@ -353,11 +355,14 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 if (XP == 3) for (int kb = 0; kb < KBX; kb += 2) put(&map_wl, kb, min(2, KBX - kb), tile);
                 for (int kb = 0; kb < KBX; kb += 2) put(&map_w, kb, min(2, KBX - kb), tile);
             };
-            if (FUSED) put_x(tile0);
+            // issue order (the MMA issuer walks the same one): X(0) .. X(LA - 1), then per tile g: H(g), X(g + LA)
+            const int total = T * NC;
+            int xc = 0, xg = 0;          // tile (within the step) and linear index of the next input part
+            if (FUSED) for (; xg < LA && xg < total; ++xg) { put_x(tile0 + xc); if (++xc == NC) xc = 0; }
             for (int t = 0; t < T; ++t)
                 for (int c = 0; c < NC; ++c) {
                     for (int kb = 0; kb < KBH; kb += 2) put(&map_u, kb, min(2, KBH - kb), tile0 + c);
-                    if (FUSED && !(t == T - 1 && c == NC - 1)) put_x(tile0 + (c + 1 == NC ? 0 : c + 1));
+                    if (FUSED && xg < total) { put_x(tile0 + xc); if (++xc == NC) xc = 0; ++xg; }
                 }
             RF_DBG(if (lane == 0) { p.dbg[blockIdx.x * 16 + 8] = dbgc[8]; p.dbg[blockIdx.x * 16 + 9] = dbgc[9]; });
         } else if (warp == CTRL_W0 + 1 && rank == 0) {
@@ -457,14 +462,23 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
             };
             // the tile after (t, c) in issue order and its buffer bookkeeping
             int buf = 0, use = 0;                 // of the tile whose recurrent part is issued next
-            if (FUSED) x_part(0, 0, 0, 0);
+            // The input parts run LA tiles ahead of the recurrent parts.  LA = 2 (NNTK_RECURRENT_FUSED_LOOKAHEAD=2, three accumulator
+            // buffers) puts X(t+1, 0) AND X(t+1, 1) into the tensor pipe while the last tile's epilogue closes step t -- measured
+            // SLOWER on the C5 GRU layer (8.11 vs 7.75 ms), so the default stays 1.
+            const int total = T * NC;
+            int xt = 0, xc = 0, xbuf = 0, xuse = 0, xg = 0;      // step, tile, buffer and use count of the next input part
+            auto x_next = [&]() {
+                x_part(xt, xc, xbuf, xuse);
+                if (++xc == NC) { xc = 0; ++xt; }
+                if (++xbuf == NB) { xbuf = 0; ++xuse; }
+                ++xg;
+            };
+            if (FUSED) while (xg < LA && xg < total) x_next();
             for (int t = 0; t < T; ++t)
                 for (int c = 0; c < NC; ++c) {
                     h_part(t, c, buf, use);
-                    int nbuf = buf + 1, nuse = use;
-                    if (nbuf == NB) { nbuf = 0; ++nuse; }
-                    if (FUSED && !(t == T - 1 && c == NC - 1)) x_part(c + 1 == NC ? t + 1 : t, c + 1 == NC ? 0 : c + 1, nbuf, nuse);
-                    buf = nbuf; use = nuse;
+                    if (FUSED && xg < total) x_next();
+                    if (++buf == NB) { buf = 0; ++use; }
                 }
             if (PUB && lane == 0) atomicMax(reinterpret_cast<int *>(const_cast<float *>(p.stats) + 2), __float_as_int(any3 ? 3.0f : 1.0f));
             RF_DBG(if (lane == 0) { for (int i = 0; i < 4; ++i) p.dbg[blockIdx.x * 16 + i] = dbgc[i]; p.dbg[blockIdx.x * 16 + 10] = clock64() - t_start;
@@ -1158,6 +1172,7 @@ static int rf_fused_run(const nntk_recurrent_args *r, int nb, const float *x, co
     if (per_step < 0) { const char *e = getenv("NNTK_RECURRENT_X_PERSTEP"); per_step = e ? atoi(e) : 1; }
     p.per_step = 0;
     p.sel = spec; p.verify = spec == 1;
+    { static int la = -1; if (la < 0) { const char *e = getenv("NNTK_RECURRENT_FUSED_LOOKAHEAD"); la = e ? atoi(e) : 1; } p.lookahead = la; }
     p.h_init = h_init ? h_init : h; p.c_init = c_init ? c_init : c;
     if (spec) {
         p.per_step = spec == 2;           // stats prepared by the caller (sampled row norms, W norms, cleared flag)
