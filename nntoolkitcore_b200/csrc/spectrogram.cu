@@ -126,7 +126,10 @@ __device__ __forceinline__ void tile_load_async(const SpecParams &p, const TileG
 // HOP5 = step / 32 when the hop is 160 (the BASELINE framing), else 0: lane L reads x[L + 32 j], so with a hop of 5 * 32 the
 // second frame's element j IS the first frame's element j + 5 -- 21 shared-memory loads per frame pair instead of 32 (the
 // kernel is LSU-wavefront bound: 180 wavefronts per pair, ncu r1).
-template <bool FULLWIN, int MODE, bool MEL, int HOP5>
+// WIN: 0 = the window size is a run-time value; otherwise it is this compile-time constant (512 = the full transform; 400 = the
+// BASELINE KWS framing).  With a run-time window every element of every frame pays a compare + select (ncu on the C5 framing:
+// FSEL 11 % + ISETP 8 % of all instructions); as a constant all but one of the 16 slots resolve at compile time.
+template <int WIN, int MODE, bool MEL, int HOP5>
 __global__ void __launch_bounds__(SPEC_THREADS, 2)
 spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const float2 *__restrict__ tw512,
                       const float *__restrict__ in, float *__restrict__ out, const uint2 *__restrict__ mel) {
@@ -155,6 +158,7 @@ spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const floa
     // per-lane constants (registers), fetched while the first tile is in flight.  The output scale is folded into the
     // window: |FFT(m w x)| = m |FFT(w x)| (magnitude), |FFT(sqrt(m) w x)|^2 = m |FFT(w x)|^2 (PSD).
     // (A negative scale -- only reachable through SpectrogramSetScaleFactor -- flips the sign afterwards.)
+    const int WS = WIN ? WIN : p.window_size;
     SpecLaneConst lc;
     spec_lane_const(lane, tw512, lc);
     const float wscale = MODE == 0 ? fabsf(p.mag_mul) : sqrtf(fabsf(p.psd_mid));
@@ -163,7 +167,7 @@ spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const floa
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
         const int n = lane + 32 * j;
-        w[j] = (FULLWIN || n < p.window_size) ? __ldg(window + n) * wscale : 0.0f;
+        w[j] = (n < WS) ? __ldg(window + n) * wscale : 0.0f;
     }
     float2 *sx = s_x + warp * NNTK_SPEC_SMEM_F2;
     float2 *x1_st = sx + spec_x1_st_base(lane);
@@ -214,13 +218,13 @@ spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const floa
                 float r[16 + HOP5];
 #pragma unroll
                 for (int k = 0; k < 16 + HOP5; ++k) {
-                    const bool as_a = k < 16 && (FULLWIN || lane + 32 * k < p.window_size);
-                    const bool as_b = k >= HOP5 && has_b && (FULLWIN || lane + 32 * (k - HOP5) < p.window_size);
+                    const bool as_a = k < 16 && (lane + 32 * k < WS);
+                    const bool as_b = k >= HOP5 && has_b && (lane + 32 * (k - HOP5) < WS);
                     r[k] = (as_a || as_b) ? xa[32 * k] : 0.0f;
                 }
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
-                    const bool in_win = FULLWIN || lane + 32 * j < p.window_size;
+                    const bool in_win = lane + 32 * j < WS;
                     const float a = in_win ? r[j] : 0.0f;
                     const float b = has_b ? (in_win ? r[j + HOP5] : 0.0f) : a;
                     v[j] = make_float2(w[j] * a, w[j] * b);
@@ -229,7 +233,7 @@ spectrogram512_kernel(SpecParams p, const float *__restrict__ window, const floa
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
                     float a = 0.0f, b = 0.0f;
-                    if (FULLWIN || lane + 32 * j < p.window_size) {
+                    if (lane + 32 * j < WS) {
                         a = xa[32 * j];
                         b = xb[32 * j];
                     }
@@ -537,17 +541,17 @@ static int spectrogram_run(const nntk_spectrogram_args *a, const nntk_mel_args *
         p.n_clips = n_clips;
         const bool fullwin = a->window_size == NNTK_SPEC_N;
         typedef void (*SpecKernel)(SpecParams, const float *, const float2 *, const float *, float *, const uint2 *);
-        static const SpecKernel kernels[16] = {
-            spectrogram512_kernel<false, 0, false, 0>, spectrogram512_kernel<true, 0, false, 0>,
-            spectrogram512_kernel<false, 1, false, 0>, spectrogram512_kernel<true, 1, false, 0>,
-            spectrogram512_kernel<false, 0, true, 0>,  spectrogram512_kernel<true, 0, true, 0>,
-            spectrogram512_kernel<false, 1, true, 0>,  spectrogram512_kernel<true, 1, true, 0>,
-            spectrogram512_kernel<false, 0, false, 5>, spectrogram512_kernel<true, 0, false, 5>,
-            spectrogram512_kernel<false, 1, false, 5>, spectrogram512_kernel<true, 1, false, 5>,
-            spectrogram512_kernel<false, 0, true, 5>,  spectrogram512_kernel<true, 0, true, 5>,
-            spectrogram512_kernel<false, 1, true, 5>,  spectrogram512_kernel<true, 1, true, 5>};
-        static size_t attr_bytes[16] = {0};
-        const int ki = (a->step == 160 ? 8 : 0) + (m ? 4 : 0) + (a->mode ? 2 : 0) + (fullwin ? 1 : 0);
+        // [hop 160][mel][mode][window class: 0 run-time, 1 full (512), 2 the 400-sample window of the BASELINE framing (hop 160 only)]
+#define SPEC_K3(MODE, MEL, HOP) spectrogram512_kernel<0, MODE, MEL, HOP>, spectrogram512_kernel<512, MODE, MEL, HOP>, \
+                                spectrogram512_kernel<(HOP ? 400 : 0), MODE, MEL, HOP>
+        static const SpecKernel kernels[24] = {
+            SPEC_K3(0, false, 0), SPEC_K3(1, false, 0), SPEC_K3(0, true, 0), SPEC_K3(1, true, 0),
+            SPEC_K3(0, false, 5), SPEC_K3(1, false, 5), SPEC_K3(0, true, 5), SPEC_K3(1, true, 5)};
+#undef SPEC_K3
+        static size_t attr_bytes[24] = {0};
+        const bool hop160 = a->step == 160;
+        const int wc = fullwin ? 1 : (hop160 && a->window_size == 400) ? 2 : 0;
+        const int ki = ((hop160 ? 4 : 0) + (m ? 2 : 0) + (a->mode ? 1 : 0)) * 3 + wc;
         const SpecKernel kern = kernels[ki];
         if (bytes > attr_bytes[ki]) {
             NNTK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
