@@ -470,13 +470,19 @@ static int recurrent_chunk(const nntk_recurrent_args *r, int b0, int nb, float *
     // 0. tensor-core mode, default activations, H % 64 == 0: ONE persistent kernel per layer (recurrent_fused.cu).  Plan 1 also
     //    computes the input projection inside that kernel -- no projection buffer, no GEMM launch; plan 2 reads the blocked
     //    hoisted projection below.
-    const int fplan = (mode == 1 && G != 1) ? nntk_cuda_recurrent_fused_plan(r, nb) : 0;
+    //    The fp32-contract mode has the same kernel for the GRU with every product in three split-fp16 passes ("fused_x3").
+    static int fused_x3 = -1;
+    if (fused_x3 < 0) { const char *e = getenv("NNTK_RECURRENT_FUSED_X3"); fused_x3 = e ? atoi(e) : 1; }
+    const bool x3_fused = mode == 2 && G == 3 && fused_x3;
+    int fplan = ((mode == 1 && G != 1) || x3_fused) ? nntk_cuda_recurrent_fused_plan(r, nb) : 0;
+    if (x3_fused && fplan != 1) fplan = 0;
     if (fplan == 1) {
         int used = 0;
         int frc = nntk_cuda_recurrent_fused(r, nb, x, nullptr, h, c, out, &used);
         if (frc) return frc;
-        if (used) { g_last_path = "fused_tc"; return 0; }
+        if (used) { g_last_path = x3_fused ? "fused_x3" : "fused_tc"; return 0; }
     }
+    if (x3_fused) fplan = 0;
     static int min_batch = -1, use_h16 = -1;
     // never below 32: the blocked projection layout rounds the chunk up to 32 sequences and the chunker only reserves that
     // rounding for chunks of at least 32 (nntk_cuda_recurrent below)
@@ -621,11 +627,17 @@ extern "C" int nntk_cuda_recurrent(const nntk_recurrent_args *r) {
         }
     if (r->batch == 0 || r->T == 0) return 0;
     // The fused persistent kernel (tensor-core mode) computes the projection itself: no workspace, so no batch chunking either
-    if (nntk_cuda_math_mode() == 1 && r->cell != 1 && nntk_cuda_recurrent_fused_plan(r, r->batch) == 1) {
-        int used = 0;
-        rc = nntk_cuda_recurrent_fused(r, r->batch, r->d_x, nullptr, r->d_h, r->d_c, r->d_out, &used);
-        if (rc) return rc;
-        if (used) { g_last_path = "fused_tc"; return 0; }
+    {
+        static int fused_x3 = -1;
+        if (fused_x3 < 0) { const char *e = getenv("NNTK_RECURRENT_FUSED_X3"); fused_x3 = e ? atoi(e) : 1; }
+        const int mm = nntk_cuda_math_mode();
+        const bool x3_fused = mm == 2 && r->cell == 3 && fused_x3;
+        if (((mm == 1 && r->cell != 1) || x3_fused) && nntk_cuda_recurrent_fused_plan(r, r->batch) == 1) {
+            int used = 0;
+            rc = nntk_cuda_recurrent_fused(r, r->batch, r->d_x, nullptr, r->d_h, r->d_c, r->d_out, &used);
+            if (rc) return rc;
+            if (used) { g_last_path = x3_fused ? "fused_x3" : "fused_tc"; return 0; }
+        }
     }
     // batch chunks that fit the workspace
     const size_t per_seq = ((size_t)r->T * r->cell * r->H + 6 * (size_t)r->H) * sizeof(float);

@@ -68,6 +68,7 @@ struct RfParams {
                                      //    max |x_t|^2 of their rows with the x tile, the issuer skips the two correction passes' MMAs for that step
     int cs;                          // cluster size: 2, 4 or 8 CTAs = 1, 2 or 4 pairs sharing every B stage by TMA multicast
     int xw_blocked_rows;             // XW mode: row_blocks of the blocked projection
+    int x3;                          // X3 kernels (fp32-contract mode): h carried as fp16 hi + lo A tiles, three passes for the recurrent part too
     int lookahead;                   // FUSED: tiles the input parts run ahead of the recurrent parts (1 or 2; NNTK_RECURRENT_FUSED_LOOKAHEAD)
     int verify;                      // one-pass plan launched on the strength of a SAMPLED pre-scan: the converters still publish every step's row
                                      //    norms and the issuer raises stats[3] when one breaks the bound (the three-pass launch behind then runs)
@@ -189,13 +190,14 @@ __device__ __forceinline__ void rf_split2(float a, float b, uint32_t &hi, uint32
 // shared-memory plan (host and device agree through this one struct)
 template <int G, bool FUSED>
 struct RfPlan {
-    int a_h, x_hi, x_lo, out_stg, bias, ring, bars, total;
+    int a_h, a_l, x_hi, x_lo, out_stg, bias, ring, bars, total;
     int sub_bytes, stage_bytes;
-    __host__ __device__ RfPlan(int H, int in, int xp, int ring_stages, bool dbx = false) {
+    __host__ __device__ RfPlan(int H, int in, int xp, int ring_stages, bool dbx = false, bool x3 = false) {
         sub_bytes = 32 * G * 128;                            // one k-block of B: [32 G rows of this CTA][64 halves]
         stage_bytes = 2 * sub_bytes;                         // a ring stage holds two k-blocks
         int o = 0;
         a_h = o; o += RF_ROWS * H * 2;                       // [H/64 k-blocks][64 rows][128 B]
+        a_l = o; o += x3 ? RF_ROWS * H * 2 : 0;              // X3 kernels: the fp16 image of h - fp16(h)
         x_hi = o; o += FUSED ? RF_ROWS * in * 2 * (dbx ? 2 : 1) : 0;   // [in/64][64 rows][128 B]; DBX kernels: two of them (steps t and t + 1)
         x_lo = o; o += (FUSED && xp == 3) ? RF_ROWS * in * 2 : 0;
         out_stg = o; o += 8 * 2048;                          // per epilogue warp: [32 rows][16 floats] (SWIZZLE_64B) or 16 x [32 rows][8 floats]
@@ -216,10 +218,15 @@ constexpr int RFB_RING_FULL = 0, RFB_RING_EMPTY = RF_MAX_RING, RFB_ACC_FULL = 2 
 // NCMAX: compile-time bound of the tiles per step (H / 64 <= NCMAX): sizes the register-resident pending-h array.
 // DBX (FUSED, one-pass plan only): 16 epilogue warps (8 units of a tile per thread, 96 registers) + 8 slim converter warps that write
 // the fp16 image of x_t straight into one of TWO x tiles (no register-resident copy: 40 registers) + 4 control warps = 896 threads.
-template <int G, bool FUSED, int NCMAX, bool DBX = false>
+// X3 (GRU, FUSED): the fp32-contract variant.  Every product is split-fp16 in three passes -- the input part as before, and the
+// recurrent part too: h_t is carried as TWO A tiles, fp16(h) and fp16(h - fp16(h)), rebuilt at the end of every step from the exact
+// fp32 state in TMEM, against U_lo and U_hi -- and the gates use expf / tanhf instead of MUFU.TANH.  Operands are exact to ~2^-22,
+// accumulation and state are fp32: the 1e-5 contract of NNTK_MATH_TF32X3, in ONE launch per layer instead of one per step.
+template <int G, bool FUSED, int NCMAX, bool DBX = false, bool X3 = false>
 __global__ void __launch_bounds__(FUSED ? (DBX ? 896 : RF_THREADS_FUSED) : RF_THREADS_XW, 1)
 recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_wl,
-                       const __grid_constant__ CUtensorMap map_u, const __grid_constant__ CUtensorMap map_out, RfParams p) {
+                       const __grid_constant__ CUtensorMap map_u, const __grid_constant__ CUtensorMap map_ul,
+                       const __grid_constant__ CUtensorMap map_out, RfParams p) {
     constexpr int NW = 64 * G;                              // N of one MMA (LSTM 256, GRU 192)
     constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(NW >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);   // f32 <- f16 x f16, K-major
     constexpr int ROWS_B = 32 * G;                          // B rows per CTA per k-block
@@ -244,7 +251,8 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     const int NB = (512 - H / S / 2) / 128;                 // accumulator buffers (3 when the pair owns <= 256 units, 2 for 512)
     const uint32_t STATE_COL = (uint32_t)(NB * 128);
     const int LA = (p.lookahead >= 2 && NB >= 3) ? 2 : 1;   // input parts issued LA tiles ahead of the recurrent parts
-    const RfPlan<G, FUSED> pl(H, IN, p.xp, p.ring_stages, DBX);
+    const RfPlan<G, FUSED> pl(H, IN, p.xp, p.ring_stages, DBX, X3);
+    uint8_t *sAl = smem + pl.a_l;
     uint8_t *sAh = smem + pl.a_h, *sXh = smem + pl.x_hi, *sXl = smem + pl.x_lo, *sOut = smem + pl.out_stg, *sRing = smem + pl.ring;
     float *sBias = reinterpret_cast<float *>(smem + pl.bias);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + pl.bars);
@@ -275,6 +283,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_wl) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_u) : "memory");
+        if (X3) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_ul) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_out) : "memory");
         for (int s = 0; s < p.ring_stages; ++s) { mbar_init(bars + RFB_RING_FULL + s, 1); mbar_init(bars + RFB_RING_EMPTY + s, (uint32_t)npairs); }
         for (int b = 0; b < 4; ++b) { mbar_init(bars + RFB_ACC_FULL + b, 1); mbar_init(bars + RFB_ACC_EMPTY + b, 2 * EPA); }
@@ -361,6 +370,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
             if (FUSED) for (; xg < LA && xg < total; ++xg) { put_x(tile0 + xc); if (++xc == NC) xc = 0; }
             for (int t = 0; t < T; ++t)
                 for (int c = 0; c < NC; ++c) {
+                    if (X3) for (int kb = 0; kb < KBH; kb += 2) put(&map_ul, kb, min(2, KBH - kb), tile0 + c);      // h_hi . U_lo first
                     for (int kb = 0; kb < KBH; kb += 2) put(&map_u, kb, min(2, KBH - kb), tile0 + c);
                     if (FUSED && xg < total) { put_x(tile0 + xc); if (++xc == NC) xc = 0; ++xg; }
                 }
@@ -453,6 +463,10 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 // The recurrent part ALWAYS accumulates: onto the input part (FUSED) or onto the hoisted projection the epilogue stored
                 // into the buffer (XW).  GRU: it lands one 32-column group to the right ([z | r | h.Uh]); x.Wh stays in group 0.
                 const uint32_t d = tmem + (uint32_t)(buf * 128) + (G == 3 ? 32u : 0u);
+                if (X3) {                // small terms first: h_hi . U_lo, then h_lo . U_hi + h_hi . U_hi off the same U_hi stage
+                    for (int kb = 0; kb < KBH; kb += 2) stage_mmas(d, ah_a, 0u, kb, min(2, KBH - kb), false);
+                    for (int kb = 0; kb < KBH; kb += 2) stage_mmas(d, ah_a, smem_u32(sAl), kb, min(2, KBH - kb), false);
+                } else
                 for (int kb = 0; kb < KBH; kb += 2) stage_mmas(d, ah_a, 0u, kb, min(2, KBH - kb), false);
                 if (rf_elect()) {
                     rf_commit(bars + RFB_ACC_FULL + buf, pair_mask);
@@ -680,6 +694,12 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 v.x = rf_pack_sat(hv[0], hv[1]); v.y = rf_pack_sat(hv[2], hv[3]); v.z = rf_pack_sat(hv[4], hv[5]); v.w = rf_pack_sat(hv[6], hv[7]);
                 const int ch = (hf * 32 + j * UPT) / 8 + e;
                 *reinterpret_cast<uint4 *>(sAh + (size_t)c * (RF_ROWS * 128) + m * 128 + ((ch ^ sw) << 4)) = v;
+                if (X3) {
+                    uint4 hi4, lo4;
+                    rf_split2(hv[0], hv[1], hi4.x, lo4.x); rf_split2(hv[2], hv[3], hi4.y, lo4.y);
+                    rf_split2(hv[4], hv[5], hi4.z, lo4.z); rf_split2(hv[6], hv[7], hi4.w, lo4.w);
+                    *reinterpret_cast<uint4 *>(sAl + (size_t)c * (RF_ROWS * 128) + m * 128 + ((ch ^ sw) << 4)) = lo4;
+                }
             }
         }
         // XW mode: the hoisted projection of a tile is STORED INTO ITS ACCUMULATOR BUFFER before the tile's MMAs run (which then
@@ -774,8 +794,9 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                     for (int u = 0; u < 8; ++u) {
                         if (G == 3) {          // gru.c:156-186; columns [x.Wh | z | r | h.Uh]
                             const float xh = a0[u] + b2[u], pz = a1[u] + b0[u], pr = a2[u] + b1[u], hu = a3[u] + b3[u];
-                            const float z = act_mufu(NNTK_ACT_SIGMOID, pz), r = act_mufu(NNTK_ACT_SIGMOID, pr);
-                            const float hh = act_mufu(NNTK_ACT_TANH, fmaf(r, hu, xh));
+                            const float z = X3 ? nntk_act(NNTK_ACT_SIGMOID, 1.0f, pz) : act_mufu(NNTK_ACT_SIGMOID, pz);
+                            const float r = X3 ? nntk_act(NNTK_ACT_SIGMOID, 1.0f, pr) : act_mufu(NNTK_ACT_SIGMOID, pr);
+                            const float hh = X3 ? nntk_act(NNTK_ACT_TANH, 1.0f, fmaf(r, hu, xh)) : act_mufu(NNTK_ACT_TANH, fmaf(r, hu, xh));
                             sn[u] = fmaf(z, st[u] - hh, hh);               // (1 - z) hh + z h_{t-1}
                             hn[e * 8 + u] = sn[u];
                         } else {               // lstm.c:199-238; columns [i | f | g | o]
@@ -795,7 +816,7 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 __syncwarp();
                 if (lane == 0) rf_arrive_cl(acc_empty0 + 8u * (uint32_t)buf);       // the accumulator buffer may be overwritten
 #pragma unroll
-                for (int i = 0; i < UPT / 2; ++i) hpend[c][i] = rf_pack_sat(hn[2 * i], hn[2 * i + 1]);
+                for (int i = 0; i < UPT / 2; ++i) if (!X3) hpend[c][i] = rf_pack_sat(hn[2 * i], hn[2 * i + 1]);
                 if (p.return_sequences && !RF_SKIP(2)) {
                     // this warp's [32 rows][UPT units] piece of h_t -> its own staging tile (UPT = 16: 64-byte rows, SWIZZLE_64B; UPT = 8:
                     // 32-byte rows, unswizzled) -> one TMA store per warp: no CTA-wide barrier in the epilogue (first version: two
@@ -828,6 +849,19 @@ recurrent_fused_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                             for (int e = 0; e < NE; ++e) {
                                 const int ch = (hf * 32 + j * UPT) / 8 + e;
                                 const uint32_t off = (uint32_t)((tile0 + cc) * (RF_ROWS * 128) + m * 128 + ((ch ^ sw) << 4));
+                                if (X3) {
+                                    // the exact fp32 h_t of tile cc sits in this thread's state columns (written above, st waited for):
+                                    // both A tiles are rebuilt from it -- no register-resident pending copy in this variant
+                                    float hx[8];
+                                    rf_ld8(tl + STATE_COL + (uint32_t)(cc * 32 + j * UPT + e * 8), hx);
+                                    rf_ld_wait();
+                                    uint4 hi4, lo4;
+                                    rf_split2(hx[0], hx[1], hi4.x, lo4.x); rf_split2(hx[2], hx[3], hi4.y, lo4.y);
+                                    rf_split2(hx[4], hx[5], hi4.z, lo4.z); rf_split2(hx[6], hx[7], hi4.w, lo4.w);
+                                    rf_sts128(sAh_a + off, hi4.x, hi4.y, hi4.z, hi4.w);
+                                    rf_sts128(smem_u32(sAl) + off, lo4.x, lo4.y, lo4.z, lo4.w);
+                                    continue;
+                                }
                                 rf_sts128(sAh_a + off, hpend[cc][4 * e], hpend[cc][4 * e + 1], hpend[cc][4 * e + 2], hpend[cc][4 * e + 3]);
                                 if (S == 2)
                                     asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sAh_peer + off), "r"(hpend[cc][4 * e]), "r"(hpend[cc][4 * e + 1]),
@@ -947,20 +981,21 @@ __half *g_rf_scratch = nullptr;
 size_t g_rf_halves = 0;
 
 template <int G, bool FUSED>
-int rf_ring_stages(int H, int in, int xp, bool dbx = false) {
+int rf_ring_stages(int H, int in, int xp, bool dbx = false, bool x3 = false) {
     int stages = RF_MAX_RING;
-    for (; stages >= 2; --stages) { RfPlan<G, FUSED> pl(H, in, xp, stages, dbx); if (pl.total <= 227 * 1024) break; }
+    for (; stages >= 2; --stages) { RfPlan<G, FUSED> pl(H, in, xp, stages, dbx, x3); if (pl.total <= 227 * 1024) break; }
     return stages;
 }
+CUtensorMap g_rf_map_ul;         // X3 launches: the tensor map of U_lo (set by the caller of rf_launch; a copy of the U map otherwise)
 
 // dry: only report whether a cluster of p.cs CTAs of this kernel can be scheduled (1 = no)
-template <int G, bool FUSED, int NCMAX, bool DBX = false>
+template <int G, bool FUSED, int NCMAX, bool DBX = false, bool X3 = false>
 int rf_launch(const CUtensorMap &mw, const CUtensorMap &mwl, const CUtensorMap &mu, const CUtensorMap &mo, RfParams &p, int pairs, cudaStream_t st, int *dry) {
-    auto kern = recurrent_fused_kernel<G, FUSED, NCMAX, DBX>;
-    const int stages = rf_ring_stages<G, FUSED>(p.H, p.in, p.xp, DBX);
+    auto kern = recurrent_fused_kernel<G, FUSED, NCMAX, DBX, X3>;
+    const int stages = rf_ring_stages<G, FUSED>(p.H, p.in, p.xp, DBX, X3);
     if (stages < 3) return 1;
     p.ring_stages = stages;
-    const RfPlan<G, FUSED> pl(p.H, p.in, p.xp, stages, DBX);
+    const RfPlan<G, FUSED> pl(p.H, p.in, p.xp, stages, DBX, X3);
     static size_t attr_smem = 0;
     if ((size_t)pl.total > attr_smem) {
         NNTK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
@@ -982,7 +1017,7 @@ int rf_launch(const CUtensorMap &mw, const CUtensorMap &mwl, const CUtensorMap &
         *dry = (clusters < maxc ? clusters : maxc) * npairs;
         return 0;
     }
-    NNTK_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mw, mwl, mu, mo, p));
+    NNTK_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mw, mwl, mu, g_rf_map_ul, mo, p));
     nntk_cuda_count_launch(1);
     return 0;
 }
@@ -1030,17 +1065,18 @@ size_t g_rf_state_floats = 0;
 // staging with the per-step decision, runs iff the bound failed or the first launch raised the flag) launch of the speculative pair;
 // the caller has prepared g_rf_stats for them.  h_init / c_init: where the prologue reads the initial state.
 static int rf_fused_run(const nntk_recurrent_args *r, int nb, const float *x, const float *xw, float *h, float *c, float *out, int *used,
-                        int spec, const float *h_init, const float *c_init) {
+                        int spec, const float *h_init, const float *c_init, int x3 = 0) {
     *used = 0;
     const int G = r->cell, H = r->H, T = r->T, IN = r->in;
     const int plan = nntk_cuda_recurrent_fused_plan(r, nb);
     if (!plan || (plan == 2 && !xw)) return 0;
     const bool fused = plan == 1 && !xw;
+    if (x3 && !(fused && G == 3)) return 0;          // the fp32-contract variant exists for the FUSED GRU only
     if ((((uintptr_t)h) | ((uintptr_t)out) | ((uintptr_t)x) | ((uintptr_t)c) | ((uintptr_t)xw)) & 15) return 0;
     EncodeTiledFn encode = get_encode();
     cudaStream_t st = nntk_stream();
-    const int xp = fused ? (spec == 1 ? 1 : rf_xpasses()) : 1;
-    const size_t un = (size_t)G * H * H, wn = fused ? (size_t)G * H * IN : 0, wln = (fused && xp == 3) ? wn : 0;
+    const int xp = fused ? ((spec == 1 && !x3) ? 1 : (x3 ? 3 : rf_xpasses())) : 1;
+    const size_t un = (size_t)G * H * H * (x3 ? 2 : 1), wn = fused ? (size_t)G * H * IN : 0, wln = (fused && xp == 3) ? wn : 0;
     if (un + wn + wln > g_rf_halves) {
         NNTK_CUDA_TRY(cudaStreamSynchronize(st));
         if (g_rf_scratch) cudaFree(g_rf_scratch);
@@ -1051,7 +1087,7 @@ static int rf_fused_run(const nntk_recurrent_args *r, int nb, const float *x, co
     __half *Up = g_rf_scratch, *Wp = g_rf_scratch + un, *Wl = wln ? g_rf_scratch + un + wn : nullptr;
     {
         const int blocks = (int)((un + 255) / 256 < 2048 ? (un + 255) / 256 : 2048);
-        rf_pack_kernel<<<blocks, 256, 0, st>>>(r->d_U, Up, nullptr, H, H, G, 0, 1, 2, 3);
+        rf_pack_kernel<<<blocks, 256, 0, st>>>(r->d_U, Up, x3 ? Up + un / 2 : nullptr, H, H, G, 0, 1, 2, 3);
         NNTK_LAUNCH_CHECK("rf_pack_kernel");
         if (fused) {
             const int bw = (int)((wn + 255) / 256 < 2048 ? (wn + 255) / 256 : 2048);
@@ -1078,7 +1114,7 @@ static int rf_fused_run(const nntk_recurrent_args *r, int nb, const float *x, co
         return 0;
     };
     int rc;
-    p.H = H; p.in = IN; p.xp = xp; p.rows = RF_ROWS; p.split = 1;
+    p.H = H; p.in = IN; p.xp = xp; p.rows = RF_ROWS; p.split = 1; p.x3 = x3;
     bool small = H <= 256;
     // NNTK_RECURRENT_FUSED_DBX=1: one-pass FUSED launches take the DBX structure (16 epilogue warps at 96 registers, slim converters,
     // double-buffered x tile).  Measured on the C5 GRU layer: 8.15 ms against 7.85 ms for the 8-warp epilogue -- twice the epilogue
@@ -1087,10 +1123,11 @@ static int rf_fused_run(const nntk_recurrent_args *r, int nb, const float *x, co
     // epilogue -> h_full -> first recurrent MMA of the next step).  Kept buildable, off by default.
     static int want_dbx = -1;
     if (want_dbx < 0) { const char *e = getenv("NNTK_RECURRENT_FUSED_DBX"); want_dbx = e ? atoi(e) : 0; }
-    const bool dbx = want_dbx && fused && xp == 1 &&
+    const bool dbx = want_dbx && fused && xp == 1 && !x3 &&
                      (G == 3 ? rf_ring_stages<3, true>(H, IN, 1, true) : rf_ring_stages<4, true>(H, IN, 1, true)) >= 3;
 #define RF_DISPATCH(DRY) \
-    (dbx ? (G == 3 ? (small ? rf_launch<3, true, 4, true>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<3, true, 8, true>(mw, mwl, mu, mo, p, pairs, st, DRY)) \
+    (x3 ? (small ? rf_launch<3, true, 4, false, true>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<3, true, 8, false, true>(mw, mwl, mu, mo, p, pairs, st, DRY)) : \
+     dbx ? (G == 3 ? (small ? rf_launch<3, true, 4, true>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<3, true, 8, true>(mw, mwl, mu, mo, p, pairs, st, DRY)) \
                    : (small ? rf_launch<4, true, 4, true>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<4, true, 8, true>(mw, mwl, mu, mo, p, pairs, st, DRY))) : \
      G == 3 ? (fused ? (small ? rf_launch<3, true, 4>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<3, true, 8>(mw, mwl, mu, mo, p, pairs, st, DRY)) \
                      : (small ? rf_launch<3, false, 4>(mw, mwl, mu, mo, p, pairs, st, DRY) : rf_launch<3, false, 8>(mw, mwl, mu, mo, p, pairs, st, DRY))) \
@@ -1123,7 +1160,7 @@ static int rf_fused_run(const nntk_recurrent_args *r, int nb, const float *x, co
     static int force_rows = -1, force_split = -1;
     if (force_rows < 0) { const char *e = getenv("NNTK_RECURRENT_FUSED_ROWS"); force_rows = e ? atoi(e) : 0; }
     if (force_split < 0) { const char *e = getenv("NNTK_RECURRENT_FUSED_SPLIT"); force_split = e ? atoi(e) : 0; }
-    const bool can_split = (H % 128) == 0;
+    const bool can_split = (H % 128) == 0 && !x3;
     bool chosen = false;
     for (int opt = 0; opt < 4 && !chosen; ++opt) {
         const int o_split = opt < 2 ? 2 : 1, o_rows = (opt & 1) ? 64 : 32;      // (2,32) (2,64) (1,32) (1,64)
@@ -1142,6 +1179,7 @@ static int rf_fused_run(const nntk_recurrent_args *r, int nb, const float *x, co
     cs = best_cs;
     p.cs = cs;
     if ((rc = enc2(&mu, Up, H))) return rc;
+    if (x3) { if ((rc = enc2(&g_rf_map_ul, Up + un / 2, H))) return rc; } else g_rf_map_ul = mu;
     if (fused) { if ((rc = enc2(&mw, Wp, IN))) return rc; } else mw = mu;
     if (Wl) { if ((rc = enc2(&mwl, Wl, IN))) return rc; } else mwl = mu;
     if (r->return_sequences) {
@@ -1174,7 +1212,9 @@ static int rf_fused_run(const nntk_recurrent_args *r, int nb, const float *x, co
     p.sel = spec; p.verify = spec == 1;
     { static int la = -1; if (la < 0) { const char *e = getenv("NNTK_RECURRENT_FUSED_LOOKAHEAD"); la = e ? atoi(e) : 1; } p.lookahead = la; }
     p.h_init = h_init ? h_init : h; p.c_init = c_init ? c_init : c;
-    if (spec) {
+    if (x3) {
+        p.stats = nullptr; p.adapt_thr = -1.0f; p.sel = 0; p.verify = 0;          // always all three passes, nothing adaptive
+    } else if (spec) {
         p.per_step = spec == 2;           // stats prepared by the caller (sampled row norms, W norms, cleared flag)
     } else if (fused && xp == 3 && adaptive && per_step) {
         // the decision moves into the kernel: per pair and per step, from the row norms its converter warps see anyway
@@ -1234,6 +1274,7 @@ extern "C" int nntk_cuda_recurrent_fused(const nntk_recurrent_args *r, int nb, c
         e = getenv("NNTK_RECURRENT_X_PERSTEP"); per_step = e ? atoi(e) : 1;
     }
     const int G = r->cell, H = r->H, T = r->T, IN = r->in;
+    if (nntk_cuda_math_mode() == 2) return xw ? 0 : rf_fused_run(r, nb, x, nullptr, h, c, out, used, 0, nullptr, nullptr, 1);
     const bool fused = !xw && nntk_cuda_recurrent_fused_plan(r, nb) == 1;
     if (!(fused && speculate && adaptive && per_step && rf_xpasses() == 3 && (IN & 3) == 0 && (G != 4 || c)))
         return rf_fused_run(r, nb, x, xw, h, c, out, used, 0, nullptr, nullptr);

@@ -298,3 +298,30 @@ def test_c4_projection_operand_passes(tf32, ref, scale, passes):
         want = rr.apply(pool[b % 64]); rr.close()
         assert_parity(got[b].cpu().numpy(), want, tol=TF32_TOL, what=f"C4 LSTM-512 T=500, inputs x {scale}: {passes} projection pass(es), sequence {b}")
     r.close()
+
+
+@pytest.mark.parametrize("in_size,H,T,B,scale", [(256, 256, 300, 130, 1.0), (64, 128, 994, 200, 0.5), (128, 64, 40, 70, 3.0)])
+def test_fused_gru_in_the_fp32_contract_mode(cuda, product, port, in_size, H, T, B, scale):
+    """NNTK_MATH_TF32X3: the persistent fused kernel with every product in three split-fp16 passes (h carried as two A tiles rebuilt
+    from the fp32 state in TMEM, expf / tanhf gates) must hold the reference's 1e-5 over hundreds of steps (gru.c:129-204)"""
+    import port_cases
+    import torch
+    assert product.NNTKSetMathMode(2) == 0
+    try:
+        rng = np.random.default_rng(18)
+        x = (scale * rng.standard_normal((B, T, in_size))).astype(np.float32)
+        h0 = (0.3 * rng.standard_normal((B, H))).astype(np.float32)
+        pick = [0, B // 2, B - 1]
+        w = port_cases.recurrent_weights("gru", in_size, H, 440)
+        want = np.stack([port_cases.recurrent(port, "gru", in_size, H, T, True, True, w, x[i], h=h0[i].copy()) for i in pick])
+        r = L.Recurrent(product, "gru", in_size, H, T); helpers.fill_recurrent(r, 440)
+        dev = torch.device("cuda:0")
+        h = torch.from_numpy(h0).to(dev)
+        got = r.apply_batch(torch.from_numpy(x).to(dev), h_state=h)
+        torch.cuda.synchronize()
+        assert _path(product) == "fused_x3"
+        assert_parity(got[pick].cpu().numpy(), want, tol=helpers.FP32_TOL, what=f"fused GRU {in_size}->{H} T={T} in the fp32-contract mode")
+        assert_parity(h[pick].cpu().numpy(), want[:, -1], tol=helpers.FP32_TOL, what="... carried state")
+        r.close()
+    finally:
+        product.NNTKSetMathMode(helpers.DEFAULT_MATH_MODE)
