@@ -54,6 +54,7 @@ os.environ["NNTK_RECURRENT_X_SPECULATE"] = "1"
 rec("lstm", 64, 128, 4, 600, 1, 1e-3, env={"NNTK_RECURRENT_FUSED_SPLIT": "2"})      # split mode forced: DSMEM exchange of h_t halves
 os.environ.pop("NNTK_RECURRENT_FUSED_SPLIT")
 rec("lstm", 72, 256, 4, 1500, 1, 1e-3)                  # XW mode behind the adaptive projection (cta_group::2 GEMM, gated fp16 / 3xbf16)
+rec("gru", 64, 128, 6, 140, 2, 1e-5)                    # fused pair kernel in the fp32-contract mode (three split-fp16 passes for both parts)
 
 # conv on tcgen05 + the fused front end (pitched K1) + the staging pipeline with host buffers (>= 3 chunks of ~32 MiB)
 assert lib.NNTKSetMathMode(1) == 0
