@@ -41,7 +41,7 @@ METRIC = "audio-sec/sec"
 MODES = {"fp32": 0, "tf32": 1, "x3": 2}
 DTYPE = {"fp32": "f32 (FFMA, 1e-5 contract)",
          "tf32": "tf32 conv/dense (f16 operands in the fused front end) + f16-operand recurrent steps on tcgen05, f32 accumulate and state (stated tolerance 1e-3)",
-         "x3": "3xTF32 split operands on tcgen05, f32-equivalent (1e-5 contract)"}
+         "x3": "3xTF32 (conv/dense) and 3x split-fp16 (fused GRU) operands on tcgen05, f32 accumulate and state, f32-equivalent (1e-5 contract)"}
 CLIP_N, CLIP_S = 160000, 10.0
 
 WORKLOADS = {
