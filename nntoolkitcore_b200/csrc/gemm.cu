@@ -277,6 +277,125 @@ extern "C" int nntk_cuda_gemm_tf32(const nntk_gemm_args *g, int split);   // gem
 // reductions run the FFMA kernel.
 #define NNTK_X3_MAX_K 1536
 
+// ---- skinny GEMM: N <= 32 outputs per row (the 12-wide TimeDistributedDense of the KWS chain) in exact fp32 ------------------
+// HBM-bound by construction (K floats read per N written), so the fp32-contract modes need no tensor core here: 3xTF32 spent a
+// whole extra pass splitting A (C5 TDD: 4.3 ms split + 3.1 ms GEMM for 8.7 GB of algorithmic traffic).  Eight lanes share a row
+// (each 16-byte chunk g + 8 i of it), W sits transposed in shared memory ([N][K]: the eight lanes read 128 contiguous bytes, the
+// four row groups of a warp the same ones) and every chunk read serves four rows; 3 shuffles per output close the sums; bias,
+// activation or the row softmax (activation_default.c:149-167: exp, sum, divide -- the sum taken over the eight lanes' shares)
+// follow in registers, each lane finishing the outputs g, g + 8, ... of its rows.
+namespace {
+// a group of eight lanes works on RPG consecutive rows at once: every W chunk read from shared memory serves all of them
+constexpr int SK_RPG = 4;
+template <int NMAX, bool SOFTMAX>
+__global__ void __launch_bounds__(256) gemm_skinny_kernel(const float *A, long long a_slab, int lda, int rows, long long M, int N, int K,
+                                                          const float *__restrict__ B, const float *__restrict__ bias, int act, float act_a,
+                                                          float *C, long long c_slab, int ldc) {
+    extern __shared__ __align__(16) float s_wt[];            // [N][K]
+    for (int i = threadIdx.x; i < N * K; i += blockDim.x) { const int n = i / K, k = i - n * K; s_wt[i] = __ldg(B + (long long)k * N + n); }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, g = lane & 7;
+    const long long groups = ((long long)gridDim.x * blockDim.x) >> 3;
+    const int k4 = K >> 2;
+    const long long m_pad = (M + 4 * SK_RPG - 1) / (4 * SK_RPG) * (4 * SK_RPG);      // all four groups of a warp run the same trip count (shuffles)
+    for (long long r0 = (((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 3) * SK_RPG; r0 < m_pad; r0 += groups * SK_RPG) {
+        const float4 *x[SK_RPG];
+        bool ok[SK_RPG];
+#pragma unroll
+        for (int q = 0; q < SK_RPG; ++q) {
+            const long long r = r0 + q;
+            ok[q] = r < M;
+            const long long slab = ok[q] ? r / rows : 0;
+            const int row = ok[q] ? (int)(r - slab * rows) : 0;
+            x[q] = reinterpret_cast<const float4 *>(A + slab * a_slab + (long long)row * lda);
+        }
+        float acc[SK_RPG][NMAX];
+#pragma unroll
+        for (int q = 0; q < SK_RPG; ++q)
+#pragma unroll
+            for (int n = 0; n < NMAX; ++n) acc[q][n] = 0.0f;
+        for (int i = g; i < k4; i += 8) {
+            float4 v[SK_RPG];
+#pragma unroll
+            for (int q = 0; q < SK_RPG; ++q) v[q] = ok[q] ? x[q][i] : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int n = 0; n < NMAX; ++n) {
+                if (n < N) {
+                    const float4 w = *reinterpret_cast<const float4 *>(s_wt + n * K + 4 * i);
+#pragma unroll
+                    for (int q = 0; q < SK_RPG; ++q) acc[q][n] = fmaf(v[q].x, w.x, fmaf(v[q].y, w.y, fmaf(v[q].z, w.z, fmaf(v[q].w, w.w, acc[q][n]))));
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < SK_RPG; ++q) {
+            // lane g ends up owning outputs g and g + 8 (.. + 24) of row q
+            float mine[NMAX / 8];
+#pragma unroll
+            for (int n = 0; n < NMAX; ++n) {
+                if (n < N) {
+                    float s = acc[q][n];
+                    s += __shfl_xor_sync(0xffffffffu, s, 1);
+                    s += __shfl_xor_sync(0xffffffffu, s, 2);
+                    s += __shfl_xor_sync(0xffffffffu, s, 4);
+                    if ((n & 7) == g) mine[n >> 3] = s + (bias ? __ldg(bias + n) : 0.0f);
+                }
+            }
+            float sum = 0.0f;
+#pragma unroll
+            for (int jj = 0; jj < NMAX / 8; ++jj) {
+                const int n = g + 8 * jj;
+                if (n < N) {
+                    if (SOFTMAX) { mine[jj] = expf(mine[jj]); sum += mine[jj]; }
+                    else mine[jj] = nntk_act(act, act_a, mine[jj]);
+                }
+            }
+            if (SOFTMAX) {
+                sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+                sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+                sum += __shfl_xor_sync(0xffffffffu, sum, 4);
+            }
+            if (ok[q]) {
+                const long long r = r0 + q;
+                const long long slab = r / rows;
+                float *c = C + slab * c_slab + (long long)(r - slab * rows) * ldc;
+#pragma unroll
+                for (int jj = 0; jj < NMAX / 8; ++jj) {
+                    const int n = g + 8 * jj;
+                    if (n < N) c[n] = SOFTMAX ? mine[jj] / sum : mine[jj];
+                }
+            }
+        }
+    }
+}
+}  // namespace
+
+// 0 done, 1 not eligible
+static int gemm_skinny(const nntk_gemm_args *a, bool softmax) {
+    static int on = -1;
+    if (on < 0) { const char *e = getenv("NNTK_GEMM_SKINNY"); on = e ? atoi(e) : 1; }
+    const int N = a->N, K = a->K;
+    if (!on || N > 32 || (K & 3) || a->d_bn || (size_t)N * K * sizeof(float) > 96 * 1024 || (a->lda & 3) || (a->a_slab_stride & 3) ||
+        (((uintptr_t)a->d_A) & 15) || (!softmax && (a->act == NNTK_ACT_SOFTMAX || a->act == NNTK_ACT_CUSTOM))) return 1;
+    const long long M = (long long)a->batch * a->rows;
+    if (M == 0) return 0;
+    const size_t smem = (size_t)N * K * sizeof(float);
+    long long blocks = ((M + SK_RPG - 1) / SK_RPG * 8 + 255) / 256;
+    const long long cap = (long long)nntk_cuda_sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    cudaStream_t st = nntk_stream();
+#define SKINNY_LAUNCH(NM, SM) do { \
+        static bool attr = false; \
+        if (!attr) { NNTK_CUDA_TRY(cudaFuncSetAttribute(gemm_skinny_kernel<NM, SM>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)); attr = true; } \
+        gemm_skinny_kernel<NM, SM><<<(unsigned)blocks, 256, smem, st>>>(a->d_A, a->a_slab_stride, a->lda, a->rows, M, N, K, a->d_B, a->d_bias, a->act, \
+                                                                       a->act_a, a->d_C, a->c_slab_stride, a->ldc); } while (0)
+    if (N <= 16) { if (softmax) SKINNY_LAUNCH(16, true); else SKINNY_LAUNCH(16, false); }
+    else { if (softmax) SKINNY_LAUNCH(32, true); else SKINNY_LAUNCH(32, false); }
+#undef SKINNY_LAUNCH
+    NNTK_LAUNCH_CHECK("gemm_skinny_kernel");
+    return 0;
+}
+
 extern "C" void nntk_cuda_gemm_tc_row_softmax(int on);      // gemm_tc.cu
 // C = softmax_rows(A B + bias) for N <= 32 on the tensor-core kernel, the softmax over each whole output row taken in the GEMM
 // epilogue (TimeDistributedDense + softmax of the KWS chain: saves the second pass over the result).  Same expf / divide as the
@@ -287,7 +406,7 @@ extern "C" int nntk_cuda_gemm_row_softmax(const nntk_gemm_args *a) {
     if (!a || !a->d_A || !a->d_B || !a->d_C || a->batch < 1 || a->rows < 1 || a->N < 1 || a->N > 32 || a->K < 1 || a->d_bn ||
         (a->act != NNTK_ACT_NONE && a->act != NNTK_ACT_IDENTITY)) return 1;
     const int mode = nntk_cuda_math_mode();
-    if (mode == 0 || (mode == 2 && a->K > NNTK_X3_MAX_K)) return 1;
+    if (mode != 1) return gemm_skinny(a, true);          // the fp32-contract modes: exact fp32, HBM-bound
     nntk_cuda_gemm_tc_row_softmax(1);
     rc = nntk_cuda_gemm_tf32(a, mode == 2);
     nntk_cuda_gemm_tc_row_softmax(0);
@@ -311,6 +430,10 @@ extern "C" int nntk_cuda_gemm(const nntk_gemm_args *a) {
     // compensate grows linearly with the reduction length (measured rel-L2 1.5e-6 at K = 1 280, 3.0e-6 at 2 560, 8.0e-6 at
     // 7 168): beyond NNTK_X3_MAX_K the mode runs the FFMA kernel.  Every BASELINE shape has K <= 1 285.
     const int mode = nntk_cuda_math_mode();
+    if (mode != 1 && a->N <= 32) {       // narrow outputs in the fp32-contract modes: the exact, HBM-bound skinny kernel
+        rc = gemm_skinny(a, false);
+        if (rc != 1) return rc;
+    }
     if (mode == 1 || (mode == 2 && a->K <= NNTK_X3_MAX_K)) {
         rc = nntk_cuda_gemm_tf32(a, mode == 2);
         if (rc != 1) return rc;   // 1 = shape not eligible for the tensor-core kernel: use the fp32 kernel
