@@ -571,7 +571,7 @@ def run_workload(env, name, steps, warmup, clk=None, with_e2e=False, with_stages
     total_ms, per, launches = time_steps(env, wl["step"], steps, warmup, clk)
     total_units = units if w["strong"] else units * env.world
     value = total_units * w["audio_s"] * steps / (total_ms * 1e-3)
-    res = dict(workload=name, value=value, unit="audio-s/s", ms_per_step=total_ms / steps, ms_per_step_median=float(np.median(per)),
+    res = dict(workload=name, value=value, unit="audio-s/s", ms_per_step=total_ms / steps, ms_per_step_median=float(np.median(per)), steps_ms=[round(float(v), 3) for v in per],
                steps=steps, warmup=warmup, scaling="strong" if w["strong"] else "weak", units_per_gpu=local_units,
                units_total=total_units, gpu_launches=launches, desc=w["desc"])
     if with_stages:
@@ -736,7 +736,7 @@ def run_ours(args):
         w = WORKLOADS[name]
         line = {
             "metric": METRIC, "value": res["value"], "unit": "audio-s/s", "n_gpus": world, "steps": args.steps, "warmup": warmup,
-            "ms_per_step": res["ms_per_step"], "ms_per_step_median": res["ms_per_step_median"], "higher_is_better": True,
+            "ms_per_step": res["ms_per_step"], "ms_per_step_median": res["ms_per_step_median"], "steps_ms": res["steps_ms"], "higher_is_better": True,
             "scaling": res["scaling"], "vs_baseline": None, "dtype": DTYPE[args.mode], "math_mode": args.mode, "data": "synthetic",
             "config": workload_config(name, world, args.units or w["units"]),
             "clocks": clk.summary(), "roofline": roofline, "stages": res.get("stages"), "cpu_baseline": cpu_baseline, "e2e": e2e,
