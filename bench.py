@@ -68,7 +68,7 @@ def peaks():
 
 class ClockSampler:
     """SM clock + throttle reasons DURING the timed region (B200_PROFILING.md recipe), polled in-process through NVML (the
-    library nvidia-smi itself queries) every millisecond; nvidia-smi child as the fallback.  Only samples between
+    library nvidia-smi itself queries) every 10 ms; nvidia-smi child as the fallback.  Only samples between
     mark_start() and mark_end() are summarised."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -115,7 +115,7 @@ class ClockSampler:
                 self.rows.append((time.perf_counter(), sm, self.mx, [n for n, b in bits if mask & b]))
             except Exception:
                 pass
-            time.sleep(0.001)
+            time.sleep(0.01)      # ~100 samples per second: NVML queries take driver locks the launching thread also needs
 
     def _read(self):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
